@@ -1,0 +1,173 @@
+/*
+ * qpolicy.h — C ABI of the B200-native Q-learning decision policy.
+ *
+ * Drop-in boundary for ONE hot path of cosmir17/Scala-akka-tensorflow-sharetrade-helper: the body
+ * of QDecisionPolicyActor (the tensorflow_scala session) and the per-step arithmetic of
+ * TrainerChildActor.computeWithFolding.  The Scala/Akka layer keeps its messages; a JNI/Panama
+ * shim forwards them to these entry points.  All `file:line` citations are
+ * relative to the reference's src/main/scala/.
+ *
+ * Conventions
+ *   - plain C, no exceptions; every function returns a qp_status unless stated; the text of the
+ *     last failure on the calling thread is available from qp_last_error().
+ *   - host pointers unless the name says otherwise; the caller owns host buffers, the library
+ *     copies or consumes them before returning.  Device memory is owned by the handle.
+ *   - a handle is thread-compatible (one call at a time), not thread-bound: each entry point
+ *     selects the handle's device itself, so any dispatcher thread may call it.
+ *   - calls are synchronous on return (the actor replies Action / Updated right after), except
+ *     the *_async ones, which only enqueue on the handle's stream.
+ *   - parameter layout: params = [ W1 (D x H, row-major) | W2 (H x 3, row-major) ], D = window + 2;
+ *     the AdaGrad accumulators use the same layout.  Biases are the constants 0.1f
+ *     (QDecisionPolicyActor.scala:42, :46) and are not parameters.
+ *   - actions: 0 = Buy, 1 = Sell, 2 = Hold (QDecisionPolicyActor.scala:17).
+ */
+#ifndef QPOLICY_H
+#define QPOLICY_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    QP_OK = 0,
+    QP_EINVAL = 1,       /* IllegalArgumentException in the reference (size guards) */
+    QP_ECUDA = 2,        /* CUDA runtime failure */
+    QP_ENCCL = 3,        /* NCCL failure */
+    QP_ESTATE = 4,       /* call made in the wrong state (e.g. no episodes created) */
+    QP_EUNSUPPORTED = 5, /* shape outside what the kernels cover */
+    QP_EIO = 6           /* checkpoint / file errors */
+} qp_status;
+
+enum { QP_BUY = 0, QP_SELL = 1, QP_HOLD = 2, QP_ACTIONS = 3 };
+enum { QP_BOOK_REFERENCE = 0, QP_BOOK_RLPY = 1 };
+
+/* Hyper-parameters: compile-time constants in the reference
+ * (QDecisionPolicyActor.scala:17-22, :50), gathered into one POD. */
+typedef struct {
+    int32_t window;          /* price-window length; reference 201 (TrainerChildActor.scala:90) */
+    int32_t hidden;          /* h1Dim = 200; must be a multiple of 4 */
+    float epsilon;           /* 0.9f */
+    float gamma;             /* 0.001f */
+    float lr;                /* AdaGrad(0.01f) */
+    float bias;              /* 0.1f, both layers */
+    float step_div;          /* 1000f in `step / 1000f` (QDecisionPolicyActor.scala:58) */
+    float adagrad_init_acc;  /* initial accumulator value, 1e-8f */
+    int32_t bookkeeping;     /* QP_BOOK_REFERENCE: Buy/Sell decided from the constructor's position
+                                (TrainerChildActor.scala:118-123); QP_BOOK_RLPY: from the carry */
+    int32_t device;          /* CUDA device ordinal */
+    uint64_t seed;           /* Philox key for weights (stream 2) and action draws (stream 1) */
+} qp_config;
+
+typedef struct qp_handle qp_handle;
+
+/* Fills *cfg with the reference's constants (QDecisionPolicyActor.scala:17-22, :50). */
+int qp_config_default(qp_config* cfg);
+
+/* QDecisionPolicyActor constructor + initialiseSession (QDecisionPolicyActor.scala:38-52, :79-83):
+ * allocates the policy on cfg->device and draws W1, W2 ~ N(0,1) from the seed. */
+int qp_create(const qp_config* cfg, qp_handle** out);
+int qp_destroy(qp_handle* h);
+
+/* D = window + 2 (inputDim, QDecisionPolicyActor.scala:18); P = D*H + 3*H.  Return the count. */
+int64_t qp_input_dim(const qp_handle* h);
+int64_t qp_param_count(const qp_handle* h);
+
+/* No counterpart in the reference (its weights live inside the Session): inject
+ * or export weights and accumulators for parity runs and checkpoints.  acc may be NULL. */
+int qp_set_weights(qp_handle* h, const float* params, const float* acc);
+int qp_get_weights(qp_handle* h, float* params, float* acc);
+/* The summed gradient of the most recent update (parity aid; no reference counterpart). */
+int qp_get_last_grad(qp_handle* h, float* grad);
+
+/* SelectionAction(currentState, step) -> Action  (QDecisionPolicyActor.scala:32, :56-62), batched.
+ *   states [B x state_len] row-major; state_len != D -> QP_EINVAL (the guard at :56-57).
+ *   steps [B]; env_ids [B] or NULL (then env id = row index) pick the Philox counter
+ *   (env id, (uint32)step, stream 1): one 24-bit uniform per row, one bounded draw if exploring.
+ *   q_out [B x 3] may be NULL. */
+int qp_select_action(qp_handle* h, const float* states, int64_t state_len, const float* steps,
+                     const int64_t* env_ids, int32_t* actions, float* q_out, int64_t B);
+
+/* UpdateQ(state, reward, nextState) -> Updated  (QDecisionPolicyActor.scala:33, :64-76), batched:
+ * TD target on the argmax of q(nextState), gradient SUM over the B rows, one AdaGrad step.
+ * B = 1 is exactly the reference's message.  A length other than D -> QP_EINVAL (:64-65). */
+int qp_update_q(qp_handle* h, const float* states, int64_t state_len, const float* rewards,
+                const float* next_states, int64_t next_state_len, int64_t B);
+
+/* ---- episode level: TrainerChildActor.train / computeWithFolding (TrainerChildActor.scala:64-103)
+ * for n_envs independent episodes that share this policy (TrainerRouterActor.scala:44, :60-66). */
+
+/* Uploads the price series ([n_series x series_len] fp32, already date-sorted as at
+ * TrainerChildActor.scala:66) and creates n_envs episodes; series_of_env[e] names the series of
+ * episode e.  series_len <= window -> QP_EINVAL (the guard at :65, :70).  env_id_base is added
+ * to the episode index to form the RNG counter, so a shard draws its global episodes' numbers.
+ * Every episode starts from (budget0, shares0, shareValue 0.0) (:84-86). */
+int qp_env_create(qp_handle* h, const float* prices, int64_t series_len, int64_t n_series,
+                  const int32_t* series_of_env, int64_t n_envs, int64_t env_id_base,
+                  double budget0, int32_t shares0);
+/* Initialise (TrainerChildActor.scala:58-60): back to step 0 and the initial position. */
+int qp_env_reset(qp_handle* h);
+/* nPrices - window (TrainerChildActor.scala:67), and how many env-steps have run.  Counts. */
+int64_t qp_env_steps_total(const qp_handle* h);
+int64_t qp_env_steps_done(const qp_handle* h);
+
+/* Runs n_steps iterations of the fold at TrainerChildActor.scala:87-102 for every episode:
+ * state build, select (QDecisionPolicyActor.scala:56-62), decision (:118-123), reward and next
+ * state (:136-146), TD update (QDecisionPolicyActor.scala:64-76, gradient SUM over episodes). */
+int qp_env_step(qp_handle* h, int32_t n_steps);
+int qp_env_step_async(qp_handle* h, int32_t n_steps);
+int qp_sync(qp_handle* h);
+
+/* Per-step record for parity checks; host arrays of n_steps x n_envs entries (x3 for q_*),
+ * step-major.  Any member may be NULL.  No counterpart in the reference. */
+typedef struct {
+    int32_t* action_sel;  /* index the policy returned */
+    int32_t* action_eff;  /* after demotion to Hold (TrainerChildActor.scala:118-123) */
+    int32_t* explored;    /* 1 if the random branch was taken */
+    int32_t* k_next;      /* argmax of q(nextState) (QDecisionPolicyActor.scala:69) */
+    float* reward;        /* fp64 reward cast to fp32 (TrainerChildActor.scala:158) */
+    float* q_s;           /* q(state) */
+    float* q_n;           /* q(nextState) */
+    float* target;        /* reward + gamma * q_n[k_next] (QDecisionPolicyActor.scala:70) */
+    double* budget;       /* carry after the step */
+    int32_t* shares;
+} qp_trace;
+int qp_env_step_trace(qp_handle* h, int32_t n_steps, const qp_trace* out);
+
+/* budget + shares * shareValue per episode (TrainerChildActor.scala:68) -> TrainedData. */
+int qp_env_get_portfolio(qp_handle* h, double* out);
+/* The fold's carry (budget, shares, shareValue) (TrainerChildActor.scala:99-102); get / set.
+ * Set also places every episode at env-step `step`.  Any pointer may be NULL. */
+int qp_env_get_state(qp_handle* h, double* budget, int32_t* shares, double* share_value);
+int qp_env_set_state(qp_handle* h, const double* budget, const int32_t* shares,
+                     const double* share_value, int64_t step);
+/* GetAvg / GetStd: mean and POPULATION standard deviation of the portfolios, reduced on the
+ * device (TrainerRouterActor.scala:89-94, :149-151). */
+int qp_env_portfolio_stats(qp_handle* h, double* mean, double* stddev);
+
+/* TrainerChildActor.train (:64-71) in one call with host buffers: qp_env_create, every step of
+ * the episode, qp_env_get_portfolio. */
+int qp_train(qp_handle* h, const float* prices, int64_t series_len, int64_t n_series,
+             const int32_t* series_of_env, int64_t n_envs, int64_t env_id_base, double budget0,
+             int32_t shares0, double* portfolios_out);
+
+/* ---- measurement aids (no reference counterpart) */
+enum { QP_KERNEL_STEP = 0, QP_KERNEL_DW1 = 1, QP_KERNEL_APPLY = 2, QP_N_KERNELS = 3 };
+/* The CUDA stream (cudaStream_t) every kernel of this handle is launched on. */
+void* qp_stream(qp_handle* h);
+/* Runs n_steps with CUDA events around each kernel; ms_sum[QP_N_KERNELS] receives the summed
+ * device time per kernel in milliseconds. */
+int qp_env_step_timed(qp_handle* h, int32_t n_steps, float* ms_sum);
+/* Kernels launched by this handle so far.  Returns the count. */
+int64_t qp_launch_count(const qp_handle* h);
+
+/* Text of the last failure on this thread ("" if none).  Never NULL. */
+const char* qp_last_error(void);
+const char* qp_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

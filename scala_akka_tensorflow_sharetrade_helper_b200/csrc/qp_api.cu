@@ -1,0 +1,612 @@
+// qp_api.cu — host side of the C ABI declared in include/qpolicy.h.
+//
+// Owns device memory, the stream and the launch sequence; contains no arithmetic of the hot path
+// (that is all in qp_kernels.cuh) and no CPU fallback: without a CUDA device qp_create fails.
+#include "qp_kernels.cuh"
+#include "../../include/qpolicy.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+using namespace qp;
+
+namespace {
+
+thread_local std::string g_err;
+
+int fail(int code, const std::string& msg) {
+    g_err = msg;
+    return code;
+}
+
+#define QP_CUDA(expr)                                                                          \
+    do {                                                                                       \
+        cudaError_t _e = (expr);                                                               \
+        if (_e != cudaSuccess)                                                                 \
+            return fail(QP_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(_e));         \
+    } while (0)
+
+#define QP_TRY(expr)                   \
+    do {                               \
+        int _s = (expr);               \
+        if (_s != QP_OK) return _s;    \
+    } while (0)
+
+template <typename T>
+struct DevBuf {
+    T* p = nullptr;
+    size_t cap = 0;  // elements
+    int ensure(size_t n) {
+        if (n <= cap) return QP_OK;
+        if (p) { cudaFree(p); p = nullptr; cap = 0; }
+        QP_CUDA(cudaMalloc(&p, std::max<size_t>(n, 1) * sizeof(T)));
+        cap = n;
+        return QP_OK;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr; cap = 0;
+    }
+};
+
+int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
+
+}  // namespace
+
+struct qp_handle {
+    qp_config cfg{};
+    Hyper hp{};
+    int64_t P = 0, P1 = 0;
+    int device = 0, num_sms = 0, max_smem = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[4] = {nullptr, nullptr, nullptr, nullptr};
+
+    DevBuf<float> params, acc, grad;
+    // scratch shared by the episode and message paths
+    DevBuf<float> dz1, xextra, part1, part2;
+    int64_t Bpad = 0;
+    // message path staging
+    DevBuf<float> m_states, m_next, m_rewards, m_steps, m_q;
+    DevBuf<int64_t> m_ids;
+    DevBuf<int32_t> m_actions;
+    // episodes
+    bool has_env = false;
+    DevBuf<float> prices;
+    DevBuf<int32_t> series_of_env, shares;
+    DevBuf<double> budget, share_value, portfolio, blocksum;
+    DevBuf<int32_t> d_step;
+    int64_t series_len = 0, n_series = 0, n_envs = 0, env_id_base = 0;
+    double B0 = 0.0;
+    int32_t N0 = 0;
+    int64_t steps_done = 0;
+
+    int64_t launches = 0;
+    // launch geometry
+    int step_warps = 0, n_rt = 0, n_ct = 0, dw1_threads = 0;
+    size_t smem_step[3] = {0, 0, 0}, smem_dw1 = 0;
+};
+
+namespace {
+
+int use_device(const qp_handle* h) {
+    QP_CUDA(cudaSetDevice(h->device));
+    return QP_OK;
+}
+
+size_t step_smem_bytes(const Hyper& hp, int mode, int nwarps) {
+    const size_t rows_x = mode == kEnvStep ? hp.wn + 1 : hp.D;
+    size_t f = (size_t)hp.D * hp.Hs + (size_t)hp.Hs * 4 + rows_x * kXStride;
+    if (mode == kMsgUpdate) f += rows_x * kXStride;
+    f += (size_t)nwarps * 2 * 3 * 32 + (size_t)hp.Hs * 3;
+    return f * sizeof(float);
+}
+
+// Host-side N(0,1) initialiser (Philox stream 2 + Box-Muller); stands in for the unseeded
+// tf.RandomNormalInitializer() at QDecisionPolicyActor.scala:41, :45.
+void gen_normal(uint64_t seed, int64_t n, float* out) {
+    for (int64_t i = 0; i < n; ++i) {
+        uint32_t r[4];
+        philox4x32_10((uint32_t)i, (uint32_t)((uint64_t)i >> 32), 0u, 2u, (uint32_t)seed,
+                      (uint32_t)(seed >> 32), r);
+        const double u1 = ((double)(r[0] >> 8) + 0.5) * (1.0 / 16777216.0);
+        const double u2 = ((double)(r[1] >> 8) + 0.5) * (1.0 / 16777216.0);
+        out[i] = (float)(std::sqrt(-2.0 * std::log(u1)) * std::cos(6.283185307179586476925286766559 * u2));
+    }
+}
+
+int ensure_scratch(qp_handle* h, int64_t B, int* grid_step, int* grid_dw1) {
+    const int64_t Bpad = round_up(B, kTileEnvs);
+    const int64_t n_tiles = Bpad / kTileEnvs;
+    const int g1 = (int)std::min<int64_t>(n_tiles, h->num_sms);
+    const int g2 = (int)std::max<int64_t>(1, std::min<int64_t>((B + 15) / 16, h->num_sms));
+    QP_TRY(h->dz1.ensure((size_t)Bpad * h->hp.H));
+    QP_TRY(h->xextra.ensure((size_t)Bpad * 2));
+    QP_TRY(h->part1.ensure((size_t)g2 * h->P1));
+    QP_TRY(h->part2.ensure((size_t)g1 * 3 * h->hp.H));
+    h->Bpad = Bpad;
+    *grid_step = g1;
+    *grid_dw1 = g2;
+    return QP_OK;
+}
+
+template <int MODE>
+int launch_step(qp_handle* h, const StepArgs& a, int grid) {
+    step_kernel<MODE><<<grid, h->step_warps * 32, h->smem_step[MODE], h->stream>>>(a);
+    h->launches++;
+    QP_CUDA(cudaGetLastError());
+    return QP_OK;
+}
+
+template <int MODE>
+int launch_dw1(qp_handle* h, const Dw1Args& a, int grid) {
+    dw1_kernel<MODE><<<grid, h->dw1_threads, h->smem_dw1, h->stream>>>(a);
+    h->launches++;
+    QP_CUDA(cudaGetLastError());
+    return QP_OK;
+}
+
+int launch_apply(qp_handle* h, int n1, int n2, int do_reduce, int do_adagrad, int step_inc) {
+    ApplyArgs a{};
+    a.hp = h->hp;
+    a.params = h->params.p; a.acc = h->acc.p; a.grad = h->grad.p;
+    a.part1 = h->part1.p; a.n1 = n1; a.part2 = h->part2.p; a.n2 = n2;
+    a.P = h->P; a.P1 = h->P1;
+    a.do_reduce = do_reduce; a.do_adagrad = do_adagrad;
+    a.d_step = h->d_step.p; a.step_inc = step_inc;
+    const int64_t threads = h->P * kApplyLanes;
+    const int blocks = (int)((threads + 255) / 256);
+    apply_kernel<<<blocks, 256, 0, h->stream>>>(a);
+    h->launches++;
+    QP_CUDA(cudaGetLastError());
+    return QP_OK;
+}
+
+// One env-step of every episode: K1, K2, K3.  ev != nullptr brackets each kernel with events.
+int enqueue_env_step(qp_handle* h, const TraceDev* trace, int32_t trace_step0, bool timed) {
+    int g1 = 0, g2 = 0;
+    QP_TRY(ensure_scratch(h, h->n_envs, &g1, &g2));
+    StepArgs s{};
+    s.hp = h->hp;
+    s.params = h->params.p;
+    s.prices = h->prices.p; s.T = h->series_len; s.series_of_env = h->series_of_env.p;
+    s.budget = h->budget.p; s.shares = h->shares.p; s.share_value = h->share_value.p;
+    s.B0 = h->B0; s.N0 = h->N0; s.env_id_base = h->env_id_base; s.d_step = h->d_step.p;
+    s.B = h->n_envs; s.Bpad = h->Bpad;
+    s.dz1 = h->dz1.p; s.xextra = h->xextra.p; s.dw2_part = h->part2.p;
+    if (trace) s.trace = *trace;
+    s.trace_step0 = trace_step0;
+    if (timed) QP_CUDA(cudaEventRecord(h->ev[0], h->stream));
+    QP_TRY(launch_step<kEnvStep>(h, s, g1));
+    if (timed) QP_CUDA(cudaEventRecord(h->ev[1], h->stream));
+
+    Dw1Args d{};
+    d.hp = h->hp;
+    d.prices = h->prices.p; d.T = h->series_len; d.series_of_env = h->series_of_env.p; d.d_step = h->d_step.p;
+    d.xextra = h->xextra.p; d.Bpad = h->Bpad; d.dz1 = h->dz1.p; d.B = h->n_envs; d.part = h->part1.p;
+    d.n_rt = h->n_rt; d.n_ct = h->n_ct;
+    QP_TRY(launch_dw1<kEnvStep>(h, d, g2));
+    if (timed) QP_CUDA(cudaEventRecord(h->ev[2], h->stream));
+
+    QP_TRY(launch_apply(h, g2, g1, 1, 1, 1));
+    if (timed) QP_CUDA(cudaEventRecord(h->ev[3], h->stream));
+    return QP_OK;
+}
+
+int check_env_steps(qp_handle* h, int32_t n_steps) {
+    if (!h) return fail(QP_EINVAL, "null handle");
+    if (!h->has_env) return fail(QP_ESTATE, "no episodes: call qp_env_create first");
+    if (n_steps < 0) return fail(QP_EINVAL, "n_steps < 0");
+    const int64_t total = h->series_len - h->hp.wn;
+    if (h->steps_done + n_steps > total)
+        return fail(QP_EINVAL, "episode has " + std::to_string(total) + " steps, " +
+                                   std::to_string(h->steps_done) + " done, asked for " + std::to_string(n_steps));
+    return QP_OK;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char* qp_last_error(void) { return g_err.c_str(); }
+const char* qp_version(void) { return "qpolicy-b200 0.1 (sm_100a)"; }
+
+int qp_config_default(qp_config* cfg) {
+    if (!cfg) return fail(QP_EINVAL, "null cfg");
+    cfg->window = 201; cfg->hidden = 200;
+    cfg->epsilon = 0.9f; cfg->gamma = 0.001f; cfg->lr = 0.01f; cfg->bias = 0.1f;
+    cfg->step_div = 1000.0f; cfg->adagrad_init_acc = 1e-8f;
+    cfg->bookkeeping = QP_BOOK_REFERENCE; cfg->device = 0; cfg->seed = 42;
+    return QP_OK;
+}
+
+int qp_create(const qp_config* cfg, qp_handle** out) {
+    if (!cfg || !out) return fail(QP_EINVAL, "null argument");
+    *out = nullptr;
+    if (cfg->window < 1 || cfg->hidden < 4) return fail(QP_EINVAL, "window >= 1 and hidden >= 4 required");
+    if (cfg->hidden % 4) return fail(QP_EINVAL, "hidden must be a multiple of 4");
+    if (cfg->bookkeeping != QP_BOOK_REFERENCE && cfg->bookkeeping != QP_BOOK_RLPY)
+        return fail(QP_EINVAL, "bookkeeping must be QP_BOOK_REFERENCE or QP_BOOK_RLPY");
+    int ndev = 0;
+    cudaError_t ce = cudaGetDeviceCount(&ndev);
+    if (ce != cudaSuccess || ndev == 0)
+        return fail(QP_ECUDA, std::string("no CUDA device: ") + cudaGetErrorString(ce) +
+                                  " (this library has no CPU path)");
+    if (cfg->device < 0 || cfg->device >= ndev) return fail(QP_EINVAL, "device ordinal out of range");
+
+    qp_handle* h = new qp_handle();
+    h->cfg = *cfg;
+    h->device = cfg->device;
+    Hyper& hp = h->hp;
+    hp.wn = cfg->window; hp.D = cfg->window + 2; hp.H = cfg->hidden;
+    hp.Hs = (int)round_up(cfg->hidden, kColsPerWarp);
+    hp.epsilon = cfg->epsilon; hp.gamma = cfg->gamma; hp.lr = cfg->lr; hp.bias = cfg->bias;
+    hp.step_div = cfg->step_div; hp.bookkeeping = cfg->bookkeeping; hp.seed = cfg->seed;
+    h->P1 = (int64_t)hp.D * hp.H;
+    h->P = h->P1 + 3LL * hp.H;
+
+    auto bail = [&](int code) { qp_destroy(h); return code; };
+    if (cudaSetDevice(h->device) != cudaSuccess) return bail(fail(QP_ECUDA, "cudaSetDevice failed"));
+    cudaDeviceProp prop{};
+    if (cudaGetDeviceProperties(&prop, h->device) != cudaSuccess) return bail(fail(QP_ECUDA, "cudaGetDeviceProperties failed"));
+    h->num_sms = prop.multiProcessorCount;
+    h->max_smem = (int)prop.sharedMemPerBlockOptin;
+
+    // launch geometry and shape limits of the register-tiled fp32 path
+    h->step_warps = hp.Hs / kColsPerWarp;
+    h->n_rt = (hp.D + kDw1Rows - 1) / kDw1Rows;
+    h->n_ct = (hp.H / 4 + 1) / 2;
+    h->dw1_threads = (int)round_up((int64_t)h->n_rt * h->n_ct, 32);
+    for (int m = 0; m < 3; ++m) h->smem_step[m] = step_smem_bytes(hp, m, h->step_warps);
+    h->smem_dw1 = (size_t)kDw1ChunkEnvs * ((size_t)h->n_rt * kDw1Rows + (size_t)h->n_ct * kDw1Cols) * sizeof(float);
+    if (h->step_warps > kMaxStepWarps || h->dw1_threads > kDw1MaxThreads ||
+        h->smem_step[kMsgUpdate] > (size_t)h->max_smem || h->smem_dw1 > (size_t)h->max_smem)
+        return bail(fail(QP_EUNSUPPORTED,
+                         "shape outside the fused fp32 path (needs W1 resident in shared memory: hidden <= 240, "
+                         "(window+2)*hidden*4 + staging <= " + std::to_string(h->max_smem) + " bytes)"));
+#define QP_BAIL_CUDA(expr)                                                                        \
+    do {                                                                                          \
+        cudaError_t _e = (expr);                                                                  \
+        if (_e != cudaSuccess) return bail(fail(QP_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(_e))); \
+    } while (0)
+    QP_BAIL_CUDA(cudaFuncSetAttribute(step_kernel<kEnvStep>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step[kEnvStep]));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(step_kernel<kMsgSelect>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step[kMsgSelect]));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(step_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step[kMsgUpdate]));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_kernel<kEnvStep>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_dw1));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_dw1));
+    QP_BAIL_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
+    for (auto& e : h->ev) QP_BAIL_CUDA(cudaEventCreate(&e));
+#undef QP_BAIL_CUDA
+    if (h->params.ensure(h->P) || h->acc.ensure(h->P) || h->grad.ensure(h->P) || h->d_step.ensure(1))
+        return bail(QP_ECUDA);
+
+    std::vector<float> w(h->P);
+    gen_normal(cfg->seed, h->P, w.data());
+    int st = qp_set_weights(h, w.data(), nullptr);
+    if (st != QP_OK) return bail(st);
+    std::vector<float> a(h->P, cfg->adagrad_init_acc);
+    st = qp_set_weights(h, nullptr, a.data());
+    if (st != QP_OK) return bail(st);
+    if (cudaMemsetAsync(h->grad.p, 0, h->P * sizeof(float), h->stream) != cudaSuccess ||
+        cudaMemsetAsync(h->d_step.p, 0, sizeof(int32_t), h->stream) != cudaSuccess ||
+        cudaStreamSynchronize(h->stream) != cudaSuccess)
+        return bail(fail(QP_ECUDA, "initial memset failed"));
+    *out = h;
+    return QP_OK;
+}
+
+int qp_destroy(qp_handle* h) {
+    if (!h) return QP_OK;
+    cudaSetDevice(h->device);
+    if (h->stream) cudaStreamSynchronize(h->stream);
+    h->params.release(); h->acc.release(); h->grad.release();
+    h->dz1.release(); h->xextra.release(); h->part1.release(); h->part2.release();
+    h->m_states.release(); h->m_next.release(); h->m_rewards.release(); h->m_steps.release();
+    h->m_q.release(); h->m_ids.release(); h->m_actions.release();
+    h->prices.release(); h->series_of_env.release(); h->shares.release();
+    h->budget.release(); h->share_value.release(); h->portfolio.release(); h->blocksum.release();
+    h->d_step.release();
+    for (auto& e : h->ev) if (e) cudaEventDestroy(e);
+    if (h->stream) cudaStreamDestroy(h->stream);
+    delete h;
+    return QP_OK;
+}
+
+int64_t qp_input_dim(const qp_handle* h) { return h ? h->hp.D : 0; }
+int64_t qp_param_count(const qp_handle* h) { return h ? h->P : 0; }
+void* qp_stream(qp_handle* h) { return h ? (void*)h->stream : nullptr; }
+int64_t qp_launch_count(const qp_handle* h) { return h ? h->launches : 0; }
+
+int qp_set_weights(qp_handle* h, const float* params, const float* acc) {
+    if (!h) return fail(QP_EINVAL, "null handle");
+    QP_TRY(use_device(h));
+    if (params) QP_CUDA(cudaMemcpyAsync(h->params.p, params, h->P * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    if (acc) QP_CUDA(cudaMemcpyAsync(h->acc.p, acc, h->P * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    QP_CUDA(cudaStreamSynchronize(h->stream));
+    return QP_OK;
+}
+
+int qp_get_weights(qp_handle* h, float* params, float* acc) {
+    if (!h) return fail(QP_EINVAL, "null handle");
+    QP_TRY(use_device(h));
+    if (params) QP_CUDA(cudaMemcpyAsync(params, h->params.p, h->P * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    if (acc) QP_CUDA(cudaMemcpyAsync(acc, h->acc.p, h->P * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    QP_CUDA(cudaStreamSynchronize(h->stream));
+    return QP_OK;
+}
+
+int qp_get_last_grad(qp_handle* h, float* grad) {
+    if (!h || !grad) return fail(QP_EINVAL, "null argument");
+    QP_TRY(use_device(h));
+    QP_CUDA(cudaMemcpyAsync(grad, h->grad.p, h->P * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    QP_CUDA(cudaStreamSynchronize(h->stream));
+    return QP_OK;
+}
+
+int qp_select_action(qp_handle* h, const float* states, int64_t state_len, const float* steps,
+                     const int64_t* env_ids, int32_t* actions, float* q_out, int64_t B) {
+    if (!h || !states || !steps || !actions) return fail(QP_EINVAL, "null argument");
+    if (state_len != h->hp.D)  // QDecisionPolicyActor.scala:56-57
+        return fail(QP_EINVAL, "SelectionAction: tensorflow input size(" + std::to_string(h->hp.D) +
+                                   ") and state(" + std::to_string(state_len) + ") size do not match");
+    if (B < 0) return fail(QP_EINVAL, "B < 0");
+    if (B == 0) return QP_OK;
+    QP_TRY(use_device(h));
+    const int D = h->hp.D;
+    QP_TRY(h->m_states.ensure((size_t)B * D));
+    QP_TRY(h->m_steps.ensure(B));
+    QP_TRY(h->m_actions.ensure(B));
+    QP_TRY(h->m_q.ensure((size_t)B * 3));
+    if (env_ids) QP_TRY(h->m_ids.ensure(B));
+    QP_CUDA(cudaMemcpyAsync(h->m_states.p, states, (size_t)B * D * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    QP_CUDA(cudaMemcpyAsync(h->m_steps.p, steps, B * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    if (env_ids) QP_CUDA(cudaMemcpyAsync(h->m_ids.p, env_ids, B * sizeof(int64_t), cudaMemcpyHostToDevice, h->stream));
+    StepArgs s{};
+    s.hp = h->hp; s.params = h->params.p;
+    s.states = h->m_states.p; s.steps = h->m_steps.p; s.env_ids = env_ids ? h->m_ids.p : nullptr;
+    s.actions_out = h->m_actions.p; s.q_out = h->m_q.p; s.B = B; s.Bpad = round_up(B, kTileEnvs);
+    const int grid = (int)std::min<int64_t>(s.Bpad / kTileEnvs, h->num_sms);
+    QP_TRY(launch_step<kMsgSelect>(h, s, grid));
+    QP_CUDA(cudaMemcpyAsync(actions, h->m_actions.p, B * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    if (q_out) QP_CUDA(cudaMemcpyAsync(q_out, h->m_q.p, (size_t)B * 3 * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
+    QP_CUDA(cudaStreamSynchronize(h->stream));
+    return QP_OK;
+}
+
+int qp_update_q(qp_handle* h, const float* states, int64_t state_len, const float* rewards,
+                const float* next_states, int64_t next_state_len, int64_t B) {
+    if (!h || !states || !rewards || !next_states) return fail(QP_EINVAL, "null argument");
+    if (state_len != h->hp.D || next_state_len != h->hp.D)  // QDecisionPolicyActor.scala:64-65
+        return fail(QP_EINVAL, "update q: tensorflow input size(" + std::to_string(h->hp.D) +
+                                   ") and state(or nextState) size(" + std::to_string(state_len) + ", " +
+                                   std::to_string(next_state_len) + ") do not match");
+    if (B < 0) return fail(QP_EINVAL, "B < 0");
+    if (B == 0) return QP_OK;
+    QP_TRY(use_device(h));
+    const int D = h->hp.D;
+    int g1 = 0, g2 = 0;
+    QP_TRY(ensure_scratch(h, B, &g1, &g2));
+    QP_TRY(h->m_states.ensure((size_t)B * D));
+    QP_TRY(h->m_next.ensure((size_t)B * D));
+    QP_TRY(h->m_rewards.ensure(B));
+    QP_CUDA(cudaMemcpyAsync(h->m_states.p, states, (size_t)B * D * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    QP_CUDA(cudaMemcpyAsync(h->m_next.p, next_states, (size_t)B * D * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    QP_CUDA(cudaMemcpyAsync(h->m_rewards.p, rewards, B * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    StepArgs s{};
+    s.hp = h->hp; s.params = h->params.p;
+    s.states = h->m_states.p; s.next_states = h->m_next.p; s.rewards = h->m_rewards.p;
+    s.B = B; s.Bpad = h->Bpad; s.dz1 = h->dz1.p; s.xextra = h->xextra.p; s.dw2_part = h->part2.p;
+    QP_TRY(launch_step<kMsgUpdate>(h, s, g1));
+    Dw1Args d{};
+    d.hp = h->hp; d.states = h->m_states.p; d.Bpad = h->Bpad; d.dz1 = h->dz1.p; d.B = B; d.part = h->part1.p;
+    d.n_rt = h->n_rt; d.n_ct = h->n_ct;
+    QP_TRY(launch_dw1<kMsgUpdate>(h, d, g2));
+    QP_TRY(launch_apply(h, g2, g1, 1, 1, 0));
+    QP_CUDA(cudaStreamSynchronize(h->stream));
+    return QP_OK;
+}
+
+int qp_env_create(qp_handle* h, const float* prices, int64_t series_len, int64_t n_series,
+                  const int32_t* series_of_env, int64_t n_envs, int64_t env_id_base,
+                  double budget0, int32_t shares0) {
+    if (!h || !prices || !series_of_env) return fail(QP_EINVAL, "null argument");
+    if (series_len <= h->hp.wn)  // TrainerChildActor.scala:65, :70
+        return fail(QP_EINVAL, "Stock price count should be more than Tensorflow input nodes");
+    if (n_series < 1 || n_envs < 1) return fail(QP_EINVAL, "n_series and n_envs must be >= 1");
+    if (series_len > INT32_MAX) return fail(QP_EINVAL, "series too long");
+    for (int64_t e = 0; e < n_envs; ++e)
+        if (series_of_env[e] < 0 || series_of_env[e] >= n_series)
+            return fail(QP_EINVAL, "series_of_env[" + std::to_string(e) + "] out of range");
+    QP_TRY(use_device(h));
+    QP_TRY(h->prices.ensure((size_t)n_series * series_len));
+    QP_TRY(h->series_of_env.ensure(n_envs));
+    QP_TRY(h->budget.ensure(n_envs));
+    QP_TRY(h->shares.ensure(n_envs));
+    QP_TRY(h->share_value.ensure(n_envs));
+    QP_TRY(h->portfolio.ensure(n_envs));
+    QP_TRY(h->blocksum.ensure(1024));
+    QP_CUDA(cudaMemcpyAsync(h->prices.p, prices, (size_t)n_series * series_len * sizeof(float), cudaMemcpyHostToDevice, h->stream));
+    QP_CUDA(cudaMemcpyAsync(h->series_of_env.p, series_of_env, n_envs * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    h->series_len = series_len; h->n_series = n_series; h->n_envs = n_envs; h->env_id_base = env_id_base;
+    h->B0 = budget0; h->N0 = shares0;
+    h->has_env = true;
+    return qp_env_reset(h);
+}
+
+int qp_env_reset(qp_handle* h) {
+    if (!h) return fail(QP_EINVAL, "null handle");
+    if (!h->has_env) return fail(QP_ESTATE, "no episodes: call qp_env_create first");
+    QP_TRY(use_device(h));
+    const int blocks = (int)((h->n_envs + 255) / 256);
+    env_init_kernel<<<blocks, 256, 0, h->stream>>>(h->budget.p, h->shares.p, h->share_value.p, h->n_envs, h->B0, h->N0);
+    h->launches++;
+    QP_CUDA(cudaGetLastError());
+    QP_CUDA(cudaMemsetAsync(h->d_step.p, 0, sizeof(int32_t), h->stream));
+    QP_CUDA(cudaStreamSynchronize(h->stream));
+    h->steps_done = 0;
+    return QP_OK;
+}
+
+int64_t qp_env_steps_total(const qp_handle* h) { return (h && h->has_env) ? h->series_len - h->hp.wn : 0; }
+int64_t qp_env_steps_done(const qp_handle* h) { return h ? h->steps_done : 0; }
+
+int qp_env_step_async(qp_handle* h, int32_t n_steps) {
+    QP_TRY(check_env_steps(h, n_steps));
+    QP_TRY(use_device(h));
+    for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step(h, nullptr, 0, false));
+    h->steps_done += n_steps;
+    return QP_OK;
+}
+
+int qp_sync(qp_handle* h) {
+    if (!h) return fail(QP_EINVAL, "null handle");
+    QP_TRY(use_device(h));
+    QP_CUDA(cudaStreamSynchronize(h->stream));
+    return QP_OK;
+}
+
+int qp_env_step(qp_handle* h, int32_t n_steps) {
+    QP_TRY(qp_env_step_async(h, n_steps));
+    return qp_sync(h);
+}
+
+int qp_env_step_timed(qp_handle* h, int32_t n_steps, float* ms_sum) {
+    if (!ms_sum) return fail(QP_EINVAL, "null ms_sum");
+    QP_TRY(check_env_steps(h, n_steps));
+    QP_TRY(use_device(h));
+    for (int k = 0; k < QP_N_KERNELS; ++k) ms_sum[k] = 0.0f;
+    for (int32_t i = 0; i < n_steps; ++i) {
+        QP_TRY(enqueue_env_step(h, nullptr, 0, true));
+        QP_CUDA(cudaEventSynchronize(h->ev[3]));
+        for (int k = 0; k < QP_N_KERNELS; ++k) {
+            float ms = 0.0f;
+            QP_CUDA(cudaEventElapsedTime(&ms, h->ev[k], h->ev[k + 1]));
+            ms_sum[k] += ms;
+        }
+        h->steps_done += 1;
+    }
+    return QP_OK;
+}
+
+int qp_env_step_trace(qp_handle* h, int32_t n_steps, const qp_trace* out) {
+    if (!out) return fail(QP_EINVAL, "null trace");
+    QP_TRY(check_env_steps(h, n_steps));
+    if (n_steps == 0) return QP_OK;
+    QP_TRY(use_device(h));
+    const size_t n = (size_t)n_steps * h->n_envs;
+    DevBuf<int32_t> asel, aeff, expl, kn, shr;
+    DevBuf<float> rew, qs, qn, tgt;
+    DevBuf<double> bud;
+    TraceDev t{};
+    int st = QP_OK;
+    auto rel = [&]() { asel.release(); aeff.release(); expl.release(); kn.release(); shr.release();
+                       rew.release(); qs.release(); qn.release(); tgt.release(); bud.release(); };
+#define QP_TR(buf, field, host, mult)                                  \
+    if (st == QP_OK && out->host) { st = buf.ensure(n * mult); t.field = buf.p; }
+    QP_TR(asel, action_sel, action_sel, 1) QP_TR(aeff, action_eff, action_eff, 1)
+    QP_TR(expl, explored, explored, 1) QP_TR(kn, k_next, k_next, 1) QP_TR(shr, shares, shares, 1)
+    QP_TR(rew, reward, reward, 1) QP_TR(qs, q_s, q_s, 3) QP_TR(qn, q_n, q_n, 3)
+    QP_TR(tgt, target, target, 1) QP_TR(bud, budget, budget, 1)
+#undef QP_TR
+    const int32_t step0 = (int32_t)h->steps_done;
+    for (int32_t i = 0; i < n_steps && st == QP_OK; ++i) st = enqueue_env_step(h, &t, step0, false);
+    if (st == QP_OK) h->steps_done += n_steps;
+    auto d2h = [&](void* dst, const void* src, size_t bytes) {
+        if (st == QP_OK && dst && cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, h->stream) != cudaSuccess)
+            st = fail(QP_ECUDA, "trace copy failed");
+    };
+    d2h(out->action_sel, asel.p, n * 4); d2h(out->action_eff, aeff.p, n * 4); d2h(out->explored, expl.p, n * 4);
+    d2h(out->k_next, kn.p, n * 4); d2h(out->shares, shr.p, n * 4); d2h(out->reward, rew.p, n * 4);
+    d2h(out->q_s, qs.p, n * 12); d2h(out->q_n, qn.p, n * 12); d2h(out->target, tgt.p, n * 4);
+    d2h(out->budget, bud.p, n * 8);
+    if (cudaStreamSynchronize(h->stream) != cudaSuccess && st == QP_OK) st = fail(QP_ECUDA, "sync failed after trace");
+    rel();
+    return st;
+}
+
+static int compute_portfolio(qp_handle* h) {
+    const int blocks = (int)((h->n_envs + 255) / 256);
+    portfolio_kernel<<<blocks, 256, 0, h->stream>>>(h->budget.p, h->shares.p, h->share_value.p, h->n_envs, h->portfolio.p);
+    h->launches++;
+    QP_CUDA(cudaGetLastError());
+    return QP_OK;
+}
+
+int qp_env_get_portfolio(qp_handle* h, double* out) {
+    if (!h || !out) return fail(QP_EINVAL, "null argument");
+    if (!h->has_env) return fail(QP_ESTATE, "no episodes: call qp_env_create first");
+    QP_TRY(use_device(h));
+    QP_TRY(compute_portfolio(h));
+    QP_CUDA(cudaMemcpyAsync(out, h->portfolio.p, h->n_envs * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    QP_CUDA(cudaStreamSynchronize(h->stream));
+    return QP_OK;
+}
+
+int qp_env_get_state(qp_handle* h, double* budget, int32_t* shares, double* share_value) {
+    if (!h) return fail(QP_EINVAL, "null handle");
+    if (!h->has_env) return fail(QP_ESTATE, "no episodes: call qp_env_create first");
+    QP_TRY(use_device(h));
+    if (budget) QP_CUDA(cudaMemcpyAsync(budget, h->budget.p, h->n_envs * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    if (shares) QP_CUDA(cudaMemcpyAsync(shares, h->shares.p, h->n_envs * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    if (share_value) QP_CUDA(cudaMemcpyAsync(share_value, h->share_value.p, h->n_envs * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+    QP_CUDA(cudaStreamSynchronize(h->stream));
+    return QP_OK;
+}
+
+int qp_env_set_state(qp_handle* h, const double* budget, const int32_t* shares,
+                     const double* share_value, int64_t step) {
+    if (!h) return fail(QP_EINVAL, "null handle");
+    if (!h->has_env) return fail(QP_ESTATE, "no episodes: call qp_env_create first");
+    if (step < 0 || step > h->series_len - h->hp.wn) return fail(QP_EINVAL, "step out of range");
+    QP_TRY(use_device(h));
+    if (budget) QP_CUDA(cudaMemcpyAsync(h->budget.p, budget, h->n_envs * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    if (shares) QP_CUDA(cudaMemcpyAsync(h->shares.p, shares, h->n_envs * sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    if (share_value) QP_CUDA(cudaMemcpyAsync(h->share_value.p, share_value, h->n_envs * sizeof(double), cudaMemcpyHostToDevice, h->stream));
+    const int32_t s32 = (int32_t)step;
+    QP_CUDA(cudaMemcpyAsync(h->d_step.p, &s32, sizeof(int32_t), cudaMemcpyHostToDevice, h->stream));
+    QP_CUDA(cudaStreamSynchronize(h->stream));
+    h->steps_done = step;
+    return QP_OK;
+}
+
+int qp_env_portfolio_stats(qp_handle* h, double* mean, double* stddev) {
+    if (!h || !mean || !stddev) return fail(QP_EINVAL, "null argument");
+    if (!h->has_env) return fail(QP_ESTATE, "no episodes: call qp_env_create first");
+    QP_TRY(use_device(h));
+    QP_TRY(compute_portfolio(h));
+    const int blocks = (int)std::min<int64_t>(1024, (h->n_envs + 255) / 256);
+    double host[1024];
+    auto pass = [&](double shift, int pw, double* total) -> int {
+        moment_kernel<<<blocks, 256, 0, h->stream>>>(h->portfolio.p, h->n_envs, shift, pw, h->blocksum.p);
+        h->launches++;
+        QP_CUDA(cudaGetLastError());
+        QP_CUDA(cudaMemcpyAsync(host, h->blocksum.p, blocks * sizeof(double), cudaMemcpyDeviceToHost, h->stream));
+        QP_CUDA(cudaStreamSynchronize(h->stream));
+        double s = 0.0;
+        for (int i = 0; i < blocks; ++i) s += host[i];
+        *total = s;
+        return QP_OK;
+    };
+    double sum = 0.0, var = 0.0;
+    QP_TRY(pass(0.0, 1, &sum));
+    const double m = sum / (double)h->n_envs;   // mean (TrainerRouterActor.scala:149)
+    QP_TRY(pass(m, 2, &var));
+    *mean = m;
+    *stddev = std::sqrt(var / (double)h->n_envs);  // population variance (:150-151)
+    return QP_OK;
+}
+
+int qp_train(qp_handle* h, const float* prices, int64_t series_len, int64_t n_series,
+             const int32_t* series_of_env, int64_t n_envs, int64_t env_id_base, double budget0,
+             int32_t shares0, double* portfolios_out) {
+    if (!portfolios_out) return fail(QP_EINVAL, "null portfolios_out");
+    QP_TRY(qp_env_create(h, prices, series_len, n_series, series_of_env, n_envs, env_id_base, budget0, shares0));
+    const int64_t total = qp_env_steps_total(h);
+    QP_TRY(qp_env_step_async(h, (int32_t)total));
+    return qp_env_get_portfolio(h, portfolios_out);
+}
+
+}  // extern "C"

@@ -1,0 +1,641 @@
+// qp_kernels.cuh — sm_100a kernels of the Q-learning decision policy hot path.
+//
+// One env-step of every episode is three launches on one stream:
+//   step_kernel   (K1)  state build from HBM-resident price series, forward of s and s',
+//                       Philox epsilon-greedy select, portfolio/reward book-keeping, TD target,
+//                       output-layer backward; writes dz1 [B,H] and per-CTA dW2 partials
+//   dw1_kernel    (K2)  dW1 = X^T · dZ1 as a split-over-episodes register-tiled contraction;
+//                       writes per-CTA partials
+//   apply_kernel  (K3)  fixed-order reduction of the partials + AdaGrad
+// Reference lines each piece replaces are cited at the piece.  No float atomics anywhere: every
+// sum has a fixed order, so a run is bit-reproducible.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace qp {
+
+constexpr int kColsPerWarp = 20;   // hidden columns owned by one warp of the step kernel
+constexpr int kTileEnvs = 32;      // episodes per tile = lanes of a warp
+constexpr int kXStride = 33;       // padded row stride of the transposed state tile (bank-conflict free)
+constexpr int kMaxStepWarps = 12;  // hidden <= 12 * 20 = 240 on this path
+constexpr int kDw1Rows = 16;       // register tile of the dW1 contraction: 16 input rows
+constexpr int kDw1Cols = 8;        //   x 8 hidden columns (two float4 groups)
+constexpr int kDw1MaxThreads = 384;
+constexpr int kDw1ChunkEnvs = 32;  // episodes staged per pass of the dW1 kernel
+constexpr int kApplyLanes = 8;     // lanes cooperating on one parameter in the apply kernel
+
+enum StepMode { kEnvStep = 0, kMsgSelect = 1, kMsgUpdate = 2 };
+
+struct Hyper {
+    int wn;        // price-window length (hist + 1)
+    int D;         // wn + 2
+    int H;         // hidden
+    int Hs;        // hidden padded to a multiple of kColsPerWarp (smem row stride of W1)
+    float epsilon, gamma, lr, bias, step_div;
+    int bookkeeping;
+    uint64_t seed;
+};
+
+struct TraceDev {
+    int32_t* action_sel; int32_t* action_eff; int32_t* explored; int32_t* k_next;
+    float* reward; float* q_s; float* q_n; float* target; double* budget; int32_t* shares;
+};
+
+struct StepArgs {
+    Hyper hp;
+    const float* params;            // [W1 | W2]
+    // episode mode
+    const float* prices; int64_t T; const int32_t* series_of_env;
+    double* budget; int32_t* shares; double* share_value;
+    double B0; int32_t N0;
+    int64_t env_id_base;
+    const int32_t* d_step;
+    // message mode
+    const float* states; const float* next_states; const float* rewards; const float* steps;
+    const int64_t* env_ids; int32_t* actions_out; float* q_out;
+    // common
+    int64_t B;                      // episodes / rows
+    int64_t Bpad;
+    float* dz1;                     // [Bpad, H]
+    float* xextra;                  // [2, Bpad]: (float)budget, (float)shares of state s
+    float* dw2_part;                // [grid, 3H]
+    TraceDev trace; int32_t trace_step0;
+};
+
+struct Dw1Args {
+    Hyper hp;
+    const float* prices; int64_t T; const int32_t* series_of_env; const int32_t* d_step;
+    const float* states;            // message mode: [B, D]
+    const float* xextra; int64_t Bpad;
+    const float* dz1;
+    int64_t B;
+    float* part;                    // [grid, D*H]
+    int n_rt, n_ct;
+};
+
+struct ApplyArgs {
+    Hyper hp;
+    float* params; float* acc; float* grad;
+    const float* part1; int n1;     // dW1 partials [n1, D*H]
+    const float* part2; int n2;     // dW2 partials [n2, 3H]
+    int64_t P, P1;
+    int do_reduce;                  // 1: grad = sum of partials; 0: grad already holds the (all-reduced) sum
+    int do_adagrad;
+    int32_t* d_step; int step_inc;
+};
+
+// ---------------------------------------------------------------------------------------------
+// Philox4x32-10, counter (id_lo, id_hi, t, stream), key = seed.  Replaces the unseeded global
+// scala.util.Random of QDecisionPolicyActor.scala:58, :62 with a reproducible counter-based draw.
+// ---------------------------------------------------------------------------------------------
+__host__ __device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3,
+                                                       uint32_t k0, uint32_t k1, uint32_t out[4]) {
+#pragma unroll
+    for (int r = 0; r < 10; ++r) {
+        const uint64_t p0 = (uint64_t)0xD2511F53u * c0;
+        const uint64_t p1 = (uint64_t)0xCD9E8D57u * c2;
+        const uint32_t n0 = (uint32_t)(p1 >> 32) ^ c1 ^ k0;
+        const uint32_t n1 = (uint32_t)p1;
+        const uint32_t n2 = (uint32_t)(p0 >> 32) ^ c3 ^ k1;
+        const uint32_t n3 = (uint32_t)p0;
+        c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+        k0 += 0x9E3779B9u;
+        k1 += 0xBB67AE85u;
+    }
+    out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+#ifdef __CUDACC__
+
+__device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gmem_src));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+// wait until at most n groups of this thread are still in flight
+__device__ __forceinline__ void cp_async_wait_pending(int n) {
+    switch (n) {
+        case 0: asm volatile("cp.async.wait_group 0;\n" ::); break;
+        case 1: asm volatile("cp.async.wait_group 1;\n" ::); break;
+        case 2: asm volatile("cp.async.wait_group 2;\n" ::); break;
+        case 3: asm volatile("cp.async.wait_group 3;\n" ::); break;
+        case 4: asm volatile("cp.async.wait_group 4;\n" ::); break;
+        case 5: asm volatile("cp.async.wait_group 5;\n" ::); break;
+        case 6: asm volatile("cp.async.wait_group 6;\n" ::); break;
+        case 7: asm volatile("cp.async.wait_group 7;\n" ::); break;
+        default: asm volatile("cp.async.wait_group 8;\n" ::); break;
+    }
+}
+
+// first-max-wins argmax, as Tensor.argmax at QDecisionPolicyActor.scala:60, :69
+__device__ __forceinline__ int argmax3(const float q[3]) {
+    int k = 0;
+    float m = q[0];
+    if (q[1] > m) { k = 1; m = q[1]; }
+    if (q[2] > m) { k = 2; }
+    return k;
+}
+
+__device__ __forceinline__ float warp_sum(float v) {
+    v += __shfl_xor_sync(0xffffffffu, v, 16);
+    v += __shfl_xor_sync(0xffffffffu, v, 8);
+    v += __shfl_xor_sync(0xffffffffu, v, 4);
+    v += __shfl_xor_sync(0xffffffffu, v, 2);
+    v += __shfl_xor_sync(0xffffffffu, v, 1);
+    return v;
+}
+
+// =============================================================================================
+// K1 — step kernel.  lane <-> episode (32 per tile), warp <-> 20 hidden columns.
+//   kEnvStep  : TrainerChildActor.scala:87-102 for env-step *d_step of every episode, with the
+//               policy's SelectionAction (QDecisionPolicyActor.scala:56-62) and the forward /
+//               TD-target part of UpdateQ (:64-71) fused in.
+//   kMsgSelect: SelectionAction on explicit state rows.
+//   kMsgUpdate: UpdateQ (forward of s and s', TD target, output-layer backward) on explicit rows.
+// Shared memory: W1 (whole, D x Hs), W2 (Hs x float4), the transposed state tile(s), the
+// cross-warp Q partials and the CTA's dW2 accumulator.
+// =============================================================================================
+template <int MODE>
+__global__ void __launch_bounds__(kMaxStepWarps * 32, 1) step_kernel(const StepArgs a) {
+    extern __shared__ __align__(16) float smem[];
+    const Hyper& hp = a.hp;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const int nthreads = blockDim.x;
+    const int D = hp.D, H = hp.H, Hs = hp.Hs, wn = hp.wn;
+    const int rows_x = (MODE == kEnvStep) ? (wn + 1) : D;
+
+    float* W1s = smem;
+    float* W2s = W1s + (size_t)D * Hs;
+    float* Xs = W2s + (size_t)Hs * 4;
+    float* Xn = Xs + (size_t)rows_x * kXStride;  // kMsgUpdate only
+    float* qpart = (MODE == kMsgUpdate) ? (Xn + (size_t)rows_x * kXStride) : Xn;
+    float* dw2acc = qpart + (size_t)nwarps * 2 * 3 * 32;
+
+    // ---- stage W1 with cp.async in groups of 32 rows, W2 / padding / accumulators directly
+    const float* W1g = a.params;
+    const float* W2g = a.params + (size_t)D * H;
+    const int H4 = H >> 2;
+    const int n_groups = (D + 31) >> 5;
+    for (int g = 0; g < n_groups; ++g) {
+        const int r0 = g << 5;
+        const int nr = min(32, D - r0);
+        for (int idx = tid; idx < nr * H4; idx += nthreads) {
+            const int r = r0 + idx / H4, c4 = idx - (idx / H4) * H4;
+            cp_async16(W1s + (size_t)r * Hs + c4 * 4, W1g + (size_t)r * H + c4 * 4);
+        }
+        cp_async_commit();
+    }
+    if (Hs > H) {
+        const int padc = Hs - H;
+        for (int idx = tid; idx < D * padc; idx += nthreads) {
+            const int r = idx / padc, c = H + (idx - r * padc);
+            W1s[(size_t)r * Hs + c] = 0.0f;
+        }
+    }
+    for (int j = tid; j < Hs; j += nthreads) {
+        float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (j < H) { w.x = W2g[j * 3 + 0]; w.y = W2g[j * 3 + 1]; w.z = W2g[j * 3 + 2]; }
+        reinterpret_cast<float4*>(W2s)[j] = w;
+    }
+    for (int j = tid; j < Hs * 3; j += nthreads) dw2acc[j] = 0.0f;
+
+    const int32_t istep = (MODE == kEnvStep) ? *a.d_step : 0;
+    const int64_t B = a.B;
+    const int64_t n_tiles = (B + kTileEnvs - 1) / kTileEnvs;
+    const int c0 = warp * kColsPerWarp;
+    const float bias = hp.bias;
+    bool first = true;
+
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        const int64_t e = tile * kTileEnvs + lane;
+        const bool valid = e < B;
+        const int64_t ec = valid ? e : (B - 1);
+
+        // ---- per-lane episode record (every warp keeps its own copy: no broadcast needed later)
+        double budget = 0.0, share_value = 0.0;
+        int32_t shares = 0;
+        if (MODE == kEnvStep) {
+            budget = a.budget[ec];
+            shares = a.shares[ec];
+            share_value = a.share_value[ec];
+        }
+
+        // ---- state tile, transposed: Xs[k][episode].  Coalesced row reads from HBM/L2.
+        // TrainerChildActor.scala:89-91: prices.slice(i, i + historyDim + 1); one extra element
+        // (index wn) is both the last input of s' (:144) and the new share value (:94).
+        for (int el = warp; el < kTileEnvs; el += nwarps) {
+            const int64_t ee = min(tile * kTileEnvs + el, B - 1);
+            if (MODE == kEnvStep) {
+                const float* src = a.prices + (int64_t)a.series_of_env[ee] * a.T + istep;
+                for (int k = lane; k < rows_x; k += 32) Xs[k * kXStride + el] = __ldg(src + k);
+            } else {
+                const float* src = a.states + ee * D;
+                for (int k = lane; k < D; k += 32) Xs[k * kXStride + el] = __ldg(src + k);
+                if (MODE == kMsgUpdate) {
+                    const float* src2 = a.next_states + ee * D;
+                    for (int k = lane; k < D; k += 32) Xn[k * kXStride + el] = __ldg(src2 + k);
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- hidden layer: z1 = x · W1 for s and s' (QDecisionPolicyActor.scala:43), k ascending
+        float acc_s[kColsPerWarp], acc_n[kColsPerWarp];
+#pragma unroll
+        for (int c = 0; c < kColsPerWarp; ++c) { acc_s[c] = 0.0f; acc_n[c] = 0.0f; }
+        const int kmax = (MODE == kEnvStep) ? wn : D;
+        float x_carry = Xs[lane];
+#pragma unroll 1
+        for (int kb = 0; kb < kmax; kb += 32) {
+            if (first) {  // W1 row group kb/32 must have landed (block-uniform branch)
+                cp_async_wait_pending(n_groups - 1 - (kb >> 5));
+                __syncthreads();
+            }
+            const int kend = min(kb + 32, kmax);
+#pragma unroll 4
+            for (int k = kb; k < kend; ++k) {
+                float x_s, x_n = 0.0f;
+                if (MODE == kEnvStep) {
+                    x_s = x_carry;
+                    x_n = Xs[(k + 1) * kXStride + lane];
+                    x_carry = x_n;
+                } else {
+                    x_s = Xs[k * kXStride + lane];
+                    if (MODE == kMsgUpdate) x_n = Xn[k * kXStride + lane];
+                }
+                const float4* w4 = reinterpret_cast<const float4*>(W1s + (size_t)k * Hs + c0);
+#pragma unroll
+                for (int j = 0; j < kColsPerWarp / 4; ++j) {
+                    const float4 w = w4[j];
+                    acc_s[4 * j + 0] = fmaf(x_s, w.x, acc_s[4 * j + 0]);
+                    acc_s[4 * j + 1] = fmaf(x_s, w.y, acc_s[4 * j + 1]);
+                    acc_s[4 * j + 2] = fmaf(x_s, w.z, acc_s[4 * j + 2]);
+                    acc_s[4 * j + 3] = fmaf(x_s, w.w, acc_s[4 * j + 3]);
+                    if (MODE != kMsgSelect) {
+                        acc_n[4 * j + 0] = fmaf(x_n, w.x, acc_n[4 * j + 0]);
+                        acc_n[4 * j + 1] = fmaf(x_n, w.y, acc_n[4 * j + 1]);
+                        acc_n[4 * j + 2] = fmaf(x_n, w.z, acc_n[4 * j + 2]);
+                        acc_n[4 * j + 3] = fmaf(x_n, w.w, acc_n[4 * j + 3]);
+                    }
+                }
+            }
+        }
+        if (first && MODE == kEnvStep) {  // the two budget/shares rows may sit in a later group
+            cp_async_wait_pending(0);
+            __syncthreads();
+        }
+        first = false;
+
+        const float* w_budget = W1s + (size_t)wn * Hs + c0;
+        const float* w_shares = W1s + (size_t)(wn + 1) * Hs + c0;
+        if (MODE == kEnvStep) {
+            // last two inputs of s: (float)budget, (float)shares (TrainerChildActor.scala:90)
+            const float xb = __double2float_rn(budget);
+            const float xs = (float)shares;
+#pragma unroll
+            for (int c = 0; c < kColsPerWarp; ++c) {
+                acc_s[c] = fmaf(xb, w_budget[c], acc_s[c]);
+                acc_s[c] = fmaf(xs, w_shares[c], acc_s[c]);
+            }
+        }
+        // h = relu(z1 + 0.1) (:43); partial of q = h · W2 over this warp's columns (:47)
+        float pq[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+        for (int c = 0; c < kColsPerWarp; ++c) {
+            const float v = acc_s[c] + bias;
+            acc_s[c] = v > 0.0f ? v : 0.0f;
+            const float4 w2 = reinterpret_cast<const float4*>(W2s)[c0 + c];
+            pq[0] = fmaf(acc_s[c], w2.x, pq[0]);
+            pq[1] = fmaf(acc_s[c], w2.y, pq[1]);
+            pq[2] = fmaf(acc_s[c], w2.z, pq[2]);
+        }
+#pragma unroll
+        for (int x = 0; x < 3; ++x) qpart[((warp * 2 + 0) * 3 + x) * 32 + lane] = pq[x];
+        __syncthreads();
+
+        float q_s[3];
+#pragma unroll
+        for (int x = 0; x < 3; ++x) {
+            float s = 0.0f;
+            for (int w = 0; w < nwarps; ++w) s += qpart[((w * 2 + 0) * 3 + x) * 32 + lane];
+            s += bias;
+            q_s[x] = s > 0.0f ? s : 0.0f;
+        }
+
+        // ---- SelectionAction (QDecisionPolicyActor.scala:56-62)
+        int action = 0, explored = 0;
+        if (MODE != kMsgUpdate) {
+            const float step_f = (MODE == kEnvStep) ? (float)istep : a.steps[ec];
+            const uint64_t env_id = (MODE == kEnvStep) ? (uint64_t)(a.env_id_base + e)
+                                                       : (uint64_t)(a.env_ids ? a.env_ids[ec] : e);
+            const uint32_t tctr = (MODE == kEnvStep) ? (uint32_t)istep : (uint32_t)step_f;
+            uint32_t r[4];
+            philox4x32_10((uint32_t)env_id, (uint32_t)(env_id >> 32), tctr, 1u,
+                          (uint32_t)hp.seed, (uint32_t)(hp.seed >> 32), r);
+            const float u = (float)(r[0] >> 8) * (1.0f / 16777216.0f);   // nextFloat(): 24 bits
+            float thr = __fdiv_rn(step_f, hp.step_div);
+            if (hp.epsilon < thr) thr = hp.epsilon;                       // Seq(epsilon, step/1000f).min
+            if (u < thr) {
+                action = argmax3(q_s);
+            } else {
+                explored = 1;
+                action = (int)(((uint64_t)r[1] * 3u) >> 32);             // nextInt(3)
+            }
+        }
+        if (MODE == kMsgSelect) {
+            if (warp == 0 && valid) {
+                a.actions_out[e] = action;
+                if (a.q_out) {
+                    a.q_out[e * 3 + 0] = q_s[0]; a.q_out[e * 3 + 1] = q_s[1]; a.q_out[e * 3 + 2] = q_s[2];
+                }
+            }
+            __syncthreads();
+            continue;
+        }
+
+        // ---- decision, reward, next state (TrainerChildActor.scala:92-96, :118-123, :136-146)
+        float r32 = 0.0f;
+        double nb = 0.0, p_new = 0.0;
+        int32_t ns = 0;
+        int a_eff = 2;
+        if (MODE == kEnvStep) {
+            p_new = (double)Xs[wn * kXStride + lane];                               // :94
+            const double cur = __dadd_rn(budget, __dmul_rn((double)shares, share_value));  // :92
+            const double base_b = hp.bookkeeping == 0 ? a.B0 : budget;
+            const int32_t base_n = hp.bookkeeping == 0 ? a.N0 : shares;
+            nb = base_b; ns = base_n;
+            if (action == 0 && base_b >= p_new) { nb = __dsub_rn(base_b, p_new); ns = base_n + 1; a_eff = 0; }
+            else if (action == 1 && base_n > 0) { nb = __dadd_rn(base_b, p_new); ns = base_n - 1; a_eff = 1; }
+            const double newp = __dadd_rn(nb, __dmul_rn((double)ns, p_new));        // :141
+            r32 = __double2float_rn(__dsub_rn(newp, cur));                          // :142, :158
+            const float xnb = __double2float_rn(nb);
+            const float xns = (float)ns;
+#pragma unroll
+            for (int c = 0; c < kColsPerWarp; ++c) {
+                acc_n[c] = fmaf(xnb, w_budget[c], acc_n[c]);
+                acc_n[c] = fmaf(xns, w_shares[c], acc_n[c]);
+            }
+        } else {
+            r32 = a.rewards[ec];
+        }
+        pq[0] = pq[1] = pq[2] = 0.0f;
+#pragma unroll
+        for (int c = 0; c < kColsPerWarp; ++c) {
+            float v = acc_n[c] + bias;
+            v = v > 0.0f ? v : 0.0f;
+            const float4 w2 = reinterpret_cast<const float4*>(W2s)[c0 + c];
+            pq[0] = fmaf(v, w2.x, pq[0]);
+            pq[1] = fmaf(v, w2.y, pq[1]);
+            pq[2] = fmaf(v, w2.z, pq[2]);
+        }
+#pragma unroll
+        for (int x = 0; x < 3; ++x) qpart[((warp * 2 + 1) * 3 + x) * 32 + lane] = pq[x];
+        __syncthreads();
+
+        // ---- UpdateQ target and output-layer backward (QDecisionPolicyActor.scala:67-73, :49)
+        float q_n[3];
+#pragma unroll
+        for (int x = 0; x < 3; ++x) {
+            float s = 0.0f;
+            for (int w = 0; w < nwarps; ++w) s += qpart[((w * 2 + 1) * 3 + x) * 32 + lane];
+            s += bias;
+            q_n[x] = s > 0.0f ? s : 0.0f;
+        }
+        const int kn = argmax3(q_n);                                                 // :69
+        const float qn_k = kn == 0 ? q_n[0] : (kn == 1 ? q_n[1] : q_n[2]);
+        const float qs_k = kn == 0 ? q_s[0] : (kn == 1 ? q_s[1] : q_s[2]);
+        const float target = __fadd_rn(r32, __fmul_rn(hp.gamma, qn_k));              // :70
+        // d/dq of square(y - q) with y[k] = target and y[j] = q[j] elsewhere; ReluGrad on q
+        const float dq = -__fmul_rn(2.0f, __fsub_rn(target, qs_k));
+        const float dz2 = (valid && qs_k > 0.0f) ? dq : 0.0f;
+
+        float dz1v[kColsPerWarp];
+#pragma unroll
+        for (int c = 0; c < kColsPerWarp; ++c) {
+            const float w2k = W2s[(c0 + c) * 4 + kn];
+            dz1v[c] = acc_s[c] > 0.0f ? __fmul_rn(dz2, w2k) : 0.0f;
+        }
+        if (valid) {
+            float4* dst = reinterpret_cast<float4*>(a.dz1 + e * H + c0);
+#pragma unroll
+            for (int j = 0; j < kColsPerWarp / 4; ++j)
+                if (c0 + 4 * j < H) dst[j] = make_float4(dz1v[4 * j], dz1v[4 * j + 1], dz1v[4 * j + 2], dz1v[4 * j + 3]);
+        }
+        // dW2[:, k] += h * dz2, reduced over the tile's episodes with a fixed shuffle tree
+#pragma unroll
+        for (int c = 0; c < kColsPerWarp; ++c) {
+            const float hv = __fmul_rn(acc_s[c], dz2);
+#pragma unroll
+            for (int x = 0; x < 3; ++x) {
+                const float s = warp_sum(kn == x ? hv : 0.0f);
+                if (lane == 0) dw2acc[(c0 + c) * 3 + x] += s;
+            }
+        }
+
+        if (warp == 0 && valid) {
+            if (MODE == kEnvStep) {
+                a.xextra[e] = __double2float_rn(budget);
+                a.xextra[a.Bpad + e] = (float)shares;
+                a.budget[e] = nb;                     // carry (TrainerChildActor.scala:99-102)
+                a.shares[e] = ns;
+                a.share_value[e] = p_new;
+                const TraceDev& t = a.trace;
+                const int64_t ti = (int64_t)(istep - a.trace_step0) * B + e;
+                if (t.action_sel) t.action_sel[ti] = action;
+                if (t.action_eff) t.action_eff[ti] = a_eff;
+                if (t.explored) t.explored[ti] = explored;
+                if (t.k_next) t.k_next[ti] = kn;
+                if (t.reward) t.reward[ti] = r32;
+                if (t.target) t.target[ti] = target;
+                if (t.budget) t.budget[ti] = nb;
+                if (t.shares) t.shares[ti] = ns;
+                if (t.q_s) { t.q_s[ti * 3] = q_s[0]; t.q_s[ti * 3 + 1] = q_s[1]; t.q_s[ti * 3 + 2] = q_s[2]; }
+                if (t.q_n) { t.q_n[ti * 3] = q_n[0]; t.q_n[ti * 3 + 1] = q_n[1]; t.q_n[ti * 3 + 2] = q_n[2]; }
+            } else if (a.q_out) {  // kMsgUpdate: optional q(s) for inspection
+                a.q_out[e * 3 + 0] = q_s[0]; a.q_out[e * 3 + 1] = q_s[1]; a.q_out[e * 3 + 2] = q_s[2];
+            }
+        }
+        __syncthreads();
+    }
+
+    cp_async_wait_pending(0);
+    __syncthreads();
+    if (MODE != kMsgSelect) {
+        float* dst = a.dw2_part + (size_t)blockIdx.x * (3 * H);
+        for (int j = tid; j < 3 * H; j += nthreads) dst[j] = dw2acc[j];
+    }
+}
+
+// =============================================================================================
+// K2 — dW1 = X^T · dZ1 (the MatMul gradient of QDecisionPolicyActor.scala:43 w.r.t. weight1),
+// split over episodes: CTA s owns episodes [B*s/S, B*(s+1)/S) and produces one D x H partial.
+// Thread (rt, ct) keeps a 16 x 8 register tile: rows rt*16.., columns {4ct..4ct+3} and
+// {4(ct+n_ct)..+3}; per episode it reads 4 + 2 float4 from shared memory for 128 FMAs.
+// =============================================================================================
+template <int MODE>
+__global__ void __launch_bounds__(kDw1MaxThreads, 1) dw1_kernel(const Dw1Args a) {
+    extern __shared__ __align__(16) float smem[];
+    const Hyper& hp = a.hp;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const int nthreads = blockDim.x;
+    const int D = hp.D, H = hp.H, wn = hp.wn;
+    const int Dp = a.n_rt * kDw1Rows, Hp = a.n_ct * kDw1Cols;
+    float* Xc = smem;                                   // [chunk][Dp]
+    float* Zc = Xc + (size_t)kDw1ChunkEnvs * Dp;        // [chunk][Hp]
+    const int32_t istep = (MODE == kEnvStep) ? *a.d_step : 0;
+
+    const int64_t S = gridDim.x;
+    const int64_t e0 = a.B * (int64_t)blockIdx.x / S, e1 = a.B * ((int64_t)blockIdx.x + 1) / S;
+    const bool active = tid < a.n_rt * a.n_ct;
+    const int rt = active ? tid / a.n_ct : 0, ct = active ? tid - (tid / a.n_ct) * a.n_ct : 0;
+
+    float acc[kDw1Rows][kDw1Cols];
+#pragma unroll
+    for (int r = 0; r < kDw1Rows; ++r)
+#pragma unroll
+        for (int c = 0; c < kDw1Cols; ++c) acc[r][c] = 0.0f;
+
+    const int H4 = H >> 2, Hp4 = Hp >> 2;
+    for (int64_t eb = e0; eb < e1; eb += kDw1ChunkEnvs) {
+        const int ne = (int)min((int64_t)kDw1ChunkEnvs, e1 - eb);
+        // stage the states of this chunk (the x fed with trainOp, QDecisionPolicyActor.scala:72)
+        for (int el = warp; el < ne; el += nwarps) {
+            const int64_t ee = eb + el;
+            if (MODE == kEnvStep) {
+                const float* src = a.prices + (int64_t)a.series_of_env[ee] * a.T + istep;
+                for (int k = lane; k < Dp; k += 32) {
+                    float v = 0.0f;
+                    if (k < wn) v = __ldg(src + k);
+                    else if (k == wn) v = a.xextra[ee];
+                    else if (k == wn + 1) v = a.xextra[a.Bpad + ee];
+                    Xc[el * Dp + k] = v;
+                }
+            } else {
+                const float* src = a.states + ee * D;
+                for (int k = lane; k < Dp; k += 32) Xc[el * Dp + k] = k < D ? __ldg(src + k) : 0.0f;
+            }
+        }
+        for (int idx = tid; idx < ne * Hp4; idx += nthreads) {
+            const int el = idx / Hp4, c4 = idx - el * Hp4;
+            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (c4 < H4) v = reinterpret_cast<const float4*>(a.dz1 + (eb + el) * H)[c4];
+            reinterpret_cast<float4*>(Zc)[el * Hp4 + c4] = v;
+        }
+        __syncthreads();
+        if (active) {
+            const float4* xp = reinterpret_cast<const float4*>(Xc + rt * kDw1Rows);
+            const float4* zp0 = reinterpret_cast<const float4*>(Zc) + ct;
+            const float4* zp1 = reinterpret_cast<const float4*>(Zc) + ct + a.n_ct;
+            const int xs4 = Dp >> 2;
+#pragma unroll 2
+            for (int el = 0; el < ne; ++el) {
+                float x[kDw1Rows], z[kDw1Cols];
+#pragma unroll
+                for (int j = 0; j < kDw1Rows / 4; ++j) {
+                    const float4 v = xp[el * xs4 + j];
+                    x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
+                }
+                const float4 za = zp0[el * Hp4], zb = zp1[el * Hp4];
+                z[0] = za.x; z[1] = za.y; z[2] = za.z; z[3] = za.w;
+                z[4] = zb.x; z[5] = zb.y; z[6] = zb.z; z[7] = zb.w;
+#pragma unroll
+                for (int r = 0; r < kDw1Rows; ++r)
+#pragma unroll
+                    for (int c = 0; c < kDw1Cols; ++c) acc[r][c] = fmaf(x[r], z[c], acc[r][c]);
+            }
+        }
+        __syncthreads();
+    }
+
+    if (active) {
+        float* out = a.part + (size_t)blockIdx.x * ((size_t)D * H);
+#pragma unroll
+        for (int r = 0; r < kDw1Rows; ++r) {
+            const int row = rt * kDw1Rows + r;
+            if (row < D) {
+                if (ct < H4)
+                    reinterpret_cast<float4*>(out + (size_t)row * H)[ct] = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
+                if (ct + a.n_ct < H4)
+                    reinterpret_cast<float4*>(out + (size_t)row * H)[ct + a.n_ct] = make_float4(acc[r][4], acc[r][5], acc[r][6], acc[r][7]);
+            }
+        }
+    }
+}
+
+// =============================================================================================
+// K3 — gradient reduction + AdaGrad.  Eight lanes per parameter sum the partials (interleaved,
+// then a fixed xor tree); the leader applies ResourceApplyAdagrad as trainOp does at
+// QDecisionPolicyActor.scala:50, :73:   accum += g*g;  var -= (g*lr) * (1/sqrt(accum)).
+// With do_reduce = 0 it applies a gradient that is already summed (after the all-reduce).
+// =============================================================================================
+__global__ void __launch_bounds__(256) apply_kernel(const ApplyArgs a) {
+    const int64_t gid = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t p = gid / kApplyLanes;
+    const int sub = (int)(gid - p * kApplyLanes);
+    if (gid == 0 && a.d_step && a.step_inc) *a.d_step += a.step_inc;
+    const bool in_range = p < a.P;  // whole 8-lane groups share p, so shuffles below stay converged per group
+    float g = 0.0f;
+    if (a.do_reduce) {
+        if (in_range) {
+            const float* src; int n; int64_t stride, off;
+            if (p < a.P1) { src = a.part1; n = a.n1; stride = a.P1; off = p; }
+            else { src = a.part2; n = a.n2; stride = a.P - a.P1; off = p - a.P1; }
+            float s = 0.0f;
+            for (int j = sub; j < n; j += kApplyLanes) s += src[(int64_t)j * stride + off];
+            g = s;
+        }
+        g += __shfl_xor_sync(0xffffffffu, g, 1);
+        g += __shfl_xor_sync(0xffffffffu, g, 2);
+        g += __shfl_xor_sync(0xffffffffu, g, 4);
+        if (in_range && sub == 0) a.grad[p] = g;
+    } else if (in_range && sub == 0) {
+        g = a.grad[p];
+    }
+    if (a.do_adagrad && in_range && sub == 0) {
+        const float acc = __fadd_rn(a.acc[p], __fmul_rn(g, g));
+        a.acc[p] = acc;
+        const float upd = __fmul_rn(__fmul_rn(g, a.hp.lr), __fdiv_rn(1.0f, __fsqrt_rn(acc)));
+        a.params[p] = __fsub_rn(a.params[p], upd);
+    }
+}
+
+// budget + shares * shareValue (TrainerChildActor.scala:68)
+__global__ void portfolio_kernel(const double* budget, const int32_t* shares, const double* sv,
+                                 int64_t n, double* out) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < n) out[e] = __dadd_rn(budget[e], __dmul_rn((double)shares[e], sv[e]));
+}
+
+// Deterministic fp64 block sums of (x - shift)^pow, pow in {1, 2}; finished on the host side of
+// the library over <= 1024 block results (TrainerRouterActor.scala:149-151).
+__global__ void __launch_bounds__(256) moment_kernel(const double* x, int64_t n, double shift, int pw,
+                                                     double* block_out) {
+    __shared__ double sh[256];
+    double s = 0.0;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+        const double d = x[i] - shift;
+        s += (pw == 2) ? d * d : d;
+    }
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int o = 128; o > 0; o >>= 1) {
+        if ((int)threadIdx.x < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) block_out[blockIdx.x] = sh[0];
+}
+
+__global__ void fill_kernel(float* p, int64_t n, float v) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+__global__ void env_init_kernel(double* budget, int32_t* shares, double* sv, int64_t n, double B0, int32_t N0) {
+    const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (e < n) { budget[e] = B0; shares[e] = N0; sv[e] = 0.0; }   // TrainerChildActor.scala:84-86
+}
+
+#endif  // __CUDACC__
+
+}  // namespace qp
