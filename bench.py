@@ -1,0 +1,329 @@
+#!/usr/bin/env python
+"""bench.py — env-steps/sec (select-action + TD update) of the Q-policy hot path on B200.
+
+    python bench.py --gpus 1 --steps K --warmup W            # our arm, one GPU
+    torchrun ... bench.py --gpus N --steps K --warmup W      # our arm, N GPUs (one rank per GPU)
+    python bench.py --impl reference --steps K --warmup W    # the CPU arm (oracle port, all host cores)
+
+A bench "step" is one pass of the hot path over one batch of synthetic input: a full episode
+(series_len - window env-steps, 799 at the default sizes) of every episode of the workload.
+N = 1 workload: BASELINE.json configs[1] — 4096 parallel episodes, hist 200 (window 201), hidden 200,
+fp32, one synthetic 1000-step quarter-tick random-walk series per episode, budget 1000, 0 shares.
+N > 1: the same per GPU (weak scaling), episodes sharded by rank, one gradient all-reduce per env-step.
+
+value  : whole-job env-steps/s with prices already resident in HBM (CUDA events on the library's stream).
+e2e    : the same through qp_train with HOST buffers: upload of the price series from pinned memory,
+         every env-step, download of the portfolios — all inside the timed region.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import numpy as np  # noqa: E402
+
+WINDOW, HIDDEN, SERIES_LEN, BUDGET0, SHARES0, SEED = 201, 200, 1000, 1000.0, 0, 42
+D = WINDOW + 2
+P = D * HIDDEN + 3 * HIDDEN
+FLOP_PER_ENV_STEP = 6 * D * HIDDEN + 16 * HIDDEN          # 246 800
+METRIC = "env-steps/sec (act+TD update)"
+UNIT = "env-steps/s"
+
+
+def bytes_per_env_step(envs_per_gpu: int) -> float:
+    """BASELINE.md §3 / SURVEY.md §8(d): 4*(Wn+1) + 40 + 24*P/N_g algorithmic bytes."""
+    return 4 * (WINDOW + 1) + 40 + 24.0 * P / envs_per_gpu
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        m = json.load(open(path))
+        return dict(hbm_gbs=float(m["hbm_gbs"]), bf16_tflops=float(m["bf16_tflops"]),
+                    bf16_sustained=float(m.get("bf16_tflops_sustained", m["bf16_tflops"])), source="measured")
+    return dict(hbm_gbs=6650.0, bf16_tflops=1590.0, bf16_sustained=1400.0, source="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu = gpu_index
+        self.proc = None
+        self.path = None
+
+    def start(self):
+        try:
+            fd, self.path = tempfile.mkstemp(suffix=".csv")
+            os.close(fd)
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50",
+                 "-i", str(self.gpu)], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+        except Exception:
+            self.proc = None
+
+    def stop(self):
+        out = dict(sm_mhz=None, sm_max_mhz=None, reasons=[], samples=0)
+        if self.proc is None:
+            return out
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        try:
+            for line in open(self.path):
+                f = [x.strip() for x in line.split(",")]
+                if len(f) < 8:
+                    continue
+                try:
+                    sm.append(float(f[1])); mx.append(float(f[2]))
+                except ValueError:
+                    continue
+                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
+                    if v == "Active":
+                        reasons.add(name)
+            os.unlink(self.path)
+        except Exception:
+            pass
+        if sm:
+            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), samples=len(sm))
+        out["reasons"] = sorted(reasons)
+        return out
+
+
+def dist_env():
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    return rank, world, local
+
+
+# =================================================================================================
+# reference arm: the CPU implementation of the path (oracle port), all host cores
+# =================================================================================================
+def run_reference(args):
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return 0
+    from oracle import oracle as O
+    n_envs = args.envs_per_gpu * max(1, args.gpus)
+    threads = O.max_threads()
+    cfg = O.Config()
+    prices = O.gen_prices(SEED, 0, n_envs, SERIES_LEN)
+    o = O.Oracle(cfg)
+    o.env_create(prices, np.arange(n_envs, dtype=np.int32), BUDGET0, SHARES0)
+    # size one step as a bounded sample: the first S env-steps of the workload's episodes
+    t0 = time.perf_counter()
+    o.env_step(1, threads=threads)
+    t1 = time.perf_counter() - t0
+    budget_s = min(120.0 / max(1, args.steps + args.warmup), 20.0)
+    S = int(max(1, min(40, budget_s / max(t1, 1e-6))))
+    total_needed = S * (args.steps + args.warmup)
+    if total_needed + 1 > o.n_steps_total:
+        S = max(1, (o.n_steps_total - 1) // (args.steps + args.warmup))
+    for _ in range(args.warmup):
+        o.env_step(S, threads=threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        o.env_step(S, threads=threads)
+    dt = time.perf_counter() - t0
+    value = args.steps * S * n_envs / dt
+    sample = f"{S} env-steps x {n_envs} episodes per bench step (prefix of the {SERIES_LEN - WINDOW}-step episode)"
+    line = dict(
+        impl="reference", metric=METRIC, value=value, unit=UNIT, n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
+        ms_per_step=dt / args.steps * 1e3, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="fp32",
+        data="synthetic", config=workload_config(args, n_envs),
+        cpu_baseline=dict(value=value, unit=UNIT, cores=threads, kind="port", sample=sample),
+        e2e=dict(value=value, unit=UNIT, h2d_bytes_per_step=0, d2h_bytes_per_step=0),
+        note="reference tensorflow_scala path cannot run here (no JVM; artefact is darwin-only): timed arm is the "
+             "C restatement oracle/qp_oracle.c, batched-SUM, pthreads over all host cores",
+    )
+    print(json.dumps(line))
+    return 0
+
+
+def workload_config(args, n_envs):
+    return dict(workload=f"configs[1]: {args.envs_per_gpu} parallel episodes per GPU, hist 200 (window {WINDOW}), "
+                         f"hidden {HIDDEN}, fp32, {SERIES_LEN}-step random-walk series per episode, budget 1000",
+                episodes=n_envs, env_steps_per_bench_step=SERIES_LEN - WINDOW, series_len=SERIES_LEN,
+                bookkeeping="REFERENCE", l2="flushed between bench steps (256 MiB write inside the timed region)",
+                parallelism=f"dp{max(1, args.gpus)} (episodes sharded, gradient all-reduce per env-step)" if args.gpus > 1 else "single GPU")
+
+
+# =================================================================================================
+# our arm
+# =================================================================================================
+def run_ours(args):
+    import torch
+    import scala_akka_tensorflow_sharetrade_helper_b200 as q
+    from oracle import oracle as O
+
+    rank, world, local = dist_env()
+    if world != max(1, args.gpus):
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("--gpus N > 1 must be launched with torch.distributed.run (one rank per GPU)")
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the product path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    n_local = args.envs_per_gpu
+    n_total = n_local * world
+    n_env_steps = SERIES_LEN - WINDOW
+    # synthetic inputs: this rank's shard of the global series / episodes
+    prices_np = O.gen_prices(SEED, rank * n_local, n_local, SERIES_LEN)
+    soe_np = np.arange(n_local, dtype=np.int32)
+    prices_pin = torch.from_numpy(prices_np).pin_memory()
+    soe_pin = torch.from_numpy(soe_np).pin_memory()
+    ports_pin = torch.empty(n_local, dtype=torch.float64).pin_memory()
+
+    pol = q.QDecisionPolicy(q.PolicyConfig(device=local, seed=SEED))
+    if world > 1:
+        pol.dist_init(dist, rank, world)
+    stream = torch.cuda.ExternalStream(pol.stream, device=torch.device("cuda", local))
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local}")
+
+    def barrier():
+        if dist is not None:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def resident_pass():
+        with torch.cuda.stream(stream):
+            flush.zero_()                           # L2 flush (126 MB L2 < 256 MiB)
+        pol.env_reset()
+        pol.env_step(n_env_steps, sync=False)
+
+    def e2e_pass():
+        with torch.cuda.stream(stream):
+            flush.zero_()
+        pol.train(prices_pin.numpy(), soe_pin.numpy(), BUDGET0, SHARES0, env_id_base=rank * n_local)
+
+    pol.env_create(prices_np, soe_np, BUDGET0, SHARES0, env_id_base=rank * n_local)
+
+    def timed(fn, k, w):
+        for _ in range(w):
+            fn()
+        barrier()
+        sampler = ClockSampler(local)
+        sampler.start()
+        l0 = pol.launch_count
+        ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        t0 = time.perf_counter()
+        with torch.cuda.stream(stream):
+            ev0.record()
+        for _ in range(k):
+            fn()
+        with torch.cuda.stream(stream):
+            ev1.record()
+        barrier()
+        wall = time.perf_counter() - t0
+        clocks = sampler.stop()
+        ms = ev0.elapsed_time(ev1)
+        launches = pol.launch_count - l0
+        if dist is not None:
+            t = torch.tensor([ms, wall], dtype=torch.float64, device=f"cuda:{local}")
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms, wall = float(t[0]), float(t[1])
+        return ms, wall, clocks, launches
+
+    ms, wall, clocks, launches = timed(resident_pass, args.steps, max(args.warmup, 3))
+    value = args.steps * n_env_steps * n_total / (ms * 1e-3)
+    e2e_ms, e2e_wall, e2e_clocks, _ = timed(e2e_pass, args.steps, 1)
+    e2e_value = args.steps * n_env_steps * n_total / (e2e_wall)
+
+    # ---- roofline of the dominant kernel, measured live with CUDA events on the launching stream
+    pol.env_reset()
+    pol.env_step(20)
+    n_prof = 200
+    kms = pol.env_step_timed(n_prof)
+    per_kernel_us = (kms / n_prof * 1e3).tolist()
+    names = ["step_kernel", "dw1_kernel", "apply_kernel"]
+    dom = int(np.argmax(per_kernel_us))
+    peaks = measured_peaks()
+    fp32_peak = pol.measure_fp32_peak()
+    # algorithmic work of each kernel per launch
+    k_bytes = [n_local * (4 * (WINDOW + 1) + 40) + 4 * P, 0.0, 24.0 * P - 4 * P]
+    k_flops = [n_local * (4 * D * HIDDEN + 16 * HIDDEN), n_local * 2 * D * HIDDEN, 6.0 * P]
+    dur = per_kernel_us[dom] * 1e-6
+    step_us = sum(per_kernel_us)
+    roofline = dict(
+        bound="hbm", kernel=names[dom], achieved=k_bytes[dom] / dur / 1e9, peak=peaks["hbm_gbs"], unit="GB/s",
+        frac=k_bytes[dom] / dur / 1e9 / peaks["hbm_gbs"], traffic=None, peak_source=peaks["source"] + " (burst copy)",
+        avg_launch_us=per_kernel_us[dom], kernel_us=dict(zip(names, per_kernel_us)),
+        binding=dict(bound="fp32-fma", note="compute-bound at fp32: 227 FLOP/B vs ridge ~11 (SURVEY.md §8d)",
+                     achieved=k_flops[dom] / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
+                     frac=k_flops[dom] / dur / 1e12 / fp32_peak if fp32_peak else None,
+                     peak_source="measured live (qp_measure_fp32_peak, dependency-free FFMA)"),
+        step=dict(us=step_us, hbm_frac=bytes_per_env_step(n_local) * n_local / (step_us * 1e-6) / 1e9 / peaks["hbm_gbs"],
+                  fp32_frac=FLOP_PER_ENV_STEP * n_local / (step_us * 1e-6) / 1e12 / fp32_peak if fp32_peak else None,
+                  bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP),
+    )
+
+    line = dict(
+        metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
+        ms_per_step=ms / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="fp32",
+        data="synthetic", config=workload_config(args, n_total), clocks=clocks,
+        e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=int(prices_np.nbytes + soe_np.nbytes),
+                 d2h_bytes_per_step=int(n_local * 8), ms_per_step=e2e_wall / args.steps * 1e3, clocks=e2e_clocks,
+                 api="qp_train (TrainerChildActor.train): pinned host prices in, portfolios out"),
+        gpu_launches=int(launches), roofline=roofline, wall_s=wall,
+    )
+
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        cfg = O.Config()
+        n_s = args.cpu_sample_steps
+        o = O.Oracle(cfg)
+        o.env_create(prices_np, soe_np, BUDGET0, SHARES0)
+        t0 = time.perf_counter()
+        o.env_step(n_s, mode=1)
+        dt = time.perf_counter() - t0
+        line["cpu_baseline"] = dict(
+            value=n_s * n_local / dt, unit=UNIT, cores=1, kind="port",
+            sample=f"first {n_s} env-steps of the same {n_local} episodes, sequential per-sample updates "
+                   f"(the reference's one-mailbox order), oracle/qp_oracle.c, {dt:.1f} s",
+            host_cores_available=O.max_threads())
+    pol.close()
+    if rank == 0:
+        print(json.dumps(line))
+    if dist is not None:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--envs-per-gpu", type=int, default=4096)
+    ap.add_argument("--cpu-sample-steps", type=int, default=30)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_ours(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

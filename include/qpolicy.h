@@ -160,6 +160,9 @@ void* qp_stream(qp_handle* h);
 /* Runs n_steps with CUDA events around each kernel; ms_sum[QP_N_KERNELS] receives the summed
  * device time per kernel in milliseconds. */
 int qp_env_step_timed(qp_handle* h, int32_t n_steps, float* ms_sum);
+/* Measured fp32-FMA throughput of the handle's GPU in TFLOP/s (dependency-free FFMA streams):
+ * the roof that binds the fp32 path; MEASURED_PEAKS.json only carries HBM and bf16 tensor peaks. */
+int qp_measure_fp32_peak(qp_handle* h, double* tflops);
 /* Kernels launched by this handle so far.  Returns the count. */
 int64_t qp_launch_count(const qp_handle* h);
 

@@ -636,6 +636,22 @@ __global__ void env_init_kernel(double* budget, int32_t* shares, double* sv, int
     if (e < n) { budget[e] = B0; shares[e] = N0; sv[e] = 0.0; }   // TrainerChildActor.scala:84-86
 }
 
+// Measurement aid: dependency-free FFMA streams, to measure the fp32-FMA roof of this GPU (the
+// binding roof of the fp32 path; MEASURED_PEAKS.json carries only HBM and bf16 tensor peaks).
+__global__ void __launch_bounds__(256) fma_peak_kernel(float* out, int iters, float a, float b) {
+    float v[16];
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = (float)(threadIdx.x + j);
+    for (int i = 0; i < iters; ++i) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) v[j] = fmaf(v[j], a, b);
+    }
+    float s = 0.0f;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) s += v[j];
+    if (s == 123.456f) out[0] = s;  // keeps the loop alive without a store in practice
+}
+
 #endif  // __CUDACC__
 
 }  // namespace qp

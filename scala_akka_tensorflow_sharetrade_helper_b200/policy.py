@@ -269,6 +269,11 @@ class QDecisionPolicy:
         self.n_envs = int(soe.size)
         return out
 
+    def measure_fp32_peak(self) -> float:
+        t = C.c_double()
+        check(self._lib.qp_measure_fp32_peak(self._h, C.byref(t)))
+        return t.value
+
     @property
     def stream(self) -> int:
         return int(self._lib.qp_stream(self._h) or 0)

@@ -1,0 +1,366 @@
+"""Parity of the CUDA path against the CPU oracle, through the C ABI (ctypes -> libqpolicy.so).
+
+Bit-exact: action indices, explore flags, share counts, budgets, rewards (integer and fp64
+book-keeping).  Within the stated fp32 tolerance (tests/_tol.py): Q-values, targets, gradients,
+updated weights; an action may differ only where the oracle's top-two Q gap is inside tolerance.
+"""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from tests import _tol
+from tests.golden.make_golden import grid_weights
+
+pytestmark = pytest.mark.gpu
+
+
+def q_mod():
+    import scala_akka_tensorflow_sharetrade_helper_b200 as q
+    return q
+
+
+def make_policy(cfg: O.Config, params=None, acc=None):
+    q = q_mod()
+    pc = q.PolicyConfig(window=cfg.wn, hidden=cfg.hidden, epsilon=cfg.epsilon, gamma=cfg.gamma, lr=cfg.lr,
+                        bias=cfg.bias, step_div=cfg.step_div, adagrad_init_acc=cfg.adagrad_init_acc,
+                        bookkeeping=cfg.bookkeeping, seed=cfg.seed)
+    pol = q.QDecisionPolicy(pc)
+    if params is not None or acc is not None:
+        pol.set_weights(params, acc)
+    return pol
+
+
+def states_of(cfg, prices, soe, i, budget, shares):
+    w = np.stack([prices[s, i:i + cfg.wn] for s in soe])
+    return np.concatenate([w, np.asarray(budget, np.float64).astype(np.float32)[:, None],
+                           np.asarray(shares, np.float32)[:, None]], axis=1)
+
+
+# ------------------------------------------------------------------------------------------------
+# construction, weights, errors
+# ------------------------------------------------------------------------------------------------
+def test_default_init_matches_oracle_generator():
+    """qp_create draws W ~ N(0,1) from the seed exactly as the oracle's host generator does."""
+    cfg = O.Config(seed=1234)
+    with make_policy(cfg) as pol:
+        p, a = pol.get_weights()
+    np.testing.assert_array_equal(p, O.gen_normal(1234, 0, cfg.P))
+    assert (a == np.float32(1e-8)).all()
+    assert abs(float(p.std()) - 1.0) < 0.02
+
+
+def test_size_guards_raise_illegal_argument():
+    """QDecisionPolicyActorSpec.scala:47-65: a 47-float state is rejected for both messages."""
+    q = q_mod()
+    good = np.array(list(range(55, 256)) + [1000, 0], np.float32)
+    wrong = np.array(list(range(55, 100)) + [1000, 0], np.float32)
+    with make_policy(O.Config()) as pol:
+        with pytest.raises(q.IllegalArgumentException, match="size"):
+            pol.receive(q.SelectionAction(wrong, 0))
+        with pytest.raises(q.IllegalArgumentException, match="size"):
+            pol.receive(q.UpdateQ(good, 10, wrong))
+        with pytest.raises(q.IllegalArgumentException):
+            pol.receive(q.UpdateQ(wrong, 10, good))
+        # TrainerChildActorSpec.scala:28-37: 45 prices
+        with pytest.raises(q.IllegalArgumentException, match="Stock price count"):
+            pol.env_create(np.arange(55, 100, dtype=np.float32)[None, :], [0], 2000.0, 0)
+        with pytest.raises(q.QPolicyError):
+            pol.env_step(1)        # no episodes yet
+        # still usable afterwards
+        assert isinstance(pol.receive(q.SelectionAction(good, 0)), q.Action)
+
+
+def test_unsupported_shape_is_reported():
+    q = q_mod()
+    with pytest.raises(q.QPolicyError, match="shape"):
+        make_policy(O.Config(wn=513, hidden=2048))
+
+
+# ------------------------------------------------------------------------------------------------
+# message level: SelectionAction / UpdateQ
+# ------------------------------------------------------------------------------------------------
+def test_policy_spec_fixture(golden_dir):
+    """The reference's own spec inputs (QDecisionPolicyActorSpec.scala:16-19, :35) through the
+    message API, against the committed golden outputs of the oracle."""
+    q = q_mod()
+    g = np.load(os.path.join(golden_dir, "policy_spec.npz"))
+    cfg = O.Config()
+    w = grid_weights(int(g["weight_seed"]), cfg.P)
+    s, s2 = g["state"], g["next_state"]
+    with make_policy(cfg, params=w) as pol:
+        a0 = pol.receive(q.SelectionAction(s, 0))                     # "return action in initial stage"
+        assert isinstance(a0, q.Action) and int(a0) == int(g["action_step0"][0])
+        act, qv = pol.select_action(s[None, :], 500.0, return_q=True)
+        _tol.assert_q_close(cfg, w, s[None, :], qv, g["q_s"])
+        assert int(act[0]) == int(g["action_step500"][0])
+        assert isinstance(pol.receive(q.UpdateQ(s, 10, s2)), q.Updated)  # "Updated"
+        grad = pol.last_grad()
+        assert (grad != 0).sum() == int(g["grad_nonzero"])
+        np.testing.assert_allclose(grad[g["sample_idx"]], g["grad_sample"], rtol=1e-4, atol=1e-4 * np.abs(g["grad_sample"]).max())
+        p, a = pol.get_weights()
+        assert np.abs(p[g["sample_idx"]] - g["params_after_sample"]).max() <= _tol.W_ATOL
+        act2, q2 = pol.select_action(s[None, :], 500.0, return_q=True)   # "return an action after updateQ"
+        _tol.assert_q_close(cfg, p, s[None, :], q2, g["q_after"])
+        assert int(act2[0]) == int(g["action_after"][0])
+
+
+@pytest.mark.parametrize("B", [1, 7, 32, 33, 257])
+@pytest.mark.parametrize("shape", [(201, 200), (8, 16), (30, 44)])
+def test_select_action_batches(B, shape):
+    cfg = O.Config(wn=shape[0], hidden=shape[1], seed=11)
+    rng = np.random.default_rng(B * 1000 + shape[0])
+    w = (O.gen_normal(5, 0, cfg.P) * 0.1).astype(np.float32)
+    x = rng.uniform(50, 150, (B, cfg.D)).astype(np.float32)
+    steps = rng.integers(0, 1200, B).astype(np.float32)
+    steps[0] = 0.0
+    ids = rng.integers(0, 2 ** 40, B).astype(np.int64)
+    o = O.Oracle(cfg, params=w)
+    a_ref, q_ref, e_ref = o.select_action(x, steps, ids)
+    with make_policy(cfg, params=w) as pol:
+        a, qv = pol.select_action(x, steps, ids, return_q=True)
+        a_noid = pol.select_action(x, steps)
+    _tol.assert_q_close(cfg, w, x, qv, q_ref)
+    _tol.assert_actions_match(cfg, w, x, a, a_ref, q_ref)
+    # explored rows depend on Philox alone: bit-exact
+    np.testing.assert_array_equal(a[e_ref == 1], a_ref[e_ref == 1])
+    a_ref2, _, _ = o.select_action(x, steps)
+    _tol.assert_actions_match(cfg, w, x, a_noid, a_ref2, q_ref)
+
+
+def test_argmax_ties_go_to_buy():
+    """Dead output ReLUs make all Q-values 0; Tensor.argmax returns the first index -> Buy."""
+    cfg = O.Config(wn=8, hidden=16)
+    w = -np.abs(O.gen_normal(3, 0, cfg.P)) - 1.0          # all-negative weights: q == 0 everywhere
+    x = np.random.default_rng(0).uniform(1, 2, (40, cfg.D)).astype(np.float32)
+    with make_policy(cfg, params=w) as pol:
+        a, qv = pol.select_action(x, 5000.0, np.arange(40), return_q=True)   # thr = 0.9
+    _, _, e_ref = O.Oracle(cfg, params=w).select_action(x, 5000.0, np.arange(40))
+    assert (qv == 0).all()
+    assert (a[e_ref == 0] == 0).all() and (e_ref == 0).sum() > 20
+
+
+@pytest.mark.parametrize("B", [1, 5, 32, 100])
+@pytest.mark.parametrize("shape", [(201, 200), (8, 16)])
+def test_update_q_batches(B, shape):
+    cfg = O.Config(wn=shape[0], hidden=shape[1])
+    rng = np.random.default_rng(B + shape[1])
+    w = (O.gen_normal(9, 0, cfg.P) * (0.05 if shape[0] > 100 else 0.3)).astype(np.float32)
+    acc = rng.uniform(0.5, 2.0, cfg.P).astype(np.float32)
+    s = rng.uniform(50, 150, (B, cfg.D)).astype(np.float32)
+    s2 = s + rng.uniform(-1, 1, (B, cfg.D)).astype(np.float32)
+    r = rng.uniform(-5, 5, B).astype(np.float32)
+    o = O.Oracle(cfg, params=w, acc=acc)
+    g_ref, info = o.td_grad(s, r, s2)
+    assert np.abs(g_ref).max() > 0, "fixture must produce a live gradient"
+    o.update_q(s, r, s2)
+    with make_policy(cfg, params=w, acc=acc) as pol:
+        pol.update_q(s, r, s2)
+        g = pol.last_grad()
+        p, a = pol.get_weights()
+    _tol.assert_grad_close(g, g_ref)
+    np.testing.assert_allclose(a, o.acc, rtol=1e-4)
+    assert np.abs(p - o.params).max() <= _tol.W_ATOL
+
+
+# ------------------------------------------------------------------------------------------------
+# episode level
+# ------------------------------------------------------------------------------------------------
+def compare_step(cfg, w, x, tr, ref, what):
+    """One env-step of every episode: device trace row `tr` against oracle trace `ref`."""
+    _tol.assert_q_close(cfg, w, x, tr["q_s"], ref["q_s"], what + " q_s")
+    n_act = _tol.assert_actions_match(cfg, w, x, tr["action_sel"], ref["action_sel"], ref["q_s"], what + " action")
+    same = tr["action_sel"] == ref["action_sel"]
+    np.testing.assert_array_equal(tr["explored"], ref["explored"], err_msg=what + " explored")
+    for k in ("action_eff", "shares", "budget", "reward"):
+        np.testing.assert_array_equal(tr[k][same], ref[k][same], err_msg=f"{what} {k}")
+    return n_act
+
+
+@pytest.mark.parametrize("bookkeeping", [O.REFERENCE, O.RLPY])
+@pytest.mark.parametrize("n_envs,N0", [(1, 0), (5, 3), (32, 1), (33, 0), (200, 2)])
+def test_env_step_teacher_forced(bookkeeping, n_envs, N0):
+    """Each step starts from the oracle's weights and episode state; device and oracle take one
+    step; everything the step produces is compared."""
+    cfg = O.Config(bookkeeping=bookkeeping, seed=77)
+    n_series = max(1, n_envs // 2)
+    prices = O.gen_prices(cfg.seed, 0, n_series, 400)
+    soe = (np.arange(n_envs) % n_series).astype(np.int32)
+    w0 = (O.gen_normal(21, 0, cfg.P) * 0.05).astype(np.float32)
+    o = O.Oracle(cfg, params=w0)
+    o.env_create(prices, soe, 1000.0, N0, env_id_base=10 ** 10)
+    with make_policy(cfg) as pol:
+        pol.env_create(prices, soe, 1000.0, N0, env_id_base=10 ** 10)
+        for i in (0, 1, 57, 150, 198):
+            o.env["step"] = i
+            w, acc = o.params.copy(), o.acc.copy()
+            b, s, v = o.env["budget"].copy(), o.env["shares"].copy(), o.env["share_value"].copy()
+            pol.set_weights(w, acc)
+            pol.env_set_state(b, s, v, step=i)
+            x = states_of(cfg, prices, soe, i, b, s)
+            ref = o.env_step(1, trace=True, want_grad=True)[0]
+            tr = {k: a[0] for k, a in pol.env_step_trace(1).items()}
+            n_diff = compare_step(cfg, w, x, tr, ref, f"step {i}")
+            if n_diff == 0:
+                _tol.assert_grad_close(pol.last_grad(), ref["grad"], f"step {i} grad")
+                p, a = pol.get_weights()
+                assert np.abs(p - o.params).max() <= _tol.W_ATOL
+                bd, sd, vd = pol.env_state()
+                np.testing.assert_array_equal(bd, o.env["budget"])
+                np.testing.assert_array_equal(sd, o.env["shares"])
+                np.testing.assert_array_equal(vd, o.env["share_value"])
+
+
+@pytest.mark.parametrize("name", ["episode_rlpy", "episode_reference", "episode_tiny", "episode_late"])
+def test_golden_episodes_free_running(golden_dir, name):
+    """Committed golden traces (oracle-generated): the device runs the same episodes free-running;
+    integer book-keeping must match bit-for-bit up to the first tolerated action divergence."""
+    g = np.load(os.path.join(golden_dir, name + ".npz"))
+    cfg = O.Config(wn=int(g["window"]), hidden=int(g["hidden"]), lr=float(g["lr"]),
+                   bookkeeping=int(g["bookkeeping"]), seed=int(g["seed"]))
+    prices = O.gen_prices(cfg.seed, 0, int(g["n_series"]), int(g["T"]))
+    w = grid_weights(cfg.seed, cfg.P) * np.float32(g["weight_scale"])
+    n_steps, i0 = int(g["n_steps"]), int(g["start_step"])
+    with make_policy(cfg, params=w) as pol:
+        pol.env_create(prices, g["series_of_env"], float(g["B0"]), int(g["N0"]))
+        if i0:
+            pol.env_set_state(step=i0)
+        tr = pol.env_step_trace(n_steps)
+        ports = pol.portfolios()
+    diverged = tr["action_sel"] != g["action_sel"]
+    first_div = np.where(diverged.any(axis=1))[0]
+    upto = int(first_div[0]) if first_div.size else n_steps
+    assert upto >= min(n_steps, 10), f"free-running parity lost already at step {upto}"
+    for k in ("action_sel", "action_eff", "explored", "k_next", "shares", "budget", "reward"):
+        np.testing.assert_array_equal(tr[k][:upto], g[k][:upto], err_msg=k)
+    scale = np.maximum(1.0, np.abs(g["q_s"][:upto]).max())
+    assert np.abs(tr["q_s"][:upto] - g["q_s"][:upto]).max() <= 1e-3 * scale   # weights drift apart slowly when free-running
+    if upto == n_steps:
+        np.testing.assert_array_equal(ports, g["portfolios"])
+
+
+def test_trainer_child_spec_through_the_actor_mirror(golden_dir):
+    """TrainerChildActorSpec.scala:59-76 through TrainerChild.receive(Train): Trained, then 2000.0."""
+    q = q_mod()
+    with make_policy(O.Config()) as pol:
+        t = q.TrainerChild(pol, 2000, 0)
+        assert t.receive("GetPortfolio") == q.NotComputed()
+        data = q.StockDataResponse("my-share", {f"d{i:04d}": float(i) for i in range(55, 257)})
+        assert t.receive("Train", data) == q.Trained()
+        assert t.receive("GetPortfolio") == q.TrainedData(2000.0)
+        assert t.receive("Initialise") == q.Initialised()
+        assert t.receive("GetPortfolio") == q.NotComputed()
+
+
+def test_message_api_reproduces_the_fused_episode_path():
+    """Driving SelectionAction / UpdateQ from a host loop that restates TrainerChildActor.scala:87-102
+    gives the same trajectory as the fused env path (same kernels' arithmetic, same Philox counters)."""
+    cfg = O.Config(wn=16, hidden=20, bookkeeping=O.RLPY, lr=1e-3, seed=5)
+    prices = O.gen_prices(cfg.seed, 0, 3, 60)
+    soe = np.array([0, 1, 2, 1], np.int32)
+    w = (O.gen_normal(8, 0, cfg.P) * 0.2).astype(np.float32)
+    with make_policy(cfg, params=w) as fused, make_policy(cfg, params=w) as msg:
+        fused.env_create(prices, soe, 300.0, 1)
+        tr = fused.env_step_trace(30)
+        budget = np.full(4, 300.0)
+        shares = np.ones(4, np.int32)
+        sv = np.zeros(4)
+        for i in range(30):
+            s = states_of(cfg, prices, soe, i, budget, shares)
+            cur = budget + shares * sv
+            a = msg.select_action(s, float(i), np.arange(4))
+            np.testing.assert_array_equal(a, tr["action_sel"][i])
+            p_new = prices[soe, i + cfg.wn].astype(np.float64)
+            nb, ns = budget.copy(), shares.copy()
+            buy = (a == 0) & (budget >= p_new)
+            sell = (a == 1) & (shares > 0)
+            nb[buy] -= p_new[buy]; ns[buy] += 1
+            nb[sell] += p_new[sell]; ns[sell] -= 1
+            reward = (nb + ns * p_new - cur).astype(np.float32)
+            s2 = states_of(cfg, prices, soe, i + 1, nb, ns)
+            msg.update_q(s, reward, s2)
+            budget, shares, sv = nb, ns, p_new
+            np.testing.assert_array_equal(shares, tr["shares"][i])
+            np.testing.assert_array_equal(budget, tr["budget"][i])
+        pf, _ = fused.get_weights()
+        pm, _ = msg.get_weights()
+        assert np.abs(pf - pm).max() <= 1e-6
+
+
+# ------------------------------------------------------------------------------------------------
+# full-size, size-independent properties (BASELINE.json configs[1]: 4096 episodes)
+# ------------------------------------------------------------------------------------------------
+def test_full_size_determinism_and_conservation():
+    cfg = O.Config(bookkeeping=O.REFERENCE)
+    n = 4096
+    prices = O.gen_prices(42, 0, n, 1000)
+    soe = np.arange(n, dtype=np.int32)
+    outs = []
+    for _ in range(2):
+        with make_policy(cfg) as pol:
+            pol.env_create(prices, soe, 1000.0, 0)
+            assert pol.steps_total == 799
+            pol.env_step(799)
+            assert pol.steps_done == 799
+            with pytest.raises(q_mod().IllegalArgumentException):
+                pol.env_step(1)                      # episode finished
+            outs.append((pol.portfolios(), pol.get_weights()[0], pol.env_state()[1], pol.portfolio_stats()))
+    # bit-reproducible: no atomics, fixed reduction order
+    np.testing.assert_array_equal(outs[0][0], outs[1][0])
+    np.testing.assert_array_equal(outs[0][1], outs[1][1])
+    # Q1: REFERENCE book-keeping from (1000, 0) never changes the portfolio value
+    assert (outs[0][0] == 1000.0).all()
+    assert set(np.unique(outs[0][2])) <= {0, 1}
+    assert outs[0][3] == (1000.0, 0.0)
+    assert np.isfinite(outs[0][1]).all()
+
+
+def test_full_size_rlpy_bookkeeping_invariants():
+    cfg = O.Config(bookkeeping=O.RLPY, lr=1e-4)
+    n = 4096
+    prices = O.gen_prices(42, 0, n, 1000)
+    w = (O.gen_normal(42, 0, cfg.P) * 0.05).astype(np.float32)
+    with make_policy(cfg, params=w) as pol:
+        pol.env_create(prices, np.arange(n, dtype=np.int32), 1000.0, 0)
+        tr = pol.env_step_trace(60)
+        b, s, v = pol.env_state()
+        ports = pol.portfolios()
+        mean, std = pol.portfolio_stats()
+    # share counts follow the effective actions exactly; budgets never go negative; quarter ticks
+    delta = np.where(tr["action_eff"] == 0, 1, np.where(tr["action_eff"] == 1, -1, 0)).sum(axis=0)
+    np.testing.assert_array_equal(s, delta)
+    assert (s >= 0).all() and (b >= 0).all()
+    assert np.array_equal(b * 4, np.round(b * 4))
+    np.testing.assert_array_equal(v, prices[:, 60 + cfg.wn - 1].astype(np.float64))
+    np.testing.assert_array_equal(ports, b + s * v)
+    # the sum of rewards telescopes to the change in portfolio value (fp64 exact on quarter ticks)
+    np.testing.assert_array_equal(tr["reward"].astype(np.float64).sum(axis=0), ports - 1000.0)
+    assert abs(mean - ports.mean()) < 1e-9 and abs(std - ports.std()) < 1e-9
+    # oracle spot-check of the first steps of a slice of episodes is covered by the teacher-forced tests
+
+
+def test_first_step_of_full_batch_against_oracle():
+    """4096 episodes, one step, full comparison with the oracle (seconds on one core)."""
+    cfg = O.Config(bookkeeping=O.RLPY)
+    n = 4096
+    prices = O.gen_prices(42, 0, n, 1000)
+    soe = np.arange(n, dtype=np.int32)
+    w = (O.gen_normal(42, 0, cfg.P) * 0.05).astype(np.float32)
+    i = 640
+    o = O.Oracle(cfg, params=w)
+    o.env_create(prices, soe, 1000.0, 2)
+    o.env["step"] = i
+    x = states_of(cfg, prices, soe, i, o.env["budget"], o.env["shares"])
+    ref = o.env_step(1, trace=True, want_grad=True)[0]
+    with make_policy(cfg, params=w) as pol:
+        pol.env_create(prices, soe, 1000.0, 2)
+        pol.env_set_state(step=i)
+        tr = {k: a[0] for k, a in pol.env_step_trace(1).items()}
+        g = pol.last_grad()
+        p, _ = pol.get_weights()
+    n_diff = compare_step(cfg, w, x, tr, ref, "full batch")
+    assert (ref["explored"] == 0).sum() > 2000          # exploit path exercised (thr = 0.64)
+    if n_diff == 0:
+        _tol.assert_grad_close(g, ref["grad"])
+        assert np.abs(p - o.params).max() <= _tol.W_ATOL
