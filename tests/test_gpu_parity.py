@@ -130,14 +130,15 @@ def test_select_action_batches(B, shape):
 
 
 def test_argmax_ties_go_to_buy():
-    """Dead output ReLUs make all Q-values 0; Tensor.argmax returns the first index -> Buy."""
+    """Dead hidden units make the three Q-values equal (relu(0 + 0.1)); Tensor.argmax returns the
+    first maximal index -> Buy."""
     cfg = O.Config(wn=8, hidden=16)
-    w = -np.abs(O.gen_normal(3, 0, cfg.P)) - 1.0          # all-negative weights: q == 0 everywhere
+    w = -np.abs(O.gen_normal(3, 0, cfg.P)) - 1.0          # all-negative weights: h == 0, q == bias everywhere
     x = np.random.default_rng(0).uniform(1, 2, (40, cfg.D)).astype(np.float32)
     with make_policy(cfg, params=w) as pol:
         a, qv = pol.select_action(x, 5000.0, np.arange(40), return_q=True)   # thr = 0.9
     _, _, e_ref = O.Oracle(cfg, params=w).select_action(x, 5000.0, np.arange(40))
-    assert (qv == 0).all()
+    assert (qv == np.float32(0.1)).all()
     assert (a[e_ref == 0] == 0).all() and (e_ref == 0).sum() > 20
 
 
