@@ -272,11 +272,13 @@ int qp_create(const qp_config* cfg, qp_handle** out) {
         cudaError_t _e = (expr);                                                                  \
         if (_e != cudaSuccess) return bail(fail(QP_ECUDA, std::string(#expr) + ": " + cudaGetErrorString(_e))); \
     } while (0)
-    QP_BAIL_CUDA(cudaFuncSetAttribute(step_kernel<kEnvStep>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step[kEnvStep]));
-    QP_BAIL_CUDA(cudaFuncSetAttribute(step_kernel<kMsgSelect>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step[kMsgSelect]));
-    QP_BAIL_CUDA(cudaFuncSetAttribute(step_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_step[kMsgUpdate]));
-    QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_kernel<kEnvStep>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_dw1));
-    QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)h->smem_dw1));
+    // The attribute is per function and per device, not per handle: always raise it to the device
+    // maximum so that handles of different shapes can coexist.
+    QP_BAIL_CUDA(cudaFuncSetAttribute(step_kernel<kEnvStep>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(step_kernel<kMsgSelect>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(step_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_kernel<kEnvStep>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     QP_BAIL_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     for (auto& e : h->ev) QP_BAIL_CUDA(cudaEventCreate(&e));
 #undef QP_BAIL_CUDA
