@@ -161,7 +161,8 @@ def test_update_q_batches(B, shape):
         g = pol.last_grad()
         p, a = pol.get_weights()
     _tol.assert_grad_close(g, g_ref)
-    np.testing.assert_allclose(a, o.acc, rtol=1e-4)
+    # acc = acc0 + g^2: twice the relative error of g, which inherits the Q tolerance through dq = 2(q - target)
+    np.testing.assert_allclose(a, o.acc, rtol=1e-3)
     assert np.abs(p - o.params).max() <= _tol.W_ATOL
 
 
