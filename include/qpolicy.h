@@ -153,6 +153,32 @@ int qp_train(qp_handle* h, const float* prices, int64_t series_len, int64_t n_se
              const int32_t* series_of_env, int64_t n_envs, int64_t env_id_base, double budget0,
              int32_t shares0, double* portfolios_out);
 
+/* ---- allocation-free variant.  No counterpart in the reference.
+ *
+ * qp_td_grad_noalloc computes what qp_update_q computes up to, but not including, the AdaGrad
+ * step: the TD gradient of B (state, reward, nextState) rows, summed over the rows, written to
+ * d_grad_out [P floats].  It exists for callers that must not touch the CUDA allocator while they
+ * are in here: an actor on a dispatcher shared with other GPU work (cudaMalloc and cudaFree
+ * serialise the whole device, and the handle-based calls above grow their scratch on demand), or a
+ * process that has given all device memory to another runtime's pool and can only pass pointers
+ * taken from that pool.  Every pointer argument is a DEVICE pointer owned by the caller; d_params
+ * has the usual layout [W1 | W2].  The call makes no cudaMalloc / cudaFree and uses no library that
+ * allocates.
+ *
+ * Its working memory is a 4 MiB array built into the library (each GPU that loads libqpolicy.so
+ * holds those 4 MiB until the process exits).  Sizes that need more are refused with QP_EINVAL and
+ * a message that states both numbers: at the reference shape (window 201, hidden 200) batches
+ * of up to 1792 rows fit.  All calls on a GPU share that one array, so two calls whose kernels overlap
+ * on the same GPU (different streams or threads) race: serialise them.  Contents left by one call
+ * are never read by the next — every word consumed is rewritten first — so nothing needs clearing.
+ * The first call on each device also does that device's one-time set-up (it resolves the array's
+ * device address and raises the kernels' shared-memory limit); make that first call before any
+ * stream capture begins.  `stream` is a cudaStream_t (NULL = default stream); the call returns
+ * after the work on it has finished. */
+int qp_td_grad_noalloc(int32_t device, const qp_config* cfg, const float* d_params,
+                       const float* d_states, const float* d_rewards, const float* d_next_states,
+                       int64_t B, float* d_grad_out, void* stream);
+
 /* ---- measurement aids (no reference counterpart) */
 enum { QP_KERNEL_STEP = 0, QP_KERNEL_DW1 = 1, QP_KERNEL_APPLY = 2, QP_N_KERNELS = 3 };
 /* The CUDA stream (cudaStream_t) every kernel of this handle is launched on. */

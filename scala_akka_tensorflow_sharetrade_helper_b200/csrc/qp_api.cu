@@ -9,6 +9,7 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -633,3 +634,134 @@ int qp_train(qp_handle* h, const float* prices, int64_t series_len, int64_t n_se
 }
 
 }  // extern "C"
+
+// =================================================================================================
+// Allocation-free TD gradient.
+//
+// Who this is for: code that must not reach the CUDA allocator when it calls into this library.
+// Two kinds of caller of this policy are in that position.  (1) An actor running on a shared
+// dispatcher next to other GPU work: cudaMalloc/cudaFree serialise the whole device, so a scratch
+// buffer that grows inside an UpdateQ stalls every other actor's stream; the handle-based entry
+// points above may do exactly that the first time a batch is larger than any seen before.
+// (2) A host process whose device memory has been handed over in full to another framework's pool
+// (a JVM-side tensor runtime, an inference server): a cudaMalloc from here simply fails, while the
+// caller can still pass us pointers that it carved out of that pool.
+//
+// The scratch this path needs (the hidden-layer backward signal and the per-CTA gradient partials)
+// therefore lives in one file-scope device array of fixed size that is part of the library image:
+// each GPU that loads libqpolicy.so carries it from load until the process exits.
+// =================================================================================================
+namespace {
+
+constexpr size_t kStaticScratchFloats = size_t(1) << 20;   // 4 MiB per GPU, stated in qpolicy.h
+constexpr int kStaticMaxSplit = 16;                        // dW1 partials kept by this variant
+constexpr int kStaticMaxDevices = 64;
+
+static __device__ __align__(256) float g_static_scratch[kStaticScratchFloats];
+
+struct StaticDevice {
+    bool ready = false;
+    float* scratch = nullptr;   // DEVICE address of g_static_scratch on this GPU
+    int num_sms = 0;
+    int max_smem = 0;
+};
+StaticDevice g_static_dev[kStaticMaxDevices];
+std::mutex g_static_mutex;
+
+// Once per device, with that device current.  In host code the name g_static_scratch is only a
+// stand-in for the symbol — handing it to a kernel would fault (or, where the GPU can reach host
+// memory, quietly use the wrong bytes) — so the device address is looked up here and kept.
+int static_setup(int device, StaticDevice** out) {
+    std::lock_guard<std::mutex> lock(g_static_mutex);
+    StaticDevice& d = g_static_dev[device];
+    if (!d.ready) {
+        float* p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void**)&p, g_static_scratch);
+        if (e != cudaSuccess || p == nullptr)
+            return fail(QP_ECUDA, std::string("cudaGetSymbolAddress(g_static_scratch): ") + cudaGetErrorString(e));
+        QP_CUDA(cudaDeviceGetAttribute(&d.num_sms, cudaDevAttrMultiProcessorCount, device));
+        QP_CUDA(cudaDeviceGetAttribute(&d.max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+        QP_CUDA(cudaFuncSetAttribute(step_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, d.max_smem));
+        QP_CUDA(cudaFuncSetAttribute(dw1_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, d.max_smem));
+        d.scratch = p;
+        d.ready = true;
+    }
+    *out = &d;
+    return QP_OK;
+}
+
+}  // namespace
+
+extern "C" int qp_td_grad_noalloc(int32_t device, const qp_config* cfg, const float* d_params,
+                                  const float* d_states, const float* d_rewards,
+                                  const float* d_next_states, int64_t B, float* d_grad_out,
+                                  void* stream) {
+    if (!cfg || !d_params || !d_states || !d_rewards || !d_next_states || !d_grad_out)
+        return fail(QP_EINVAL, "null argument");
+    if (device < 0 || device >= kStaticMaxDevices) return fail(QP_EINVAL, "device ordinal out of range");
+    if (cfg->window < 1 || cfg->hidden < 4 || cfg->hidden % 4)
+        return fail(QP_EINVAL, "window >= 1 and hidden a multiple of 4 (>= 4) required");
+    if (B < 1) return fail(QP_EINVAL, "B < 1");
+    QP_CUDA(cudaSetDevice(device));
+    StaticDevice* dev = nullptr;
+    QP_TRY(static_setup(device, &dev));
+
+    Hyper hp{};
+    hp.wn = cfg->window; hp.D = cfg->window + 2; hp.H = cfg->hidden;
+    hp.Hs = (int)round_up(cfg->hidden, kColsPerWarp);
+    hp.epsilon = cfg->epsilon; hp.gamma = cfg->gamma; hp.lr = cfg->lr; hp.bias = cfg->bias;
+    hp.step_div = cfg->step_div; hp.bookkeeping = cfg->bookkeeping; hp.seed = cfg->seed;
+    const int64_t P1 = (int64_t)hp.D * hp.H, P = P1 + 3LL * hp.H;
+    const int step_warps = hp.Hs / kColsPerWarp;
+    const int n_rt = (hp.D + kDw1Rows - 1) / kDw1Rows, n_ct = (hp.H / 4 + 1) / 2;
+    const int dw1_threads = (int)round_up((int64_t)n_rt * n_ct, 32);
+    const size_t smem_step = step_smem_bytes(hp, kMsgUpdate, step_warps);
+    const size_t smem_dw1 = (size_t)kDw1ChunkEnvs * ((size_t)n_rt * kDw1Rows + (size_t)n_ct * kDw1Cols) * sizeof(float);
+    if (step_warps > kMaxStepWarps || dw1_threads > kDw1MaxThreads || smem_step > (size_t)dev->max_smem ||
+        smem_dw1 > (size_t)dev->max_smem)
+        return fail(QP_EUNSUPPORTED, "shape outside the fused fp32 path");
+
+    // carve the fixed array: [dz1 | dW1 partials | dW2 partials], each piece 256-byte aligned
+    const int64_t Bpad = round_up(B, kTileEnvs);
+    const int g1 = (int)std::min<int64_t>(Bpad / kTileEnvs, dev->num_sms);
+    const int g2 = (int)std::max<int64_t>(1, std::min<int64_t>((B + 15) / 16, kStaticMaxSplit));
+    const size_t n_dz1 = (size_t)round_up(Bpad * hp.H, 64);
+    const size_t n_p1 = (size_t)round_up((int64_t)g2 * P1, 64);
+    const size_t n_p2 = (size_t)round_up((int64_t)g1 * 3 * hp.H, 64);
+    if (n_dz1 + n_p1 + n_p2 > kStaticScratchFloats)
+        return fail(QP_EINVAL, "qp_td_grad_noalloc: B = " + std::to_string(B) + " rows at window " +
+                                   std::to_string(hp.wn) + ", hidden " + std::to_string(hp.H) + " need " +
+                                   std::to_string((n_dz1 + n_p1 + n_p2) * sizeof(float)) +
+                                   " bytes of scratch; the built-in array holds " +
+                                   std::to_string(kStaticScratchFloats * sizeof(float)) +
+                                   " (use a smaller batch, or qp_update_q which allocates)");
+    float* dz1 = dev->scratch;
+    float* part1 = dz1 + n_dz1;
+    float* part2 = part1 + n_p1;
+    cudaStream_t st = (cudaStream_t)stream;
+
+    // Nothing in the array has to start at zero: every word the reduction reads is written earlier
+    // in this same call (K1 writes all of dz1 and its dW2 partial, K2 writes whole D x H partials),
+    // so whatever the previous call left behind is never observed.
+    StepArgs s{};
+    s.hp = hp; s.params = d_params;
+    s.states = d_states; s.next_states = d_next_states; s.rewards = d_rewards;
+    s.B = B; s.Bpad = Bpad; s.dz1 = dz1; s.dw2_part = part2;
+    step_kernel<kMsgUpdate><<<g1, step_warps * 32, smem_step, st>>>(s);
+    QP_CUDA(cudaGetLastError());
+
+    Dw1Args d{};
+    d.hp = hp; d.states = d_states; d.Bpad = Bpad; d.dz1 = dz1; d.B = B; d.part = part1;
+    d.n_rt = n_rt; d.n_ct = n_ct;
+    dw1_kernel<kMsgUpdate><<<g2, dw1_threads, smem_dw1, st>>>(d);
+    QP_CUDA(cudaGetLastError());
+
+    ApplyArgs a{};
+    a.hp = hp; a.grad = d_grad_out;
+    a.part1 = part1; a.n1 = g2; a.part2 = part2; a.n2 = g1;
+    a.P = P; a.P1 = P1; a.do_reduce = 1; a.do_adagrad = 0;
+    apply_kernel<<<(int)((P * kApplyLanes + 255) / 256), 256, 0, st>>>(a);
+    QP_CUDA(cudaGetLastError());
+    QP_CUDA(cudaStreamSynchronize(st));
+    return QP_OK;
+}
