@@ -153,6 +153,19 @@ int qp_train(qp_handle* h, const float* prices, int64_t series_len, int64_t n_se
              const int32_t* series_of_env, int64_t n_envs, int64_t env_id_base, double budget0,
              int32_t shares0, double* portfolios_out);
 
+/* ---- several GPUs: episodes are sharded over ranks (one process per GPU, env_id_base = first
+ * global episode of the shard), weights are replicated, and each env-step exchanges ONE thing: a SUM
+ * all-reduce of the P-float gradient (NCCL over NVLink), after which every rank applies the same
+ * AdaGrad step.  This is the synchronous form of the reference's children sharing one policy actor
+ * (TrainerRouterActor.scala:44, :60-66); the reference itself has no collective.
+ * qp_dist_unique_id: rank 0 obtains a 128-byte rendezvous id and hands it to the other ranks by
+ * whatever channel the host has (torch.distributed, Akka remoting, a file).  qp_dist_init: every
+ * rank joins; subsequent qp_env_step* calls all-reduce.  NCCL is resolved with dlopen at first use. */
+#define QP_DIST_ID_BYTES 128
+int qp_dist_unique_id(void* out, size_t out_bytes);
+int qp_dist_init(qp_handle* h, const void* unique_id, int32_t rank, int32_t world);
+int qp_dist_nccl_version(int32_t* version);
+
 /* ---- allocation-free variant.  No counterpart in the reference.
  *
  * qp_td_grad_noalloc computes what qp_update_q computes up to, but not including, the AdaGrad

@@ -259,6 +259,12 @@ class Oracle:
                 traces.append(rec)
         return traces
 
+    def adagrad(self, g):
+        """Apply one ResourceApplyAdagrad step with an externally summed gradient (multi-rank tests)."""
+        g = np.ascontiguousarray(g, self.dtype)
+        cc = self.cfg.c()
+        self.lib.qpo_adagrad(C.byref(cc), _p(self.params), _p(self.acc), _p(g), C.c_int64(self.cfg.P))
+
     def portfolios(self):
         ev = self.env
         return ev["budget"] + ev["shares"] * ev["share_value"]  # TrainerChildActor.scala:68

@@ -7,5 +7,6 @@ include/qpolicy.h), policy / trainer (host-side mirrors of the reference's actor
 from ._build import build, LIB_PATH  # noqa: F401
 from .policy import (Action, Buy, Hold, IllegalArgumentException, PolicyConfig, QDecisionPolicy,  # noqa: F401
                      QPolicyError, SelectionAction, Sell, UpdateQ, Updated)
+from .sharding import shard  # noqa: F401
 from .trainer import (Initialised, NotComputed, StockDataResponse, Trained, TrainedData,  # noqa: F401
                       TrainerChild, TrainerRouter)

@@ -53,6 +53,9 @@ SIGNATURES = {
     "qp_env_set_state": (C.c_int, [_H, _P, _P, _P, C.c_int64]),
     "qp_env_portfolio_stats": (C.c_int, [_H, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "qp_train": (C.c_int, [_H, _P, C.c_int64, C.c_int64, _P, C.c_int64, C.c_int64, C.c_double, C.c_int32, _P]),
+    "qp_dist_unique_id": (C.c_int, [_P, C.c_size_t]),
+    "qp_dist_init": (C.c_int, [_H, _P, C.c_int32, C.c_int32]),
+    "qp_dist_nccl_version": (C.c_int, [C.POINTER(C.c_int32)]),
     "qp_td_grad_noalloc": (C.c_int, [C.c_int32, C.POINTER(QpConfig), _P, _P, _P, _P, C.c_int64, _P, C.c_void_p]),
     "qp_stream": (C.c_void_p, [_H]),
     "qp_env_step_timed": (C.c_int, [_H, C.c_int32, _P]),

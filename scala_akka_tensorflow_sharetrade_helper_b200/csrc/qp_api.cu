@@ -5,6 +5,8 @@
 #include "qp_kernels.cuh"
 #include "../../include/qpolicy.h"
 
+#include <dlfcn.h>
+
 #include <algorithm>
 #include <cmath>
 #include <cstdio>
@@ -56,6 +58,49 @@ struct DevBuf {
 
 int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
 
+// ---- NCCL, resolved at run time (dlopen) so that the library has no link-time dependency on it
+// and shares the copy a host process may already have loaded (e.g. the one bundled with torch).
+typedef struct ncclComm* ncclComm_t;
+typedef struct { char internal[128]; } ncclUniqueId;
+typedef int ncclResult_t;
+constexpr int kNcclFloat32 = 7, kNcclSum = 0;   // ncclDataType_t / ncclRedOp_t values of nccl.h
+
+struct NcclApi {
+    void* lib = nullptr;
+    ncclResult_t (*GetUniqueId)(ncclUniqueId*) = nullptr;
+    ncclResult_t (*CommInitRank)(ncclComm_t*, int, ncclUniqueId, int) = nullptr;
+    ncclResult_t (*AllReduce)(const void*, void*, size_t, int, int, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    const char* (*GetErrorString)(ncclResult_t) = nullptr;
+    ncclResult_t (*GetVersion)(int*) = nullptr;
+};
+NcclApi g_nccl;
+
+int nccl_load() {
+    if (g_nccl.lib) return QP_OK;
+    void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) lib = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+    if (!lib) return fail(QP_ENCCL, std::string("cannot load libnccl.so.2: ") + dlerror());
+    NcclApi a;
+    a.lib = lib;
+    a.GetUniqueId = (decltype(a.GetUniqueId))dlsym(lib, "ncclGetUniqueId");
+    a.CommInitRank = (decltype(a.CommInitRank))dlsym(lib, "ncclCommInitRank");
+    a.AllReduce = (decltype(a.AllReduce))dlsym(lib, "ncclAllReduce");
+    a.CommDestroy = (decltype(a.CommDestroy))dlsym(lib, "ncclCommDestroy");
+    a.GetErrorString = (decltype(a.GetErrorString))dlsym(lib, "ncclGetErrorString");
+    a.GetVersion = (decltype(a.GetVersion))dlsym(lib, "ncclGetVersion");
+    if (!a.GetUniqueId || !a.CommInitRank || !a.AllReduce || !a.CommDestroy || !a.GetErrorString)
+        return fail(QP_ENCCL, "libnccl.so.2 lacks a required symbol");
+    g_nccl = a;
+    return QP_OK;
+}
+
+#define QP_NCCL(expr)                                                                             \
+    do {                                                                                          \
+        ncclResult_t _r = (expr);                                                                 \
+        if (_r != 0) return fail(QP_ENCCL, std::string(#expr) + ": " + g_nccl.GetErrorString(_r)); \
+    } while (0)
+
 }  // namespace
 
 struct qp_handle {
@@ -86,6 +131,9 @@ struct qp_handle {
     int64_t steps_done = 0;
 
     int64_t launches = 0;
+    // data parallelism over GPUs: one SUM all-reduce of the gradient per env-step
+    ncclComm_t comm = nullptr;
+    int rank = 0, world = 1;
     // launch geometry
     int step_warps = 0, n_rt = 0, n_ct = 0, dw1_threads = 0;
     size_t smem_step[3] = {0, 0, 0}, smem_dw1 = 0;
@@ -192,7 +240,15 @@ int enqueue_env_step(qp_handle* h, const TraceDev* trace, int32_t trace_step0, b
     QP_TRY(launch_dw1<kEnvStep>(h, d, g2));
     if (timed) QP_CUDA(cudaEventRecord(h->ev[2], h->stream));
 
-    QP_TRY(launch_apply(h, g2, g1, 1, 1, 1));
+    if (h->world > 1) {
+        // sum the partials, all-reduce the P-float gradient over the ranks, then every rank applies
+        // the identical sum: replicas stay bit-identical without any weight broadcast
+        QP_TRY(launch_apply(h, g2, g1, 1, 0, 0));
+        QP_NCCL(g_nccl.AllReduce(h->grad.p, h->grad.p, (size_t)h->P, kNcclFloat32, kNcclSum, h->comm, h->stream));
+        QP_TRY(launch_apply(h, 0, 0, 0, 1, 1));
+    } else {
+        QP_TRY(launch_apply(h, g2, g1, 1, 1, 1));
+    }
     if (timed) QP_CUDA(cudaEventRecord(h->ev[3], h->stream));
     return QP_OK;
 }
@@ -305,6 +361,7 @@ int qp_destroy(qp_handle* h) {
     if (!h) return QP_OK;
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
+    if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
     h->params.release(); h->acc.release(); h->grad.release();
     h->dz1.release(); h->xextra.release(); h->part1.release(); h->part2.release();
     h->m_states.release(); h->m_next.release(); h->m_rewards.release(); h->m_steps.release();
@@ -599,6 +656,38 @@ int qp_env_portfolio_stats(qp_handle* h, double* mean, double* stddev) {
     QP_TRY(pass(m, 2, &var));
     *mean = m;
     *stddev = std::sqrt(var / (double)h->n_envs);  // population variance (:150-151)
+    return QP_OK;
+}
+
+int qp_dist_unique_id(void* out, size_t out_bytes) {
+    if (!out || out_bytes < QP_DIST_ID_BYTES) return fail(QP_EINVAL, "need a 128-byte buffer");
+    QP_TRY(nccl_load());
+    ncclUniqueId id;
+    QP_NCCL(g_nccl.GetUniqueId(&id));
+    std::memcpy(out, id.internal, QP_DIST_ID_BYTES);
+    return QP_OK;
+}
+
+int qp_dist_init(qp_handle* h, const void* unique_id, int32_t rank, int32_t world) {
+    if (!h || !unique_id) return fail(QP_EINVAL, "null argument");
+    if (world < 1 || rank < 0 || rank >= world) return fail(QP_EINVAL, "rank/world out of range");
+    if (h->comm) return fail(QP_ESTATE, "qp_dist_init called twice");
+    if (world == 1) { h->rank = 0; h->world = 1; return QP_OK; }
+    QP_TRY(nccl_load());
+    QP_TRY(use_device(h));
+    ncclUniqueId id;
+    std::memcpy(id.internal, unique_id, QP_DIST_ID_BYTES);
+    QP_NCCL(g_nccl.CommInitRank(&h->comm, world, id, rank));
+    h->rank = rank; h->world = world;
+    return QP_OK;
+}
+
+int qp_dist_nccl_version(int32_t* version) {
+    if (!version) return fail(QP_EINVAL, "null argument");
+    QP_TRY(nccl_load());
+    int v = 0;
+    if (g_nccl.GetVersion) QP_NCCL(g_nccl.GetVersion(&v));
+    *version = v;
     return QP_OK;
 }
 

@@ -269,6 +269,20 @@ class QDecisionPolicy:
         self.n_envs = int(soe.size)
         return out
 
+    def dist_init(self, dist, rank: int, world: int):
+        """Join the gradient all-reduce group.  `dist` is an initialised torch.distributed (any backend):
+        it only carries the 128-byte NCCL rendezvous id from rank 0 to the others."""
+        import torch
+        buf = (C.c_ubyte * 128)()
+        if rank == 0:
+            check(self._lib.qp_dist_unique_id(buf, 128))
+        ids = [bytes(buf)]
+        if world > 1:
+            dist.broadcast_object_list(ids, src=0)
+        uid = (C.c_ubyte * 128).from_buffer_copy(ids[0])
+        check(self._lib.qp_dist_init(self._h, uid, int(rank), int(world)))
+        del torch
+
     def measure_fp32_peak(self) -> float:
         t = C.c_double()
         check(self._lib.qp_measure_fp32_peak(self._h, C.byref(t)))

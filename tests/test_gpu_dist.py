@@ -1,0 +1,83 @@
+"""Two-GPU test of the sharded path through the C ABI: qp_dist_init + the per-step NCCL gradient
+all-reduce.  Needs >= 2 GPUs (skipped on the 1-GPU box; run with `gpurun --gpus 2`)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+
+from oracle import oracle as O
+from tests import _tol
+
+pytestmark = pytest.mark.gpu
+
+N_LOCAL, N_STEPS, T = 96, 5, 260
+
+
+def _n_gpus():
+    try:
+        import torch
+        return torch.cuda.device_count()
+    except Exception:
+        return 0
+
+
+def _worker(rank, world, port, out_dir):
+    import torch
+    import torch.distributed as dist
+    import scala_akka_tensorflow_sharetrade_helper_b200 as q
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    torch.cuda.set_device(rank)
+    dist.init_process_group("gloo", rank=rank, world_size=world)   # host plumbing only: carries the NCCL id
+    cfg = O.Config(bookkeeping=O.RLPY)
+    first, count = q.shard(N_LOCAL * world, rank, world)
+    prices = O.gen_prices(cfg.seed, first, count, T)
+    w = (O.gen_normal(cfg.seed, 0, cfg.P) * 0.05).astype(np.float32)
+    with q.QDecisionPolicy(q.PolicyConfig(bookkeeping=1, device=rank)) as pol:
+        pol.set_weights(w)
+        pol.dist_init(dist, rank, world)
+        pol.env_create(prices, np.arange(count), 1000.0, 1, env_id_base=first)
+        tr = pol.env_step_trace(N_STEPS)
+        p, a = pol.get_weights()
+        g = pol.last_grad()
+    np.savez(os.path.join(out_dir, f"rank{rank}.npz"), params=p, acc=a, grad=g, shares=tr["shares"],
+             budget=tr["budget"], action_sel=tr["action_sel"], q_s=tr["q_s"])
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.skipif(_n_gpus() < 2, reason="needs two GPUs")
+def test_two_gpus_match_one_gpu(tmp_path):
+    import torch.multiprocessing as mp
+    import scala_akka_tensorflow_sharetrade_helper_b200 as q
+    world = 2
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        port = s.getsockname()[1]
+    ctx = mp.get_context("spawn")
+    procs = [ctx.Process(target=_worker, args=(r, world, port, str(tmp_path))) for r in range(world)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(300)
+        assert p.exitcode == 0
+    parts = [np.load(tmp_path / f"rank{r}.npz") for r in range(world)]
+    # replicas bit-identical: same all-reduced sum, same AdaGrad arithmetic
+    np.testing.assert_array_equal(parts[0]["params"], parts[1]["params"])
+    np.testing.assert_array_equal(parts[0]["acc"], parts[1]["acc"])
+    np.testing.assert_array_equal(parts[0]["grad"], parts[1]["grad"])
+    # against one GPU holding every episode
+    cfg = O.Config(bookkeeping=O.RLPY)
+    n = N_LOCAL * world
+    prices = O.gen_prices(cfg.seed, 0, n, T)
+    w = (O.gen_normal(cfg.seed, 0, cfg.P) * 0.05).astype(np.float32)
+    with q.QDecisionPolicy(q.PolicyConfig(bookkeeping=1)) as pol:
+        pol.set_weights(w)
+        pol.env_create(prices, np.arange(n), 1000.0, 1)
+        tr = pol.env_step_trace(N_STEPS)
+        p1, _ = pol.get_weights()
+        g1 = pol.last_grad()
+    for k in ("shares", "budget", "action_sel"):
+        np.testing.assert_array_equal(np.concatenate([p[k] for p in parts], axis=1), tr[k], err_msg=k)
+    _tol.assert_grad_close(parts[0]["grad"], g1, "2-GPU vs 1-GPU gradient of the last step")
+    assert np.abs(parts[0]["params"] - p1).max() <= N_STEPS * _tol.W_ATOL
