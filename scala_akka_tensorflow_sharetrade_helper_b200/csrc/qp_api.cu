@@ -103,6 +103,17 @@ int nccl_load() {
 
 }  // namespace
 
+namespace {
+// Launch geometry and shared-memory budget of the register-tiled fp32 path for one shape.
+struct Geometry {
+    int step_warps = 0;                 // K1: one warp per 20 hidden columns
+    size_t smem_step[3] = {0, 0, 0};
+    int n_rt = 0, cg_max = 0, dw1_tiles = 0, dw1_threads = 0;   // K2
+    size_t smem_dw1 = 0;
+};
+
+}  // namespace
+
 struct qp_handle {
     qp_config cfg{};
     Hyper hp{};
@@ -134,9 +145,7 @@ struct qp_handle {
     // data parallelism over GPUs: one SUM all-reduce of the gradient per env-step
     ncclComm_t comm = nullptr;
     int rank = 0, world = 1;
-    // launch geometry
-    int step_warps = 0, n_rt = 0, n_ct = 0, dw1_threads = 0;
-    size_t smem_step[3] = {0, 0, 0}, smem_dw1 = 0;
+    Geometry geo;
 };
 
 namespace {
@@ -151,7 +160,33 @@ size_t step_smem_bytes(const Hyper& hp, int mode, int nwarps) {
     size_t f = (size_t)hp.D * hp.Hs + (size_t)hp.Hs * 4 + rows_x * kXStride;
     if (mode == kMsgUpdate) f += rows_x * kXStride;
     f += (size_t)nwarps * 2 * 3 * 32 + (size_t)hp.Hs * 3;
-    return f * sizeof(float);
+    f = (f + 3) & ~(size_t)3;
+    return f * sizeof(float) + (size_t)((hp.D + 31) / 32) * sizeof(uint64_t);   // + one mbarrier per W1 row group
+}
+
+int make_geometry(const Hyper& hp, int max_smem, Geometry* g) {
+    g->step_warps = hp.Hs / kColsPerWarp;
+    for (int m = 0; m < 3; ++m) g->smem_step[m] = step_smem_bytes(hp, m, g->step_warps);
+    const int H4 = hp.H / 4;
+    g->n_rt = (hp.D + kDw1Rows - 1) / kDw1Rows;
+    int T = std::max(1, (hp.H + kDw1TileCols - 1) / kDw1TileCols);
+    while (T < H4 && (int64_t)g->n_rt * ((H4 + T - 1) / T) > kDw1MaxThreads) ++T;
+    g->dw1_tiles = T;
+    g->cg_max = (H4 + T - 1) / T;
+    g->dw1_threads = (int)round_up((int64_t)g->n_rt * g->cg_max, 32);
+    g->smem_dw1 = (size_t)kDw1Stages * kDw1ChunkEnvs *
+                  ((size_t)g->n_rt * kDw1Rows + (size_t)g->cg_max * kDw1Cols) * sizeof(float);
+    if (g->step_warps > kMaxStepWarps || g->dw1_threads > kDw1MaxThreads ||
+        g->smem_step[kMsgUpdate] > (size_t)max_smem || g->smem_dw1 > (size_t)max_smem)
+        return fail(QP_EUNSUPPORTED,
+                    "shape outside the fused fp32 path (needs W1 resident in shared memory: hidden <= 240, "
+                    "(window+2)*hidden*4 + staging <= " + std::to_string(max_smem) + " bytes)");
+    return QP_OK;
+}
+
+// episode splits of the dW1 grid: enough episodes per split to be worth a partial, all SMs used
+int dw1_splits(int64_t B, int num_sms, int tiles) {
+    return (int)std::max<int64_t>(1, std::min<int64_t>((B + 15) / 16, std::max(1, num_sms / tiles)));
 }
 
 // Host-side N(0,1) initialiser (Philox stream 2 + Box-Muller); stands in for the unseeded
@@ -171,7 +206,7 @@ int ensure_scratch(qp_handle* h, int64_t B, int* grid_step, int* grid_dw1) {
     const int64_t Bpad = round_up(B, kTileEnvs);
     const int64_t n_tiles = Bpad / kTileEnvs;
     const int g1 = (int)std::min<int64_t>(n_tiles, h->num_sms);
-    const int g2 = (int)std::max<int64_t>(1, std::min<int64_t>((B + 15) / 16, h->num_sms));
+    const int g2 = dw1_splits(B, h->num_sms, h->geo.dw1_tiles);
     QP_TRY(h->dz1.ensure((size_t)Bpad * h->hp.H));
     QP_TRY(h->xextra.ensure((size_t)Bpad * 2));
     QP_TRY(h->part1.ensure((size_t)g2 * h->P1));
@@ -184,7 +219,7 @@ int ensure_scratch(qp_handle* h, int64_t B, int* grid_step, int* grid_dw1) {
 
 template <int MODE>
 int launch_step(qp_handle* h, const StepArgs& a, int grid) {
-    step_kernel<MODE><<<grid, h->step_warps * 32, h->smem_step[MODE], h->stream>>>(a);
+    step_kernel<MODE><<<grid, h->geo.step_warps * 32, h->geo.smem_step[MODE], h->stream>>>(a);
     h->launches++;
     QP_CUDA(cudaGetLastError());
     return QP_OK;
@@ -192,7 +227,7 @@ int launch_step(qp_handle* h, const StepArgs& a, int grid) {
 
 template <int MODE>
 int launch_dw1(qp_handle* h, const Dw1Args& a, int grid) {
-    dw1_kernel<MODE><<<grid, h->dw1_threads, h->smem_dw1, h->stream>>>(a);
+    dw1_kernel<MODE><<<dim3(grid, h->geo.dw1_tiles), h->geo.dw1_threads, h->geo.smem_dw1, h->stream>>>(a);
     h->launches++;
     QP_CUDA(cudaGetLastError());
     return QP_OK;
@@ -236,7 +271,7 @@ int enqueue_env_step(qp_handle* h, const TraceDev* trace, int32_t trace_step0, b
     d.hp = h->hp;
     d.prices = h->prices.p; d.T = h->series_len; d.series_of_env = h->series_of_env.p; d.d_step = h->d_step.p;
     d.xextra = h->xextra.p; d.Bpad = h->Bpad; d.dz1 = h->dz1.p; d.B = h->n_envs; d.part = h->part1.p;
-    d.n_rt = h->n_rt; d.n_ct = h->n_ct;
+    d.n_rt = h->geo.n_rt; d.cg_max = h->geo.cg_max;
     QP_TRY(launch_dw1<kEnvStep>(h, d, g2));
     if (timed) QP_CUDA(cudaEventRecord(h->ev[2], h->stream));
 
@@ -313,17 +348,7 @@ int qp_create(const qp_config* cfg, qp_handle** out) {
     h->max_smem = (int)prop.sharedMemPerBlockOptin;
 
     // launch geometry and shape limits of the register-tiled fp32 path
-    h->step_warps = hp.Hs / kColsPerWarp;
-    h->n_rt = (hp.D + kDw1Rows - 1) / kDw1Rows;
-    h->n_ct = (hp.H / 4 + 1) / 2;
-    h->dw1_threads = (int)round_up((int64_t)h->n_rt * h->n_ct, 32);
-    for (int m = 0; m < 3; ++m) h->smem_step[m] = step_smem_bytes(hp, m, h->step_warps);
-    h->smem_dw1 = (size_t)kDw1ChunkEnvs * ((size_t)h->n_rt * kDw1Rows + (size_t)h->n_ct * kDw1Cols) * sizeof(float);
-    if (h->step_warps > kMaxStepWarps || h->dw1_threads > kDw1MaxThreads ||
-        h->smem_step[kMsgUpdate] > (size_t)h->max_smem || h->smem_dw1 > (size_t)h->max_smem)
-        return bail(fail(QP_EUNSUPPORTED,
-                         "shape outside the fused fp32 path (needs W1 resident in shared memory: hidden <= 240, "
-                         "(window+2)*hidden*4 + staging <= " + std::to_string(h->max_smem) + " bytes)"));
+    if (make_geometry(hp, h->max_smem, &h->geo) != QP_OK) return bail(QP_EUNSUPPORTED);
 #define QP_BAIL_CUDA(expr)                                                                        \
     do {                                                                                          \
         cudaError_t _e = (expr);                                                                  \
@@ -462,7 +487,7 @@ int qp_update_q(qp_handle* h, const float* states, int64_t state_len, const floa
     QP_TRY(launch_step<kMsgUpdate>(h, s, g1));
     Dw1Args d{};
     d.hp = h->hp; d.states = h->m_states.p; d.Bpad = h->Bpad; d.dz1 = h->dz1.p; d.B = B; d.part = h->part1.p;
-    d.n_rt = h->n_rt; d.n_ct = h->n_ct;
+    d.n_rt = h->geo.n_rt; d.cg_max = h->geo.cg_max;
     QP_TRY(launch_dw1<kMsgUpdate>(h, d, g2));
     QP_TRY(launch_apply(h, g2, g1, 1, 1, 0));
     QP_CUDA(cudaStreamSynchronize(h->stream));
@@ -538,17 +563,33 @@ int qp_env_step_timed(qp_handle* h, int32_t n_steps, float* ms_sum) {
     QP_TRY(check_env_steps(h, n_steps));
     QP_TRY(use_device(h));
     for (int k = 0; k < QP_N_KERNELS; ++k) ms_sum[k] = 0.0f;
-    for (int32_t i = 0; i < n_steps; ++i) {
-        QP_TRY(enqueue_env_step(h, nullptr, 0, true));
-        QP_CUDA(cudaEventSynchronize(h->ev[3]));
-        for (int k = 0; k < QP_N_KERNELS; ++k) {
-            float ms = 0.0f;
-            QP_CUDA(cudaEventElapsedTime(&ms, h->ev[k], h->ev[k + 1]));
-            ms_sum[k] += ms;
+    // Events are recorded for a batch of steps without any host synchronisation in between, so the
+    // kernels run back to back as they do in qp_env_step; each interval is one kernel plus the
+    // launch gap that follows it.
+    constexpr int kBatch = 32;
+    std::vector<cudaEvent_t> evs((size_t)kBatch * 4, nullptr);
+    for (auto& e : evs) QP_CUDA(cudaEventCreate(&e));
+    int st = QP_OK;
+    for (int32_t done = 0; done < n_steps && st == QP_OK; done += kBatch) {
+        const int nb = std::min<int32_t>(kBatch, n_steps - done);
+        for (int i = 0; i < nb && st == QP_OK; ++i) {
+            for (int k = 0; k < 4; ++k) h->ev[k] = evs[(size_t)i * 4 + k];
+            st = enqueue_env_step(h, nullptr, 0, true);
         }
-        h->steps_done += 1;
+        if (st == QP_OK && cudaStreamSynchronize(h->stream) != cudaSuccess) st = fail(QP_ECUDA, "sync failed");
+        for (int i = 0; i < nb && st == QP_OK; ++i)
+            for (int k = 0; k < QP_N_KERNELS; ++k) {
+                float ms = 0.0f;
+                if (cudaEventElapsedTime(&ms, evs[(size_t)i * 4 + k], evs[(size_t)i * 4 + k + 1]) != cudaSuccess)
+                    st = fail(QP_ECUDA, "cudaEventElapsedTime failed");
+                ms_sum[k] += ms;
+            }
+        if (st == QP_OK) h->steps_done += nb;
     }
-    return QP_OK;
+    for (int k = 0; k < 4; ++k) h->ev[k] = nullptr;
+    for (auto& e : evs) cudaEventDestroy(e);
+    for (auto& e : h->ev) if (cudaEventCreate(&e) != cudaSuccess && st == QP_OK) st = fail(QP_ECUDA, "cudaEventCreate failed");
+    return st;
 }
 
 int qp_env_step_trace(qp_handle* h, int32_t n_steps, const qp_trace* out) {
@@ -801,19 +842,13 @@ extern "C" int qp_td_grad_noalloc(int32_t device, const qp_config* cfg, const fl
     hp.epsilon = cfg->epsilon; hp.gamma = cfg->gamma; hp.lr = cfg->lr; hp.bias = cfg->bias;
     hp.step_div = cfg->step_div; hp.bookkeeping = cfg->bookkeeping; hp.seed = cfg->seed;
     const int64_t P1 = (int64_t)hp.D * hp.H, P = P1 + 3LL * hp.H;
-    const int step_warps = hp.Hs / kColsPerWarp;
-    const int n_rt = (hp.D + kDw1Rows - 1) / kDw1Rows, n_ct = (hp.H / 4 + 1) / 2;
-    const int dw1_threads = (int)round_up((int64_t)n_rt * n_ct, 32);
-    const size_t smem_step = step_smem_bytes(hp, kMsgUpdate, step_warps);
-    const size_t smem_dw1 = (size_t)kDw1ChunkEnvs * ((size_t)n_rt * kDw1Rows + (size_t)n_ct * kDw1Cols) * sizeof(float);
-    if (step_warps > kMaxStepWarps || dw1_threads > kDw1MaxThreads || smem_step > (size_t)dev->max_smem ||
-        smem_dw1 > (size_t)dev->max_smem)
-        return fail(QP_EUNSUPPORTED, "shape outside the fused fp32 path");
+    Geometry geo;
+    QP_TRY(make_geometry(hp, dev->max_smem, &geo));
 
     // carve the fixed array: [dz1 | dW1 partials | dW2 partials], each piece 256-byte aligned
     const int64_t Bpad = round_up(B, kTileEnvs);
     const int g1 = (int)std::min<int64_t>(Bpad / kTileEnvs, dev->num_sms);
-    const int g2 = (int)std::max<int64_t>(1, std::min<int64_t>((B + 15) / 16, kStaticMaxSplit));
+    const int g2 = std::min(dw1_splits(B, dev->num_sms, geo.dw1_tiles), kStaticMaxSplit);
     const size_t n_dz1 = (size_t)round_up(Bpad * hp.H, 64);
     const size_t n_p1 = (size_t)round_up((int64_t)g2 * P1, 64);
     const size_t n_p2 = (size_t)round_up((int64_t)g1 * 3 * hp.H, 64);
@@ -836,13 +871,13 @@ extern "C" int qp_td_grad_noalloc(int32_t device, const qp_config* cfg, const fl
     s.hp = hp; s.params = d_params;
     s.states = d_states; s.next_states = d_next_states; s.rewards = d_rewards;
     s.B = B; s.Bpad = Bpad; s.dz1 = dz1; s.dw2_part = part2;
-    step_kernel<kMsgUpdate><<<g1, step_warps * 32, smem_step, st>>>(s);
+    step_kernel<kMsgUpdate><<<g1, geo.step_warps * 32, geo.smem_step[kMsgUpdate], st>>>(s);
     QP_CUDA(cudaGetLastError());
 
     Dw1Args d{};
     d.hp = hp; d.states = d_states; d.Bpad = Bpad; d.dz1 = dz1; d.B = B; d.part = part1;
-    d.n_rt = n_rt; d.n_ct = n_ct;
-    dw1_kernel<kMsgUpdate><<<g2, dw1_threads, smem_dw1, st>>>(d);
+    d.n_rt = geo.n_rt; d.cg_max = geo.cg_max;
+    dw1_kernel<kMsgUpdate><<<dim3(g2, geo.dw1_tiles), geo.dw1_threads, geo.smem_dw1, st>>>(d);
     QP_CUDA(cudaGetLastError());
 
     ApplyArgs a{};

@@ -19,10 +19,12 @@ constexpr int kColsPerWarp = 20;   // hidden columns owned by one warp of the st
 constexpr int kTileEnvs = 32;      // episodes per tile = lanes of a warp
 constexpr int kXStride = 33;       // padded row stride of the transposed state tile (bank-conflict free)
 constexpr int kMaxStepWarps = 12;  // hidden <= 12 * 20 = 240 on this path
-constexpr int kDw1Rows = 16;       // register tile of the dW1 contraction: 16 input rows
-constexpr int kDw1Cols = 8;        //   x 8 hidden columns (two float4 groups)
+constexpr int kDw1Rows = 8;        // register tile of the dW1 contraction: 8 input rows
+constexpr int kDw1Cols = 4;        //   x 4 hidden columns (one float4 group)
 constexpr int kDw1MaxThreads = 384;
-constexpr int kDw1ChunkEnvs = 32;  // episodes staged per pass of the dW1 kernel
+constexpr int kDw1ChunkEnvs = 32;  // episodes per pipeline stage of the dW1 kernel
+constexpr int kDw1Stages = 2;
+constexpr int kDw1TileCols = 52;   // target width of one column tile of dW1 (grid.y = ceil(H / 52))
 constexpr int kApplyLanes = 8;     // lanes cooperating on one parameter in the apply kernel
 
 enum StepMode { kEnvStep = 0, kMsgSelect = 1, kMsgUpdate = 2 };
@@ -70,8 +72,9 @@ struct Dw1Args {
     const float* xextra; int64_t Bpad;
     const float* dz1;
     int64_t B;
-    float* part;                    // [grid, D*H]
-    int n_rt, n_ct;
+    float* part;                    // [grid.x, D*H]
+    int n_rt;                       // row tiles of 8:  ceil(D / 8)
+    int cg_max;                     // float4 column groups per column tile (max over tiles)
 };
 
 struct ApplyArgs {
@@ -112,6 +115,10 @@ __device__ __forceinline__ void cp_async16(void* smem_dst, const void* gmem_src)
     const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(d), "l"(gmem_src));
 }
+__device__ __forceinline__ void cp_async4(void* smem_dst, const void* gmem_src) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;\n" ::"r"(d), "l"(gmem_src));
+}
 __device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
 // wait until at most n groups of this thread are still in flight
 __device__ __forceinline__ void cp_async_wait_pending(int n) {
@@ -125,6 +132,33 @@ __device__ __forceinline__ void cp_async_wait_pending(int n) {
         case 6: asm volatile("cp.async.wait_group 6;\n" ::); break;
         case 7: asm volatile("cp.async.wait_group 7;\n" ::); break;
         default: asm volatile("cp.async.wait_group 8;\n" ::); break;
+    }
+}
+
+// ---- TMA bulk copy (cp.async.bulk, SASS UBLKCP) completing on an mbarrier -----------------------
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_fence_init() { asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory"); }
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"((uint32_t)__cvta_generic_to_shared(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void bulk_g2s(void* smem_dst, const void* gmem_src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(
+                     (uint32_t)__cvta_generic_to_shared(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"((uint32_t)__cvta_generic_to_shared(bar))
+                 : "memory");
+}
+// Waits for phase `parity` of the barrier.  Bounded: a copy that never lands traps the kernel
+// instead of hanging the GPU.
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    const uint32_t addr = (uint32_t)__cvta_generic_to_shared(bar);
+    for (uint32_t spins = 0;; ++spins) {
+        uint32_t done;
+        asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
+                     : "=r"(done) : "r"(addr), "r"(parity) : "memory");
+        if (done) return;
+        if (spins > (1u << 24)) __trap();
     }
 }
 
@@ -171,20 +205,37 @@ __global__ void __launch_bounds__(kMaxStepWarps * 32, 1) step_kernel(const StepA
     float* Xn = Xs + (size_t)rows_x * kXStride;  // kMsgUpdate only
     float* qpart = (MODE == kMsgUpdate) ? (Xn + (size_t)rows_x * kXStride) : Xn;
     float* dw2acc = qpart + (size_t)nwarps * 2 * 3 * 32;
+    const int n_groups = (D + 31) >> 5;          // W1 arrives in groups of 32 rows, one mbarrier each
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (((size_t)(dw2acc - smem) + (size_t)Hs * 3 + 3) & ~(size_t)3));
 
-    // ---- stage W1 with cp.async in groups of 32 rows, W2 / padding / accumulators directly
+    // ---- stage W1 with TMA bulk copies (one per row, issued by warp 0), W2 / padding directly
     const float* W1g = a.params;
     const float* W2g = a.params + (size_t)D * H;
-    const int H4 = H >> 2;
-    const int n_groups = (D + 31) >> 5;
-    for (int g = 0; g < n_groups; ++g) {
-        const int r0 = g << 5;
-        const int nr = min(32, D - r0);
-        for (int idx = tid; idx < nr * H4; idx += nthreads) {
-            const int r = r0 + idx / H4, c4 = idx - (idx / H4) * H4;
-            cp_async16(W1s + (size_t)r * Hs + c4 * 4, W1g + (size_t)r * H + c4 * 4);
+    if (tid == 0) {
+        for (int g = 0; g < n_groups; ++g) mbar_init(bars + g, 1);
+        mbar_fence_init();
+    }
+    __syncthreads();
+    if (warp == 0) {
+        if (lane == 0)
+            for (int g = 0; g < n_groups; ++g)
+                mbar_arrive_expect_tx(bars + g, (uint32_t)(min(32, D - (g << 5)) * H * (int)sizeof(float)));
+        __syncwarp();
+        if (Hs == H) {   // rows are contiguous in shared memory too: one copy per 32-row group
+            if (lane < n_groups) {
+                const int r0 = lane << 5;
+                bulk_g2s(W1s + (size_t)r0 * Hs, W1g + (size_t)r0 * H,
+                         (uint32_t)(min(32, D - r0) * H * (int)sizeof(float)), bars + lane);
+            }
+            for (int g = 32 + lane; g < n_groups; g += 32) {
+                const int r0 = g << 5;
+                bulk_g2s(W1s + (size_t)r0 * Hs, W1g + (size_t)r0 * H,
+                         (uint32_t)(min(32, D - r0) * H * (int)sizeof(float)), bars + g);
+            }
+        } else {
+            for (int r = lane; r < D; r += 32)
+                bulk_g2s(W1s + (size_t)r * Hs, W1g + (size_t)r * H, (uint32_t)(H * sizeof(float)), bars + (r >> 5));
         }
-        cp_async_commit();
     }
     if (Hs > H) {
         const int padc = Hs - H;
@@ -224,19 +275,28 @@ __global__ void __launch_bounds__(kMaxStepWarps * 32, 1) step_kernel(const StepA
         // ---- state tile, transposed: Xs[k][episode].  Coalesced row reads from HBM/L2.
         // TrainerChildActor.scala:89-91: prices.slice(i, i + historyDim + 1); one extra element
         // (index wn) is both the last input of s' (:144) and the new share value (:94).
-        for (int el = warp; el < kTileEnvs; el += nwarps) {
-            const int64_t ee = min(tile * kTileEnvs + el, B - 1);
-            if (MODE == kEnvStep) {
-                const float* src = a.prices + (int64_t)a.series_of_env[ee] * a.T + istep;
-                for (int k = lane; k < rows_x; k += 32) Xs[k * kXStride + el] = __ldg(src + k);
-            } else {
-                const float* src = a.states + ee * D;
-                for (int k = lane; k < D; k += 32) Xs[k * kXStride + el] = __ldg(src + k);
+        // Work items = (episode, 32-element segment); each lane knows its own episode's row start
+        // and hands it to the warp by shuffle, so the loads of several items are in flight at once.
+        {
+            const float* my_row;
+            if (MODE == kEnvStep) my_row = a.prices + (int64_t)a.series_of_env[ec] * a.T + istep;
+            else my_row = a.states + ec * D;
+            const float* my_row2 = (MODE == kMsgUpdate) ? a.next_states + ec * D : nullptr;
+            const int segs = (rows_x + 31) >> 5;
+            const int items = kTileEnvs * segs;
+            for (int it = warp; it < items; it += nwarps) {
+                const int el = it & 31, k = ((it >> 5) << 5) + lane;
+                const float* src = reinterpret_cast<const float*>(
+                    __shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(my_row), el));
+                if (k < rows_x) cp_async4(Xs + k * kXStride + el, src + k);
                 if (MODE == kMsgUpdate) {
-                    const float* src2 = a.next_states + ee * D;
-                    for (int k = lane; k < D; k += 32) Xn[k * kXStride + el] = __ldg(src2 + k);
+                    const float* src2 = reinterpret_cast<const float*>(
+                        __shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(my_row2), el));
+                    if (k < rows_x) cp_async4(Xn + k * kXStride + el, src2 + k);
                 }
             }
+            cp_async_commit();
+            cp_async_wait_pending(0);
         }
         __syncthreads();
 
@@ -248,10 +308,7 @@ __global__ void __launch_bounds__(kMaxStepWarps * 32, 1) step_kernel(const StepA
         float x_carry = Xs[lane];
 #pragma unroll 1
         for (int kb = 0; kb < kmax; kb += 32) {
-            if (first) {  // W1 row group kb/32 must have landed (block-uniform branch)
-                cp_async_wait_pending(n_groups - 1 - (kb >> 5));
-                __syncthreads();
-            }
+            if (first) mbar_wait(bars + (kb >> 5), 0);  // W1 row group kb/32 must have landed
             const int kend = min(kb + 32, kmax);
 #pragma unroll 4
             for (int k = kb; k < kend; ++k) {
@@ -281,10 +338,7 @@ __global__ void __launch_bounds__(kMaxStepWarps * 32, 1) step_kernel(const StepA
                 }
             }
         }
-        if (first && MODE == kEnvStep) {  // the two budget/shares rows may sit in a later group
-            cp_async_wait_pending(0);
-            __syncthreads();
-        }
+        if (first && MODE == kEnvStep) mbar_wait(bars + n_groups - 1, 0);  // budget/shares rows: last group
         first = false;
 
         const float* w_budget = W1s + (size_t)wn * Hs + c0;
@@ -459,7 +513,6 @@ __global__ void __launch_bounds__(kMaxStepWarps * 32, 1) step_kernel(const StepA
         __syncthreads();
     }
 
-    cp_async_wait_pending(0);
     __syncthreads();
     if (MODE != kMsgSelect) {
         float* dst = a.dw2_part + (size_t)blockIdx.x * (3 * H);
@@ -468,10 +521,12 @@ __global__ void __launch_bounds__(kMaxStepWarps * 32, 1) step_kernel(const StepA
 }
 
 // =============================================================================================
-// K2 — dW1 = X^T · dZ1 (the MatMul gradient of QDecisionPolicyActor.scala:43 w.r.t. weight1),
-// split over episodes: CTA s owns episodes [B*s/S, B*(s+1)/S) and produces one D x H partial.
-// Thread (rt, ct) keeps a 16 x 8 register tile: rows rt*16.., columns {4ct..4ct+3} and
-// {4(ct+n_ct)..+3}; per episode it reads 4 + 2 float4 from shared memory for 128 FMAs.
+// K2 — dW1 = X^T · dZ1 (the MatMul gradient of QDecisionPolicyActor.scala:43 w.r.t. weight1) on a
+// 2-D grid: blockIdx.x = split s over episodes [B*s/S, B*(s+1)/S), blockIdx.y = column tile t of
+// about 52 hidden columns.  One D x (tile) partial per CTA, so only S (= #SM / T) partials exist —
+// the 2-D split trades a T-fold re-read of the L2-resident price windows for a T-fold cut of the
+// partial traffic.  Thread (rt, ct) keeps an 8 x 4 register tile; per episode it reads 2 + 1
+// float4 from shared memory for 32 FMAs.  Episodes stream through a 2-stage cp.async pipeline.
 // =============================================================================================
 template <int MODE>
 __global__ void __launch_bounds__(kDw1MaxThreads, 1) dw1_kernel(const Dw1Args a) {
@@ -480,15 +535,17 @@ __global__ void __launch_bounds__(kDw1MaxThreads, 1) dw1_kernel(const Dw1Args a)
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
     const int nthreads = blockDim.x;
     const int D = hp.D, H = hp.H, wn = hp.wn;
-    const int Dp = a.n_rt * kDw1Rows, Hp = a.n_ct * kDw1Cols;
-    float* Xc = smem;                                   // [chunk][Dp]
-    float* Zc = Xc + (size_t)kDw1ChunkEnvs * Dp;        // [chunk][Hp]
+    const int H4 = H >> 2;
+    const int T = gridDim.y, t = blockIdx.y;
+    const int cg0 = (H4 * t) / T, width = (H4 * (t + 1)) / T - cg0;     // this tile's float4 column groups
+    const int Dp = a.n_rt * kDw1Rows, Wp = a.cg_max * kDw1Cols;
+    const size_t stage_floats = (size_t)kDw1ChunkEnvs * (Dp + Wp);
     const int32_t istep = (MODE == kEnvStep) ? *a.d_step : 0;
 
     const int64_t S = gridDim.x;
     const int64_t e0 = a.B * (int64_t)blockIdx.x / S, e1 = a.B * ((int64_t)blockIdx.x + 1) / S;
-    const bool active = tid < a.n_rt * a.n_ct;
-    const int rt = active ? tid / a.n_ct : 0, ct = active ? tid - (tid / a.n_ct) * a.n_ct : 0;
+    const int rt = tid / a.cg_max, ct = tid - rt * a.cg_max;
+    const bool active = rt < a.n_rt && ct < width;
 
     float acc[kDw1Rows][kDw1Cols];
 #pragma unroll
@@ -496,69 +553,75 @@ __global__ void __launch_bounds__(kDw1MaxThreads, 1) dw1_kernel(const Dw1Args a)
 #pragma unroll
         for (int c = 0; c < kDw1Cols; ++c) acc[r][c] = 0.0f;
 
-    const int H4 = H >> 2, Hp4 = Hp >> 2;
-    for (int64_t eb = e0; eb < e1; eb += kDw1ChunkEnvs) {
-        const int ne = (int)min((int64_t)kDw1ChunkEnvs, e1 - eb);
-        // stage the states of this chunk (the x fed with trainOp, QDecisionPolicyActor.scala:72)
+    // the states fed with trainOp (QDecisionPolicyActor.scala:72): price window + budget + shares
+    auto prefetch = [&](int64_t eb, int ne, float* Xc, float* Zc) {
         for (int el = warp; el < ne; el += nwarps) {
             const int64_t ee = eb + el;
+            float* dst = Xc + el * Dp;
             if (MODE == kEnvStep) {
                 const float* src = a.prices + (int64_t)a.series_of_env[ee] * a.T + istep;
                 for (int k = lane; k < Dp; k += 32) {
-                    float v = 0.0f;
-                    if (k < wn) v = __ldg(src + k);
-                    else if (k == wn) v = a.xextra[ee];
-                    else if (k == wn + 1) v = a.xextra[a.Bpad + ee];
-                    Xc[el * Dp + k] = v;
+                    if (k < wn) cp_async4(dst + k, src + k);       // rows are only 4-byte aligned
+                    else dst[k] = (k == wn) ? a.xextra[ee] : ((k == wn + 1) ? a.xextra[a.Bpad + ee] : 0.0f);
                 }
             } else {
                 const float* src = a.states + ee * D;
-                for (int k = lane; k < Dp; k += 32) Xc[el * Dp + k] = k < D ? __ldg(src + k) : 0.0f;
+                for (int k = lane; k < Dp; k += 32) {
+                    if (k < D) cp_async4(dst + k, src + k);
+                    else dst[k] = 0.0f;
+                }
             }
         }
-        for (int idx = tid; idx < ne * Hp4; idx += nthreads) {
-            const int el = idx / Hp4, c4 = idx - el * Hp4;
-            float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-            if (c4 < H4) v = reinterpret_cast<const float4*>(a.dz1 + (eb + el) * H)[c4];
-            reinterpret_cast<float4*>(Zc)[el * Hp4 + c4] = v;
+        for (int idx = tid; idx < ne * a.cg_max; idx += nthreads) {
+            const int el = idx / a.cg_max, c = idx - el * a.cg_max;
+            float* dst = Zc + el * Wp + c * 4;
+            if (c < width) cp_async16(dst, a.dz1 + (eb + el) * H + (cg0 + c) * 4);
+            else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
         }
+    };
+
+    const int n_chunks = (int)((e1 - e0 + kDw1ChunkEnvs - 1) / kDw1ChunkEnvs);
+    if (n_chunks > 0) prefetch(e0, (int)min((int64_t)kDw1ChunkEnvs, e1 - e0), smem, smem + (size_t)kDw1ChunkEnvs * Dp);
+    cp_async_commit();
+    for (int c = 0; c < n_chunks; ++c) {
+        const int64_t eb = e0 + (int64_t)c * kDw1ChunkEnvs;
+        const int ne = (int)min((int64_t)kDw1ChunkEnvs, e1 - eb);
+        float* Xc = smem + (size_t)(c & 1) * stage_floats;
+        float* Zc = Xc + (size_t)kDw1ChunkEnvs * Dp;
+        if (c + 1 < n_chunks) {
+            float* Xn = smem + (size_t)((c + 1) & 1) * stage_floats;
+            prefetch(eb + kDw1ChunkEnvs, (int)min((int64_t)kDw1ChunkEnvs, e1 - eb - kDw1ChunkEnvs), Xn,
+                     Xn + (size_t)kDw1ChunkEnvs * Dp);
+        }
+        cp_async_commit();
+        cp_async_wait_pending(1);      // everything but the group just committed has landed
         __syncthreads();
         if (active) {
             const float4* xp = reinterpret_cast<const float4*>(Xc + rt * kDw1Rows);
-            const float4* zp0 = reinterpret_cast<const float4*>(Zc) + ct;
-            const float4* zp1 = reinterpret_cast<const float4*>(Zc) + ct + a.n_ct;
-            const int xs4 = Dp >> 2;
-#pragma unroll 2
+            const float4* zp = reinterpret_cast<const float4*>(Zc) + ct;
+            const int xs4 = Dp >> 2, zs4 = Wp >> 2;
+#pragma unroll 4
             for (int el = 0; el < ne; ++el) {
-                float x[kDw1Rows], z[kDw1Cols];
-#pragma unroll
-                for (int j = 0; j < kDw1Rows / 4; ++j) {
-                    const float4 v = xp[el * xs4 + j];
-                    x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
-                }
-                const float4 za = zp0[el * Hp4], zb = zp1[el * Hp4];
-                z[0] = za.x; z[1] = za.y; z[2] = za.z; z[3] = za.w;
-                z[4] = zb.x; z[5] = zb.y; z[6] = zb.z; z[7] = zb.w;
+                const float4 x0 = xp[el * xs4], x1 = xp[el * xs4 + 1], z = zp[el * zs4];
+                const float x[kDw1Rows] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+                const float zz[kDw1Cols] = {z.x, z.y, z.z, z.w};
 #pragma unroll
                 for (int r = 0; r < kDw1Rows; ++r)
 #pragma unroll
-                    for (int c = 0; c < kDw1Cols; ++c) acc[r][c] = fmaf(x[r], z[c], acc[r][c]);
+                    for (int cc = 0; cc < kDw1Cols; ++cc) acc[r][cc] = fmaf(x[r], zz[cc], acc[r][cc]);
             }
         }
-        __syncthreads();
+        __syncthreads();               // the stage just read is refilled by the next iteration's prefetch
     }
+    cp_async_wait_pending(0);
 
     if (active) {
         float* out = a.part + (size_t)blockIdx.x * ((size_t)D * H);
 #pragma unroll
         for (int r = 0; r < kDw1Rows; ++r) {
             const int row = rt * kDw1Rows + r;
-            if (row < D) {
-                if (ct < H4)
-                    reinterpret_cast<float4*>(out + (size_t)row * H)[ct] = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
-                if (ct + a.n_ct < H4)
-                    reinterpret_cast<float4*>(out + (size_t)row * H)[ct + a.n_ct] = make_float4(acc[r][4], acc[r][5], acc[r][6], acc[r][7]);
-            }
+            if (row < D)
+                reinterpret_cast<float4*>(out + (size_t)row * H)[cg0 + ct] = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
         }
     }
 }
