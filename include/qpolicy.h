@@ -120,6 +120,18 @@ int qp_env_step(qp_handle* h, int32_t n_steps);
 int qp_env_step_async(qp_handle* h, int32_t n_steps);
 int qp_sync(qp_handle* h);
 
+/* Execution options (no reference counterpart).  "fused" (default 1): when the episodes fit one
+ * 32-episode tile per SM and a single GPU is used, qp_env_step* run as ONE persistent cooperative
+ * kernel for all requested steps (price windows stay in shared memory, two grid barriers per
+ * step); 0 forces the three-kernels-per-step path that larger batches and multi-GPU runs use.
+ * Read-only: "fused_active" = 1 if the next qp_env_step would take the persistent kernel. */
+int qp_set_option(qp_handle* h, const char* key, int64_t value);
+int qp_get_option(qp_handle* h, const char* key, int64_t* value);
+/* Tuning aid: with option "phase_clocks" = 1 the persistent kernel's CTA 0 stamps clock64() at 8
+ * phase boundaries of every env-step of a launch; this copies the [n_steps x 8] stamps of the last
+ * launch to out. */
+int qp_debug_phase_clocks(qp_handle* h, int32_t n_steps, int64_t* out);
+
 /* Per-step record for parity checks; host arrays of n_steps x n_envs entries (x3 for q_*),
  * step-major.  Any member may be NULL.  No counterpart in the reference. */
 typedef struct {

@@ -47,6 +47,9 @@ SIGNATURES = {
     "qp_env_step": (C.c_int, [_H, C.c_int32]),
     "qp_env_step_async": (C.c_int, [_H, C.c_int32]),
     "qp_sync": (C.c_int, [_H]),
+    "qp_set_option": (C.c_int, [_H, C.c_char_p, C.c_int64]),
+    "qp_get_option": (C.c_int, [_H, C.c_char_p, C.POINTER(C.c_int64)]),
+    "qp_debug_phase_clocks": (C.c_int, [_H, C.c_int32, _P]),
     "qp_env_step_trace": (C.c_int, [_H, C.c_int32, C.POINTER(QpTrace)]),
     "qp_env_get_portfolio": (C.c_int, [_H, _P]),
     "qp_env_get_state": (C.c_int, [_H, _P, _P, _P]),

@@ -110,6 +110,9 @@ struct Geometry {
     size_t smem_step[3] = {0, 0, 0};
     int n_rt = 0, cg_max = 0, dw1_tiles = 0, dw1_threads = 0;   // K2
     size_t smem_dw1 = 0;
+    bool ep_ok = false;                 // persistent episode kernel usable for this shape
+    int ep_n_rt = 0, ep_n_ct = 0, ep_threads = 0;
+    size_t smem_ep = 0;
 };
 
 }  // namespace
@@ -146,6 +149,10 @@ struct qp_handle {
     ncclComm_t comm = nullptr;
     int rank = 0, world = 1;
     Geometry geo;
+    bool allow_fused = true;            // qp_set_option("fused", 0) forces the three-kernel path
+    DevBuf<long long> dbg;              // phase stamps of the persistent kernel (qp_debug_phase_clocks)
+    bool want_dbg = false;
+    bool coop_launch = false;
 };
 
 namespace {
@@ -176,6 +183,20 @@ int make_geometry(const Hyper& hp, int max_smem, Geometry* g) {
     g->dw1_threads = (int)round_up((int64_t)g->n_rt * g->cg_max, 32);
     g->smem_dw1 = (size_t)kDw1Stages * kDw1ChunkEnvs *
                   ((size_t)g->n_rt * kDw1Rows + (size_t)g->cg_max * kDw1Cols) * sizeof(float);
+    // persistent episode kernel
+    g->ep_n_rt = (hp.wn + 1 + kEpRows - 1) / kEpRows;
+    g->ep_n_ct = (H4 + 1) / 2;
+    g->ep_threads = (int)std::max<int64_t>(32 * g->step_warps, round_up((int64_t)g->ep_n_rt * g->ep_n_ct, 32));
+    {
+        const size_t Dp = (size_t)g->ep_n_rt * kEpRows, Hp = (size_t)g->ep_n_ct * kEpCols;
+        size_t f = (size_t)hp.D * hp.Hs + (size_t)hp.Hs * 4 + Dp * kXStride + 64 +
+                   (size_t)g->step_warps * 2 * 3 * 32 + (size_t)hp.Hs * 3;
+        f = (f + 3) & ~(size_t)3;
+        g->smem_ep = f * sizeof(float) + (size_t)((hp.D + 31) / 32) * sizeof(uint64_t);
+        g->ep_ok = g->ep_threads <= kEpMaxThreads && g->step_warps <= kMaxStepWarps &&
+                   (int64_t)hp.wn * kTileEnvs <= 24LL * g->ep_threads &&
+                   (size_t)kTileEnvs * Hp <= (size_t)hp.D * hp.Hs && g->smem_ep <= (size_t)max_smem;
+    }
     if (g->step_warps > kMaxStepWarps || g->dw1_threads > kDw1MaxThreads ||
         g->smem_step[kMsgUpdate] > (size_t)max_smem || g->smem_dw1 > (size_t)max_smem)
         return fail(QP_EUNSUPPORTED,
@@ -288,6 +309,44 @@ int enqueue_env_step(qp_handle* h, const TraceDev* trace, int32_t trace_step0, b
     return QP_OK;
 }
 
+bool use_fused(const qp_handle* h) {
+    return h->allow_fused && h->coop_launch && h->world == 1 && h->geo.ep_ok &&
+           h->n_envs <= (int64_t)kTileEnvs * h->num_sms;
+}
+
+// n_steps env-steps of every episode in ONE cooperative launch of the persistent episode kernel.
+int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace, int32_t trace_step0) {
+    if (n_steps <= 0) return QP_OK;
+    const int64_t Bpad = round_up(h->n_envs, kTileEnvs);
+    const int64_t n_tiles = Bpad / kTileEnvs;
+    QP_TRY(h->part1.ensure((size_t)n_tiles * h->P1));
+    QP_TRY(h->part2.ensure((size_t)n_tiles * 3 * h->hp.H));
+    EpisodeArgs ea{};
+    StepArgs& s = ea.s;
+    s.hp = h->hp;
+    s.params = h->params.p;
+    s.prices = h->prices.p; s.T = h->series_len; s.series_of_env = h->series_of_env.p;
+    s.budget = h->budget.p; s.shares = h->shares.p; s.share_value = h->share_value.p;
+    s.B0 = h->B0; s.N0 = h->N0; s.env_id_base = h->env_id_base; s.d_step = h->d_step.p;
+    s.B = h->n_envs; s.Bpad = Bpad; s.dw2_part = h->part2.p;
+    if (trace) s.trace = *trace;
+    s.trace_step0 = trace_step0;
+    ea.step0 = (int32_t)h->steps_done; ea.n_steps = n_steps;
+    ea.acc = h->acc.p; ea.grad = h->grad.p; ea.params_rw = h->params.p; ea.part1 = h->part1.p;
+    ea.d_step_rw = h->d_step.p;
+    ea.n_rt = h->geo.ep_n_rt; ea.n_ct = h->geo.ep_n_ct; ea.nwf = h->geo.step_warps;
+    ea.dbg = nullptr;
+    if (h->want_dbg) {
+        QP_TRY(h->dbg.ensure((size_t)n_steps * 8));
+        ea.dbg = h->dbg.p;
+    }
+    void* args[] = {&ea};
+    QP_CUDA(cudaLaunchCooperativeKernel((const void*)episode_kernel, dim3(h->num_sms), dim3(h->geo.ep_threads),
+                                        args, h->geo.smem_ep, h->stream));
+    h->launches++;
+    return QP_OK;
+}
+
 int check_env_steps(qp_handle* h, int32_t n_steps) {
     if (!h) return fail(QP_EINVAL, "null handle");
     if (!h->has_env) return fail(QP_ESTATE, "no episodes: call qp_env_create first");
@@ -361,6 +420,12 @@ int qp_create(const qp_config* cfg, qp_handle** out) {
     QP_BAIL_CUDA(cudaFuncSetAttribute(step_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_kernel<kEnvStep>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(episode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
+    {
+        int coop = 0;
+        QP_BAIL_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->device));
+        h->coop_launch = coop != 0;
+    }
     QP_BAIL_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     for (auto& e : h->ev) QP_BAIL_CUDA(cudaEventCreate(&e));
 #undef QP_BAIL_CUDA
@@ -393,7 +458,7 @@ int qp_destroy(qp_handle* h) {
     h->m_q.release(); h->m_ids.release(); h->m_actions.release();
     h->prices.release(); h->series_of_env.release(); h->shares.release();
     h->budget.release(); h->share_value.release(); h->portfolio.release(); h->blocksum.release();
-    h->d_step.release();
+    h->d_step.release(); h->dbg.release();
     for (auto& e : h->ev) if (e) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -541,7 +606,11 @@ int64_t qp_env_steps_done(const qp_handle* h) { return h ? h->steps_done : 0; }
 int qp_env_step_async(qp_handle* h, int32_t n_steps) {
     QP_TRY(check_env_steps(h, n_steps));
     QP_TRY(use_device(h));
-    for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step(h, nullptr, 0, false));
+    if (use_fused(h)) {
+        QP_TRY(enqueue_env_steps_fused(h, n_steps, nullptr, 0));
+    } else {
+        for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step(h, nullptr, 0, false));
+    }
     h->steps_done += n_steps;
     return QP_OK;
 }
@@ -563,6 +632,15 @@ int qp_env_step_timed(qp_handle* h, int32_t n_steps, float* ms_sum) {
     QP_TRY(check_env_steps(h, n_steps));
     QP_TRY(use_device(h));
     for (int k = 0; k < QP_N_KERNELS; ++k) ms_sum[k] = 0.0f;
+    if (use_fused(h)) {   // one persistent kernel: its whole duration goes to slot QP_KERNEL_STEP
+        QP_CUDA(cudaEventRecord(h->ev[0], h->stream));
+        QP_TRY(enqueue_env_steps_fused(h, n_steps, nullptr, 0));
+        QP_CUDA(cudaEventRecord(h->ev[1], h->stream));
+        QP_CUDA(cudaEventSynchronize(h->ev[1]));
+        QP_CUDA(cudaEventElapsedTime(&ms_sum[0], h->ev[0], h->ev[1]));
+        h->steps_done += n_steps;
+        return QP_OK;
+    }
     // Events are recorded for a batch of steps without any host synchronisation in between, so the
     // kernels run back to back as they do in qp_env_step; each interval is one kernel plus the
     // launch gap that follows it.
@@ -613,7 +691,11 @@ int qp_env_step_trace(qp_handle* h, int32_t n_steps, const qp_trace* out) {
     QP_TR(tgt, target, target, 1) QP_TR(bud, budget, budget, 1)
 #undef QP_TR
     const int32_t step0 = (int32_t)h->steps_done;
-    for (int32_t i = 0; i < n_steps && st == QP_OK; ++i) st = enqueue_env_step(h, &t, step0, false);
+    if (use_fused(h)) {
+        st = enqueue_env_steps_fused(h, n_steps, &t, step0);
+    } else {
+        for (int32_t i = 0; i < n_steps && st == QP_OK; ++i) st = enqueue_env_step(h, &t, step0, false);
+    }
     if (st == QP_OK) h->steps_done += n_steps;
     auto d2h = [&](void* dst, const void* src, size_t bytes) {
         if (st == QP_OK && dst && cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, h->stream) != cudaSuccess)
@@ -698,6 +780,29 @@ int qp_env_portfolio_stats(qp_handle* h, double* mean, double* stddev) {
     *mean = m;
     *stddev = std::sqrt(var / (double)h->n_envs);  // population variance (:150-151)
     return QP_OK;
+}
+
+int qp_debug_phase_clocks(qp_handle* h, int32_t n_steps, int64_t* out) {
+    if (!h || !out) return fail(QP_EINVAL, "null argument");
+    if (!h->dbg.p || (size_t)n_steps * 8 > h->dbg.cap) return fail(QP_ESTATE, "no phase stamps recorded");
+    QP_TRY(use_device(h));
+    QP_CUDA(cudaMemcpyAsync(out, h->dbg.p, (size_t)n_steps * 8 * sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
+    QP_CUDA(cudaStreamSynchronize(h->stream));
+    return QP_OK;
+}
+
+int qp_set_option(qp_handle* h, const char* key, int64_t value) {
+    if (!h || !key) return fail(QP_EINVAL, "null argument");
+    if (std::strcmp(key, "phase_clocks") == 0) { h->want_dbg = value != 0; return QP_OK; }
+    if (std::strcmp(key, "fused") == 0) { h->allow_fused = value != 0; return QP_OK; }
+    return fail(QP_EINVAL, std::string("unknown option: ") + key);
+}
+
+int qp_get_option(qp_handle* h, const char* key, int64_t* value) {
+    if (!h || !key || !value) return fail(QP_EINVAL, "null argument");
+    if (std::strcmp(key, "fused") == 0) { *value = h->allow_fused ? 1 : 0; return QP_OK; }
+    if (std::strcmp(key, "fused_active") == 0) { *value = (h->has_env && use_fused(h)) ? 1 : 0; return QP_OK; }
+    return fail(QP_EINVAL, std::string("unknown option: ") + key);
 }
 
 int qp_dist_unique_id(void* out, size_t out_bytes) {

@@ -12,6 +12,9 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#ifdef __CUDACC__
+#include <cooperative_groups.h>
+#endif
 
 namespace qp {
 
@@ -26,6 +29,9 @@ constexpr int kDw1ChunkEnvs = 32;  // episodes per pipeline stage of the dW1 ker
 constexpr int kDw1Stages = 2;
 constexpr int kDw1TileCols = 52;   // target width of one column tile of dW1 (grid.y = ceil(H / 52))
 constexpr int kApplyLanes = 8;     // lanes cooperating on one parameter in the apply kernel
+constexpr int kEpRows = 16;        // persistent kernel: register tile of its dW1 contraction, 16 rows
+constexpr int kEpCols = 8;         //   x 8 columns (float4 groups ct and ct + n_ct)
+constexpr int kEpMaxThreads = 384;
 
 enum StepMode { kEnvStep = 0, kMsgSelect = 1, kMsgUpdate = 2 };
 
@@ -75,6 +81,18 @@ struct Dw1Args {
     float* part;                    // [grid.x, D*H]
     int n_rt;                       // row tiles of 8:  ceil(D / 8)
     int cg_max;                     // float4 column groups per column tile (max over tiles)
+};
+
+struct EpisodeArgs {
+    StepArgs s;                     // episode-mode fields of the step kernel
+    int32_t step0, n_steps;         // env-steps [step0, step0 + n_steps) in this launch
+    float* acc; float* grad;        // AdaGrad accumulators, summed gradient (kept for qp_get_last_grad)
+    float* params_rw;               // same buffer as s.params, writable
+    float* part1;                   // [n_tiles, D*H] dW1 partials (one per CTA that owns a tile)
+    int32_t* d_step_rw;
+    int n_rt, n_ct;                 // 16-row tiles, pairs of float4 column groups
+    int nwf;                        // forward warps (one per 20 hidden columns)
+    long long* dbg;                 // optional [n_steps][8] clock64 stamps of CTA 0 (phase timing aid)
 };
 
 struct ApplyArgs {
@@ -697,6 +715,440 @@ __global__ void fill_kernel(float* p, int64_t n, float v) {
 __global__ void env_init_kernel(double* budget, int32_t* shares, double* sv, int64_t n, double B0, int32_t N0) {
     const int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (e < n) { budget[e] = B0; shares[e] = N0; sv[e] = 0.0; }   // TrainerChildActor.scala:84-86
+}
+
+// =============================================================================================
+// Persistent episode kernel — the latency path for up to 32 x #SM episodes (configs 1, 2, 5).
+// One cooperative launch runs n_steps env-steps: CTA c owns episodes [32c, 32c+32) for the whole
+// launch and keeps their price window in shared memory, shifting it by one row per step (one new
+// price per episode per step instead of re-staging 202), and their carry (budget, shares, share
+// value) in registers.  Per step:
+//   phase A (per CTA)  TMA bulk load of the current W1 into shared memory; forward of s and s',
+//                      select, book-keeping, TD target (as step_kernel<kEnvStep>); then the dW1
+//                      contraction of its 32 episodes straight from the shared-memory window
+//                      (16 x 8 register tiles) -> one D x H partial per CTA
+//   grid.sync
+//   phase B (all CTAs) fixed-order sum of the partials + AdaGrad on a slice of the parameters
+//   grid.sync
+// Arithmetic and summation orders inside a tile are those of the three-kernel path; the only
+// difference is the split of the gradient sum (per 32-episode tile instead of per S-split).
+// =============================================================================================
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async;\n" ::: "memory"); }
+
+__global__ void __launch_bounds__(kEpMaxThreads, 1) episode_kernel(const EpisodeArgs ea) {
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    extern __shared__ __align__(16) float smem[];
+    const StepArgs& a = ea.s;
+    const Hyper& hp = a.hp;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nthreads = blockDim.x;
+    const int D = hp.D, H = hp.H, Hs = hp.Hs, wn = hp.wn, nwf = ea.nwf;
+    const int H4 = H >> 2;
+    const int Dp = ea.n_rt * kEpRows;            // rows of the window tile incl. padding (>= wn + 1)
+    const int Hp = ea.n_ct * kEpCols;            // row stride of the dz1 tile
+
+    float* W1s = smem;                            // [D][Hs]; after the forward: Z tile [32][Hp]
+    float* W2s = W1s + (size_t)D * Hs;
+    float* Xs = W2s + (size_t)Hs * 4;             // [Dp][33] transposed price window, row k = p[i + k]
+    float* XE = Xs + (size_t)Dp * kXStride;       // [2][32] (float)budget, (float)shares of state s
+    float* qpart = XE + 64;
+    float* dw2acc = qpart + (size_t)nwf * 2 * 3 * 32;
+    const int n_groups = (D + 31) >> 5;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (((size_t)(dw2acc - smem) + (size_t)Hs * 3 + 3) & ~(size_t)3));
+    float* Zs = W1s;
+
+    const int64_t B = a.B;
+    const int64_t n_tiles = (B + kTileEnvs - 1) / kTileEnvs;
+    const bool has_tile = (int64_t)blockIdx.x < n_tiles;
+    const int64_t e = (int64_t)blockIdx.x * kTileEnvs + lane;
+    const bool valid = has_tile && e < B;
+    const int64_t ec = has_tile ? (valid ? e : B - 1) : 0;
+    const bool fwd_warp = warp < nwf;
+    const int c0 = warp * kColsPerWarp;
+    const float bias = hp.bias;
+    const float* W1g = a.params;
+    const float* W2g = a.params + (size_t)D * H;
+
+    if (tid == 0) {
+        for (int g = 0; g < n_groups; ++g) mbar_init(bars + g, 1);
+        mbar_fence_init();
+    }
+    // carry of the fold (TrainerChildActor.scala:84-86, :99-102), one copy per warp
+    double budget = a.budget[ec], share_value = a.share_value[ec];
+    int32_t shares = a.shares[ec];
+    const float* my_row = a.prices + (int64_t)a.series_of_env[ec] * a.T;
+    // initial window: rows 0..wn of step0; rows beyond stay zero
+    for (int idx = tid; idx < Dp * kXStride; idx += nthreads) Xs[idx] = 0.0f;
+    __syncthreads();
+    if (has_tile) {
+        const int segs = (wn + 1 + 31) >> 5, items = kTileEnvs * segs, nw = nthreads >> 5;
+        for (int it = warp; it < items; it += nw) {
+            const int el = it & 31, k = ((it >> 5) << 5) + lane;
+            const float* src = reinterpret_cast<const float*>(
+                __shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(my_row), el)) + ea.step0;
+            if (k <= wn) cp_async4(Xs + k * kXStride + el, src + k);
+        }
+        cp_async_commit();
+        cp_async_wait_pending(0);
+    }
+    __syncthreads();
+
+    for (int32_t sidx = 0; sidx < ea.n_steps; ++sidx) {
+        const int32_t istep = ea.step0 + sidx;
+        const uint32_t parity = (uint32_t)sidx & 1u;
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 0] = clock64();
+        // ---- current weights into shared memory (written by phase B of the previous step)
+        if (has_tile) {
+            if (warp == 0) {
+                fence_proxy_async();   // generic-proxy writes (phase B, Z tile) before async-proxy copies
+                if (lane == 0)
+                    for (int g = 0; g < n_groups; ++g)
+                        mbar_arrive_expect_tx(bars + g, (uint32_t)(min(32, D - (g << 5)) * H * (int)sizeof(float)));
+                __syncwarp();
+                if (Hs == H) {
+                    for (int g = lane; g < n_groups; g += 32) {
+                        const int r0 = g << 5;
+                        bulk_g2s(W1s + (size_t)r0 * Hs, W1g + (size_t)r0 * H,
+                                 (uint32_t)(min(32, D - r0) * H * (int)sizeof(float)), bars + g);
+                    }
+                } else {
+                    for (int r = lane; r < D; r += 32)
+                        bulk_g2s(W1s + (size_t)r * Hs, W1g + (size_t)r * H, (uint32_t)(H * sizeof(float)), bars + (r >> 5));
+                }
+            }
+            if (Hs > H) {
+                const int padc = Hs - H;
+                for (int idx = tid; idx < D * padc; idx += nthreads) {
+                    const int r = idx / padc, c = H + (idx - r * padc);
+                    W1s[(size_t)r * Hs + c] = 0.0f;
+                }
+            }
+            for (int j = tid; j < Hs; j += nthreads) {
+                float4 w = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (j < H) { w.x = __ldcg(W2g + j * 3 + 0); w.y = __ldcg(W2g + j * 3 + 1); w.z = __ldcg(W2g + j * 3 + 2); }
+                reinterpret_cast<float4*>(W2s)[j] = w;
+            }
+            for (int j = tid; j < Hs * 3; j += nthreads) dw2acc[j] = 0.0f;
+        }
+        // the price that enters the window at the end of this step (row wn + 1 of this step)
+        float p_next = 0.0f;
+        if (has_tile && warp == 0 && (int64_t)istep + wn + 1 < a.T) p_next = __ldg(my_row + istep + wn + 1);
+        __syncthreads();
+
+        float q_s[3] = {0.f, 0.f, 0.f}, q_n[3] = {0.f, 0.f, 0.f};
+        float acc_s[kColsPerWarp], acc_n[kColsPerWarp];
+        int action = 0, explored = 0, a_eff = 2, kn = 0;
+        float r32 = 0.0f, target = 0.0f, dz2 = 0.0f;
+        double nb = budget, p_new = 0.0;
+        int32_t ns = shares;
+
+        // ---- hidden layer for s and s' (QDecisionPolicyActor.scala:43), k ascending
+        if (has_tile && fwd_warp) {
+#pragma unroll
+            for (int c = 0; c < kColsPerWarp; ++c) { acc_s[c] = 0.0f; acc_n[c] = 0.0f; }
+            float x_carry = Xs[lane];
+#pragma unroll 1
+            for (int kb = 0; kb < wn; kb += 32) {
+                mbar_wait(bars + (kb >> 5), parity);
+                const int kend = min(kb + 32, wn);
+#pragma unroll 4
+                for (int k = kb; k < kend; ++k) {
+                    const float x_s = x_carry;
+                    const float x_n = Xs[(k + 1) * kXStride + lane];
+                    x_carry = x_n;
+                    const float4* w4 = reinterpret_cast<const float4*>(W1s + (size_t)k * Hs + c0);
+#pragma unroll
+                    for (int j = 0; j < kColsPerWarp / 4; ++j) {
+                        const float4 w = w4[j];
+                        acc_s[4 * j + 0] = fmaf(x_s, w.x, acc_s[4 * j + 0]);
+                        acc_s[4 * j + 1] = fmaf(x_s, w.y, acc_s[4 * j + 1]);
+                        acc_s[4 * j + 2] = fmaf(x_s, w.z, acc_s[4 * j + 2]);
+                        acc_s[4 * j + 3] = fmaf(x_s, w.w, acc_s[4 * j + 3]);
+                        acc_n[4 * j + 0] = fmaf(x_n, w.x, acc_n[4 * j + 0]);
+                        acc_n[4 * j + 1] = fmaf(x_n, w.y, acc_n[4 * j + 1]);
+                        acc_n[4 * j + 2] = fmaf(x_n, w.z, acc_n[4 * j + 2]);
+                        acc_n[4 * j + 3] = fmaf(x_n, w.w, acc_n[4 * j + 3]);
+                    }
+                }
+            }
+            mbar_wait(bars + n_groups - 1, parity);
+            const float* w_budget = W1s + (size_t)wn * Hs + c0;
+            const float* w_shares = W1s + (size_t)(wn + 1) * Hs + c0;
+            const float xb = __double2float_rn(budget);
+            const float xs = (float)shares;
+            float pq[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+            for (int c = 0; c < kColsPerWarp; ++c) {
+                acc_s[c] = fmaf(xb, w_budget[c], acc_s[c]);
+                acc_s[c] = fmaf(xs, w_shares[c], acc_s[c]);
+                const float v = acc_s[c] + bias;
+                acc_s[c] = v > 0.0f ? v : 0.0f;
+                const float4 w2 = reinterpret_cast<const float4*>(W2s)[c0 + c];
+                pq[0] = fmaf(acc_s[c], w2.x, pq[0]);
+                pq[1] = fmaf(acc_s[c], w2.y, pq[1]);
+                pq[2] = fmaf(acc_s[c], w2.z, pq[2]);
+            }
+#pragma unroll
+            for (int x = 0; x < 3; ++x) qpart[((warp * 2 + 0) * 3 + x) * 32 + lane] = pq[x];
+        }
+        __syncthreads();
+
+        if (has_tile && fwd_warp) {
+#pragma unroll
+            for (int x = 0; x < 3; ++x) {
+                float s = 0.0f;
+                for (int w = 0; w < nwf; ++w) s += qpart[((w * 2 + 0) * 3 + x) * 32 + lane];
+                s += bias;
+                q_s[x] = s > 0.0f ? s : 0.0f;
+            }
+            // SelectionAction (QDecisionPolicyActor.scala:56-62)
+            const uint64_t env_id = (uint64_t)(a.env_id_base + e);
+            uint32_t r[4];
+            philox4x32_10((uint32_t)env_id, (uint32_t)(env_id >> 32), (uint32_t)istep, 1u,
+                          (uint32_t)hp.seed, (uint32_t)(hp.seed >> 32), r);
+            const float u = (float)(r[0] >> 8) * (1.0f / 16777216.0f);
+            float thr = __fdiv_rn((float)istep, hp.step_div);
+            if (hp.epsilon < thr) thr = hp.epsilon;
+            if (u < thr) action = argmax3(q_s);
+            else { explored = 1; action = (int)(((uint64_t)r[1] * 3u) >> 32); }
+            // decision, reward, next state (TrainerChildActor.scala:92-96, :118-123, :136-146)
+            p_new = (double)Xs[wn * kXStride + lane];
+            const double cur = __dadd_rn(budget, __dmul_rn((double)shares, share_value));
+            const double base_b = hp.bookkeeping == 0 ? a.B0 : budget;
+            const int32_t base_n = hp.bookkeeping == 0 ? a.N0 : shares;
+            nb = base_b; ns = base_n;
+            if (action == 0 && base_b >= p_new) { nb = __dsub_rn(base_b, p_new); ns = base_n + 1; a_eff = 0; }
+            else if (action == 1 && base_n > 0) { nb = __dadd_rn(base_b, p_new); ns = base_n - 1; a_eff = 1; }
+            const double newp = __dadd_rn(nb, __dmul_rn((double)ns, p_new));
+            r32 = __double2float_rn(__dsub_rn(newp, cur));
+            const float xnb = __double2float_rn(nb);
+            const float xns = (float)ns;
+            const float* w_budget = W1s + (size_t)wn * Hs + c0;
+            const float* w_shares = W1s + (size_t)(wn + 1) * Hs + c0;
+            float pq[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+            for (int c = 0; c < kColsPerWarp; ++c) {
+                acc_n[c] = fmaf(xnb, w_budget[c], acc_n[c]);
+                acc_n[c] = fmaf(xns, w_shares[c], acc_n[c]);
+                float v = acc_n[c] + bias;
+                v = v > 0.0f ? v : 0.0f;
+                const float4 w2 = reinterpret_cast<const float4*>(W2s)[c0 + c];
+                pq[0] = fmaf(v, w2.x, pq[0]);
+                pq[1] = fmaf(v, w2.y, pq[1]);
+                pq[2] = fmaf(v, w2.z, pq[2]);
+            }
+#pragma unroll
+            for (int x = 0; x < 3; ++x) qpart[((warp * 2 + 1) * 3 + x) * 32 + lane] = pq[x];
+        }
+        __syncthreads();     // after this barrier nobody reads W1s any more: the Z tile may overwrite it
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 1] = clock64();
+
+        if (has_tile && fwd_warp) {
+            // UpdateQ target and output-layer backward (QDecisionPolicyActor.scala:67-73, :49)
+#pragma unroll
+            for (int x = 0; x < 3; ++x) {
+                float s = 0.0f;
+                for (int w = 0; w < nwf; ++w) s += qpart[((w * 2 + 1) * 3 + x) * 32 + lane];
+                s += bias;
+                q_n[x] = s > 0.0f ? s : 0.0f;
+            }
+            kn = argmax3(q_n);
+            const float qn_k = kn == 0 ? q_n[0] : (kn == 1 ? q_n[1] : q_n[2]);
+            const float qs_k = kn == 0 ? q_s[0] : (kn == 1 ? q_s[1] : q_s[2]);
+            target = __fadd_rn(r32, __fmul_rn(hp.gamma, qn_k));
+            const float dq = -__fmul_rn(2.0f, __fsub_rn(target, qs_k));
+            dz2 = (valid && qs_k > 0.0f) ? dq : 0.0f;
+            float4* zdst = reinterpret_cast<float4*>(Zs + (size_t)lane * Hp + c0);
+#pragma unroll
+            for (int j = 0; j < kColsPerWarp / 4; ++j) {
+                float v[4];
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const int c = 4 * j + q;
+                    const float w2k = W2s[(c0 + c) * 4 + kn];
+                    v[q] = acc_s[c] > 0.0f ? __fmul_rn(dz2, w2k) : 0.0f;
+                }
+                if (c0 + 4 * j < Hp) zdst[j] = make_float4(v[0], v[1], v[2], v[3]);
+            }
+#pragma unroll
+            for (int c = 0; c < kColsPerWarp; ++c) {
+                const float hv = __fmul_rn(acc_s[c], dz2);
+#pragma unroll
+                for (int x = 0; x < 3; ++x) {
+                    const float sred = warp_sum(kn == x ? hv : 0.0f);
+                    if (lane == 0) dw2acc[(c0 + c) * 3 + x] += sred;
+                }
+            }
+            if (warp == 0) {
+                XE[lane] = __double2float_rn(budget);
+                XE[32 + lane] = (float)shares;
+                if (valid) {
+                    const TraceDev& t = a.trace;
+                    const int64_t ti = (int64_t)(istep - a.trace_step0) * B + e;
+                    if (t.action_sel) t.action_sel[ti] = action;
+                    if (t.action_eff) t.action_eff[ti] = a_eff;
+                    if (t.explored) t.explored[ti] = explored;
+                    if (t.k_next) t.k_next[ti] = kn;
+                    if (t.reward) t.reward[ti] = r32;
+                    if (t.target) t.target[ti] = target;
+                    if (t.budget) t.budget[ti] = nb;
+                    if (t.shares) t.shares[ti] = ns;
+                    if (t.q_s) { t.q_s[ti * 3] = q_s[0]; t.q_s[ti * 3 + 1] = q_s[1]; t.q_s[ti * 3 + 2] = q_s[2]; }
+                    if (t.q_n) { t.q_n[ti * 3] = q_n[0]; t.q_n[ti * 3 + 1] = q_n[1]; t.q_n[ti * 3 + 2] = q_n[2]; }
+                }
+            }
+            budget = nb; shares = ns; share_value = p_new;     // carry (TrainerChildActor.scala:99-102)
+        }
+        // zero the padding columns of the Z tile (when H/4 is odd) so the contraction reads zeros
+        if (has_tile && Hp > H)
+            for (int idx = tid; idx < kTileEnvs * (Hp - H); idx += nthreads) {
+                const int el = idx / (Hp - H), c = H + (idx - el * (Hp - H));
+                Zs[(size_t)el * Hp + c] = 0.0f;
+            }
+        __syncthreads();
+
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 2] = clock64();
+        // ---- dW1 partial of this tile: X^T · dZ1 over its 32 episodes, straight from shared memory
+        if (has_tile) {
+            float* out = ea.part1 + (size_t)blockIdx.x * ((size_t)D * H);
+            const int rt = tid / ea.n_ct, ct = tid - rt * ea.n_ct;
+            if (rt < ea.n_rt) {
+                float acc[kEpRows][kEpCols];
+#pragma unroll
+                for (int r = 0; r < kEpRows; ++r)
+#pragma unroll
+                    for (int c = 0; c < kEpCols; ++c) acc[r][c] = 0.0f;
+                const float* xp = Xs + (size_t)rt * kEpRows * kXStride;
+                const float4* zp0 = reinterpret_cast<const float4*>(Zs) + ct;
+                const float4* zp1 = reinterpret_cast<const float4*>(Zs) + ct + ea.n_ct;
+                const int zs4 = Hp >> 2;
+#pragma unroll 2
+                for (int el = 0; el < kTileEnvs; ++el) {
+                    float x[kEpRows];
+#pragma unroll
+                    for (int r = 0; r < kEpRows; ++r) x[r] = xp[r * kXStride + el];
+                    const float4 za = zp0[el * zs4], zb = zp1[el * zs4];
+                    const float z[kEpCols] = {za.x, za.y, za.z, za.w, zb.x, zb.y, zb.z, zb.w};
+#pragma unroll
+                    for (int r = 0; r < kEpRows; ++r)
+#pragma unroll
+                        for (int c = 0; c < kEpCols; ++c) acc[r][c] = fmaf(x[r], z[c], acc[r][c]);
+                }
+#pragma unroll
+                for (int r = 0; r < kEpRows; ++r) {
+                    const int row = rt * kEpRows + r;
+                    if (row < wn) {     // window rows only; budget/shares rows follow below
+                        if (ct < H4)
+                            reinterpret_cast<float4*>(out + (size_t)row * H)[ct] = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
+                        if (ct + ea.n_ct < H4)
+                            reinterpret_cast<float4*>(out + (size_t)row * H)[ct + ea.n_ct] = make_float4(acc[r][4], acc[r][5], acc[r][6], acc[r][7]);
+                    }
+                }
+            }
+            // rows wn (budget) and wn + 1 (shares) of dW1
+            for (int idx = tid; idx < 2 * H; idx += nthreads) {
+                const int m = idx / H, c = idx - m * H;
+                float sacc = 0.0f;
+                for (int el = 0; el < kTileEnvs; ++el) sacc = fmaf(XE[m * 32 + el], Zs[(size_t)el * Hp + c], sacc);
+                out[(size_t)(wn + m) * H + c] = sacc;
+            }
+            float* dst2 = a.dw2_part + (size_t)blockIdx.x * (3 * H);
+            for (int j = tid; j < 3 * H; j += nthreads) dst2[j] = dw2acc[j];
+        }
+        __syncthreads();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 3] = clock64();
+        // ---- slide the window: row k <- row k + 1 (k < wn), row wn <- the new price
+        if (has_tile) {
+            constexpr int kMaxPer = 24;
+            float keep[kMaxPer];
+            const int total = wn * kTileEnvs;                 // elements (k, el), k in [0, wn)
+#pragma unroll
+            for (int j = 0; j < kMaxPer; ++j) {
+                const int idx = tid + j * nthreads;
+                if (idx < total) keep[j] = Xs[((idx >> 5) + 1) * kXStride + (idx & 31)];
+            }
+            __syncthreads();
+#pragma unroll
+            for (int j = 0; j < kMaxPer; ++j) {
+                const int idx = tid + j * nthreads;
+                if (idx < total) Xs[(idx >> 5) * kXStride + (idx & 31)] = keep[j];
+            }
+            if (warp == 0) Xs[wn * kXStride + lane] = p_next;
+        }
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 4] = clock64();
+        __threadfence();
+        grid.sync();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 5] = clock64();
+
+        // ---- phase B: gradient sum over the tiles (fixed order) + AdaGrad, all CTAs.
+        // Four lanes share one float4 of parameters; each lane loads its partials (j = sub, sub+4, ...)
+        // eight at a time before adding them, so that the L2 round trips overlap.
+        {
+            const int64_t total_threads = (int64_t)gridDim.x * nthreads;
+            const int64_t P1 = (int64_t)D * H, P = P1 + 3 * (int64_t)H;
+            const int64_t n_tasks = ((P >> 2) * 4 + 31) / 32 * 32;
+            const int n1 = (int)n_tiles;
+            for (int64_t task = (int64_t)blockIdx.x * nthreads + tid; task < n_tasks; task += total_threads) {
+                const int64_t g4 = task >> 2;             // float4 group of parameters
+                const int sub = (int)(task & 3);
+                const int64_t p = g4 << 2;
+                const bool in_range = p < P;
+                float4 gsum = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (in_range) {
+                    const float* src; int64_t stride, off;
+                    if (p < P1) { src = ea.part1; stride = P1; off = p; }
+                    else { src = a.dw2_part; stride = P - P1; off = p - P1; }
+                    for (int j0 = sub; j0 < n1; j0 += 32) {
+                        float4 v[8];
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            const int j = j0 + 4 * u;
+                            v[u] = (j < n1) ? __ldcg(reinterpret_cast<const float4*>(src + (int64_t)j * stride + off))
+                                            : make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+#pragma unroll
+                        for (int u = 0; u < 8; ++u) {
+                            gsum.x += v[u].x; gsum.y += v[u].y; gsum.z += v[u].z; gsum.w += v[u].w;
+                        }
+                    }
+                }
+#pragma unroll
+                for (int m = 1; m <= 2; m <<= 1) {
+                    gsum.x += __shfl_xor_sync(0xffffffffu, gsum.x, m);
+                    gsum.y += __shfl_xor_sync(0xffffffffu, gsum.y, m);
+                    gsum.z += __shfl_xor_sync(0xffffffffu, gsum.z, m);
+                    gsum.w += __shfl_xor_sync(0xffffffffu, gsum.w, m);
+                }
+                if (in_range && sub == 0) {
+                    *reinterpret_cast<float4*>(ea.grad + p) = gsum;
+                    float4 av = *reinterpret_cast<float4*>(ea.acc + p);
+                    float4 wv = *reinterpret_cast<float4*>(ea.params_rw + p);
+                    const float gg[4] = {gsum.x, gsum.y, gsum.z, gsum.w};
+                    float aa[4] = {av.x, av.y, av.z, av.w};
+                    float ww[4] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) {
+                        aa[q] = __fadd_rn(aa[q], __fmul_rn(gg[q], gg[q]));
+                        ww[q] = __fsub_rn(ww[q], __fmul_rn(__fmul_rn(gg[q], hp.lr), __fdiv_rn(1.0f, __fsqrt_rn(aa[q]))));
+                    }
+                    *reinterpret_cast<float4*>(ea.acc + p) = make_float4(aa[0], aa[1], aa[2], aa[3]);
+                    *reinterpret_cast<float4*>(ea.params_rw + p) = make_float4(ww[0], ww[1], ww[2], ww[3]);
+                }
+            }
+        }
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 6] = clock64();
+        __threadfence();
+        grid.sync();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 7] = clock64();
+    }
+
+    if (has_tile && warp == 0 && valid) {
+        a.budget[e] = budget;
+        a.shares[e] = shares;
+        a.share_value[e] = share_value;
+    }
+    if (blockIdx.x == 0 && tid == 0) *ea.d_step_rw = ea.step0 + ea.n_steps;
 }
 
 // Measurement aid: dependency-free FFMA streams, to measure the fp32-FMA roof of this GPU (the

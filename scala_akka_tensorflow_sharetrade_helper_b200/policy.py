@@ -212,6 +212,19 @@ class QDecisionPolicy:
     def sync(self):
         check(self._lib.qp_sync(self._h))
 
+    def set_option(self, key: str, value: int):
+        check(self._lib.qp_set_option(self._h, key.encode(), int(value)))
+
+    def get_option(self, key: str) -> int:
+        v = C.c_int64()
+        check(self._lib.qp_get_option(self._h, key.encode(), C.byref(v)))
+        return int(v.value)
+
+    def phase_clocks(self, n_steps):
+        out = np.zeros((n_steps, 8), np.int64)
+        check(self._lib.qp_debug_phase_clocks(self._h, int(n_steps), _ptr(out)))
+        return out
+
     def env_step_timed(self, n_steps):
         ms = np.zeros(_capi.QP_N_KERNELS, np.float32)
         check(self._lib.qp_env_step_timed(self._h, int(n_steps), _ptr(ms)))

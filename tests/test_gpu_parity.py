@@ -21,7 +21,7 @@ def q_mod():
     return q
 
 
-def make_policy(cfg: O.Config, params=None, acc=None):
+def make_policy(cfg: O.Config, params=None, acc=None, fused=None):
     q = q_mod()
     pc = q.PolicyConfig(window=cfg.wn, hidden=cfg.hidden, epsilon=cfg.epsilon, gamma=cfg.gamma, lr=cfg.lr,
                         bias=cfg.bias, step_div=cfg.step_div, adagrad_init_acc=cfg.adagrad_init_acc,
@@ -29,6 +29,8 @@ def make_policy(cfg: O.Config, params=None, acc=None):
     pol = q.QDecisionPolicy(pc)
     if params is not None or acc is not None:
         pol.set_weights(params, acc)
+    if fused is not None:
+        pol.set_option("fused", int(fused))   # 1: persistent episode kernel, 0: three kernels per step
     return pol
 
 
@@ -180,9 +182,10 @@ def compare_step(cfg, w, x, tr, ref, what):
     return n_act
 
 
+@pytest.mark.parametrize("fused", [1, 0])
 @pytest.mark.parametrize("bookkeeping", [O.REFERENCE, O.RLPY])
 @pytest.mark.parametrize("n_envs,N0", [(1, 0), (5, 3), (32, 1), (33, 0), (200, 2)])
-def test_env_step_teacher_forced(bookkeeping, n_envs, N0):
+def test_env_step_teacher_forced(bookkeeping, n_envs, N0, fused):
     """Each step starts from the oracle's weights and episode state; device and oracle take one
     step; everything the step produces is compared."""
     cfg = O.Config(bookkeeping=bookkeeping, seed=77)
@@ -192,8 +195,9 @@ def test_env_step_teacher_forced(bookkeeping, n_envs, N0):
     w0 = (O.gen_normal(21, 0, cfg.P) * 0.05).astype(np.float32)
     o = O.Oracle(cfg, params=w0)
     o.env_create(prices, soe, 1000.0, N0, env_id_base=10 ** 10)
-    with make_policy(cfg) as pol:
+    with make_policy(cfg, fused=fused) as pol:
         pol.env_create(prices, soe, 1000.0, N0, env_id_base=10 ** 10)
+        assert pol.get_option("fused_active") == fused
         for i in (0, 1, 57, 150, 198):
             o.env["step"] = i
             w, acc = o.params.copy(), o.acc.copy()
@@ -214,8 +218,9 @@ def test_env_step_teacher_forced(bookkeeping, n_envs, N0):
                 np.testing.assert_array_equal(vd, o.env["share_value"])
 
 
+@pytest.mark.parametrize("fused", [1, 0])
 @pytest.mark.parametrize("name", ["episode_rlpy", "episode_reference", "episode_tiny", "episode_late"])
-def test_golden_episodes_free_running(golden_dir, name):
+def test_golden_episodes_free_running(golden_dir, name, fused):
     """Committed golden traces (oracle-generated): the device runs the same episodes free-running;
     integer book-keeping must match bit-for-bit up to the first tolerated action divergence."""
     g = np.load(os.path.join(golden_dir, name + ".npz"))
@@ -224,7 +229,7 @@ def test_golden_episodes_free_running(golden_dir, name):
     prices = O.gen_prices(cfg.seed, 0, int(g["n_series"]), int(g["T"]))
     w = grid_weights(cfg.seed, cfg.P) * np.float32(g["weight_scale"])
     n_steps, i0 = int(g["n_steps"]), int(g["start_step"])
-    with make_policy(cfg, params=w) as pol:
+    with make_policy(cfg, params=w, fused=fused) as pol:
         pol.env_create(prices, g["series_of_env"], float(g["B0"]), int(g["N0"]))
         if i0:
             pol.env_set_state(step=i0)
@@ -288,6 +293,34 @@ def test_message_api_reproduces_the_fused_episode_path():
         pf, _ = fused.get_weights()
         pm, _ = msg.get_weights()
         assert np.abs(pf - pm).max() <= 1e-6
+
+
+def test_persistent_kernel_matches_three_kernel_path():
+    """The same 300 episodes for 40 env-steps through the persistent cooperative kernel and through
+    the three-kernels-per-step path: identical book-keeping, weights equal within the gradient-sum
+    re-association (the two paths split the sum over episodes differently)."""
+    cfg = O.Config(bookkeeping=O.RLPY, lr=1e-4, seed=9)
+    n = 300
+    prices = O.gen_prices(cfg.seed, 0, 50, 400)
+    soe = (np.arange(n) % 50).astype(np.int32)
+    w = (O.gen_normal(3, 0, cfg.P) * 0.05).astype(np.float32)
+    res = []
+    for fused in (1, 0):
+        with make_policy(cfg, params=w, fused=fused) as pol:
+            pol.env_create(prices, soe, 1000.0, 1)
+            pol.env_set_state(step=120)
+            assert pol.get_option("fused_active") == fused
+            tr = pol.env_step_trace(25)
+            pol.env_step(15)                     # continue without trace: state carried across launches
+            res.append((tr, pol.get_weights()[0], pol.env_state(), pol.steps_done))
+    (ta, wa, sa, da), (tb, wb, sb, db) = res
+    assert da == db == 160
+    for k in ("action_sel", "action_eff", "explored", "shares", "budget", "reward", "k_next"):
+        np.testing.assert_array_equal(ta[k], tb[k], err_msg=k)
+    np.testing.assert_allclose(ta["q_s"], tb["q_s"], rtol=1e-4, atol=1e-3)
+    for x, y in zip(sa, sb):
+        np.testing.assert_array_equal(x, y)
+    assert np.abs(wa - wb).max() <= 40 * _tol.W_ATOL
 
 
 # ------------------------------------------------------------------------------------------------
