@@ -162,7 +162,8 @@ def workload_config(args, n_envs):
                          f"hidden {HIDDEN}, fp32, {SERIES_LEN}-step random-walk series per episode, budget 1000",
                 episodes=n_envs, env_steps_per_bench_step=SERIES_LEN - WINDOW, series_len=SERIES_LEN,
                 bookkeeping="REFERENCE", l2="flushed between bench steps (256 MiB write inside the timed region)",
-                parallelism=f"dp{max(1, args.gpus)} (episodes sharded, gradient all-reduce per env-step)" if args.gpus > 1 else "single GPU")
+                parallelism=f"dp{max(1, args.gpus)} (episodes sharded, gradient all-reduce per env-step)" if args.gpus > 1
+                else "single GPU, persistent cooperative kernel")
 
 
 # =================================================================================================
@@ -251,32 +252,63 @@ def run_ours(args):
     e2e_value = args.steps * n_env_steps * n_total / (e2e_wall)
 
     # ---- roofline of the dominant kernel, measured live with CUDA events on the launching stream
-    pol.env_reset()
-    pol.env_step(20)
-    n_prof = 200
-    kms = pol.env_step_timed(n_prof)
-    per_kernel_us = (kms / n_prof * 1e3).tolist()
-    names = ["step_kernel", "dw1_kernel", "apply_kernel"]
-    dom = int(np.argmax(per_kernel_us))
     peaks = measured_peaks()
     fp32_peak = pol.measure_fp32_peak()
-    # algorithmic work of each kernel per launch
-    k_bytes = [n_local * (4 * (WINDOW + 1) + 40) + 4 * P, 0.0, 24.0 * P - 4 * P]
-    k_flops = [n_local * (4 * D * HIDDEN + 16 * HIDDEN), n_local * 2 * D * HIDDEN, 6.0 * P]
-    dur = per_kernel_us[dom] * 1e-6
-    step_us = sum(per_kernel_us)
-    roofline = dict(
-        bound="hbm", kernel=names[dom], achieved=k_bytes[dom] / dur / 1e9, peak=peaks["hbm_gbs"], unit="GB/s",
-        frac=k_bytes[dom] / dur / 1e9 / peaks["hbm_gbs"], traffic=None, peak_source=peaks["source"] + " (burst copy)",
-        avg_launch_us=per_kernel_us[dom], kernel_us=dict(zip(names, per_kernel_us)),
-        binding=dict(bound="fp32-fma", note="compute-bound at fp32: 227 FLOP/B vs ridge ~11 (SURVEY.md §8d)",
-                     achieved=k_flops[dom] / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
-                     frac=k_flops[dom] / dur / 1e12 / fp32_peak if fp32_peak else None,
-                     peak_source="measured live (qp_measure_fp32_peak, dependency-free FFMA)"),
-        step=dict(us=step_us, hbm_frac=bytes_per_env_step(n_local) * n_local / (step_us * 1e-6) / 1e9 / peaks["hbm_gbs"],
-                  fp32_frac=FLOP_PER_ENV_STEP * n_local / (step_us * 1e-6) / 1e12 / fp32_peak if fp32_peak else None,
-                  bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP),
-    )
+    n_prof = 200
+    fused = bool(pol.get_option("fused_active"))
+
+    def split_path_us():
+        pol.env_reset()
+        pol.env_step(20)
+        kms = pol.env_step_timed(n_prof)
+        return (kms / n_prof * 1e3).tolist()
+
+    if fused:
+        # one persistent kernel runs every env-step of a launch: its duration / steps is the step time
+        pol.env_reset()
+        pol.env_step(20)
+        ep_us = float(pol.env_step_timed(n_prof)[0]) / n_prof * 1e3
+        pol.set_option("fused", 0)
+        split_us = split_path_us()
+        pol.set_option("fused", 1)
+        names = ["step_kernel", "dw1_kernel", "apply_kernel"]
+        dur = ep_us * 1e-6
+        step_bytes = bytes_per_env_step(n_local) * n_local
+        step_flops = float(FLOP_PER_ENV_STEP) * n_local
+        roofline = dict(
+            bound="hbm", kernel="episode_kernel (persistent, all env-steps of a launch)",
+            achieved=step_bytes / dur / 1e9, peak=peaks["hbm_gbs"], unit="GB/s",
+            frac=step_bytes / dur / 1e9 / peaks["hbm_gbs"], traffic=None,
+            peak_source=peaks["source"] + " (burst copy)", avg_launch_us=ep_us * n_prof, us_per_env_step=ep_us,
+            binding=dict(bound="fp32-fma", note="compute-bound at fp32: 227 FLOP/B vs ridge ~11 (SURVEY.md §8d); "
+                         "inside the SM the forward sweep is limited by shared-memory wavefronts (DESIGN.md §4)",
+                         achieved=step_flops / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
+                         frac=step_flops / dur / 1e12 / fp32_peak if fp32_peak else None,
+                         peak_source="measured live (qp_measure_fp32_peak, dependency-free FFMA)"),
+            bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP,
+            three_kernel_path_us=dict(zip(names, split_us)),
+        )
+    else:
+        per_kernel_us = split_path_us()
+        names = ["step_kernel", "dw1_kernel", "apply_kernel(+allreduce)" if world > 1 else "apply_kernel"]
+        dom = int(np.argmax(per_kernel_us))
+        # algorithmic work of each kernel per launch
+        k_bytes = [n_local * (4 * (WINDOW + 1) + 40) + 4 * P, n_local * 4 * (WINDOW + 2), 24.0 * P - 4 * P]
+        k_flops = [n_local * (4 * D * HIDDEN + 16 * HIDDEN), n_local * 2 * D * HIDDEN, 6.0 * P]
+        dur = per_kernel_us[dom] * 1e-6
+        step_us = sum(per_kernel_us)
+        roofline = dict(
+            bound="hbm", kernel=names[dom], achieved=k_bytes[dom] / dur / 1e9, peak=peaks["hbm_gbs"], unit="GB/s",
+            frac=k_bytes[dom] / dur / 1e9 / peaks["hbm_gbs"], traffic=None, peak_source=peaks["source"] + " (burst copy)",
+            avg_launch_us=per_kernel_us[dom], kernel_us=dict(zip(names, per_kernel_us)),
+            binding=dict(bound="fp32-fma", note="compute-bound at fp32: 227 FLOP/B vs ridge ~11 (SURVEY.md §8d)",
+                         achieved=k_flops[dom] / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
+                         frac=k_flops[dom] / dur / 1e12 / fp32_peak if fp32_peak else None,
+                         peak_source="measured live (qp_measure_fp32_peak, dependency-free FFMA)"),
+            step=dict(us=step_us, hbm_frac=bytes_per_env_step(n_local) * n_local / (step_us * 1e-6) / 1e9 / peaks["hbm_gbs"],
+                      fp32_frac=FLOP_PER_ENV_STEP * n_local / (step_us * 1e-6) / 1e12 / fp32_peak if fp32_peak else None,
+                      bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP),
+        )
 
     line = dict(
         metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
