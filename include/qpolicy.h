@@ -165,6 +165,36 @@ int qp_train(qp_handle* h, const float* prices, int64_t series_len, int64_t n_se
              const int32_t* series_of_env, int64_t n_envs, int64_t env_id_base, double budget0,
              int32_t shares0, double* portfolios_out);
 
+/* ---- batching front-end for the router fan-out (TrainerRouterActor.scala:60-66, :88): many child
+ * actors, on any threads, queue their SelectionAction / UpdateQ messages; one qp_flush answers all
+ * queued selects with ONE launch (using the weights as they are at the flush) and then turns all
+ * queued updates into ONE gradient-SUM step.  Enqueue calls are thread-safe and never touch the GPU;
+ * the size guards of QDecisionPolicyActor.scala:56-57, :64-65 apply at enqueue time (QP_EINVAL).
+ * qp_take_action returns the action of a ticket from the most recent flush that held selects. */
+int qp_enqueue_select(qp_handle* h, const float* state, int64_t state_len, float step, int64_t env_id,
+                      int64_t* ticket);
+int qp_enqueue_update(qp_handle* h, const float* state, int64_t state_len, float reward,
+                      const float* next_state, int64_t next_state_len);
+int qp_flush(qp_handle* h, int64_t* n_selects, int64_t* n_updates);
+int qp_take_action(qp_handle* h, int64_t ticket, int32_t* action);
+int64_t qp_pending(qp_handle* h);   /* queued messages; returns the count */
+
+/* ---- policy checkpoint: weights, AdaGrad accumulators, UpdateQ counter and (if episodes exist) the
+ * episodes' carry and step.  Fills the reference's empty saveSnapshot hook, called every 500
+ * updates (QDecisionPolicyActor.scala:74, :91-93): qp_set_snapshot(path, 500) arms exactly that.
+ * The RNG is counter-based, so (env id, step) in the checkpoint is all the RNG state there is. */
+int qp_save_checkpoint(qp_handle* h, const char* path);
+int qp_load_checkpoint(qp_handle* h, const char* path);
+int qp_set_snapshot(qp_handle* h, const char* path, int64_t every);
+int64_t qp_iteration(const qp_handle* h);   /* `iteration` of QDecisionPolicyActor.scala:54, :76 */
+
+/* ---- price ingest: the text format of MSFT-stock-prices-revised.txt, `price, yyyy-MM-dd` per line,
+ * parsed as SharePriceGetter.queryData does (SharePriceGetter.scala:89-101, :104-108): fields split on
+ * ',' and trimmed, rows with fewer than two fields or an unparsable price/date dropped, a repeated
+ * date keeps its last row, result sorted by date and narrowed to fp32 (TrainerChildActor.scala:66).
+ * Host-only (needs no GPU).  out may be NULL to query the count. */
+int qp_parse_prices(const char* text, size_t len, float* out, int64_t capacity, int64_t* n_out);
+
 /* ---- several GPUs: episodes are sharded over ranks (one process per GPU, env_id_base = first
  * global episode of the shard), weights are replicated, and each env-step exchanges ONE thing: a SUM
  * all-reduce of the P-float gradient (NCCL over NVLink), after which every rank applies the same

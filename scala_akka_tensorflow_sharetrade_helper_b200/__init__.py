@@ -5,7 +5,8 @@ Layout: csrc/ (kernels + C ABI implementation), _build (nvcc, in-tree), _capi (c
 include/qpolicy.h), policy / trainer (host-side mirrors of the reference's actor messages).
 """
 from ._build import build, LIB_PATH  # noqa: F401
-from .policy import (Action, Buy, Hold, IllegalArgumentException, PolicyConfig, QDecisionPolicy,  # noqa: F401
+from .ingest import parse_prices, load_price_file  # noqa: F401
+from .policy import (Action, BatchingPolicy, Buy, Hold, IllegalArgumentException, PolicyConfig, QDecisionPolicy,  # noqa: F401
                      QPolicyError, SelectionAction, Sell, UpdateQ, Updated)
 from .sharding import shard  # noqa: F401
 from .trainer import (Initialised, NotComputed, StockDataResponse, Trained, TrainedData,  # noqa: F401

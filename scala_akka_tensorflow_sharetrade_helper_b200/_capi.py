@@ -56,6 +56,16 @@ SIGNATURES = {
     "qp_env_set_state": (C.c_int, [_H, _P, _P, _P, C.c_int64]),
     "qp_env_portfolio_stats": (C.c_int, [_H, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
     "qp_train": (C.c_int, [_H, _P, C.c_int64, C.c_int64, _P, C.c_int64, C.c_int64, C.c_double, C.c_int32, _P]),
+    "qp_enqueue_select": (C.c_int, [_H, _P, C.c_int64, C.c_float, C.c_int64, C.POINTER(C.c_int64)]),
+    "qp_enqueue_update": (C.c_int, [_H, _P, C.c_int64, C.c_float, _P, C.c_int64]),
+    "qp_flush": (C.c_int, [_H, C.POINTER(C.c_int64), C.POINTER(C.c_int64)]),
+    "qp_take_action": (C.c_int, [_H, C.c_int64, C.POINTER(C.c_int32)]),
+    "qp_pending": (C.c_int64, [_H]),
+    "qp_save_checkpoint": (C.c_int, [_H, C.c_char_p]),
+    "qp_load_checkpoint": (C.c_int, [_H, C.c_char_p]),
+    "qp_set_snapshot": (C.c_int, [_H, C.c_char_p, C.c_int64]),
+    "qp_iteration": (C.c_int64, [_H]),
+    "qp_parse_prices": (C.c_int, [C.c_char_p, C.c_size_t, _P, C.c_int64, C.POINTER(C.c_int64)]),
     "qp_dist_unique_id": (C.c_int, [_P, C.c_size_t]),
     "qp_dist_init": (C.c_int, [_H, _P, C.c_int32, C.c_int32]),
     "qp_dist_nccl_version": (C.c_int, [C.POINTER(C.c_int32)]),

@@ -11,6 +11,9 @@
 #include <cmath>
 #include <cstdio>
 #include <cstring>
+#include <cerrno>
+#include <cstdlib>
+#include <map>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -148,6 +151,17 @@ struct qp_handle {
     // data parallelism over GPUs: one SUM all-reduce of the gradient per env-step
     ncclComm_t comm = nullptr;
     int rank = 0, world = 1;
+    // batching front-end (config 5): child actors enqueue rows, one flush = one GPU launch per kind
+    std::mutex qmu;
+    std::vector<float> q_states, q_steps, u_states, u_rewards, u_next;
+    std::vector<int64_t> q_ids;
+    std::vector<int32_t> q_results;
+    int64_t ticket_base = 0;            // ticket of q_results[0]
+    int64_t next_ticket = 0;
+    // UpdateQ counter and snapshot hook (QDecisionPolicyActor.scala:74, :76)
+    int64_t iteration = 0;
+    std::string snapshot_path;
+    int64_t snapshot_every = 500;
     Geometry geo;
     bool allow_fused = true;            // qp_set_option("fused", 0) forces the three-kernel path
     DevBuf<long long> dbg;              // phase stamps of the persistent kernel (qp_debug_phase_clocks)
@@ -556,6 +570,12 @@ int qp_update_q(qp_handle* h, const float* states, int64_t state_len, const floa
     QP_TRY(launch_dw1<kMsgUpdate>(h, d, g2));
     QP_TRY(launch_apply(h, g2, g1, 1, 1, 0));
     QP_CUDA(cudaStreamSynchronize(h->stream));
+    // if (iteration % 500 == 0 && iteration != 0) saveSnapshot(...)  — QDecisionPolicyActor.scala:74;
+    // the reference's saveSnapshot is an empty stub (:91-93), here it writes a checkpoint if a path is set
+    if (!h->snapshot_path.empty() && h->snapshot_every > 0 && h->iteration != 0 &&
+        h->iteration % h->snapshot_every == 0)
+        QP_TRY(qp_save_checkpoint(h, h->snapshot_path.c_str()));
+    h->iteration += 1;                   // context.become(iterateUpdate(session, iteration + 1)) (:76)
     return QP_OK;
 }
 
@@ -779,6 +799,243 @@ int qp_env_portfolio_stats(qp_handle* h, double* mean, double* stddev) {
     QP_TRY(pass(m, 2, &var));
     *mean = m;
     *stddev = std::sqrt(var / (double)h->n_envs);  // population variance (:150-151)
+    return QP_OK;
+}
+
+// ---- batching front-end -------------------------------------------------------------------------
+int qp_enqueue_select(qp_handle* h, const float* state, int64_t state_len, float step, int64_t env_id,
+                      int64_t* ticket) {
+    if (!h || !state || !ticket) return fail(QP_EINVAL, "null argument");
+    if (state_len != h->hp.D)
+        return fail(QP_EINVAL, "SelectionAction: tensorflow input size(" + std::to_string(h->hp.D) +
+                                   ") and state(" + std::to_string(state_len) + ") size do not match");
+    std::lock_guard<std::mutex> lock(h->qmu);
+    h->q_states.insert(h->q_states.end(), state, state + state_len);
+    h->q_steps.push_back(step);
+    h->q_ids.push_back(env_id);
+    *ticket = h->next_ticket++;
+    return QP_OK;
+}
+
+int qp_enqueue_update(qp_handle* h, const float* state, int64_t state_len, float reward,
+                      const float* next_state, int64_t next_state_len) {
+    if (!h || !state || !next_state) return fail(QP_EINVAL, "null argument");
+    if (state_len != h->hp.D || next_state_len != h->hp.D)
+        return fail(QP_EINVAL, "update q: tensorflow input size(" + std::to_string(h->hp.D) +
+                                   ") and state(or nextState) size(" + std::to_string(state_len) + ", " +
+                                   std::to_string(next_state_len) + ") do not match");
+    std::lock_guard<std::mutex> lock(h->qmu);
+    h->u_states.insert(h->u_states.end(), state, state + state_len);
+    h->u_next.insert(h->u_next.end(), next_state, next_state + next_state_len);
+    h->u_rewards.push_back(reward);
+    return QP_OK;
+}
+
+int qp_flush(qp_handle* h, int64_t* n_selects, int64_t* n_updates) {
+    if (!h) return fail(QP_EINVAL, "null handle");
+    // take the queues under the lock, run the GPU work outside it so that actors keep enqueuing
+    std::vector<float> qs, qst, us, ur, un;
+    std::vector<int64_t> qi;
+    int64_t first_ticket = 0;
+    {
+        std::lock_guard<std::mutex> lock(h->qmu);
+        qs.swap(h->q_states); qst.swap(h->q_steps); qi.swap(h->q_ids);
+        us.swap(h->u_states); ur.swap(h->u_rewards); un.swap(h->u_next);
+        first_ticket = h->next_ticket - (int64_t)qst.size();
+    }
+    const int64_t ns = (int64_t)qst.size(), nu = (int64_t)ur.size();
+    if (ns > 0) {   // every queued SelectionAction is answered with the weights as they are now ...
+        std::vector<int32_t> res((size_t)ns, 0);
+        QP_TRY(qp_select_action(h, qs.data(), h->hp.D, qst.data(), qi.data(), res.data(), nullptr, ns));
+        std::lock_guard<std::mutex> lock(h->qmu);
+        h->q_results.swap(res);
+        h->ticket_base = first_ticket;
+    }
+    if (nu > 0)     // ... then every queued UpdateQ becomes one gradient-SUM step
+        QP_TRY(qp_update_q(h, us.data(), h->hp.D, ur.data(), un.data(), h->hp.D, nu));
+    if (n_selects) *n_selects = ns;
+    if (n_updates) *n_updates = nu;
+    return QP_OK;
+}
+
+int qp_take_action(qp_handle* h, int64_t ticket, int32_t* action) {
+    if (!h || !action) return fail(QP_EINVAL, "null argument");
+    std::lock_guard<std::mutex> lock(h->qmu);
+    if (ticket >= h->next_ticket - (int64_t)h->q_steps.size() && ticket < h->next_ticket)
+        return fail(QP_ESTATE, "ticket " + std::to_string(ticket) + " is still queued: call qp_flush first");
+    const int64_t idx = ticket - h->ticket_base;
+    if (idx < 0 || idx >= (int64_t)h->q_results.size())
+        return fail(QP_EINVAL, "ticket " + std::to_string(ticket) + " is not from the most recent flush");
+    *action = h->q_results[(size_t)idx];
+    return QP_OK;
+}
+
+int64_t qp_pending(qp_handle* h) {
+    if (!h) return 0;
+    std::lock_guard<std::mutex> lock(h->qmu);
+    return (int64_t)h->q_steps.size() + (int64_t)h->u_rewards.size();
+}
+
+// ---- checkpoint (fills the reference's saveSnapshot stub, QDecisionPolicyActor.scala:74, :91-93) -----
+namespace {
+struct CkptHeader {
+    char magic[8];            // "QPCKPT1\0"
+    int32_t window, hidden, bookkeeping, has_env;
+    float epsilon, gamma, lr, bias, step_div, adagrad_init_acc;
+    uint64_t seed;
+    int64_t P, iteration, steps_done, n_envs, env_id_base;
+    double B0;
+    int32_t N0, reserved;
+};
+}  // namespace
+
+int qp_save_checkpoint(qp_handle* h, const char* path) {
+    if (!h || !path) return fail(QP_EINVAL, "null argument");
+    QP_TRY(use_device(h));
+    CkptHeader hd{};
+    std::memcpy(hd.magic, "QPCKPT1", 8);
+    hd.window = h->cfg.window; hd.hidden = h->cfg.hidden; hd.bookkeeping = h->cfg.bookkeeping;
+    hd.has_env = h->has_env ? 1 : 0;
+    hd.epsilon = h->cfg.epsilon; hd.gamma = h->cfg.gamma; hd.lr = h->cfg.lr; hd.bias = h->cfg.bias;
+    hd.step_div = h->cfg.step_div; hd.adagrad_init_acc = h->cfg.adagrad_init_acc; hd.seed = h->cfg.seed;
+    hd.P = h->P; hd.iteration = h->iteration; hd.steps_done = h->steps_done;
+    hd.n_envs = h->has_env ? h->n_envs : 0; hd.env_id_base = h->env_id_base; hd.B0 = h->B0; hd.N0 = h->N0;
+    std::vector<float> w(h->P), a(h->P);
+    QP_TRY(qp_get_weights(h, w.data(), a.data()));
+    std::vector<double> b, v;
+    std::vector<int32_t> sh;
+    if (h->has_env) {
+        b.resize(h->n_envs); v.resize(h->n_envs); sh.resize(h->n_envs);
+        QP_TRY(qp_env_get_state(h, b.data(), sh.data(), v.data()));
+    }
+    const std::string tmp = std::string(path) + ".tmp";
+    FILE* f = std::fopen(tmp.c_str(), "wb");
+    if (!f) return fail(QP_EIO, "cannot open " + tmp + ": " + std::strerror(errno));
+    bool ok = std::fwrite(&hd, sizeof hd, 1, f) == 1 && std::fwrite(w.data(), 4, w.size(), f) == w.size() &&
+              std::fwrite(a.data(), 4, a.size(), f) == a.size();
+    if (ok && h->has_env)
+        ok = std::fwrite(b.data(), 8, b.size(), f) == b.size() && std::fwrite(sh.data(), 4, sh.size(), f) == sh.size() &&
+             std::fwrite(v.data(), 8, v.size(), f) == v.size();
+    ok = (std::fclose(f) == 0) && ok;
+    if (!ok) { std::remove(tmp.c_str()); return fail(QP_EIO, "short write to " + tmp); }
+    if (std::rename(tmp.c_str(), path) != 0) return fail(QP_EIO, std::string("rename failed: ") + std::strerror(errno));
+    return QP_OK;
+}
+
+int qp_load_checkpoint(qp_handle* h, const char* path) {
+    if (!h || !path) return fail(QP_EINVAL, "null argument");
+    FILE* f = std::fopen(path, "rb");
+    if (!f) return fail(QP_EIO, std::string("cannot open ") + path + ": " + std::strerror(errno));
+    CkptHeader hd{};
+    auto bad = [&](const std::string& m) { std::fclose(f); return fail(QP_EIO, m); };
+    if (std::fread(&hd, sizeof hd, 1, f) != 1 || std::memcmp(hd.magic, "QPCKPT1", 8) != 0) return bad("not a qpolicy checkpoint");
+    if (hd.window != h->cfg.window || hd.hidden != h->cfg.hidden || hd.P != h->P)
+        return bad("checkpoint shape (window " + std::to_string(hd.window) + ", hidden " + std::to_string(hd.hidden) +
+                   ") does not match the policy");
+    std::vector<float> w(h->P), a(h->P);
+    if (std::fread(w.data(), 4, w.size(), f) != w.size() || std::fread(a.data(), 4, a.size(), f) != a.size())
+        return bad("truncated checkpoint");
+    std::vector<double> b, v;
+    std::vector<int32_t> sh;
+    if (hd.has_env) {
+        if (!h->has_env || hd.n_envs != h->n_envs) return bad("checkpoint holds " + std::to_string(hd.n_envs) +
+                                                            " episodes; create the same episodes before loading");
+        b.resize(hd.n_envs); v.resize(hd.n_envs); sh.resize(hd.n_envs);
+        if (std::fread(b.data(), 8, b.size(), f) != b.size() || std::fread(sh.data(), 4, sh.size(), f) != sh.size() ||
+            std::fread(v.data(), 8, v.size(), f) != v.size())
+            return bad("truncated checkpoint (episodes)");
+    }
+    std::fclose(f);
+    QP_TRY(qp_set_weights(h, w.data(), a.data()));
+    h->iteration = hd.iteration;
+    if (hd.has_env) QP_TRY(qp_env_set_state(h, b.data(), sh.data(), v.data(), hd.steps_done));
+    return QP_OK;
+}
+
+int qp_set_snapshot(qp_handle* h, const char* path, int64_t every) {
+    if (!h) return fail(QP_EINVAL, "null handle");
+    h->snapshot_path = path ? path : "";
+    h->snapshot_every = every;
+    return QP_OK;
+}
+
+int64_t qp_iteration(const qp_handle* h) { return h ? h->iteration : 0; }
+
+// ---- price ingest (SharePriceGetter.scala:89-101, :104-108; TrainerChildActor.scala:66) ---------------
+namespace {
+bool parse_date_key(const std::string& s, int32_t* key) {
+    // DateTimeFormatter.ofPattern("yyyy-MM-dd"), default SMART resolver: 4-digit year, 2-digit month
+    // and day; a day of 29..31 beyond the month's length resolves to the month's last day.
+    if (s.size() != 10 || s[4] != '-' || s[7] != '-') return false;
+    for (int i : {0, 1, 2, 3, 5, 6, 8, 9}) if (s[i] < '0' || s[i] > '9') return false;
+    const int y = (s[0] - '0') * 1000 + (s[1] - '0') * 100 + (s[2] - '0') * 10 + (s[3] - '0');
+    const int m = (s[5] - '0') * 10 + (s[6] - '0');
+    int d = (s[8] - '0') * 10 + (s[9] - '0');
+    if (y < 1 || m < 1 || m > 12 || d < 1 || d > 31) return false;
+    static const int len[12] = {31, 28, 31, 30, 31, 30, 31, 31, 30, 31, 30, 31};
+    int last = len[m - 1];
+    if (m == 2 && ((y % 4 == 0 && y % 100 != 0) || y % 400 == 0)) last = 29;
+    if (d > last) d = last;
+    *key = y * 10000 + m * 100 + d;
+    return true;
+}
+
+bool parse_double(const std::string& s, double* out) {
+    // String.toDouble = java.lang.Double.parseDouble: optional sign, decimal / exponent forms,
+    // "NaN", "Infinity", and an optional trailing f/F/d/D type suffix; hex floats are accepted too.
+    if (s.empty()) return false;
+    std::string t = s;
+    const char lastc = t.back();
+    if ((lastc == 'f' || lastc == 'F' || lastc == 'd' || lastc == 'D') && t.size() > 1 &&
+        !(t.size() >= 2 && (t[0] == '0' && (t[1] == 'x' || t[1] == 'X'))))
+        t.pop_back();
+    if (t == "NaN" || t == "+NaN" || t == "-NaN") { *out = std::nan(""); return true; }
+    if (t == "Infinity" || t == "+Infinity") { *out = INFINITY; return true; }
+    if (t == "-Infinity") { *out = -INFINITY; return true; }
+    for (char c : t) if (!((c >= '0' && c <= '9') || c == '.' || c == 'e' || c == 'E' || c == '+' || c == '-')) return false;
+    char* end = nullptr;
+    errno = 0;
+    const double v = std::strtod(t.c_str(), &end);
+    if (end == t.c_str() || *end != '\0') return false;
+    *out = v;
+    return true;
+}
+
+std::string trim_java(const std::string& s) {   // String.trim(): strips chars <= ' '
+    size_t a = 0, b = s.size();
+    while (a < b && (unsigned char)s[a] <= ' ') ++a;
+    while (b > a && (unsigned char)s[b - 1] <= ' ') --b;
+    return s.substr(a, b - a);
+}
+}  // namespace
+
+int qp_parse_prices(const char* text, size_t len, float* out, int64_t capacity, int64_t* n_out) {
+    if (!text || !n_out) return fail(QP_EINVAL, "null argument");
+    std::map<int32_t, double> by_date;      // HashMap(parsed: _*): a repeated date keeps the LAST row
+    size_t pos = 0;
+    while (pos < len) {
+        size_t eol = pos;
+        while (eol < len && text[eol] != '\n') ++eol;
+        size_t end = eol;
+        if (end > pos && text[end - 1] == '\r') --end;     // getLines strips \r\n as well
+        std::vector<std::string> fields;
+        size_t fs = pos;
+        for (size_t i = pos; i <= end; ++i)
+            if (i == end || text[i] == ',') { fields.push_back(trim_java(std::string(text + fs, i - fs))); fs = i + 1; }
+        while (!fields.empty() && fields.back().empty()) fields.pop_back();   // String.split drops trailing empties
+        if (fields.size() >= 2) {           // case Seq(price, date) | Seq(price, date, _*)
+            int32_t key; double price;
+            if (parse_date_key(fields[1], &key) && parse_double(fields[0], &price)) by_date[key] = price;
+        }
+        pos = eol + 1;
+    }
+    *n_out = (int64_t)by_date.size();
+    if (out) {
+        if (capacity < *n_out) return fail(QP_EINVAL, "output holds " + std::to_string(capacity) + " prices, " +
+                                                          std::to_string(*n_out) + " parsed");
+        int64_t i = 0;
+        for (const auto& kv : by_date) out[i++] = (float)kv.second;   // sorted by date; .toFloat (TrainerChildActor.scala:66)
+    }
     return QP_OK;
 }
 

@@ -296,6 +296,17 @@ class QDecisionPolicy:
         check(self._lib.qp_dist_init(self._h, uid, int(rank), int(world)))
         del torch
 
+    # ---- checkpoint (the reference's saveSnapshot stub, QDecisionPolicyActor.scala:74, :91-93) ------
+    def save_checkpoint(self, path: str):
+        check(self._lib.qp_save_checkpoint(self._h, str(path).encode()))
+
+    def load_checkpoint(self, path: str):
+        check(self._lib.qp_load_checkpoint(self._h, str(path).encode()))
+        self.iteration = int(self._lib.qp_iteration(self._h))
+
+    def set_snapshot(self, path, every: int = 500):
+        check(self._lib.qp_set_snapshot(self._h, None if path is None else str(path).encode(), int(every)))
+
     def measure_fp32_peak(self) -> float:
         t = C.c_double()
         check(self._lib.qp_measure_fp32_peak(self._h, C.byref(t)))
@@ -308,3 +319,41 @@ class QDecisionPolicy:
     @property
     def launch_count(self) -> int:
         return int(self._lib.qp_launch_count(self._h))
+
+
+class BatchingPolicy:
+    """Front-end for many child actors sharing one policy (TrainerRouterActor.scala:44, :60-66): each
+    child enqueues its SelectionAction / UpdateQ; flush() answers all of them with one GPU launch per
+    kind.  enqueue_* are thread-safe and do not touch the GPU."""
+
+    def __init__(self, policy: QDecisionPolicy):
+        self.policy = policy
+        self._lib = policy._lib
+        self._h = policy._h
+
+    def enqueue_select(self, state, step: float, env_id: int) -> int:
+        state = _f32(state).reshape(-1)
+        t = C.c_int64()
+        check(self._lib.qp_enqueue_select(self._h, _ptr(state), state.size, float(step), int(env_id), C.byref(t)))
+        return int(t.value)
+
+    def enqueue_update(self, state, reward: float, next_state) -> None:
+        state = _f32(state).reshape(-1)
+        next_state = _f32(next_state).reshape(-1)
+        check(self._lib.qp_enqueue_update(self._h, _ptr(state), state.size, float(reward), _ptr(next_state), next_state.size))
+
+    def flush(self):
+        ns, nu = C.c_int64(), C.c_int64()
+        check(self._lib.qp_flush(self._h, C.byref(ns), C.byref(nu)))
+        if nu.value:
+            self.policy.iteration += 1
+        return int(ns.value), int(nu.value)
+
+    def action(self, ticket: int) -> Action:
+        a = C.c_int32()
+        check(self._lib.qp_take_action(self._h, int(ticket), C.byref(a)))
+        return Action(int(a.value))
+
+    @property
+    def pending(self) -> int:
+        return int(self._lib.qp_pending(self._h))
