@@ -3,6 +3,7 @@
 // Owns device memory, the stream and the launch sequence; contains no arithmetic of the hot path
 // (that is all in qp_kernels.cuh) and no CPU fallback: without a CUDA device qp_create fails.
 #include "qp_kernels.cuh"
+#include "qp_wide.cuh"
 #include "../../include/qpolicy.h"
 
 #include <dlfcn.h>
@@ -163,6 +164,10 @@ struct qp_handle {
     std::string snapshot_path;
     int64_t snapshot_every = 500;
     Geometry geo;
+    bool tile_ok = false;               // W1 fits in shared memory: per-tile kernels usable
+    bool wide = false;                  // GEMM-organised path (qp_wide.cuh)
+    DevBuf<float> wZ1, wdZ1, wdz2;
+    DevBuf<int32_t> wkn;
     bool allow_fused = true;            // qp_set_option("fused", 0) forces the three-kernel path
     DevBuf<long long> dbg;              // phase stamps of the persistent kernel (qp_debug_phase_clocks)
     bool want_dbg = false;
@@ -323,8 +328,54 @@ int enqueue_env_step(qp_handle* h, const TraceDev* trace, int32_t trace_step0, b
     return QP_OK;
 }
 
+// One env-step on the GEMM-organised path: G1, E1, E2, G2, apply (see qp_wide.cuh).
+int enqueue_env_step_wide(qp_handle* h, const TraceDev* trace, int32_t trace_step0) {
+    const Hyper& hp = h->hp;
+    const int64_t B = h->n_envs, Bpad = round_up(B, kTileEnvs);
+    const int tiles_m = (hp.D + kWgBM - 1) / kWgBM, tiles_n = (hp.H + kWgBN - 1) / kWgBN;
+    const int S = (int)std::max<int64_t>(1, std::min<int64_t>({(int64_t)32, B / 256 > 0 ? B / 256 : 1,
+                                                                (h->num_sms * 6 + tiles_m * tiles_n - 1) / (tiles_m * tiles_n)}));
+    const int colblocks = (hp.H + 255) / 256;
+    const int S2 = (int)std::max<int64_t>(1, std::min<int64_t>(B / 64 > 0 ? B / 64 : 1, (h->num_sms * 2) / colblocks));
+    QP_TRY(h->wZ1.ensure((size_t)2 * B * hp.H));
+    QP_TRY(h->wdZ1.ensure((size_t)B * hp.H));
+    QP_TRY(h->wdz2.ensure(B));
+    QP_TRY(h->wkn.ensure(B));
+    QP_TRY(h->xextra.ensure((size_t)Bpad * 2));
+    QP_TRY(h->part1.ensure((size_t)S * h->P1));
+    QP_TRY(h->part2.ensure((size_t)S2 * 3 * hp.H));
+    WideArgs a{};
+    a.hp = hp; a.params = h->params.p;
+    a.prices = h->prices.p; a.T = h->series_len; a.series_of_env = h->series_of_env.p; a.d_step = h->d_step.p;
+    a.budget = h->budget.p; a.shares = h->shares.p; a.share_value = h->share_value.p;
+    a.B0 = h->B0; a.N0 = h->N0; a.env_id_base = h->env_id_base;
+    a.B = B; a.Bpad = Bpad;
+    a.Z1 = h->wZ1.p; a.dZ1 = h->wdZ1.p; a.xextra = h->xextra.p; a.kn = h->wkn.p; a.dz2 = h->wdz2.p;
+    a.part1 = h->part1.p; a.part2 = h->part2.p; a.n_split = S; a.n_split2 = S2;
+    if (trace) a.trace = *trace;
+    a.trace_step0 = trace_step0;
+    wide_gemm_kernel<0><<<dim3((unsigned)((2 * B + kWgBM - 1) / kWgBM), tiles_n), kWgThreads, 0, h->stream>>>(a);
+    QP_CUDA(cudaGetLastError());
+    const int row_blocks = (int)std::min<int64_t>((B + 7) / 8, (int64_t)h->num_sms * 4);
+    wide_row_kernel<<<row_blocks, 256, (size_t)hp.H * 6 * sizeof(float), h->stream>>>(a);
+    QP_CUDA(cudaGetLastError());
+    wide_dw2_kernel<<<dim3(colblocks, S2), 256, 0, h->stream>>>(a);
+    QP_CUDA(cudaGetLastError());
+    wide_gemm_kernel<1><<<dim3(tiles_m, tiles_n, S), kWgThreads, 0, h->stream>>>(a);
+    QP_CUDA(cudaGetLastError());
+    h->launches += 4;
+    if (h->world > 1) {
+        QP_TRY(launch_apply(h, S, S2, 1, 0, 0));
+        QP_NCCL(g_nccl.AllReduce(h->grad.p, h->grad.p, (size_t)h->P, kNcclFloat32, kNcclSum, h->comm, h->stream));
+        QP_TRY(launch_apply(h, 0, 0, 0, 1, 1));
+    } else {
+        QP_TRY(launch_apply(h, S, S2, 1, 1, 1));
+    }
+    return QP_OK;
+}
+
 bool use_fused(const qp_handle* h) {
-    return h->allow_fused && h->coop_launch && h->world == 1 && h->geo.ep_ok &&
+    return !h->wide && h->allow_fused && h->coop_launch && h->world == 1 && h->geo.ep_ok &&
            h->n_envs <= (int64_t)kTileEnvs * h->num_sms;
 }
 
@@ -421,7 +472,17 @@ int qp_create(const qp_config* cfg, qp_handle** out) {
     h->max_smem = (int)prop.sharedMemPerBlockOptin;
 
     // launch geometry and shape limits of the register-tiled fp32 path
-    if (make_geometry(hp, h->max_smem, &h->geo) != QP_OK) return bail(QP_EUNSUPPORTED);
+    h->tile_ok = make_geometry(hp, h->max_smem, &h->geo) == QP_OK;
+    if (!h->tile_ok) {
+        // W1 does not fit in shared memory: organise the step around GEMMs (qp_wide.cuh)
+        if (hp.H % 128 != 0 || hp.H / 32 > kWideMaxColsPerLane)
+            return bail(fail(QP_EUNSUPPORTED, "shape outside both paths: the per-tile path needs W1 resident in shared "
+                                              "memory (hidden <= 240, (window+2)*hidden*4 + staging <= " +
+                                                  std::to_string(h->max_smem) + " bytes); the GEMM path needs hidden to be a "
+                                              "multiple of 128 and <= 2048"));
+        h->wide = true;
+        h->geo.ep_ok = false;
+    }
 #define QP_BAIL_CUDA(expr)                                                                        \
     do {                                                                                          \
         cudaError_t _e = (expr);                                                                  \
@@ -435,6 +496,7 @@ int qp_create(const qp_config* cfg, qp_handle** out) {
     QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_kernel<kEnvStep>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     QP_BAIL_CUDA(cudaFuncSetAttribute(episode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(wide_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     {
         int coop = 0;
         QP_BAIL_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->device));
@@ -470,6 +532,7 @@ int qp_destroy(qp_handle* h) {
     h->dz1.release(); h->xextra.release(); h->part1.release(); h->part2.release();
     h->m_states.release(); h->m_next.release(); h->m_rewards.release(); h->m_steps.release();
     h->m_q.release(); h->m_ids.release(); h->m_actions.release();
+    h->wZ1.release(); h->wdZ1.release(); h->wdz2.release(); h->wkn.release();
     h->prices.release(); h->series_of_env.release(); h->shares.release();
     h->budget.release(); h->share_value.release(); h->portfolio.release(); h->blocksum.release();
     h->d_step.release(); h->dbg.release();
@@ -518,6 +581,7 @@ int qp_select_action(qp_handle* h, const float* states, int64_t state_len, const
                                    ") and state(" + std::to_string(state_len) + ") size do not match");
     if (B < 0) return fail(QP_EINVAL, "B < 0");
     if (B == 0) return QP_OK;
+    if (h->wide) return fail(QP_EUNSUPPORTED, "message-level SelectionAction is not available on the GEMM path yet; use qp_env_*");
     QP_TRY(use_device(h));
     const int D = h->hp.D;
     QP_TRY(h->m_states.ensure((size_t)B * D));
@@ -549,6 +613,7 @@ int qp_update_q(qp_handle* h, const float* states, int64_t state_len, const floa
                                    std::to_string(next_state_len) + ") do not match");
     if (B < 0) return fail(QP_EINVAL, "B < 0");
     if (B == 0) return QP_OK;
+    if (h->wide) return fail(QP_EUNSUPPORTED, "message-level UpdateQ is not available on the GEMM path yet; use qp_env_*");
     QP_TRY(use_device(h));
     const int D = h->hp.D;
     int g1 = 0, g2 = 0;
@@ -626,7 +691,9 @@ int64_t qp_env_steps_done(const qp_handle* h) { return h ? h->steps_done : 0; }
 int qp_env_step_async(qp_handle* h, int32_t n_steps) {
     QP_TRY(check_env_steps(h, n_steps));
     QP_TRY(use_device(h));
-    if (use_fused(h)) {
+    if (h->wide) {
+        for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_wide(h, nullptr, 0));
+    } else if (use_fused(h)) {
         QP_TRY(enqueue_env_steps_fused(h, n_steps, nullptr, 0));
     } else {
         for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step(h, nullptr, 0, false));
@@ -652,6 +719,15 @@ int qp_env_step_timed(qp_handle* h, int32_t n_steps, float* ms_sum) {
     QP_TRY(check_env_steps(h, n_steps));
     QP_TRY(use_device(h));
     for (int k = 0; k < QP_N_KERNELS; ++k) ms_sum[k] = 0.0f;
+    if (h->wide) {        // five kernels per step; the whole batch of steps is timed into slot QP_KERNEL_STEP
+        QP_CUDA(cudaEventRecord(h->ev[0], h->stream));
+        for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_wide(h, nullptr, 0));
+        QP_CUDA(cudaEventRecord(h->ev[1], h->stream));
+        QP_CUDA(cudaEventSynchronize(h->ev[1]));
+        QP_CUDA(cudaEventElapsedTime(&ms_sum[0], h->ev[0], h->ev[1]));
+        h->steps_done += n_steps;
+        return QP_OK;
+    }
     if (use_fused(h)) {   // one persistent kernel: its whole duration goes to slot QP_KERNEL_STEP
         QP_CUDA(cudaEventRecord(h->ev[0], h->stream));
         QP_TRY(enqueue_env_steps_fused(h, n_steps, nullptr, 0));
@@ -711,7 +787,9 @@ int qp_env_step_trace(qp_handle* h, int32_t n_steps, const qp_trace* out) {
     QP_TR(tgt, target, target, 1) QP_TR(bud, budget, budget, 1)
 #undef QP_TR
     const int32_t step0 = (int32_t)h->steps_done;
-    if (use_fused(h)) {
+    if (h->wide) {
+        for (int32_t i = 0; i < n_steps && st == QP_OK; ++i) st = enqueue_env_step_wide(h, &t, step0);
+    } else if (use_fused(h)) {
         st = enqueue_env_steps_fused(h, n_steps, &t, step0);
     } else {
         for (int32_t i = 0; i < n_steps && st == QP_OK; ++i) st = enqueue_env_step(h, &t, step0, false);
@@ -1052,12 +1130,20 @@ int qp_set_option(qp_handle* h, const char* key, int64_t value) {
     if (!h || !key) return fail(QP_EINVAL, "null argument");
     if (std::strcmp(key, "phase_clocks") == 0) { h->want_dbg = value != 0; return QP_OK; }
     if (std::strcmp(key, "fused") == 0) { h->allow_fused = value != 0; return QP_OK; }
+    if (std::strcmp(key, "wide") == 0) {
+        if (value == 0 && !h->tile_ok) return fail(QP_EINVAL, "this shape only runs on the GEMM path");
+        if (value != 0 && (h->hp.H % 128 != 0 || h->hp.H / 32 > kWideMaxColsPerLane))
+            return fail(QP_EINVAL, "the GEMM path needs hidden to be a multiple of 128 and <= 2048");
+        h->wide = value != 0;
+        return QP_OK;
+    }
     return fail(QP_EINVAL, std::string("unknown option: ") + key);
 }
 
 int qp_get_option(qp_handle* h, const char* key, int64_t* value) {
     if (!h || !key || !value) return fail(QP_EINVAL, "null argument");
     if (std::strcmp(key, "fused") == 0) { *value = h->allow_fused ? 1 : 0; return QP_OK; }
+    if (std::strcmp(key, "wide") == 0) { *value = h->wide ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "fused_active") == 0) { *value = (h->has_env && use_fused(h)) ? 1 : 0; return QP_OK; }
     return fail(QP_EINVAL, std::string("unknown option: ") + key);
 }

@@ -77,7 +77,7 @@ def test_size_guards_raise_illegal_argument():
 def test_unsupported_shape_is_reported():
     q = q_mod()
     with pytest.raises(q.QPolicyError, match="shape"):
-        make_policy(O.Config(wn=513, hidden=2048))
+        make_policy(O.Config(wn=513, hidden=2052))     # fits neither the per-tile path nor the GEMM path
 
 
 # ------------------------------------------------------------------------------------------------
@@ -321,6 +321,70 @@ def test_persistent_kernel_matches_three_kernel_path():
     for x, y in zip(sa, sb):
         np.testing.assert_array_equal(x, y)
     assert np.abs(wa - wb).max() <= 40 * _tol.W_ATOL
+
+
+# ------------------------------------------------------------------------------------------------
+# GEMM-organised path (BASELINE.json configs[3]: hist 512 -> window 513, hidden 2048)
+# ------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("shape,n_envs", [((40, 256), 70), ((30, 128), 300), ((513, 2048), 130)])
+@pytest.mark.parametrize("bookkeeping", [O.REFERENCE, O.RLPY])
+def test_wide_path_teacher_forced(shape, n_envs, bookkeeping):
+    cfg = O.Config(wn=shape[0], hidden=shape[1], bookkeeping=bookkeeping, seed=13)
+    T = shape[0] + 40
+    n_series = max(1, n_envs // 3)
+    prices = O.gen_prices(cfg.seed, 0, n_series, T)
+    soe = (np.arange(n_envs) % n_series).astype(np.int32)
+    w0 = (O.gen_normal(2, 0, cfg.P) * (0.02 if shape[1] > 1000 else 0.05)).astype(np.float32)
+    o = O.Oracle(cfg, params=w0)
+    o.env_create(prices, soe, 1000.0, 2, env_id_base=77)
+    with make_policy(cfg) as pol:
+        pol.set_option("wide", 1)
+        assert pol.get_option("wide") == 1 and pol.get_option("fused_active") == 0
+        pol.env_create(prices, soe, 1000.0, 2, env_id_base=77)
+        for i in (0, 17, 38):
+            o.env["step"] = i
+            w, acc = o.params.copy(), o.acc.copy()
+            b, s, v = o.env["budget"].copy(), o.env["shares"].copy(), o.env["share_value"].copy()
+            pol.set_weights(w, acc)
+            pol.env_set_state(b, s, v, step=i)
+            x = states_of(cfg, prices, soe, i, b, s)
+            ref = o.env_step(1, trace=True, want_grad=True)[0]
+            tr = {k: a[0] for k, a in pol.env_step_trace(1).items()}
+            n_diff = compare_step(cfg, w, x, tr, ref, f"wide step {i}")
+            if n_diff == 0:
+                _tol.assert_grad_close(pol.last_grad(), ref["grad"], f"wide step {i} grad")
+                p, a = pol.get_weights()
+                assert np.abs(p - o.params).max() <= _tol.W_ATOL
+                bd, sd, vd = pol.env_state()
+                np.testing.assert_array_equal(bd, o.env["budget"])
+                np.testing.assert_array_equal(sd, o.env["shares"])
+
+
+def test_wide_path_matches_tile_path():
+    """A shape both paths can run (window 30, hidden 128): same episodes, 20 steps, free-running."""
+    cfg = O.Config(wn=30, hidden=128, bookkeeping=O.RLPY, lr=1e-4, seed=4)
+    n = 200
+    prices = O.gen_prices(cfg.seed, 0, 40, 120)
+    soe = (np.arange(n) % 40).astype(np.int32)
+    w = (O.gen_normal(6, 0, cfg.P) * 0.1).astype(np.float32)
+    res = []
+    for wide in (1, 0):
+        with make_policy(cfg, params=w, fused=0) as pol:
+            pol.set_option("wide", wide)
+            pol.env_create(prices, soe, 500.0, 1)
+            pol.env_set_state(step=40)
+            tr = pol.env_step_trace(20)
+            res.append((tr, pol.get_weights()[0], pol.env_state()))
+    (ta, wa, sa), (tb, wb, sb) = res
+    for k in ("action_sel", "action_eff", "explored", "shares", "budget", "reward", "k_next"):
+        np.testing.assert_array_equal(ta[k], tb[k], err_msg=k)
+    np.testing.assert_allclose(ta["q_s"], tb["q_s"], rtol=1e-4, atol=1e-3)
+    assert np.abs(wa - wb).max() <= 20 * _tol.W_ATOL
+    q = q_mod()
+    with make_policy(cfg, params=w) as pol:
+        pol.set_option("wide", 1)
+        with pytest.raises(q.QPolicyError, match="GEMM path"):
+            pol.select_action(np.zeros((1, cfg.D), np.float32), 0.0)
 
 
 # ------------------------------------------------------------------------------------------------
