@@ -36,8 +36,26 @@ WINDOW, HIDDEN, SERIES_LEN, BUDGET0, SHARES0, SEED = 201, 200, 1000, 1000.0, 0, 
 D = WINDOW + 2
 P = D * HIDDEN + 3 * HIDDEN
 FLOP_PER_ENV_STEP = 6 * D * HIDDEN + 16 * HIDDEN          # 246 800
+ROLLOUT = SERIES_LEN - WINDOW                             # env-steps per bench step
 METRIC = "env-steps/sec (act+TD update)"
 UNIT = "env-steps/s"
+WORKLOAD_NAME = "configs[1]"
+
+
+def set_workload(name: str, args):
+    """configs[1] (default): 4096 episodes, window 201, hidden 200.  'wide' = configs[3]: hist 512
+    (window 513), hidden 2048, batch 65 536 on one GPU; a bench step is then a 16-env-step slice."""
+    global WINDOW, HIDDEN, D, P, FLOP_PER_ENV_STEP, ROLLOUT, WORKLOAD_NAME
+    if name == "wide":
+        WINDOW, HIDDEN, WORKLOAD_NAME = 513, 2048, "configs[3] (wide policy)"
+        D = WINDOW + 2
+        P = D * HIDDEN + 3 * HIDDEN
+        FLOP_PER_ENV_STEP = 6 * D * HIDDEN + 16 * HIDDEN
+        ROLLOUT = args.rollout_steps or 16
+        if args.envs_per_gpu == 4096:
+            args.envs_per_gpu = 65536 // max(1, args.gpus)
+    elif args.rollout_steps:
+        ROLLOUT = args.rollout_steps
 
 
 def bytes_per_env_step(envs_per_gpu: int) -> float:
@@ -123,7 +141,7 @@ def run_reference(args):
     from oracle import oracle as O
     n_envs = args.envs_per_gpu * max(1, args.gpus)
     threads = O.max_threads()
-    cfg = O.Config()
+    cfg = O.Config(wn=WINDOW, hidden=HIDDEN)
     prices = O.gen_prices(SEED, 0, n_envs, SERIES_LEN)
     o = O.Oracle(cfg)
     o.env_create(prices, np.arange(n_envs, dtype=np.int32), BUDGET0, SHARES0)
@@ -144,6 +162,8 @@ def run_reference(args):
     dt = time.perf_counter() - t0
     value = args.steps * S * n_envs / dt
     sample = f"{S} env-steps x {n_envs} episodes per bench step (prefix of the {SERIES_LEN - WINDOW}-step episode)"
+    if S * (args.steps + args.warmup) + 1 > o.n_steps_total:
+        raise SystemExit("reference arm: episode too short for the requested steps")
     line = dict(
         impl="reference", metric=METRIC, value=value, unit=UNIT, n_gpus=args.gpus, steps=args.steps, warmup=args.warmup,
         ms_per_step=dt / args.steps * 1e3, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="fp32",
@@ -158,9 +178,9 @@ def run_reference(args):
 
 
 def workload_config(args, n_envs):
-    return dict(workload=f"configs[1]: {args.envs_per_gpu} parallel episodes per GPU, hist 200 (window {WINDOW}), "
+    return dict(workload=f"{WORKLOAD_NAME}: {args.envs_per_gpu} parallel episodes per GPU, hist {WINDOW - 1} (window {WINDOW}), "
                          f"hidden {HIDDEN}, fp32, {SERIES_LEN}-step random-walk series per episode, budget 1000",
-                episodes=n_envs, env_steps_per_bench_step=SERIES_LEN - WINDOW, series_len=SERIES_LEN,
+                episodes=n_envs, env_steps_per_bench_step=ROLLOUT, series_len=SERIES_LEN,
                 bookkeeping="REFERENCE", l2="flushed between bench steps (256 MiB write inside the timed region)",
                 parallelism=f"dp{max(1, args.gpus)} (episodes sharded, gradient all-reduce per env-step)" if args.gpus > 1
                 else "single GPU, persistent cooperative kernel")
@@ -188,7 +208,7 @@ def run_ours(args):
 
     n_local = args.envs_per_gpu
     n_total = n_local * world
-    n_env_steps = SERIES_LEN - WINDOW
+    n_env_steps = ROLLOUT
     # synthetic inputs: this rank's shard of the global series / episodes
     prices_np = O.gen_prices(SEED, rank * n_local, n_local, SERIES_LEN)
     soe_np = np.arange(n_local, dtype=np.int32)
@@ -196,7 +216,7 @@ def run_ours(args):
     soe_pin = torch.from_numpy(soe_np).pin_memory()
     ports_pin = torch.empty(n_local, dtype=torch.float64).pin_memory()
 
-    pol = q.QDecisionPolicy(q.PolicyConfig(device=local, seed=SEED))
+    pol = q.QDecisionPolicy(q.PolicyConfig(window=WINDOW, hidden=HIDDEN, device=local, seed=SEED))
     if world > 1:
         pol.dist_init(dist, rank, world)
     stream = torch.cuda.ExternalStream(pol.stream, device=torch.device("cuda", local))
@@ -216,7 +236,12 @@ def run_ours(args):
     def e2e_pass():
         with torch.cuda.stream(stream):
             flush.zero_()
-        pol.train(prices_pin.numpy(), soe_pin.numpy(), BUDGET0, SHARES0, env_id_base=rank * n_local)
+        if n_env_steps == SERIES_LEN - WINDOW:
+            pol.train(prices_pin.numpy(), soe_pin.numpy(), BUDGET0, SHARES0, env_id_base=rank * n_local)
+        else:   # a slice of the episode: the same three calls qp_train makes, stopped early
+            pol.env_create(prices_pin.numpy(), soe_pin.numpy(), BUDGET0, SHARES0, env_id_base=rank * n_local)
+            pol.env_step(n_env_steps, sync=False)
+            pol.portfolios()
 
     pol.env_create(prices_np, soe_np, BUDGET0, SHARES0, env_id_base=rank * n_local)
 
@@ -254,8 +279,9 @@ def run_ours(args):
     # ---- roofline of the dominant kernel, measured live with CUDA events on the launching stream
     peaks = measured_peaks()
     fp32_peak = pol.measure_fp32_peak()
-    n_prof = 200
+    n_prof = 200 if HIDDEN <= 256 else 8
     fused = bool(pol.get_option("fused_active"))
+    wide = bool(pol.get_option("wide"))
 
     def split_path_us():
         pol.env_reset()
@@ -263,7 +289,22 @@ def run_ours(args):
         kms = pol.env_step_timed(n_prof)
         return (kms / n_prof * 1e3).tolist()
 
-    if fused:
+    if wide:
+        pol.env_reset()
+        pol.env_step(2)
+        ep_us = float(pol.env_step_timed(n_prof)[0]) / n_prof * 1e3
+        dur = ep_us * 1e-6
+        step_flops = float(FLOP_PER_ENV_STEP) * n_local
+        step_bytes = bytes_per_env_step(n_local) * n_local
+        roofline = dict(
+            bound="hbm", kernel="GEMM-organised step (G1, E1, E2, G2, apply)", achieved=step_bytes / dur / 1e9,
+            peak=peaks["hbm_gbs"], unit="GB/s", frac=step_bytes / dur / 1e9 / peaks["hbm_gbs"], traffic=None,
+            peak_source=peaks["source"] + " (burst copy)", avg_launch_us=ep_us, us_per_env_step=ep_us,
+            binding=dict(bound="fp32-fma", achieved=step_flops / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
+                         frac=step_flops / dur / 1e12 / fp32_peak if fp32_peak else None,
+                         peak_source="measured live (qp_measure_fp32_peak, dependency-free FFMA)"),
+            bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP)
+    elif fused:
         # one persistent kernel runs every env-step of a launch: its duration / steps is the step time
         pol.env_reset()
         pol.env_step(20)
@@ -321,7 +362,7 @@ def run_ours(args):
     )
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
-        cfg = O.Config()
+        cfg = O.Config(wn=WINDOW, hidden=HIDDEN)
         n_s = args.cpu_sample_steps
         o = O.Oracle(cfg)
         o.env_create(prices_np, soe_np, BUDGET0, SHARES0)
@@ -351,7 +392,10 @@ def main():
     ap.add_argument("--envs-per-gpu", type=int, default=4096)
     ap.add_argument("--cpu-sample-steps", type=int, default=30)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--workload", default="config2", choices=["config2", "wide"])
+    ap.add_argument("--rollout-steps", type=int, default=0, help="env-steps per bench step (default: the whole episode)")
     args = ap.parse_args()
+    set_workload(args.workload, args)
     if args.impl == "reference":
         return run_reference(args)
     return run_ours(args)

@@ -127,6 +127,11 @@ int qp_sync(qp_handle* h);
  * Read-only: "fused_active" = 1 if the next qp_env_step would take the persistent kernel. */
 int qp_set_option(qp_handle* h, const char* key, int64_t value);
 int qp_get_option(qp_handle* h, const char* key, int64_t* value);
+/* Test hook for the tcgen05 tensor-core GEMM of the GEMM-organised path, on its own:
+ * C[M,N] = A[M,K] · B[N,K]^T with host buffers; passes = 3 (3xTF32, fp32-grade) or 1 (plain TF32);
+ * K must be a multiple of 32*splits.  ms_out (may be NULL) receives the device time of one launch. */
+int qp_debug_tc_gemm(int32_t device, int64_t M, int64_t N, int64_t K, const float* A, const float* B, float* C,
+                     int32_t passes, int32_t splits, float* ms_out);
 /* Tuning aid: with option "phase_clocks" = 1 the persistent kernel's CTA 0 stamps clock64() at 8
  * phase boundaries of every env-step of a launch; this copies the [n_steps x 8] stamps of the last
  * launch to out. */

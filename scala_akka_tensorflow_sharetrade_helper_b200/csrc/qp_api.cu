@@ -4,6 +4,7 @@
 // (that is all in qp_kernels.cuh) and no CPU fallback: without a CUDA device qp_create fails.
 #include "qp_kernels.cuh"
 #include "qp_wide.cuh"
+#include "qp_tc.cuh"
 #include "../../include/qpolicy.h"
 
 #include <dlfcn.h>
@@ -1115,6 +1116,110 @@ int qp_parse_prices(const char* text, size_t len, float* out, int64_t capacity, 
         for (const auto& kv : by_date) out[i++] = (float)kv.second;   // sorted by date; .toFloat (TrainerChildActor.scala:66)
     }
     return QP_OK;
+}
+
+// ---- tcgen05 GEMM plumbing ------------------------------------------------------------------------
+namespace {
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// The library links only the static runtime; the one driver call it needs is looked up at run time.
+int get_encode_tiled(EncodeTiledFn* out) {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        QP_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+        if (!p || q != cudaDriverEntryPointSuccess) return fail(QP_ECUDA, "cuTensorMapEncodeTiled is not available in this driver");
+        fn = (EncodeTiledFn)p;
+    }
+    *out = fn;
+    return QP_OK;
+}
+
+// 2-D fp32 tensor [outer][inner] with row pitch `pitch_bytes`, boxes of 128 rows x 32 elements
+// (128 B), 128-byte swizzle — the layout the K-major UMMA descriptor in qp_tc.cuh expects.
+int make_tmap(CUtensorMap* m, const float* base, uint64_t inner, uint64_t outer, uint64_t pitch_bytes) {
+    EncodeTiledFn enc = nullptr;
+    QP_TRY(get_encode_tiled(&enc));
+    const cuuint64_t dims[2] = {inner, outer};
+    const cuuint64_t strides[1] = {pitch_bytes};
+    const cuuint32_t box[2] = {kTcBK, kTcBM};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(QP_ECUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+    return QP_OK;
+}
+
+int launch_tc_gemm(cudaStream_t st, const CUtensorMap& a_hi, const CUtensorMap& a_lo, const CUtensorMap& b_hi,
+                   const CUtensorMap& b_lo, const TcGemmArgs& g, int tiles_m, int tiles_n, int splits) {
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    QP_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        QP_CUDA(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmemBytes));
+        attr_set[dev] = true;
+    }
+    tc_gemm_kernel<<<dim3(tiles_m, tiles_n, splits), 256, kTcSmemBytes, st>>>(a_hi, a_lo, b_hi, b_lo, g);
+    QP_CUDA(cudaGetLastError());
+    return QP_OK;
+}
+}  // namespace
+
+// Test hook for the tensor-core GEMM alone: C[M,N] = A[M,K] · B[N,K]^T with host buffers.
+int qp_debug_tc_gemm(int32_t device, int64_t M, int64_t N, int64_t K, const float* A, const float* B, float* C,
+                     int32_t passes, int32_t splits, float* ms_out) {
+    if (!A || !B || !C) return fail(QP_EINVAL, "null argument");
+    if (M < 1 || N < 1 || K < 32 || splits < 1 || K % (32 * splits) != 0 || (passes != 1 && passes != 3))
+        return fail(QP_EINVAL, "need K a multiple of 32*splits and passes in {1, 3}");
+    QP_CUDA(cudaSetDevice(device));
+    DevBuf<float> dA, dAh, dAl, dB, dBh, dBl, dC;
+    const int tiles_m = (int)((M + kTcBM - 1) / kTcBM), tiles_n = (int)((N + kTcBN - 1) / kTcBN);
+    QP_TRY(dA.ensure(M * K)); QP_TRY(dAh.ensure(M * K)); QP_TRY(dAl.ensure(M * K));
+    QP_TRY(dB.ensure(N * K)); QP_TRY(dBh.ensure(N * K)); QP_TRY(dBl.ensure(N * K));
+    QP_TRY(dC.ensure((size_t)splits * M * N));
+    auto rel = [&]() { dA.release(); dAh.release(); dAl.release(); dB.release(); dBh.release(); dBl.release(); dC.release(); };
+    int st = QP_OK;
+    auto run = [&]() -> int {
+        QP_CUDA(cudaMemcpy(dA.p, A, M * K * sizeof(float), cudaMemcpyHostToDevice));
+        QP_CUDA(cudaMemcpy(dB.p, B, N * K * sizeof(float), cudaMemcpyHostToDevice));
+        tc_split_kernel<<<(unsigned)((M * K + 255) / 256), 256>>>(dA.p, dAh.p, dAl.p, M * K);
+        tc_split_kernel<<<(unsigned)((N * K + 255) / 256), 256>>>(dB.p, dBh.p, dBl.p, N * K);
+        QP_CUDA(cudaGetLastError());
+        CUtensorMap ta_hi, ta_lo, tb_hi, tb_lo;
+        QP_TRY(make_tmap(&ta_hi, dAh.p, K, M, K * sizeof(float)));
+        QP_TRY(make_tmap(&ta_lo, dAl.p, K, M, K * sizeof(float)));
+        QP_TRY(make_tmap(&tb_hi, dBh.p, K, N, K * sizeof(float)));
+        QP_TRY(make_tmap(&tb_lo, dBl.p, K, N, K * sizeof(float)));
+        TcGemmArgs g{};
+        g.nkb = (int)(K / 32 / splits); g.passes = passes;
+        g.C = dC.p; g.ldc = N; g.c_split_stride = M * N; g.m_valid = (int)M; g.n_valid = (int)N;
+        cudaEvent_t e0, e1;
+        QP_CUDA(cudaEventCreate(&e0)); QP_CUDA(cudaEventCreate(&e1));
+        QP_TRY(launch_tc_gemm(nullptr, ta_hi, ta_lo, tb_hi, tb_lo, g, tiles_m, tiles_n, splits));   // warm-up
+        QP_CUDA(cudaEventRecord(e0));
+        QP_TRY(launch_tc_gemm(nullptr, ta_hi, ta_lo, tb_hi, tb_lo, g, tiles_m, tiles_n, splits));
+        QP_CUDA(cudaEventRecord(e1));
+        QP_CUDA(cudaDeviceSynchronize());
+        float ms = 0.f;
+        QP_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+        if (ms_out) *ms_out = ms;
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
+        std::vector<float> part((size_t)splits * M * N);
+        QP_CUDA(cudaMemcpy(part.data(), dC.p, part.size() * sizeof(float), cudaMemcpyDeviceToHost));
+        for (int64_t i = 0; i < M * N; ++i) {
+            float s = 0.f;
+            for (int z = 0; z < splits; ++z) s += part[(size_t)z * M * N + i];
+            C[i] = s;
+        }
+        return QP_OK;
+    };
+    st = run();
+    rel();
+    return st;
 }
 
 int qp_debug_phase_clocks(qp_handle* h, int32_t n_steps, int64_t* out) {
