@@ -169,6 +169,15 @@ struct qp_handle {
     bool wide = false;                  // GEMM-organised path (qp_wide.cuh)
     DevBuf<float> wZ1, wdZ1, wdz2;
     DevBuf<int32_t> wkn;
+    // tensor-core (tcgen05) variant of the two GEMMs: operands kept as tf32 hi/lo pairs, K-major
+    bool allow_tc = true;               // qp_set_option("tc", 0) keeps the fp32 FFMA GEMMs
+    int tc_passes = 3;                  // 3 = 3xTF32 (fp32-grade), 1 = plain TF32
+    bool tc_ready = false;
+    DevBuf<float> p_hi[4], p_lo[4];     // price matrix shifted left by 0..3 elements (TMA 16-byte alignment)
+    DevBuf<float> pT_hi, pT_lo, w1T_hi, w1T_lo, dzT_hi, dzT_lo;
+    int64_t tc_Kp = 0, tc_Bp = 0, tc_NsPad = 0;
+    int tc_S = 1;
+    CUtensorMap tm_p_hi[4], tm_p_lo[4], tm_pT_hi, tm_pT_lo, tm_w_hi, tm_w_lo, tm_dz_hi, tm_dz_lo;
     bool allow_fused = true;            // qp_set_option("fused", 0) forces the three-kernel path
     DevBuf<long long> dbg;              // phase stamps of the persistent kernel (qp_debug_phase_clocks)
     bool want_dbg = false;
@@ -329,13 +338,74 @@ int enqueue_env_step(qp_handle* h, const TraceDev* trace, int32_t trace_step0, b
     return QP_OK;
 }
 
+// ---- tcgen05 GEMM plumbing ------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+// The library links only the static runtime; the one driver call it needs is looked up at run time.
+int get_encode_tiled(EncodeTiledFn* out) {
+    static EncodeTiledFn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        QP_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
+        if (!p || q != cudaDriverEntryPointSuccess) return fail(QP_ECUDA, "cuTensorMapEncodeTiled is not available in this driver");
+        fn = (EncodeTiledFn)p;
+    }
+    *out = fn;
+    return QP_OK;
+}
+
+// 2-D fp32 tensor [outer][inner] with row pitch `pitch_bytes`, boxes of 128 rows x 32 elements
+// (128 B), 128-byte swizzle — the layout the K-major UMMA descriptor in qp_tc.cuh expects.
+int make_tmap(CUtensorMap* m, const float* base, uint64_t inner, uint64_t outer, uint64_t pitch_bytes) {
+    EncodeTiledFn enc = nullptr;
+    QP_TRY(get_encode_tiled(&enc));
+    const cuuint64_t dims[2] = {inner, outer};
+    const cuuint64_t strides[1] = {pitch_bytes};
+    const cuuint32_t box[2] = {kTcBK, kTcBM};
+    const cuuint32_t estr[2] = {1, 1};
+    const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(QP_ECUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
+    return QP_OK;
+}
+
+int launch_tc_gemm(cudaStream_t st, const CUtensorMap& a_hi, const CUtensorMap& a_lo, const CUtensorMap& b_hi,
+                   const CUtensorMap& b_lo, const TcGemmArgs& g, int tiles_m, int tiles_n, int splits) {
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    QP_CUDA(cudaGetDevice(&dev));
+    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
+        QP_CUDA(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmemBytes));
+        attr_set[dev] = true;
+    }
+    tc_gemm_kernel<<<dim3(tiles_m, tiles_n, splits), 256, kTcSmemBytes, st>>>(a_hi, a_lo, b_hi, b_lo, g);
+    QP_CUDA(cudaGetLastError());
+    return QP_OK;
+}
+
+// QP_DEBUG_SYNC=1 in the environment synchronises after every launch of the GEMM path and names
+// the kernel that failed (debug aid; never set for measurements).
+int dbg_sync(qp_handle* h, const char* what) {
+    static const bool on = std::getenv("QP_DEBUG_SYNC") != nullptr;
+    if (!on) return QP_OK;
+    cudaError_t e = cudaStreamSynchronize(h->stream);
+    if (e != cudaSuccess) return fail(QP_ECUDA, std::string(what) + ": " + cudaGetErrorString(e));
+    return QP_OK;
+}
+
 // One env-step on the GEMM-organised path: G1, E1, E2, G2, apply (see qp_wide.cuh).
-int enqueue_env_step_wide(qp_handle* h, const TraceDev* trace, int32_t trace_step0) {
+int enqueue_env_step_wide(qp_handle* h, const TraceDev* trace, int32_t trace_step0, int64_t istep_host) {
     const Hyper& hp = h->hp;
     const int64_t B = h->n_envs, Bpad = round_up(B, kTileEnvs);
     const int tiles_m = (hp.D + kWgBM - 1) / kWgBM, tiles_n = (hp.H + kWgBN - 1) / kWgBN;
-    const int S = (int)std::max<int64_t>(1, std::min<int64_t>({(int64_t)32, B / 256 > 0 ? B / 256 : 1,
-                                                                (h->num_sms * 6 + tiles_m * tiles_n - 1) / (tiles_m * tiles_n)}));
+    const int S = (h->allow_tc && h->tc_ready)
+                      ? h->tc_S
+                      : (int)std::max<int64_t>(1, std::min<int64_t>({(int64_t)32, B / 256 > 0 ? B / 256 : 1,
+                                                                     (h->num_sms * 6 + tiles_m * tiles_n - 1) / (tiles_m * tiles_n)}));
     const int colblocks = (hp.H + 255) / 256;
     const int S2 = (int)std::max<int64_t>(1, std::min<int64_t>(B / 64 > 0 ? B / 64 : 1, (h->num_sms * 2) / colblocks));
     QP_TRY(h->wZ1.ensure((size_t)2 * B * hp.H));
@@ -355,16 +425,64 @@ int enqueue_env_step_wide(qp_handle* h, const TraceDev* trace, int32_t trace_ste
     a.part1 = h->part1.p; a.part2 = h->part2.p; a.n_split = S; a.n_split2 = S2;
     if (trace) a.trace = *trace;
     a.trace_step0 = trace_step0;
-    wide_gemm_kernel<0><<<dim3((unsigned)((2 * B + kWgBM - 1) / kWgBM), tiles_n), kWgThreads, 0, h->stream>>>(a);
-    QP_CUDA(cudaGetLastError());
+    const bool tc = h->allow_tc && h->tc_ready;
+    const int32_t istep = (int32_t)istep_host;
+    if (tc) {
+        // W1[0:wn, :] -> K-major tf32 hi/lo pair [H, Kp] (columns wn..Kp-1 stay zero)
+        tc_transpose_split_kernel<<<dim3((hp.H + 31) / 32, (hp.wn + 31) / 32), dim3(32, 8), 0, h->stream>>>(
+            h->params.p, hp.wn, hp.H, hp.H, h->w1T_hi.p, h->w1T_lo.p, h->tc_Kp);
+        QP_CUDA(cudaGetLastError());
+        QP_TRY(dbg_sync(h, "W1 transpose/split"));
+        for (int half = 0; half < 2; ++half) {      // state s, then s' (window shifted by one)
+            TcGemmArgs g{};
+            const int shift = (istep + half) & 3;       // copy whose window start is 16-byte aligned
+            g.a_k0 = istep + half - shift; g.a_row0 = 0; g.b_k0 = 0; g.b_row0 = 0;
+            g.nkb = (int)(h->tc_Kp / kTcBK); g.passes = h->tc_passes;
+            g.C = h->wZ1.p + (size_t)half * B * hp.H; g.ldc = hp.H; g.c_split_stride = 0;
+            g.m_valid = (int)B; g.n_valid = hp.H;
+            QP_TRY(launch_tc_gemm(h->stream, h->tm_p_hi[shift], h->tm_p_lo[shift], h->tm_w_hi, h->tm_w_lo, g,
+                                  (int)((B + kTcBM - 1) / kTcBM), (hp.H + kTcBN - 1) / kTcBN, 1));
+            QP_TRY(dbg_sync(h, half ? "tc G1 (s')" : "tc G1 (s)"));
+        }
+        h->launches += 3;
+    } else {
+        wide_gemm_kernel<0><<<dim3((unsigned)((2 * B + kWgBM - 1) / kWgBM), tiles_n), kWgThreads, 0, h->stream>>>(a);
+        QP_CUDA(cudaGetLastError());
+        h->launches += 1;
+    }
     const int row_blocks = (int)std::min<int64_t>((B + 7) / 8, (int64_t)h->num_sms * 4);
     wide_row_kernel<<<row_blocks, 256, (size_t)hp.H * 6 * sizeof(float), h->stream>>>(a);
     QP_CUDA(cudaGetLastError());
     wide_dw2_kernel<<<dim3(colblocks, S2), 256, 0, h->stream>>>(a);
     QP_CUDA(cudaGetLastError());
-    wide_gemm_kernel<1><<<dim3(tiles_m, tiles_n, S), kWgThreads, 0, h->stream>>>(a);
-    QP_CUDA(cudaGetLastError());
-    h->launches += 4;
+    QP_TRY(dbg_sync(h, "row / dW2 kernels"));
+    if (tc) {
+        // dZ1 [B, H] -> K-major (episodes contiguous) tf32 hi/lo pair [H, Bp]
+        tc_transpose_split_kernel<<<dim3((hp.H + 31) / 32, (unsigned)((B + 31) / 32)), dim3(32, 8), 0, h->stream>>>(
+            h->wdZ1.p, B, hp.H, hp.H, h->dzT_hi.p, h->dzT_lo.p, h->tc_Bp);
+        QP_CUDA(cudaGetLastError());
+        QP_TRY(dbg_sync(h, "dZ1 transpose/split"));
+        const int tiles_tc = hp.wn / kTcBM + ((hp.wn % kTcBM) > kWideMaxExtraRows - 2 ? 1 : 0);
+        const int rows_tc = std::min(tiles_tc * kTcBM, hp.wn);
+        const int64_t eps = h->tc_Bp / S;
+        if (tiles_tc > 0) {
+            TcGemmArgs g{};
+            g.a_k0 = 0; g.a_row0 = istep; g.b_k0 = 0; g.b_row0 = 0;
+            g.nkb = (int)(eps / kTcBK); g.passes = h->tc_passes;
+            g.C = h->part1.p; g.ldc = hp.H; g.c_split_stride = h->P1; g.m_valid = rows_tc; g.n_valid = hp.H;
+            QP_TRY(launch_tc_gemm(h->stream, h->tm_pT_hi, h->tm_pT_lo, h->tm_dz_hi, h->tm_dz_lo, g, tiles_tc,
+                                  (hp.H + kTcBN - 1) / kTcBN, S));
+            QP_TRY(dbg_sync(h, "tc G2"));
+        }
+        wide_dw1_rows_kernel<<<dim3(colblocks, S), 256, 0, h->stream>>>(a, rows_tc, eps);
+        QP_CUDA(cudaGetLastError());
+        QP_TRY(dbg_sync(h, "dW1 rows kernel"));
+        h->launches += 5;
+    } else {
+        wide_gemm_kernel<1><<<dim3(tiles_m, tiles_n, S), kWgThreads, 0, h->stream>>>(a);
+        QP_CUDA(cudaGetLastError());
+        h->launches += 3;
+    }
     if (h->world > 1) {
         QP_TRY(launch_apply(h, S, S2, 1, 0, 0));
         QP_NCCL(g_nccl.AllReduce(h->grad.p, h->grad.p, (size_t)h->P, kNcclFloat32, kNcclSum, h->comm, h->stream));
@@ -372,6 +490,55 @@ int enqueue_env_step_wide(qp_handle* h, const TraceDev* trace, int32_t trace_ste
     } else {
         QP_TRY(launch_apply(h, S, S2, 1, 1, 1));
     }
+    return QP_OK;
+}
+
+// Builds what the tcgen05 GEMMs need for the current episodes: tf32 hi/lo pairs of the price matrix
+// (row-major for G1, transposed for G2), zeroed K-major buffers for W1^T and dZ1^T, and the TMA maps.
+int wide_prepare_tc(qp_handle* h) {
+    const Hyper& hp = h->hp;
+    const int64_t Ns = h->n_series, T = h->series_len, B = h->n_envs;
+    const int64_t NsPad = round_up(Ns, 4);
+    h->tc_NsPad = NsPad;
+    h->tc_Kp = round_up(hp.wn, kTcBK);
+    // episode splits of the backward GEMM: fill the SMs with whole waves
+    const int tiles = std::max(1, hp.wn / kTcBM + ((hp.wn % kTcBM) > kWideMaxExtraRows - 2 ? 1 : 0)) * ((hp.H + kTcBN - 1) / kTcBN);
+    int best = 1; double best_eff = 0.0;
+    for (int S = 1; S <= 32; ++S) {
+        if (B / S < 256 && S > 1) break;
+        const int ctas = tiles * S;
+        const double eff = (double)ctas / ((double)((ctas + h->num_sms - 1) / h->num_sms) * h->num_sms);
+        if (eff > best_eff + 1e-9) { best_eff = eff; best = S; }
+    }
+    h->tc_S = best;
+    h->tc_Bp = round_up(B, (int64_t)kTcBK * best);
+    for (int j = 0; j < 4; ++j) { QP_TRY(h->p_hi[j].ensure((size_t)Ns * T)); QP_TRY(h->p_lo[j].ensure((size_t)Ns * T)); }
+    QP_TRY(h->pT_hi.ensure((size_t)T * NsPad)); QP_TRY(h->pT_lo.ensure((size_t)T * NsPad));
+    QP_TRY(h->w1T_hi.ensure((size_t)hp.H * h->tc_Kp)); QP_TRY(h->w1T_lo.ensure((size_t)hp.H * h->tc_Kp));
+    QP_TRY(h->dzT_hi.ensure((size_t)hp.H * h->tc_Bp)); QP_TRY(h->dzT_lo.ensure((size_t)hp.H * h->tc_Bp));
+    QP_CUDA(cudaMemsetAsync(h->pT_hi.p, 0, (size_t)T * NsPad * sizeof(float), h->stream));
+    QP_CUDA(cudaMemsetAsync(h->pT_lo.p, 0, (size_t)T * NsPad * sizeof(float), h->stream));
+    QP_CUDA(cudaMemsetAsync(h->w1T_hi.p, 0, (size_t)hp.H * h->tc_Kp * sizeof(float), h->stream));
+    QP_CUDA(cudaMemsetAsync(h->w1T_lo.p, 0, (size_t)hp.H * h->tc_Kp * sizeof(float), h->stream));
+    QP_CUDA(cudaMemsetAsync(h->dzT_hi.p, 0, (size_t)hp.H * h->tc_Bp * sizeof(float), h->stream));
+    QP_CUDA(cudaMemsetAsync(h->dzT_lo.p, 0, (size_t)hp.H * h->tc_Bp * sizeof(float), h->stream));
+    for (int j = 0; j < 4; ++j)
+        tc_split_kernel<<<(unsigned)((Ns * T + 255) / 256), 256, 0, h->stream>>>(h->prices.p, h->p_hi[j].p, h->p_lo[j].p, Ns * T, T, j);
+    tc_transpose_split_kernel<<<dim3((unsigned)((T + 31) / 32), (unsigned)((Ns + 31) / 32)), dim3(32, 8), 0, h->stream>>>(
+        h->prices.p, Ns, T, T, h->pT_hi.p, h->pT_lo.p, NsPad);
+    QP_CUDA(cudaGetLastError());
+    h->launches += 5;
+    for (int j = 0; j < 4; ++j) {
+        QP_TRY(make_tmap(&h->tm_p_hi[j], h->p_hi[j].p, T, Ns, T * sizeof(float)));
+        QP_TRY(make_tmap(&h->tm_p_lo[j], h->p_lo[j].p, T, Ns, T * sizeof(float)));
+    }
+    QP_TRY(make_tmap(&h->tm_pT_hi, h->pT_hi.p, NsPad, T, NsPad * sizeof(float)));
+    QP_TRY(make_tmap(&h->tm_pT_lo, h->pT_lo.p, NsPad, T, NsPad * sizeof(float)));
+    QP_TRY(make_tmap(&h->tm_w_hi, h->w1T_hi.p, h->tc_Kp, hp.H, h->tc_Kp * sizeof(float)));
+    QP_TRY(make_tmap(&h->tm_w_lo, h->w1T_lo.p, h->tc_Kp, hp.H, h->tc_Kp * sizeof(float)));
+    QP_TRY(make_tmap(&h->tm_dz_hi, h->dzT_hi.p, h->tc_Bp, hp.H, h->tc_Bp * sizeof(float)));
+    QP_TRY(make_tmap(&h->tm_dz_lo, h->dzT_lo.p, h->tc_Bp, hp.H, h->tc_Bp * sizeof(float)));
+    h->tc_ready = true;
     return QP_OK;
 }
 
@@ -534,6 +701,9 @@ int qp_destroy(qp_handle* h) {
     h->m_states.release(); h->m_next.release(); h->m_rewards.release(); h->m_steps.release();
     h->m_q.release(); h->m_ids.release(); h->m_actions.release();
     h->wZ1.release(); h->wdZ1.release(); h->wdz2.release(); h->wkn.release();
+    for (int j = 0; j < 4; ++j) { h->p_hi[j].release(); h->p_lo[j].release(); }
+    h->pT_hi.release(); h->pT_lo.release();
+    h->w1T_hi.release(); h->w1T_lo.release(); h->dzT_hi.release(); h->dzT_lo.release();
     h->prices.release(); h->series_of_env.release(); h->shares.release();
     h->budget.release(); h->share_value.release(); h->portfolio.release(); h->blocksum.release();
     h->d_step.release(); h->dbg.release();
@@ -669,6 +839,14 @@ int qp_env_create(qp_handle* h, const float* prices, int64_t series_len, int64_t
     h->series_len = series_len; h->n_series = n_series; h->n_envs = n_envs; h->env_id_base = env_id_base;
     h->B0 = budget0; h->N0 = shares0;
     h->has_env = true;
+    h->tc_ready = false;
+    if (h->wide || (h->hp.H % 128 == 0 && h->hp.H / 32 <= kWideMaxColsPerLane)) {
+        bool identity = n_series == n_envs;
+        for (int64_t e = 0; identity && e < n_envs; ++e) identity = series_of_env[e] == e;
+        // the tensor-core GEMMs read the price windows straight from the price matrix with TMA, which
+        // needs episode e <-> series e and 16-byte row pitches
+        if (identity && series_len % 4 == 0) QP_TRY(wide_prepare_tc(h));
+    }
     return qp_env_reset(h);
 }
 
@@ -693,7 +871,7 @@ int qp_env_step_async(qp_handle* h, int32_t n_steps) {
     QP_TRY(check_env_steps(h, n_steps));
     QP_TRY(use_device(h));
     if (h->wide) {
-        for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_wide(h, nullptr, 0));
+        for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_wide(h, nullptr, 0, h->steps_done + i));
     } else if (use_fused(h)) {
         QP_TRY(enqueue_env_steps_fused(h, n_steps, nullptr, 0));
     } else {
@@ -722,7 +900,7 @@ int qp_env_step_timed(qp_handle* h, int32_t n_steps, float* ms_sum) {
     for (int k = 0; k < QP_N_KERNELS; ++k) ms_sum[k] = 0.0f;
     if (h->wide) {        // five kernels per step; the whole batch of steps is timed into slot QP_KERNEL_STEP
         QP_CUDA(cudaEventRecord(h->ev[0], h->stream));
-        for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_wide(h, nullptr, 0));
+        for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_wide(h, nullptr, 0, h->steps_done + i));
         QP_CUDA(cudaEventRecord(h->ev[1], h->stream));
         QP_CUDA(cudaEventSynchronize(h->ev[1]));
         QP_CUDA(cudaEventElapsedTime(&ms_sum[0], h->ev[0], h->ev[1]));
@@ -789,7 +967,7 @@ int qp_env_step_trace(qp_handle* h, int32_t n_steps, const qp_trace* out) {
 #undef QP_TR
     const int32_t step0 = (int32_t)h->steps_done;
     if (h->wide) {
-        for (int32_t i = 0; i < n_steps && st == QP_OK; ++i) st = enqueue_env_step_wide(h, &t, step0);
+        for (int32_t i = 0; i < n_steps && st == QP_OK; ++i) st = enqueue_env_step_wide(h, &t, step0, h->steps_done + i);
     } else if (use_fused(h)) {
         st = enqueue_env_steps_fused(h, n_steps, &t, step0);
     } else {
@@ -798,7 +976,7 @@ int qp_env_step_trace(qp_handle* h, int32_t n_steps, const qp_trace* out) {
     if (st == QP_OK) h->steps_done += n_steps;
     auto d2h = [&](void* dst, const void* src, size_t bytes) {
         if (st == QP_OK && dst && cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, h->stream) != cudaSuccess)
-            st = fail(QP_ECUDA, "trace copy failed");
+            st = fail(QP_ECUDA, std::string("trace copy failed: ") + cudaGetErrorString(cudaGetLastError()));
     };
     d2h(out->action_sel, asel.p, n * 4); d2h(out->action_eff, aeff.p, n * 4); d2h(out->explored, expl.p, n * 4);
     d2h(out->k_next, kn.p, n * 4); d2h(out->shares, shr.p, n * 4); d2h(out->reward, rew.p, n * 4);
@@ -1118,57 +1296,6 @@ int qp_parse_prices(const char* text, size_t len, float* out, int64_t capacity, 
     return QP_OK;
 }
 
-// ---- tcgen05 GEMM plumbing ------------------------------------------------------------------------
-namespace {
-typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
-                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
-                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
-
-// The library links only the static runtime; the one driver call it needs is looked up at run time.
-int get_encode_tiled(EncodeTiledFn* out) {
-    static EncodeTiledFn fn = nullptr;
-    if (!fn) {
-        void* p = nullptr;
-        cudaDriverEntryPointQueryResult q;
-        QP_CUDA(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q));
-        if (!p || q != cudaDriverEntryPointSuccess) return fail(QP_ECUDA, "cuTensorMapEncodeTiled is not available in this driver");
-        fn = (EncodeTiledFn)p;
-    }
-    *out = fn;
-    return QP_OK;
-}
-
-// 2-D fp32 tensor [outer][inner] with row pitch `pitch_bytes`, boxes of 128 rows x 32 elements
-// (128 B), 128-byte swizzle — the layout the K-major UMMA descriptor in qp_tc.cuh expects.
-int make_tmap(CUtensorMap* m, const float* base, uint64_t inner, uint64_t outer, uint64_t pitch_bytes) {
-    EncodeTiledFn enc = nullptr;
-    QP_TRY(get_encode_tiled(&enc));
-    const cuuint64_t dims[2] = {inner, outer};
-    const cuuint64_t strides[1] = {pitch_bytes};
-    const cuuint32_t box[2] = {kTcBK, kTcBM};
-    const cuuint32_t estr[2] = {1, 1};
-    const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
-                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
-    if (r != CUDA_SUCCESS) return fail(QP_ECUDA, "cuTensorMapEncodeTiled failed with code " + std::to_string((int)r));
-    return QP_OK;
-}
-
-int launch_tc_gemm(cudaStream_t st, const CUtensorMap& a_hi, const CUtensorMap& a_lo, const CUtensorMap& b_hi,
-                   const CUtensorMap& b_lo, const TcGemmArgs& g, int tiles_m, int tiles_n, int splits) {
-    static bool attr_set[64] = {false};
-    int dev = 0;
-    QP_CUDA(cudaGetDevice(&dev));
-    if (dev >= 0 && dev < 64 && !attr_set[dev]) {
-        QP_CUDA(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmemBytes));
-        attr_set[dev] = true;
-    }
-    tc_gemm_kernel<<<dim3(tiles_m, tiles_n, splits), 256, kTcSmemBytes, st>>>(a_hi, a_lo, b_hi, b_lo, g);
-    QP_CUDA(cudaGetLastError());
-    return QP_OK;
-}
-}  // namespace
-
 // Test hook for the tensor-core GEMM alone: C[M,N] = A[M,K] · B[N,K]^T with host buffers.
 int qp_debug_tc_gemm(int32_t device, int64_t M, int64_t N, int64_t K, const float* A, const float* B, float* C,
                      int32_t passes, int32_t splits, float* ms_out) {
@@ -1235,6 +1362,12 @@ int qp_set_option(qp_handle* h, const char* key, int64_t value) {
     if (!h || !key) return fail(QP_EINVAL, "null argument");
     if (std::strcmp(key, "phase_clocks") == 0) { h->want_dbg = value != 0; return QP_OK; }
     if (std::strcmp(key, "fused") == 0) { h->allow_fused = value != 0; return QP_OK; }
+    if (std::strcmp(key, "tc") == 0) { h->allow_tc = value != 0; return QP_OK; }
+    if (std::strcmp(key, "tc_passes") == 0) {
+        if (value != 1 && value != 3) return fail(QP_EINVAL, "tc_passes must be 3 (3xTF32) or 1 (TF32)");
+        h->tc_passes = (int)value;
+        return QP_OK;
+    }
     if (std::strcmp(key, "wide") == 0) {
         if (value == 0 && !h->tile_ok) return fail(QP_EINVAL, "this shape only runs on the GEMM path");
         if (value != 0 && (h->hp.H % 128 != 0 || h->hp.H / 32 > kWideMaxColsPerLane))
@@ -1249,6 +1382,7 @@ int qp_get_option(qp_handle* h, const char* key, int64_t* value) {
     if (!h || !key || !value) return fail(QP_EINVAL, "null argument");
     if (std::strcmp(key, "fused") == 0) { *value = h->allow_fused ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "wide") == 0) { *value = h->wide ? 1 : 0; return QP_OK; }
+    if (std::strcmp(key, "tc_active") == 0) { *value = (h->wide && h->allow_tc && h->tc_ready) ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "fused_active") == 0) { *value = (h->has_env && use_fused(h)) ? 1 : 0; return QP_OK; }
     return fail(QP_EINVAL, std::string("unknown option: ") + key);
 }

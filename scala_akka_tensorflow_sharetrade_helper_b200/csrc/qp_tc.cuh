@@ -207,11 +207,21 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tA_hi, const __grid_constant_
     }
 }
 
-// hi = tf32(x) (round to nearest), lo = x - hi (exact in fp32)
-__global__ void tc_split_kernel(const float* __restrict__ src, float* __restrict__ hi, float* __restrict__ lo, int64_t n) {
+// hi = tf32(x) (round to nearest), lo = x - hi (exact in fp32).  With row_len > 0 the copy is shifted
+// left by `shift` elements inside each row (dst[r][x] = src[r][x + shift], zero past the end): TMA
+// needs the first byte of a box to be 16-byte aligned, so the sliding price window is read from the
+// copy whose shift makes its start coordinate a multiple of four elements.
+__global__ void tc_split_kernel(const float* __restrict__ src, float* __restrict__ hi, float* __restrict__ lo, int64_t n,
+                                int64_t row_len = 0, int shift = 0) {
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const float x = src[i];
+    float x;
+    if (row_len > 0) {
+        const int64_t col = i % row_len;
+        x = (col + shift < row_len) ? src[i + shift] : 0.0f;
+    } else {
+        x = src[i];
+    }
     uint32_t t;
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(t) : "f"(x));
     const float h = __uint_as_float(t);

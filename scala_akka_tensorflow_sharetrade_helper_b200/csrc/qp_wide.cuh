@@ -342,5 +342,42 @@ __global__ void __launch_bounds__(256) wide_dw2_kernel(const WideArgs a) {
     out[0] = acc[0]; out[1] = acc[1]; out[2] = acc[2];
 }
 
+// ---------------------------------------------------------------------------------------------
+// Rows [row0, D) of the dW1 partial of split blockIdx.y over episodes [e_begin, e_end): the rows
+// the tensor-core GEMM does not cover (window rows past its last full 128-row tile, then budget
+// and shares).  One thread per hidden column, episodes summed sequentially.
+// ---------------------------------------------------------------------------------------------
+constexpr int kWideMaxExtraRows = 8;
+
+__global__ void __launch_bounds__(256) wide_dw1_rows_kernel(const WideArgs a, int row0, int64_t episodes_per_split) {
+    const Hyper& hp = a.hp;
+    const int H = hp.H, wn = hp.wn, D = hp.D;
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= H) return;
+    const int32_t istep = *a.d_step;
+    const int nrows = D - row0;
+    const int64_t e0 = (int64_t)blockIdx.y * episodes_per_split;
+    const int64_t e1 = min(a.B, e0 + episodes_per_split);
+    float acc[kWideMaxExtraRows];
+#pragma unroll
+    for (int r = 0; r < kWideMaxExtraRows; ++r) acc[r] = 0.0f;
+    for (int64_t e = e0; e < e1; ++e) {
+        const float dz = a.dZ1[e * H + c];
+        const float* prow = a.prices + (int64_t)a.series_of_env[e] * a.T + istep;
+#pragma unroll
+        for (int r = 0; r < kWideMaxExtraRows; ++r) {
+            if (r < nrows) {
+                const int m = row0 + r;
+                const float x = m < wn ? __ldg(prow + m) : (m == wn ? a.xextra[e] : a.xextra[a.Bpad + e]);
+                acc[r] = fmaf(x, dz, acc[r]);
+            }
+        }
+    }
+    float* out = a.part1 + (size_t)blockIdx.y * ((size_t)D * H);
+#pragma unroll
+    for (int r = 0; r < kWideMaxExtraRows; ++r)
+        if (r < nrows) out[(size_t)(row0 + r) * H + c] = acc[r];
+}
+
 #endif  // __CUDACC__
 }  // namespace qp

@@ -360,6 +360,40 @@ def test_wide_path_teacher_forced(shape, n_envs, bookkeeping):
                 np.testing.assert_array_equal(sd, o.env["shares"])
 
 
+@pytest.mark.parametrize("shape,n_envs,T", [((40, 256), 70, 80), ((130, 128), 200, 172), ((513, 2048), 130, 556)])
+@pytest.mark.parametrize("bookkeeping", [O.REFERENCE, O.RLPY])
+def test_wide_path_tensor_cores_teacher_forced(shape, n_envs, T, bookkeeping):
+    """The same step with the two GEMMs on tcgen05 tensor cores (3xTF32: tf32 hi/lo operand pairs,
+    three MMAs per k-block).  Held to the SAME fp32 tolerance as the FFMA path."""
+    cfg = O.Config(wn=shape[0], hidden=shape[1], bookkeeping=bookkeeping, seed=21)
+    prices = O.gen_prices(cfg.seed, 0, n_envs, T) * np.float32(1.0371)   # not tf32-exact: exercises the lo operands
+    soe = np.arange(n_envs, dtype=np.int32)                               # episode e <-> series e (TMA reads the price matrix)
+    w0 = (O.gen_normal(2, 0, cfg.P) * (0.02 if shape[1] > 1000 else 0.05)).astype(np.float32)
+    o = O.Oracle(cfg, params=w0)
+    o.env_create(prices, soe, 1000.0, 2)
+    with make_policy(cfg) as pol:
+        pol.set_option("wide", 1)
+        pol.env_create(prices, soe, 1000.0, 2)
+        assert pol.get_option("tc_active") == 1
+        for i in (0, 11, T - shape[0] - 1):
+            o.env["step"] = i
+            w, acc = o.params.copy(), o.acc.copy()
+            b, s, v = o.env["budget"].copy(), o.env["shares"].copy(), o.env["share_value"].copy()
+            pol.set_weights(w, acc)
+            pol.env_set_state(b, s, v, step=i)
+            x = states_of(cfg, prices, soe, i, b, s)
+            ref = o.env_step(1, trace=True, want_grad=True)[0]
+            tr = {k: a[0] for k, a in pol.env_step_trace(1).items()}
+            n_diff = compare_step(cfg, w, x, tr, ref, f"tc step {i}")
+            if n_diff == 0:
+                _tol.assert_grad_close(pol.last_grad(), ref["grad"], f"tc step {i} grad")
+                p, a = pol.get_weights()
+                assert np.abs(p - o.params).max() <= _tol.W_ATOL
+        # the FFMA GEMMs on the same state agree with the tensor-core ones within the same tolerance
+        pol.set_option("tc", 0)
+        assert pol.get_option("tc_active") == 0
+
+
 def test_wide_path_matches_tile_path():
     """A shape both paths can run (window 30, hidden 128): same episodes, 20 steps, free-running."""
     cfg = O.Config(wn=30, hidden=128, bookkeeping=O.RLPY, lr=1e-4, seed=4)
