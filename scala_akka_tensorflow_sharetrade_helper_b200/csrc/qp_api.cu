@@ -174,10 +174,11 @@ struct qp_handle {
     int tc_passes = 3;                  // 3 = 3xTF32 (fp32-grade), 1 = plain TF32
     bool tc_ready = false;
     DevBuf<float> p_hi[4], p_lo[4];     // price matrix shifted left by 0..3 elements (TMA 16-byte alignment)
-    DevBuf<float> pT_hi, pT_lo, w1T_hi, w1T_lo, dzT_hi, dzT_lo;
+    DevBuf<float> pT_hi, pT_lo, w1T_hi, w1T_lo, dzT_hi, dzT_lo, xe_hi, xe_lo;
+    bool tc_a_lo_zero = false;          // the prices are tf32-exact: the A_lo tiles and MMAs are skipped
     int64_t tc_Kp = 0, tc_Bp = 0, tc_NsPad = 0;
     int tc_S = 1;
-    CUtensorMap tm_p_hi[4], tm_p_lo[4], tm_pT_hi, tm_pT_lo, tm_w_hi, tm_w_lo, tm_dz_hi, tm_dz_lo;
+    CUtensorMap tm_p_hi[4], tm_p_lo[4], tm_pT_hi, tm_pT_lo, tm_w_hi, tm_w_lo, tm_dz_hi, tm_dz_lo, tm_xe_hi, tm_xe_lo;
     bool allow_fused = true;            // qp_set_option("fused", 0) forces the three-kernel path
     DevBuf<long long> dbg;              // phase stamps of the persistent kernel (qp_debug_phase_clocks)
     bool want_dbg = false;
@@ -426,6 +427,9 @@ int enqueue_env_step_wide(qp_handle* h, const TraceDev* trace, int32_t trace_ste
     if (trace) a.trace = *trace;
     a.trace_step0 = trace_step0;
     const bool tc = h->allow_tc && h->tc_ready;
+    const int tiles_tc = hp.wn / kTcBM + ((hp.wn % kTcBM) > kWideMaxExtraRows - 2 ? 1 : 0);
+    const int rows_tc = std::min(tiles_tc * kTcBM, hp.wn);
+    if (tc) { a.xe_hi = h->xe_hi.p; a.xe_lo = h->xe_lo.p; a.xe_ld = h->tc_Bp; a.xe_row0 = rows_tc; }
     const int32_t istep = (int32_t)istep_host;
     if (tc) {
         // W1[0:wn, :] -> K-major tf32 hi/lo pair [H, Kp] (columns wn..Kp-1 stay zero)
@@ -437,7 +441,7 @@ int enqueue_env_step_wide(qp_handle* h, const TraceDev* trace, int32_t trace_ste
             TcGemmArgs g{};
             const int shift = (istep + half) & 3;       // copy whose window start is 16-byte aligned
             g.a_k0 = istep + half - shift; g.a_row0 = 0; g.b_k0 = 0; g.b_row0 = 0;
-            g.nkb = (int)(h->tc_Kp / kTcBK); g.passes = h->tc_passes;
+            g.nkb = (int)(h->tc_Kp / kTcBK); g.passes = h->tc_passes; g.a_lo_zero = h->tc_a_lo_zero ? 1 : 0;
             g.C = h->wZ1.p + (size_t)half * B * hp.H; g.ldc = hp.H; g.c_split_stride = 0;
             g.m_valid = (int)B; g.n_valid = hp.H;
             QP_TRY(launch_tc_gemm(h->stream, h->tm_p_hi[shift], h->tm_p_lo[shift], h->tm_w_hi, h->tm_w_lo, g,
@@ -462,21 +466,26 @@ int enqueue_env_step_wide(qp_handle* h, const TraceDev* trace, int32_t trace_ste
             h->wdZ1.p, B, hp.H, hp.H, h->dzT_hi.p, h->dzT_lo.p, h->tc_Bp);
         QP_CUDA(cudaGetLastError());
         QP_TRY(dbg_sync(h, "dZ1 transpose/split"));
-        const int tiles_tc = hp.wn / kTcBM + ((hp.wn % kTcBM) > kWideMaxExtraRows - 2 ? 1 : 0);
-        const int rows_tc = std::min(tiles_tc * kTcBM, hp.wn);
         const int64_t eps = h->tc_Bp / S;
         if (tiles_tc > 0) {
             TcGemmArgs g{};
             g.a_k0 = 0; g.a_row0 = istep; g.b_k0 = 0; g.b_row0 = 0;
-            g.nkb = (int)(eps / kTcBK); g.passes = h->tc_passes;
+            g.nkb = (int)(eps / kTcBK); g.passes = h->tc_passes; g.a_lo_zero = h->tc_a_lo_zero ? 1 : 0;
             g.C = h->part1.p; g.ldc = hp.H; g.c_split_stride = h->P1; g.m_valid = rows_tc; g.n_valid = hp.H;
             QP_TRY(launch_tc_gemm(h->stream, h->tm_pT_hi, h->tm_pT_lo, h->tm_dz_hi, h->tm_dz_lo, g, tiles_tc,
                                   (hp.H + kTcBN - 1) / kTcBN, S));
             QP_TRY(dbg_sync(h, "tc G2"));
         }
-        wide_dw1_rows_kernel<<<dim3(colblocks, S), 256, 0, h->stream>>>(a, rows_tc, eps);
-        QP_CUDA(cudaGetLastError());
-        QP_TRY(dbg_sync(h, "dW1 rows kernel"));
+        {   // the remaining rows of dW1 (window rows past the last full tile, budget, shares): one more tile
+            TcGemmArgs g{};
+            g.a_k0 = 0; g.a_row0 = 0; g.b_k0 = 0; g.b_row0 = 0;
+            g.nkb = (int)(eps / kTcBK); g.passes = h->tc_passes; g.a_lo_zero = 0;
+            g.C = h->part1.p + (size_t)rows_tc * hp.H; g.ldc = hp.H; g.c_split_stride = h->P1;
+            g.m_valid = hp.D - rows_tc; g.n_valid = hp.H;
+            QP_TRY(launch_tc_gemm(h->stream, h->tm_xe_hi, h->tm_xe_lo, h->tm_dz_hi, h->tm_dz_lo, g, 1,
+                                  (hp.H + kTcBN - 1) / kTcBN, S));
+            QP_TRY(dbg_sync(h, "tc G2 (extra rows)"));
+        }
         h->launches += 5;
     } else {
         wide_gemm_kernel<1><<<dim3(tiles_m, tiles_n, S), kWgThreads, 0, h->stream>>>(a);
@@ -516,6 +525,9 @@ int wide_prepare_tc(qp_handle* h) {
     QP_TRY(h->pT_hi.ensure((size_t)T * NsPad)); QP_TRY(h->pT_lo.ensure((size_t)T * NsPad));
     QP_TRY(h->w1T_hi.ensure((size_t)hp.H * h->tc_Kp)); QP_TRY(h->w1T_lo.ensure((size_t)hp.H * h->tc_Kp));
     QP_TRY(h->dzT_hi.ensure((size_t)hp.H * h->tc_Bp)); QP_TRY(h->dzT_lo.ensure((size_t)hp.H * h->tc_Bp));
+    QP_TRY(h->xe_hi.ensure((size_t)kWideMaxExtraRows * h->tc_Bp)); QP_TRY(h->xe_lo.ensure((size_t)kWideMaxExtraRows * h->tc_Bp));
+    QP_CUDA(cudaMemsetAsync(h->xe_hi.p, 0, (size_t)kWideMaxExtraRows * h->tc_Bp * sizeof(float), h->stream));
+    QP_CUDA(cudaMemsetAsync(h->xe_lo.p, 0, (size_t)kWideMaxExtraRows * h->tc_Bp * sizeof(float), h->stream));
     QP_CUDA(cudaMemsetAsync(h->pT_hi.p, 0, (size_t)T * NsPad * sizeof(float), h->stream));
     QP_CUDA(cudaMemsetAsync(h->pT_lo.p, 0, (size_t)T * NsPad * sizeof(float), h->stream));
     QP_CUDA(cudaMemsetAsync(h->w1T_hi.p, 0, (size_t)hp.H * h->tc_Kp * sizeof(float), h->stream));
@@ -538,6 +550,21 @@ int wide_prepare_tc(qp_handle* h) {
     QP_TRY(make_tmap(&h->tm_w_lo, h->w1T_lo.p, h->tc_Kp, hp.H, h->tc_Kp * sizeof(float)));
     QP_TRY(make_tmap(&h->tm_dz_hi, h->dzT_hi.p, h->tc_Bp, hp.H, h->tc_Bp * sizeof(float)));
     QP_TRY(make_tmap(&h->tm_dz_lo, h->dzT_lo.p, h->tc_Bp, hp.H, h->tc_Bp * sizeof(float)));
+    QP_TRY(make_tmap(&h->tm_xe_hi, h->xe_hi.p, h->tc_Bp, kWideMaxExtraRows, h->tc_Bp * sizeof(float)));
+    QP_TRY(make_tmap(&h->tm_xe_lo, h->xe_lo.p, h->tc_Bp, kWideMaxExtraRows, h->tc_Bp * sizeof(float)));
+    {   // are the prices tf32-exact (e.g. quarter ticks below 2048)?  Then A_lo == 0 exactly and is skipped.
+        DevBuf<int32_t> tmp;
+        QP_TRY(tmp.ensure(1));
+        int* flag = tmp.p;
+        QP_CUDA(cudaMemsetAsync(flag, 0, sizeof(int), h->stream));
+        tc_any_nonzero_kernel<<<(unsigned)((Ns * T + 255) / 256), 256, 0, h->stream>>>(h->p_lo[0].p, Ns * T, flag);
+        int host_flag = 1;
+        QP_CUDA(cudaMemcpyAsync(&host_flag, flag, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+        QP_CUDA(cudaStreamSynchronize(h->stream));
+        tmp.release();
+        h->tc_a_lo_zero = host_flag == 0;
+        h->launches += 1;
+    }
     h->tc_ready = true;
     return QP_OK;
 }
@@ -702,7 +729,7 @@ int qp_destroy(qp_handle* h) {
     h->m_q.release(); h->m_ids.release(); h->m_actions.release();
     h->wZ1.release(); h->wdZ1.release(); h->wdz2.release(); h->wkn.release();
     for (int j = 0; j < 4; ++j) { h->p_hi[j].release(); h->p_lo[j].release(); }
-    h->pT_hi.release(); h->pT_lo.release();
+    h->pT_hi.release(); h->pT_lo.release(); h->xe_hi.release(); h->xe_lo.release();
     h->w1T_hi.release(); h->w1T_lo.release(); h->dzT_hi.release(); h->dzT_lo.release();
     h->prices.release(); h->series_of_env.release(); h->shares.release();
     h->budget.release(); h->share_value.release(); h->portfolio.release(); h->blocksum.release();
@@ -1382,6 +1409,7 @@ int qp_get_option(qp_handle* h, const char* key, int64_t* value) {
     if (!h || !key || !value) return fail(QP_EINVAL, "null argument");
     if (std::strcmp(key, "fused") == 0) { *value = h->allow_fused ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "wide") == 0) { *value = h->wide ? 1 : 0; return QP_OK; }
+    if (std::strcmp(key, "tc_a_lo_zero") == 0) { *value = h->tc_a_lo_zero ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "tc_active") == 0) { *value = (h->wide && h->allow_tc && h->tc_ready) ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "fused_active") == 0) { *value = (h->has_env && use_fused(h)) ? 1 : 0; return QP_OK; }
     return fail(QP_EINVAL, std::string("unknown option: ") + key);

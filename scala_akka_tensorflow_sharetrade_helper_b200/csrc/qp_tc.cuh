@@ -34,6 +34,7 @@ struct TcGemmArgs {
     int b_k0, b_row0;
     int nkb;                // k-blocks of 32 per split (blockIdx.z)
     int passes;             // 3 = 3xTF32, 1 = TF32
+    int a_lo_zero;          // 1: every A_lo element is exactly 0 (A is tf32-exact): its tile and MMA are skipped
     float* C; int64_t ldc; int64_t c_split_stride;
     int m_valid, n_valid;   // rows / columns of C that exist
 };
@@ -131,6 +132,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tA_hi, const __grid_constant_
     const int a_row = g.a_row0 + blockIdx.x * kTcBM;
     const int b_row = g.b_row0 + blockIdx.y * kTcBN;
     const bool three = g.passes == 3;
+    const bool use_a_lo = three && !g.a_lo_zero;
 
     if (warp == 0 && lane == 0) {
         // ---------------- TMA producer ----------------
@@ -139,14 +141,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tA_hi, const __grid_constant_
             const uint32_t ph = (uint32_t)(kb / kTcStages) & 1u;
             tc_wait(empty + s, ph ^ 1u);
             uint8_t* st = base + (size_t)s * kTcStageBytes;
-            mbar_arrive_expect_tx(full + s, (uint32_t)(three ? 4 : 2) * kTcTileBytes);
+            mbar_arrive_expect_tx(full + s, (uint32_t)(three ? (use_a_lo ? 4 : 3) : 2) * kTcTileBytes);
             const int ak = g.a_k0 + kbase + kb * kTcBK, bk = g.b_k0 + kbase + kb * kTcBK;
             tma_load_2d(st, &tA_hi, ak, a_row, full + s);
             tma_load_2d(st + 2 * kTcTileBytes, &tB_hi, bk, b_row, full + s);
-            if (three) {
-                tma_load_2d(st + kTcTileBytes, &tA_lo, ak, a_row, full + s);
-                tma_load_2d(st + 3 * kTcTileBytes, &tB_lo, bk, b_row, full + s);
-            }
+            if (use_a_lo) tma_load_2d(st + kTcTileBytes, &tA_lo, ak, a_row, full + s);
+            if (three) tma_load_2d(st + 3 * kTcTileBytes, &tB_lo, bk, b_row, full + s);
         }
     } else if (warp == 1 && lane == 0) {
         // ---------------- MMA issuer ----------------
@@ -163,10 +163,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tA_hi, const __grid_constant_
             for (int k4 = 0; k4 < kTcBK / 8; ++k4) {
                 const uint64_t adv = (uint64_t)(k4 * 2);          // 8 tf32 = 32 B = 2 x 16 B along K
                 tc_mma_tf32(tmem_base, da_hi + adv, db_hi + adv, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
-                if (three) {
-                    tc_mma_tf32(tmem_base, da_lo + adv, db_hi + adv, idesc, 1u);
-                    tc_mma_tf32(tmem_base, da_hi + adv, db_lo + adv, idesc, 1u);
-                }
+                if (use_a_lo) tc_mma_tf32(tmem_base, da_lo + adv, db_hi + adv, idesc, 1u);
+                if (three) tc_mma_tf32(tmem_base, da_hi + adv, db_lo + adv, idesc, 1u);
             }
             tc_commit(empty + s);        // the stage is free once these MMAs have read it
         }
@@ -227,6 +225,12 @@ __global__ void tc_split_kernel(const float* __restrict__ src, float* __restrict
     const float h = __uint_as_float(t);
     hi[i] = h;
     lo[i] = x - h;
+}
+
+// flag[0] = 1 if any element is non-zero (used to learn whether a lo array is identically zero)
+__global__ void tc_any_nonzero_kernel(const float* __restrict__ x, int64_t n, int* flag) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n && x[i] != 0.0f) atomicOr(flag, 1);
 }
 
 // src [R, C] row-major  ->  hiT / loT [C, ldt] (transposed, K-major for the tensor core), zero padding

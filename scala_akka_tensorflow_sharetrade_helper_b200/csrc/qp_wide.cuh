@@ -16,6 +16,7 @@ namespace qp {
 
 constexpr int kWgBM = 128, kWgBN = 128, kWgBK = 16, kWgThreads = 256;
 constexpr int kWgAStride = kWgBM + 4;     // padded: the forward A tile is stored transposed
+constexpr int kWideMaxExtraRows = 8;      // rows of dW1 handled outside G2's 128-row tiles on the tensor-core path
 
 struct WideArgs {
     Hyper hp;
@@ -33,6 +34,9 @@ struct WideArgs {
     float* part2;         // [S2, 3H]
     int n_split;          // episode splits of G2
     int n_split2;         // episode splits of E2
+    // tensor-core variant: the rows of X^T the 128-row tiles of G2 do not cover (window rows from
+    // xe_row0 on, then budget, shares), as a K-major tf32 hi/lo matrix [kWideMaxExtraRows, xe_ld]
+    float* xe_hi; float* xe_lo; int64_t xe_ld; int xe_row0;
     TraceDev trace; int32_t trace_step0;
 };
 
@@ -188,15 +192,19 @@ __global__ void __launch_bounds__(256) wide_row_kernel(const WideArgs a) {
     const Hyper& hp = a.hp;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
     const int H = hp.H, wn = hp.wn, D = hp.D;
-    float* W2s = smem;                       // [H] float4
-    float* Wb = W2s + (size_t)H * 4;         // [H] budget row of W1
-    float* Ws = Wb + H;                      // [H] shares row of W1
+    // A lane owns columns c = 128 j + 4 lane + q (so that its global accesses are float4).  The three
+    // per-column tables are stored permuted, index p(c) = (4 j + q) * 32 + lane, so that for a fixed
+    // (j, q) the 32 lanes read consecutive words: no bank conflicts.
+    float* W2s = smem;                       // [H] float4 (w2[c][0..2], 0), permuted
+    float* Wb = W2s + (size_t)H * 4;         // [H] budget row of W1, permuted
+    float* Ws = Wb + H;                      // [H] shares row of W1, permuted
     const float* W1g = a.params;
     const float* W2g = a.params + (size_t)D * H;
-    for (int j = tid; j < H; j += blockDim.x) {
-        reinterpret_cast<float4*>(W2s)[j] = make_float4(W2g[j * 3], W2g[j * 3 + 1], W2g[j * 3 + 2], 0.f);
-        Wb[j] = W1g[(size_t)wn * H + j];
-        Ws[j] = W1g[(size_t)(wn + 1) * H + j];
+    for (int c = tid; c < H; c += blockDim.x) {
+        const int p = (((c >> 7) << 2) + (c & 3)) * 32 + ((c & 127) >> 2);
+        reinterpret_cast<float4*>(W2s)[p] = make_float4(W2g[c * 3], W2g[c * 3 + 1], W2g[c * 3 + 2], 0.f);
+        Wb[p] = W1g[(size_t)wn * H + c];
+        Ws[p] = W1g[(size_t)(wn + 1) * H + c];
     }
     __syncthreads();
     const int32_t istep = *a.d_step;
@@ -211,20 +219,27 @@ __global__ void __launch_bounds__(256) wide_row_kernel(const WideArgs a) {
         const float4* zs4 = reinterpret_cast<const float4*>(a.Z1 + e * H);
         const float4* zn4 = reinterpret_cast<const float4*>(a.Z1 + (a.B + e) * H);
 
+        // both Z1 rows of this episode are fetched up front (32 independent 16-byte loads per lane):
+        // the row of s' does not depend on the action, only its budget/shares terms do
+        float4 zsv[kWideMaxColsPerLane / 4], znv[kWideMaxColsPerLane / 4];
+#pragma unroll
+        for (int j = 0; j < kWideMaxColsPerLane / 4; ++j)
+            if (j < nchunk) { zsv[j] = __ldcs(zs4 + j * 32 + lane); znv[j] = __ldcs(zn4 + j * 32 + lane); }
+
         // hidden layer of s and its Q-values (QDecisionPolicyActor.scala:43, :47)
         float hs[kWideMaxColsPerLane];
         float pq[3] = {0.f, 0.f, 0.f};
 #pragma unroll
         for (int j = 0; j < kWideMaxColsPerLane / 4; ++j) {
             if (j < nchunk) {
-                const int c = j * 128 + lane * 4;
-                const float4 z = zs4[c >> 2];
+                const float4 z = zsv[j];
                 const float zz[4] = {z.x, z.y, z.z, z.w};
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    const float h = wide_hidden(zz[q], xb, xs, Wb[c + q], Ws[c + q], bias);
+                    const int p = (j * 4 + q) * 32 + lane;
+                    const float h = wide_hidden(zz[q], xb, xs, Wb[p], Ws[p], bias);
                     hs[j * 4 + q] = h;
-                    const float4 w2 = reinterpret_cast<const float4*>(W2s)[c + q];
+                    const float4 w2 = reinterpret_cast<const float4*>(W2s)[p];
                     pq[0] = fmaf(h, w2.x, pq[0]); pq[1] = fmaf(h, w2.y, pq[1]); pq[2] = fmaf(h, w2.z, pq[2]);
                 }
             }
@@ -263,13 +278,13 @@ __global__ void __launch_bounds__(256) wide_row_kernel(const WideArgs a) {
 #pragma unroll
         for (int j = 0; j < kWideMaxColsPerLane / 4; ++j) {
             if (j < nchunk) {
-                const int c = j * 128 + lane * 4;
-                const float4 z = zn4[c >> 2];
+                const float4 z = znv[j];
                 const float zz[4] = {z.x, z.y, z.z, z.w};
 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    const float h = wide_hidden(zz[q], xnb, xns, Wb[c + q], Ws[c + q], bias);
-                    const float4 w2 = reinterpret_cast<const float4*>(W2s)[c + q];
+                    const int p = (j * 4 + q) * 32 + lane;
+                    const float h = wide_hidden(zz[q], xnb, xns, Wb[p], Ws[p], bias);
+                    const float4 w2 = reinterpret_cast<const float4*>(W2s)[p];
                     pq[0] = fmaf(h, w2.x, pq[0]); pq[1] = fmaf(h, w2.y, pq[1]); pq[2] = fmaf(h, w2.z, pq[2]);
                 }
             }
@@ -292,10 +307,22 @@ __global__ void __launch_bounds__(256) wide_row_kernel(const WideArgs a) {
                 const int c = j * 128 + lane * 4;
                 float v[4];
 #pragma unroll
-                for (int q = 0; q < 4; ++q)
-                    v[q] = hs[j * 4 + q] > 0.0f ? __fmul_rn(dz2, W2s[(c + q) * 4 + kn]) : 0.0f;
+                for (int q = 0; q < 4; ++q) {
+                    const float4 w2 = reinterpret_cast<const float4*>(W2s)[(j * 4 + q) * 32 + lane];
+                    const float w2k = kn == 0 ? w2.x : (kn == 1 ? w2.y : w2.z);
+                    v[q] = hs[j * 4 + q] > 0.0f ? __fmul_rn(dz2, w2k) : 0.0f;
+                }
                 dz4[c >> 2] = make_float4(v[0], v[1], v[2], v[3]);
             }
+        }
+        if (a.xe_hi && lane < D - a.xe_row0) {
+            const int m = a.xe_row0 + lane;
+            const float x = m < wn ? __ldg(prow + m) : (m == wn ? xb : xs);
+            uint32_t t;
+            asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(t) : "f"(x));
+            const float hpart = __uint_as_float(t);
+            a.xe_hi[(int64_t)lane * a.xe_ld + e] = hpart;
+            a.xe_lo[(int64_t)lane * a.xe_ld + e] = x - hpart;
         }
         if (lane == 0) {
             a.xextra[e] = xb; a.xextra[a.Bpad + e] = xs;
@@ -340,43 +367,6 @@ __global__ void __launch_bounds__(256) wide_dw2_kernel(const WideArgs a) {
     }
     float* out = a.part2 + (size_t)blockIdx.y * (3 * H) + (size_t)c * 3;
     out[0] = acc[0]; out[1] = acc[1]; out[2] = acc[2];
-}
-
-// ---------------------------------------------------------------------------------------------
-// Rows [row0, D) of the dW1 partial of split blockIdx.y over episodes [e_begin, e_end): the rows
-// the tensor-core GEMM does not cover (window rows past its last full 128-row tile, then budget
-// and shares).  One thread per hidden column, episodes summed sequentially.
-// ---------------------------------------------------------------------------------------------
-constexpr int kWideMaxExtraRows = 8;
-
-__global__ void __launch_bounds__(256) wide_dw1_rows_kernel(const WideArgs a, int row0, int64_t episodes_per_split) {
-    const Hyper& hp = a.hp;
-    const int H = hp.H, wn = hp.wn, D = hp.D;
-    const int c = blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= H) return;
-    const int32_t istep = *a.d_step;
-    const int nrows = D - row0;
-    const int64_t e0 = (int64_t)blockIdx.y * episodes_per_split;
-    const int64_t e1 = min(a.B, e0 + episodes_per_split);
-    float acc[kWideMaxExtraRows];
-#pragma unroll
-    for (int r = 0; r < kWideMaxExtraRows; ++r) acc[r] = 0.0f;
-    for (int64_t e = e0; e < e1; ++e) {
-        const float dz = a.dZ1[e * H + c];
-        const float* prow = a.prices + (int64_t)a.series_of_env[e] * a.T + istep;
-#pragma unroll
-        for (int r = 0; r < kWideMaxExtraRows; ++r) {
-            if (r < nrows) {
-                const int m = row0 + r;
-                const float x = m < wn ? __ldg(prow + m) : (m == wn ? a.xextra[e] : a.xextra[a.Bpad + e]);
-                acc[r] = fmaf(x, dz, acc[r]);
-            }
-        }
-    }
-    float* out = a.part1 + (size_t)blockIdx.y * ((size_t)D * H);
-#pragma unroll
-    for (int r = 0; r < kWideMaxExtraRows; ++r)
-        if (r < nrows) out[(size_t)(row0 + r) * H + c] = acc[r];
 }
 
 #endif  // __CUDACC__
