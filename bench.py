@@ -296,14 +296,34 @@ def run_ours(args):
         dur = ep_us * 1e-6
         step_flops = float(FLOP_PER_ENV_STEP) * n_local
         step_bytes = bytes_per_env_step(n_local) * n_local
-        roofline = dict(
-            bound="hbm", kernel="GEMM-organised step (G1, E1, E2, G2, apply)", achieved=step_bytes / dur / 1e9,
-            peak=peaks["hbm_gbs"], unit="GB/s", frac=step_bytes / dur / 1e9 / peaks["hbm_gbs"], traffic=None,
-            peak_source=peaks["source"] + " (burst copy)", avg_launch_us=ep_us, us_per_env_step=ep_us,
-            binding=dict(bound="fp32-fma", achieved=step_flops / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
-                         frac=step_flops / dur / 1e12 / fp32_peak if fp32_peak else None,
-                         peak_source="measured live (qp_measure_fp32_peak, dependency-free FFMA)"),
-            bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP)
+        tc_on = bool(pol.get_option("tc_active"))
+        passes = 3
+        # TF32 tensor peak is not in MEASURED_PEAKS.json; it is half the measured bf16 figure by construction
+        tf32_peak = peaks["bf16_tflops"] / 2.0
+        if tc_on:
+            roofline = dict(
+                bound="tensor", kernel="tc_gemm_kernel (tcgen05 kind::tf32, 3xTF32) inside the GEMM-organised step",
+                achieved=step_flops / dur / 1e12, peak=tf32_peak / passes, unit="TFLOP/s",
+                frac=step_flops / dur / 1e12 / (tf32_peak / passes), traffic=None,
+                peak_source=peaks["source"] + " bf16 burst / 2 (tf32) / 3 (three MMAs per product for fp32-grade accuracy)",
+                us_per_env_step=ep_us, avg_launch_us=ep_us,
+                note="achieved counts algorithmic FLOPs of the whole step (GEMMs + row kernel + transposes); the GEMMs "
+                     "themselves are L2-bandwidth-bound at 128x128 tiles with fp32 hi/lo operands (DESIGN.md §4)",
+                hbm=dict(achieved=step_bytes / dur / 1e9, peak=peaks["hbm_gbs"], unit="GB/s",
+                         frac=step_bytes / dur / 1e9 / peaks["hbm_gbs"]),
+                fp32_equivalent=dict(achieved=step_flops / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
+                                     frac=step_flops / dur / 1e12 / fp32_peak if fp32_peak else None),
+                a_lo_zero=bool(pol.get_option("tc_a_lo_zero")),
+                bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP)
+        else:
+            roofline = dict(
+                bound="hbm", kernel="GEMM-organised step, fp32 FFMA GEMMs (G1, E1, E2, G2, apply)", achieved=step_bytes / dur / 1e9,
+                peak=peaks["hbm_gbs"], unit="GB/s", frac=step_bytes / dur / 1e9 / peaks["hbm_gbs"], traffic=None,
+                peak_source=peaks["source"] + " (burst copy)", avg_launch_us=ep_us, us_per_env_step=ep_us,
+                binding=dict(bound="fp32-fma", achieved=step_flops / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
+                             frac=step_flops / dur / 1e12 / fp32_peak if fp32_peak else None,
+                             peak_source="measured live (qp_measure_fp32_peak, dependency-free FFMA)"),
+                bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP)
     elif fused:
         # one persistent kernel runs every env-step of a launch: its duration / steps is the step time
         pol.env_reset()
@@ -329,6 +349,12 @@ def run_ours(args):
             bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP,
             three_kernel_path_us=dict(zip(names, split_us)),
         )
+        # DRAM traffic from the committed ncu --set full capture of a 30-step launch of this kernel
+        # (profiles/r1_v2_ncu_episode_kernel_summary.csv: 9.40 MB read + 4.91 MB written), per env-step;
+        # far below the algorithmic bytes because windows stay in shared memory and weights/partials in L2
+        if n_local == 4096 and HIDDEN == 200:
+            roofline["traffic"] = (9.397248e6 + 4.906752e6) / 30.0
+            roofline["traffic_note"] = "bytes per env-step of 4096 episodes, from profiles/r1_v2_ncu_episode_kernel_summary.csv"
     else:
         per_kernel_us = split_path_us()
         names = ["step_kernel", "dw1_kernel", "apply_kernel(+allreduce)" if world > 1 else "apply_kernel"]
@@ -362,17 +388,21 @@ def run_ours(args):
     )
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        # bounded sample (~10-30 s of one core): a prefix of the episodes of a subset of the workload,
+        # sized by FLOPs so that the wide workload does not take hours
         cfg = O.Config(wn=WINDOW, hidden=HIDDEN)
-        n_s = args.cpu_sample_steps
+        budget_flop = 3.0e10
+        n_s_envs = int(min(n_local, 4096))
+        n_s = int(max(1, min(args.cpu_sample_steps, budget_flop / (FLOP_PER_ENV_STEP * n_s_envs))))
         o = O.Oracle(cfg)
-        o.env_create(prices_np, soe_np, BUDGET0, SHARES0)
+        o.env_create(prices_np[:n_s_envs], soe_np[:n_s_envs], BUDGET0, SHARES0)
         t0 = time.perf_counter()
         o.env_step(n_s, mode=1)
         dt = time.perf_counter() - t0
         line["cpu_baseline"] = dict(
-            value=n_s * n_local / dt, unit=UNIT, cores=1, kind="port",
-            sample=f"first {n_s} env-steps of the same {n_local} episodes, sequential per-sample updates "
-                   f"(the reference's one-mailbox order), oracle/qp_oracle.c, {dt:.1f} s",
+            value=n_s * n_s_envs / dt, unit=UNIT, cores=1, kind="port",
+            sample=f"first {n_s} env-steps of the first {n_s_envs} episodes of the workload, sequential per-sample "
+                   f"updates (the reference's one-mailbox order), oracle/qp_oracle.c, {dt:.1f} s",
             host_cores_available=O.max_threads())
     pol.close()
     if rank == 0:

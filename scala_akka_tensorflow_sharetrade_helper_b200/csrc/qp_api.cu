@@ -383,7 +383,7 @@ int launch_tc_gemm(cudaStream_t st, const CUtensorMap& a_hi, const CUtensorMap& 
         QP_CUDA(cudaFuncSetAttribute(tc_gemm_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kTcSmemBytes));
         attr_set[dev] = true;
     }
-    tc_gemm_kernel<<<dim3(tiles_m, tiles_n, splits), 256, kTcSmemBytes, st>>>(a_hi, a_lo, b_hi, b_lo, g);
+    tc_gemm_kernel<<<dim3(tiles_n, tiles_m, splits), 256, kTcSmemBytes, st>>>(a_hi, a_lo, b_hi, b_lo, g);
     QP_CUDA(cudaGetLastError());
     return QP_OK;
 }

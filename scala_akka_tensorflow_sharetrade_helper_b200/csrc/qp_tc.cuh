@@ -128,9 +128,12 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tA_hi, const __grid_constant_
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
+    // N tiles vary fastest in launch order: the CTAs that share an A tile run back to back, so A is
+    // fetched from HBM once and the (small) B matrix stays L2-resident
+    const int m_tile = blockIdx.y, n_tile = blockIdx.x;
     const int kbase = blockIdx.z * g.nkb * kTcBK;
-    const int a_row = g.a_row0 + blockIdx.x * kTcBM;
-    const int b_row = g.b_row0 + blockIdx.y * kTcBN;
+    const int a_row = g.a_row0 + m_tile * kTcBM;
+    const int b_row = g.b_row0 + n_tile * kTcBN;
     const bool three = g.passes == 3;
     const bool use_a_lo = three && !g.a_lo_zero;
 
@@ -174,8 +177,8 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tA_hi, const __grid_constant_
         tc_wait(tmem_full, 0);
         tc_fence_after();
         const int q = warp & 3;                                     // TMEM lane quarter this warp may read
-        const int64_t m = (int64_t)blockIdx.x * kTcBM + q * 32 + lane;
-        float* crow = g.C + (size_t)blockIdx.z * g.c_split_stride + m * g.ldc + (int64_t)blockIdx.y * kTcBN;
+        const int64_t m = (int64_t)m_tile * kTcBM + q * 32 + lane;
+        float* crow = g.C + (size_t)blockIdx.z * g.c_split_stride + m * g.ldc + (int64_t)n_tile * kTcBN;
 #pragma unroll 1
         for (int c0 = 0; c0 < kTcBN; c0 += 16) {
             uint32_t r[16];
@@ -189,7 +192,7 @@ tc_gemm_kernel(const __grid_constant__ CUtensorMap tA_hi, const __grid_constant_
             if (m < g.m_valid) {
 #pragma unroll
                 for (int j = 0; j < 4; ++j) {
-                    const int n = blockIdx.y * kTcBN + c0 + 4 * j;
+                    const int n = n_tile * kTcBN + c0 + 4 * j;
                     if (n < g.n_valid)
                         *reinterpret_cast<float4*>(crow + c0 + 4 * j) =
                             make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
