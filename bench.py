@@ -183,7 +183,8 @@ def workload_config(args, n_envs):
                 episodes=n_envs, env_steps_per_bench_step=ROLLOUT, series_len=SERIES_LEN,
                 bookkeeping="REFERENCE", l2="flushed between bench steps (256 MiB write inside the timed region)",
                 parallelism=f"dp{max(1, args.gpus)} (episodes sharded, gradient all-reduce per env-step)" if args.gpus > 1
-                else "single GPU, persistent cooperative kernel")
+                else ("single GPU, GEMM-organised step (tcgen05 3xTF32 GEMMs)" if HIDDEN > 256
+                      else "single GPU, persistent cooperative kernel"))
 
 
 # =================================================================================================
