@@ -290,7 +290,24 @@ def run_ours(args):
         kms = pol.env_step_timed(n_prof)
         return (kms / n_prof * 1e3).tolist()
 
-    if wide:
+    fused_step = bool(pol.get_option("fused_step_active"))
+    if fused_step:
+        pol.env_reset()
+        pol.env_step(20)
+        ep_us = float(pol.env_step_timed(n_prof)[0]) / n_prof * 1e3
+        dur = ep_us * 1e-6
+        step_bytes = bytes_per_env_step(n_local) * n_local
+        step_flops = float(FLOP_PER_ENV_STEP) * n_local
+        roofline = dict(
+            bound="hbm", kernel="episode_kernel (one fused step) + sum + NCCL all-reduce + AdaGrad, per GPU",
+            achieved=step_bytes / dur / 1e9, peak=peaks["hbm_gbs"], unit="GB/s",
+            frac=step_bytes / dur / 1e9 / peaks["hbm_gbs"], traffic=None, peak_source=peaks["source"] + " (burst copy)",
+            us_per_env_step=ep_us, avg_launch_us=ep_us,
+            binding=dict(bound="fp32-fma", achieved=step_flops / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
+                         frac=step_flops / dur / 1e12 / fp32_peak if fp32_peak else None,
+                         peak_source="measured live (qp_measure_fp32_peak, dependency-free FFMA)"),
+            bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP)
+    elif wide:
         pol.env_reset()
         pol.env_step(2)
         ep_us = float(pol.env_step_timed(n_prof)[0]) / n_prof * 1e3

@@ -575,7 +575,8 @@ bool use_fused(const qp_handle* h) {
 }
 
 // n_steps env-steps of every episode in ONE cooperative launch of the persistent episode kernel.
-int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace, int32_t trace_step0) {
+int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace, int32_t trace_step0,
+                            bool apply_in_kernel = true, int32_t step_offset = 0) {
     if (n_steps <= 0) return QP_OK;
     const int64_t Bpad = round_up(h->n_envs, kTileEnvs);
     const int64_t n_tiles = Bpad / kTileEnvs;
@@ -591,7 +592,8 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
     s.B = h->n_envs; s.Bpad = Bpad; s.dw2_part = h->part2.p;
     if (trace) s.trace = *trace;
     s.trace_step0 = trace_step0;
-    ea.step0 = (int32_t)h->steps_done; ea.n_steps = n_steps;
+    ea.step0 = (int32_t)h->steps_done + step_offset; ea.n_steps = n_steps;
+    ea.apply_in_kernel = apply_in_kernel ? 1 : 0;
     ea.acc = h->acc.p; ea.grad = h->grad.p; ea.params_rw = h->params.p; ea.part1 = h->part1.p;
     ea.d_step_rw = h->d_step.p;
     ea.n_rt = h->geo.ep_n_rt; ea.n_ct = h->geo.ep_n_ct; ea.nwf = h->geo.step_warps;
@@ -604,6 +606,23 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
     QP_CUDA(cudaLaunchCooperativeKernel((const void*)episode_kernel, dim3(h->num_sms), dim3(h->geo.ep_threads),
                                         args, h->geo.smem_ep, h->stream));
     h->launches++;
+    return QP_OK;
+}
+
+// Several GPUs, episodes fit one tile per SM: each env-step is the persistent kernel's phase A as ONE
+// launch (forward, select, book-keeping and the dW1 contraction fused), then sum of partials,
+// all-reduce of the gradient, AdaGrad.
+bool use_fused_step(const qp_handle* h) {
+    return !h->wide && h->allow_fused && h->coop_launch && h->world > 1 && h->geo.ep_ok &&
+           h->n_envs <= (int64_t)kTileEnvs * h->num_sms;
+}
+
+int enqueue_env_step_fused_dist(qp_handle* h, const TraceDev* trace, int32_t trace_step0, int32_t step_offset) {
+    QP_TRY(enqueue_env_steps_fused(h, 1, trace, trace_step0, false, step_offset));
+    const int n_tiles = (int)(round_up(h->n_envs, kTileEnvs) / kTileEnvs);
+    QP_TRY(launch_apply(h, n_tiles, n_tiles, 1, 0, 0));
+    QP_NCCL(g_nccl.AllReduce(h->grad.p, h->grad.p, (size_t)h->P, kNcclFloat32, kNcclSum, h->comm, h->stream));
+    QP_TRY(launch_apply(h, 0, 0, 0, 1, 1));
     return QP_OK;
 }
 
@@ -901,6 +920,8 @@ int qp_env_step_async(qp_handle* h, int32_t n_steps) {
         for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_wide(h, nullptr, 0, h->steps_done + i));
     } else if (use_fused(h)) {
         QP_TRY(enqueue_env_steps_fused(h, n_steps, nullptr, 0));
+    } else if (use_fused_step(h)) {
+        for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_fused_dist(h, nullptr, 0, i));
     } else {
         for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step(h, nullptr, 0, false));
     }
@@ -928,6 +949,15 @@ int qp_env_step_timed(qp_handle* h, int32_t n_steps, float* ms_sum) {
     if (h->wide) {        // five kernels per step; the whole batch of steps is timed into slot QP_KERNEL_STEP
         QP_CUDA(cudaEventRecord(h->ev[0], h->stream));
         for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_wide(h, nullptr, 0, h->steps_done + i));
+        QP_CUDA(cudaEventRecord(h->ev[1], h->stream));
+        QP_CUDA(cudaEventSynchronize(h->ev[1]));
+        QP_CUDA(cudaEventElapsedTime(&ms_sum[0], h->ev[0], h->ev[1]));
+        h->steps_done += n_steps;
+        return QP_OK;
+    }
+    if (use_fused_step(h)) {   // fused step kernel + sum + all-reduce + AdaGrad per step, timed as a whole
+        QP_CUDA(cudaEventRecord(h->ev[0], h->stream));
+        for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_fused_dist(h, nullptr, 0, i));
         QP_CUDA(cudaEventRecord(h->ev[1], h->stream));
         QP_CUDA(cudaEventSynchronize(h->ev[1]));
         QP_CUDA(cudaEventElapsedTime(&ms_sum[0], h->ev[0], h->ev[1]));
@@ -997,6 +1027,8 @@ int qp_env_step_trace(qp_handle* h, int32_t n_steps, const qp_trace* out) {
         for (int32_t i = 0; i < n_steps && st == QP_OK; ++i) st = enqueue_env_step_wide(h, &t, step0, h->steps_done + i);
     } else if (use_fused(h)) {
         st = enqueue_env_steps_fused(h, n_steps, &t, step0);
+    } else if (use_fused_step(h)) {
+        for (int32_t i = 0; i < n_steps && st == QP_OK; ++i) st = enqueue_env_step_fused_dist(h, &t, step0, i);
     } else {
         for (int32_t i = 0; i < n_steps && st == QP_OK; ++i) st = enqueue_env_step(h, &t, step0, false);
     }
@@ -1412,6 +1444,7 @@ int qp_get_option(qp_handle* h, const char* key, int64_t* value) {
     if (std::strcmp(key, "tc_a_lo_zero") == 0) { *value = h->tc_a_lo_zero ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "tc_active") == 0) { *value = (h->wide && h->allow_tc && h->tc_ready) ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "fused_active") == 0) { *value = (h->has_env && use_fused(h)) ? 1 : 0; return QP_OK; }
+    if (std::strcmp(key, "fused_step_active") == 0) { *value = (h->has_env && use_fused_step(h)) ? 1 : 0; return QP_OK; }
     return fail(QP_EINVAL, std::string("unknown option: ") + key);
 }
 

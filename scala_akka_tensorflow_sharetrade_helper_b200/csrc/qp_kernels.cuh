@@ -93,6 +93,8 @@ struct EpisodeArgs {
     int n_rt, n_ct;                 // 16-row tiles, pairs of float4 column groups
     int nwf;                        // forward warps (one per 20 hidden columns)
     long long* dbg;                 // optional [n_steps][8] clock64 stamps of CTA 0 (phase timing aid)
+    int apply_in_kernel;            // 1: phase B (sum + AdaGrad) runs in the kernel; 0: exactly one env-step, the
+                                    // partials are left for apply_kernel (multi-GPU: an all-reduce sits in between)
 };
 
 struct ApplyArgs {
@@ -1058,6 +1060,7 @@ __global__ void __launch_bounds__(kEpMaxThreads, 1) episode_kernel(const Episode
         }
         __syncthreads();
         if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 3] = clock64();
+        if (!ea.apply_in_kernel) break;     // grid-uniform: single-step launch, the host continues with apply_kernel
         // ---- slide the window: row k <- row k + 1 (k < wn), row wn <- the new price
         if (has_tile) {
             constexpr int kMaxPer = 24;
@@ -1148,7 +1151,7 @@ __global__ void __launch_bounds__(kEpMaxThreads, 1) episode_kernel(const Episode
         a.shares[e] = shares;
         a.share_value[e] = share_value;
     }
-    if (blockIdx.x == 0 && tid == 0) *ea.d_step_rw = ea.step0 + ea.n_steps;
+    if (ea.apply_in_kernel && blockIdx.x == 0 && tid == 0) *ea.d_step_rw = ea.step0 + ea.n_steps;
 }
 
 // Measurement aid: dependency-free FFMA streams, to measure the fp32-FMA roof of this GPU (the
