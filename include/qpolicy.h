@@ -212,6 +212,16 @@ int qp_parse_prices(const char* text, size_t len, float* out, int64_t capacity, 
 int qp_dist_unique_id(void* out, size_t out_bytes);
 int qp_dist_init(qp_handle* h, const void* unique_id, int32_t rank, int32_t world);
 int qp_dist_nccl_version(int32_t* version);
+/* Optional, after qp_dist_init, ranks on ONE node (<= 8): gradient all-reduce INSIDE the persistent
+ * episode kernel over NVLink peer memory instead of NCCL launches between kernels.  Each rank exports a
+ * 64-byte CUDA IPC handle of its exchange buffer (qp_dist_p2p_export), the host gathers the world's
+ * handles in rank order and gives them to every rank (qp_dist_p2p_import).  Per env-step every rank
+ * then publishes its gradient, raises a flag in each peer's memory, and sums all ranks' gradients in
+ * rank order before AdaGrad — bit-identical on every rank.  All ranks must step in lock-step with
+ * the same n_steps.  If either call fails (no peer access) the NCCL path stays in use. */
+#define QP_DIST_IPC_BYTES 64
+int qp_dist_p2p_export(qp_handle* h, void* out, size_t out_bytes);
+int qp_dist_p2p_import(qp_handle* h, const void* handles, int32_t world);
 
 /* ---- allocation-free variant.  No counterpart in the reference.
  *

@@ -69,6 +69,8 @@ SIGNATURES = {
     "qp_parse_prices": (C.c_int, [C.c_char_p, C.c_size_t, _P, C.c_int64, C.POINTER(C.c_int64)]),
     "qp_dist_unique_id": (C.c_int, [_P, C.c_size_t]),
     "qp_dist_init": (C.c_int, [_H, _P, C.c_int32, C.c_int32]),
+    "qp_dist_p2p_export": (C.c_int, [_H, _P, C.c_size_t]),
+    "qp_dist_p2p_import": (C.c_int, [_H, _P, C.c_int32]),
     "qp_dist_nccl_version": (C.c_int, [C.POINTER(C.c_int32)]),
     "qp_td_grad_noalloc": (C.c_int, [C.c_int32, C.POINTER(QpConfig), _P, _P, _P, _P, C.c_int64, _P, C.c_void_p]),
     "qp_stream": (C.c_void_p, [_H]),

@@ -153,6 +153,11 @@ struct qp_handle {
     // data parallelism over GPUs: one SUM all-reduce of the gradient per env-step
     ncclComm_t comm = nullptr;
     int rank = 0, world = 1;
+    // in-kernel all-reduce over NVLink peer memory (persistent kernel, world > 1)
+    void* p2p_block = nullptr;          // [256 B of flags | 2 * P floats] exported to the other ranks
+    void* p2p_peer_block[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    bool p2p_ready = false, allow_p2p = true;
+    unsigned int p2p_flag_base = 0;
     // batching front-end (config 5): child actors enqueue rows, one flush = one GPU launch per kind
     std::mutex qmu;
     std::vector<float> q_states, q_steps, u_states, u_rewards, u_next;
@@ -570,7 +575,9 @@ int wide_prepare_tc(qp_handle* h) {
 }
 
 bool use_fused(const qp_handle* h) {
-    return !h->wide && h->allow_fused && h->coop_launch && h->world == 1 && h->geo.ep_ok &&
+    const bool single = h->world == 1;
+    const bool peers = h->world > 1 && h->world <= 8 && h->p2p_ready && h->allow_p2p;
+    return !h->wide && h->allow_fused && h->coop_launch && (single || peers) && h->geo.ep_ok &&
            h->n_envs <= (int64_t)kTileEnvs * h->num_sms;
 }
 
@@ -594,6 +601,15 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
     s.trace_step0 = trace_step0;
     ea.step0 = (int32_t)h->steps_done + step_offset; ea.n_steps = n_steps;
     ea.apply_in_kernel = apply_in_kernel ? 1 : 0;
+    ea.world = 1; ea.rank = 0;
+    if (apply_in_kernel && h->world > 1) {     // in-kernel all-reduce over peer memory
+        ea.world = h->world; ea.rank = h->rank; ea.flag_base = h->p2p_flag_base;
+        for (int r = 0; r < h->world; ++r) {
+            ea.flags[r] = reinterpret_cast<unsigned int*>(h->p2p_peer_block[r]);
+            ea.xg[r] = reinterpret_cast<float*>(reinterpret_cast<char*>(h->p2p_peer_block[r]) + 256);
+        }
+        h->p2p_flag_base += (unsigned int)n_steps;
+    }
     ea.acc = h->acc.p; ea.grad = h->grad.p; ea.params_rw = h->params.p; ea.part1 = h->part1.p;
     ea.d_step_rw = h->d_step.p;
     ea.n_rt = h->geo.ep_n_rt; ea.n_ct = h->geo.ep_n_ct; ea.nwf = h->geo.step_warps;
@@ -613,7 +629,7 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
 // launch (forward, select, book-keeping and the dW1 contraction fused), then sum of partials,
 // all-reduce of the gradient, AdaGrad.
 bool use_fused_step(const qp_handle* h) {
-    return !h->wide && h->allow_fused && h->coop_launch && h->world > 1 && h->geo.ep_ok &&
+    return !h->wide && h->allow_fused && h->coop_launch && h->world > 1 && !use_fused(h) && h->geo.ep_ok &&
            h->n_envs <= (int64_t)kTileEnvs * h->num_sms;
 }
 
@@ -742,6 +758,9 @@ int qp_destroy(qp_handle* h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
+    for (int r = 0; r < 8; ++r)
+        if (h->p2p_peer_block[r] && r != h->rank) cudaIpcCloseMemHandle(h->p2p_peer_block[r]);
+    if (h->p2p_block) cudaFree(h->p2p_block);
     h->params.release(); h->acc.release(); h->grad.release();
     h->dz1.release(); h->xextra.release(); h->part1.release(); h->part2.release();
     h->m_states.release(); h->m_next.release(); h->m_rewards.release(); h->m_steps.release();
@@ -1422,6 +1441,7 @@ int qp_set_option(qp_handle* h, const char* key, int64_t value) {
     if (std::strcmp(key, "phase_clocks") == 0) { h->want_dbg = value != 0; return QP_OK; }
     if (std::strcmp(key, "fused") == 0) { h->allow_fused = value != 0; return QP_OK; }
     if (std::strcmp(key, "tc") == 0) { h->allow_tc = value != 0; return QP_OK; }
+    if (std::strcmp(key, "p2p") == 0) { h->allow_p2p = value != 0; return QP_OK; }
     if (std::strcmp(key, "tc_passes") == 0) {
         if (value != 1 && value != 3) return fail(QP_EINVAL, "tc_passes must be 3 (3xTF32) or 1 (TF32)");
         h->tc_passes = (int)value;
@@ -1441,6 +1461,7 @@ int qp_get_option(qp_handle* h, const char* key, int64_t* value) {
     if (!h || !key || !value) return fail(QP_EINVAL, "null argument");
     if (std::strcmp(key, "fused") == 0) { *value = h->allow_fused ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "wide") == 0) { *value = h->wide ? 1 : 0; return QP_OK; }
+    if (std::strcmp(key, "p2p_active") == 0) { *value = (h->has_env && h->world > 1 && use_fused(h)) ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "tc_a_lo_zero") == 0) { *value = h->tc_a_lo_zero ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "tc_active") == 0) { *value = (h->wide && h->allow_tc && h->tc_ready) ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "fused_active") == 0) { *value = (h->has_env && use_fused(h)) ? 1 : 0; return QP_OK; }
@@ -1468,6 +1489,40 @@ int qp_dist_init(qp_handle* h, const void* unique_id, int32_t rank, int32_t worl
     std::memcpy(id.internal, unique_id, QP_DIST_ID_BYTES);
     QP_NCCL(g_nccl.CommInitRank(&h->comm, world, id, rank));
     h->rank = rank; h->world = world;
+    return QP_OK;
+}
+
+int qp_dist_p2p_export(qp_handle* h, void* out, size_t out_bytes) {
+    if (!h || !out || out_bytes < QP_DIST_IPC_BYTES) return fail(QP_EINVAL, "need a 64-byte buffer");
+    static_assert(sizeof(cudaIpcMemHandle_t) == QP_DIST_IPC_BYTES, "IPC handle size");
+    QP_TRY(use_device(h));
+    if (!h->p2p_block) {
+        const size_t bytes = 256 + (size_t)2 * h->P * sizeof(float);
+        QP_CUDA(cudaMalloc(&h->p2p_block, bytes));
+        QP_CUDA(cudaMemset(h->p2p_block, 0, bytes));
+        QP_CUDA(cudaDeviceSynchronize());
+    }
+    cudaIpcMemHandle_t hd;
+    QP_CUDA(cudaIpcGetMemHandle(&hd, h->p2p_block));
+    std::memcpy(out, &hd, sizeof hd);
+    return QP_OK;
+}
+
+int qp_dist_p2p_import(qp_handle* h, const void* handles, int32_t world) {
+    if (!h || !handles) return fail(QP_EINVAL, "null argument");
+    if (world != h->world || world > 8) return fail(QP_EINVAL, "world must match qp_dist_init and be <= 8");
+    if (!h->p2p_block) return fail(QP_ESTATE, "call qp_dist_p2p_export first");
+    QP_TRY(use_device(h));
+    for (int r = 0; r < world; ++r) {
+        if (r == h->rank) { h->p2p_peer_block[r] = h->p2p_block; continue; }
+        cudaIpcMemHandle_t hd;
+        std::memcpy(&hd, static_cast<const char*>(handles) + (size_t)r * QP_DIST_IPC_BYTES, sizeof hd);
+        void* ptr = nullptr;
+        QP_CUDA(cudaIpcOpenMemHandle(&ptr, hd, cudaIpcMemLazyEnablePeerAccess));
+        h->p2p_peer_block[r] = ptr;
+    }
+    h->p2p_ready = true;
+    h->p2p_flag_base = 0;
     return QP_OK;
 }
 

@@ -95,6 +95,13 @@ struct EpisodeArgs {
     long long* dbg;                 // optional [n_steps][8] clock64 stamps of CTA 0 (phase timing aid)
     int apply_in_kernel;            // 1: phase B (sum + AdaGrad) runs in the kernel; 0: exactly one env-step, the
                                     // partials are left for apply_kernel (multi-GPU: an all-reduce sits in between)
+    // in-kernel gradient all-reduce over NVLink peer memory (world > 1): every rank publishes its
+    // local gradient in its own exchange buffer, raises a flag in every peer's memory, then sums all
+    // ranks' buffers in rank order (identical on every rank) and applies AdaGrad
+    int world, rank;
+    float* xg[8];                   // exchange buffers [2][P] of every rank (peer-mapped); xg[rank] is local
+    unsigned int* flags[8];         // flag arrays [8] of every rank (peer-mapped): flags[r][q] = steps published by q, seen at r
+    unsigned int flag_base;         // value of the flags before this launch
 };
 
 struct ApplyArgs {
@@ -1092,6 +1099,8 @@ __global__ void __launch_bounds__(kEpMaxThreads, 1) episode_kernel(const Episode
             const int64_t P1 = (int64_t)D * H, P = P1 + 3 * (int64_t)H;
             const int64_t n_tasks = ((P >> 2) * 4 + 31) / 32 * 32;
             const int n1 = (int)n_tiles;
+            const bool multi = ea.world > 1;
+            float* xg_local = multi ? ea.xg[ea.rank] + (size_t)(sidx & 1) * P : nullptr;
             for (int64_t task = (int64_t)blockIdx.x * nthreads + tid; task < n_tasks; task += total_threads) {
                 const int64_t g4 = task >> 2;             // float4 group of parameters
                 const int sub = (int)(task & 3);
@@ -1124,10 +1133,60 @@ __global__ void __launch_bounds__(kEpMaxThreads, 1) episode_kernel(const Episode
                     gsum.w += __shfl_xor_sync(0xffffffffu, gsum.w, m);
                 }
                 if (in_range && sub == 0) {
-                    *reinterpret_cast<float4*>(ea.grad + p) = gsum;
+                    if (multi) {
+                        *reinterpret_cast<float4*>(xg_local + p) = gsum;      // this rank's share of the sum
+                    } else {
+                        *reinterpret_cast<float4*>(ea.grad + p) = gsum;
+                        float4 av = *reinterpret_cast<float4*>(ea.acc + p);
+                        float4 wv = *reinterpret_cast<float4*>(ea.params_rw + p);
+                        const float gg[4] = {gsum.x, gsum.y, gsum.z, gsum.w};
+                        float aa[4] = {av.x, av.y, av.z, av.w};
+                        float ww[4] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+                        for (int q = 0; q < 4; ++q) {
+                            aa[q] = __fadd_rn(aa[q], __fmul_rn(gg[q], gg[q]));
+                            ww[q] = __fsub_rn(ww[q], __fmul_rn(__fmul_rn(gg[q], hp.lr), __fdiv_rn(1.0f, __fsqrt_rn(aa[q]))));
+                        }
+                        *reinterpret_cast<float4*>(ea.acc + p) = make_float4(aa[0], aa[1], aa[2], aa[3]);
+                        *reinterpret_cast<float4*>(ea.params_rw + p) = make_float4(ww[0], ww[1], ww[2], ww[3]);
+                    }
+                }
+            }
+            if (multi) {
+                // ---- gradient all-reduce over NVLink peer memory, fused with the AdaGrad apply
+                __threadfence_system();
+                grid.sync();                                   // this rank's gradient is complete and visible
+                const unsigned int want = ea.flag_base + (unsigned int)sidx + 1u;
+                if (blockIdx.x == 0 && tid < ea.world)         // raise my flag in every rank's memory (posted NVLink writes)
+                    asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(ea.flags[tid] + ea.rank), "r"(want) : "memory");
+                if (tid < ea.world) {                          // every CTA waits on the LOCAL copies of all ranks' flags
+                    const unsigned int* f = ea.flags[ea.rank] + tid;
+                    unsigned long long t0 = 0;
+                    for (unsigned int spins = 0;; ++spins) {
+                        unsigned int v;
+                        asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+                        if ((int)(v - want) >= 0) break;
+                        if ((spins & 4095u) == 4095u) {
+                            unsigned long long t;
+                            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                            if (t0 == 0) t0 = t;
+                            else if (t - t0 > 20000000000ull) __trap();   // a rank never arrived: fail instead of hanging
+                        }
+                    }
+                }
+                __syncthreads();
+                // sum the ranks' gradients in rank order (bit-identical on every rank) and apply AdaGrad
+                const size_t boff = (size_t)(sidx & 1) * P;
+                for (int64_t p = ((int64_t)blockIdx.x * nthreads + tid) * 4; p < P; p += total_threads * 4) {
+                    float4 gs = make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int r = 0; r < ea.world; ++r) {
+                        const float4 v = __ldcv(reinterpret_cast<const float4*>(ea.xg[r] + boff + p));
+                        gs.x += v.x; gs.y += v.y; gs.z += v.z; gs.w += v.w;
+                    }
+                    *reinterpret_cast<float4*>(ea.grad + p) = gs;
                     float4 av = *reinterpret_cast<float4*>(ea.acc + p);
                     float4 wv = *reinterpret_cast<float4*>(ea.params_rw + p);
-                    const float gg[4] = {gsum.x, gsum.y, gsum.z, gsum.w};
+                    const float gg[4] = {gs.x, gs.y, gs.z, gs.w};
                     float aa[4] = {av.x, av.y, av.z, av.w};
                     float ww[4] = {wv.x, wv.y, wv.z, wv.w};
 #pragma unroll

@@ -282,7 +282,7 @@ class QDecisionPolicy:
         self.n_envs = int(soe.size)
         return out
 
-    def dist_init(self, dist, rank: int, world: int):
+    def dist_init(self, dist, rank: int, world: int, p2p: bool = True):
         """Join the gradient all-reduce group.  `dist` is an initialised torch.distributed (any backend):
         it only carries the 128-byte NCCL rendezvous id from rank 0 to the others."""
         import torch
@@ -295,6 +295,22 @@ class QDecisionPolicy:
         uid = (C.c_ubyte * 128).from_buffer_copy(ids[0])
         check(self._lib.qp_dist_init(self._h, uid, int(rank), int(world)))
         del torch
+        self.p2p = False
+        if world > 1 and p2p:
+            # NVLink peer-memory all-reduce inside the persistent kernel: exchange CUDA IPC handles
+            hbuf = (C.c_ubyte * 64)()
+            ok = self._lib.qp_dist_p2p_export(self._h, hbuf, 64) == _capi.QP_OK
+            gathered = [None] * world
+            dist.all_gather_object(gathered, (ok, bytes(hbuf)))
+            if all(g[0] for g in gathered):
+                blob = b"".join(g[1] for g in gathered)
+                ok = self._lib.qp_dist_p2p_import(self._h, (C.c_ubyte * len(blob)).from_buffer_copy(blob), world) == _capi.QP_OK
+            else:
+                ok = False
+            flags = [None] * world
+            dist.all_gather_object(flags, bool(ok))
+            self.p2p = all(flags)
+            self.set_option("p2p", 1 if self.p2p else 0)   # every rank must take the same path
 
     # ---- checkpoint (the reference's saveSnapshot stub, QDecisionPolicyActor.scala:74, :91-93) ------
     def save_checkpoint(self, path: str):
