@@ -1,0 +1,27 @@
+"""configs[2]/configs[4] per-GPU shape: 131 072 episodes on one GPU (512 tickers x 256 episodes each, or
+131 072 distinct series), three-kernels-per-step path.  Usage: python profiles/fanout_workload.py [tickers] [steps]"""
+import os
+import sys
+import time
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+
+import scala_akka_tensorflow_sharetrade_helper_b200 as q
+from oracle import oracle as O
+
+tickers = int(sys.argv[1]) if len(sys.argv) > 1 else 512
+steps = int(sys.argv[2]) if len(sys.argv) > 2 else 40
+n = 131072
+prices = O.gen_prices(42, 0, tickers, 1000)
+soe = (np.arange(n) // (n // tickers)).astype(np.int32)
+with q.QDecisionPolicy(q.PolicyConfig()) as pol:
+    pol.env_create(prices, soe, 1000.0, 0)
+    assert pol.get_option("fused_active") == 0
+    pol.env_step(10)
+    t0 = time.perf_counter()
+    pol.env_step(steps)
+    dt = time.perf_counter() - t0
+    kms = pol.env_step_timed(steps) / steps * 1e3
+    print(f"tickers {tickers} episodes {n}: {dt / steps * 1e6:.1f} us/env-step -> {n * steps / dt:.4g} env-steps/s; "
+          f"kernels us {kms.tolist()}")

@@ -115,6 +115,9 @@ struct Geometry {
     size_t smem_step[3] = {0, 0, 0};
     int n_rt = 0, cg_max = 0, dw1_tiles = 0, dw1_threads = 0;   // K2
     size_t smem_dw1 = 0;
+    bool big_ok = false;                // large-batch K2 (16 x 8 tiles, one split per SM) usable for this shape
+    int big_n_rt = 0, big_n_ct = 0, big_threads = 0;
+    size_t smem_big = 0;
     bool ep_ok = false;                 // persistent episode kernel usable for this shape
     int ep_n_rt = 0, ep_n_ct = 0, ep_threads = 0;
     size_t smem_ep = 0;
@@ -218,6 +221,13 @@ int make_geometry(const Hyper& hp, int max_smem, Geometry* g) {
     g->dw1_threads = (int)round_up((int64_t)g->n_rt * g->cg_max, 32);
     g->smem_dw1 = (size_t)kDw1Stages * kDw1ChunkEnvs *
                   ((size_t)g->n_rt * kDw1Rows + (size_t)g->cg_max * kDw1Cols) * sizeof(float);
+    // large-batch K2
+    g->big_n_rt = (hp.D + kDw1BigRows - 1) / kDw1BigRows;
+    g->big_n_ct = (H4 + 1) / 2;
+    g->big_threads = (int)round_up((int64_t)g->big_n_rt * g->big_n_ct, 32);
+    g->smem_big = (size_t)kDw1Stages * kDw1ChunkEnvs *
+                  ((size_t)g->big_n_rt * kDw1BigRows + (size_t)g->big_n_ct * kDw1BigCols) * sizeof(float);
+    g->big_ok = g->big_threads <= kDw1MaxThreads && g->smem_big <= (size_t)max_smem;
     // persistent episode kernel
     g->ep_n_rt = (hp.wn + 1 + kEpRows - 1) / kEpRows;
     g->ep_n_ct = (H4 + 1) / 2;
@@ -239,6 +249,9 @@ int make_geometry(const Hyper& hp, int max_smem, Geometry* g) {
                     "(window+2)*hidden*4 + staging <= " + std::to_string(max_smem) + " bytes)");
     return QP_OK;
 }
+
+// large batches: one split per SM, the big-tile kernel
+bool dw1_use_big(const Geometry& g, int64_t B, int num_sms) { return g.big_ok && B >= (int64_t)128 * num_sms; }
 
 // episode splits of the dW1 grid: enough episodes per split to be worth a partial, all SMs used
 int dw1_splits(int64_t B, int num_sms, int tiles) {
@@ -262,7 +275,7 @@ int ensure_scratch(qp_handle* h, int64_t B, int* grid_step, int* grid_dw1) {
     const int64_t Bpad = round_up(B, kTileEnvs);
     const int64_t n_tiles = Bpad / kTileEnvs;
     const int g1 = (int)std::min<int64_t>(n_tiles, h->num_sms);
-    const int g2 = dw1_splits(B, h->num_sms, h->geo.dw1_tiles);
+    const int g2 = dw1_use_big(h->geo, B, h->num_sms) ? h->num_sms : dw1_splits(B, h->num_sms, h->geo.dw1_tiles);
     QP_TRY(h->dz1.ensure((size_t)Bpad * h->hp.H));
     QP_TRY(h->xextra.ensure((size_t)Bpad * 2));
     QP_TRY(h->part1.ensure((size_t)g2 * h->P1));
@@ -282,7 +295,16 @@ int launch_step(qp_handle* h, const StepArgs& a, int grid) {
 }
 
 template <int MODE>
-int launch_dw1(qp_handle* h, const Dw1Args& a, int grid) {
+int launch_dw1(qp_handle* h, const Dw1Args& a_in, int grid) {
+    if (dw1_use_big(h->geo, a_in.B, h->num_sms)) {
+        Dw1Args a = a_in;
+        a.n_rt = h->geo.big_n_rt; a.cg_max = h->geo.big_n_ct;
+        dw1_big_kernel<MODE><<<grid, h->geo.big_threads, h->geo.smem_big, h->stream>>>(a);
+        h->launches++;
+        QP_CUDA(cudaGetLastError());
+        return QP_OK;
+    }
+    const Dw1Args& a = a_in;
     dw1_kernel<MODE><<<dim3(grid, h->geo.dw1_tiles), h->geo.dw1_threads, h->geo.smem_dw1, h->stream>>>(a);
     h->launches++;
     QP_CUDA(cudaGetLastError());
@@ -725,6 +747,8 @@ int qp_create(const qp_config* cfg, qp_handle** out) {
     QP_BAIL_CUDA(cudaFuncSetAttribute(step_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_kernel<kEnvStep>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_big_kernel<kEnvStep>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_big_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     QP_BAIL_CUDA(cudaFuncSetAttribute(episode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     QP_BAIL_CUDA(cudaFuncSetAttribute(wide_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     {

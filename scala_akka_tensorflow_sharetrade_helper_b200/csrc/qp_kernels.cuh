@@ -654,6 +654,121 @@ __global__ void __launch_bounds__(kDw1MaxThreads, 1) dw1_kernel(const Dw1Args a)
 }
 
 // =============================================================================================
+// K2, large-batch form — used when every CTA owns at least a few hundred episodes (configs[2]:
+// 131 072 episodes per GPU).  One split per SM and the whole D x H partial per CTA: with that many
+// episodes per split the partial traffic is negligible, and the bigger 16 x 8 register tile needs
+// only 24 shared-memory wavefronts per 128 FMAs (the 8 x 4 tile of the 2-D grid needs ~9 per 32).
+// Same 2-stage cp.async pipeline as above.
+// =============================================================================================
+constexpr int kDw1BigRows = 16, kDw1BigCols = 8;
+
+template <int MODE>
+__global__ void __launch_bounds__(kDw1MaxThreads, 1) dw1_big_kernel(const Dw1Args a) {
+    extern __shared__ __align__(16) float smem[];
+    const Hyper& hp = a.hp;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarps = blockDim.x >> 5;
+    const int nthreads = blockDim.x;
+    const int D = hp.D, H = hp.H, wn = hp.wn;
+    const int H4 = H >> 2;
+    const int n_rt = a.n_rt, n_ct = a.cg_max;                 // here: 16-row tiles, pairs of float4 column groups
+    const int Dp = n_rt * kDw1BigRows, Hp = n_ct * kDw1BigCols;
+    const size_t stage_floats = (size_t)kDw1ChunkEnvs * (Dp + Hp);
+    const int32_t istep = (MODE == kEnvStep) ? *a.d_step : 0;
+    const int64_t S = gridDim.x;
+    const int64_t e0 = a.B * (int64_t)blockIdx.x / S, e1 = a.B * ((int64_t)blockIdx.x + 1) / S;
+    const int rt = tid / n_ct, ct = tid - rt * n_ct;
+    const bool active = rt < n_rt;
+
+    float acc[kDw1BigRows][kDw1BigCols];
+#pragma unroll
+    for (int r = 0; r < kDw1BigRows; ++r)
+#pragma unroll
+        for (int c = 0; c < kDw1BigCols; ++c) acc[r][c] = 0.0f;
+
+    auto prefetch = [&](int64_t eb, int ne, float* Xc, float* Zc) {
+        for (int el = warp; el < ne; el += nwarps) {
+            const int64_t ee = eb + el;
+            float* dst = Xc + el * Dp;
+            if (MODE == kEnvStep) {
+                const float* src = a.prices + (int64_t)a.series_of_env[ee] * a.T + istep;
+                for (int k = lane; k < Dp; k += 32) {
+                    if (k < wn) cp_async4(dst + k, src + k);
+                    else dst[k] = (k == wn) ? a.xextra[ee] : ((k == wn + 1) ? a.xextra[a.Bpad + ee] : 0.0f);
+                }
+            } else {
+                const float* src = a.states + ee * D;
+                for (int k = lane; k < Dp; k += 32) {
+                    if (k < D) cp_async4(dst + k, src + k);
+                    else dst[k] = 0.0f;
+                }
+            }
+        }
+        const int Hp4 = Hp >> 2;
+        for (int idx = tid; idx < ne * Hp4; idx += nthreads) {
+            const int el = idx / Hp4, c4 = idx - el * Hp4;
+            float* dst = Zc + el * Hp + c4 * 4;
+            if (c4 < H4) cp_async16(dst, a.dz1 + (eb + el) * H + c4 * 4);
+            else *reinterpret_cast<float4*>(dst) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+    };
+
+    const int n_chunks = (int)((e1 - e0 + kDw1ChunkEnvs - 1) / kDw1ChunkEnvs);
+    if (n_chunks > 0) prefetch(e0, (int)min((int64_t)kDw1ChunkEnvs, e1 - e0), smem, smem + (size_t)kDw1ChunkEnvs * Dp);
+    cp_async_commit();
+    for (int c = 0; c < n_chunks; ++c) {
+        const int64_t eb = e0 + (int64_t)c * kDw1ChunkEnvs;
+        const int ne = (int)min((int64_t)kDw1ChunkEnvs, e1 - eb);
+        float* Xc = smem + (size_t)(c & 1) * stage_floats;
+        float* Zc = Xc + (size_t)kDw1ChunkEnvs * Dp;
+        if (c + 1 < n_chunks) {
+            float* Xn = smem + (size_t)((c + 1) & 1) * stage_floats;
+            prefetch(eb + kDw1ChunkEnvs, (int)min((int64_t)kDw1ChunkEnvs, e1 - eb - kDw1ChunkEnvs), Xn,
+                     Xn + (size_t)kDw1ChunkEnvs * Dp);
+        }
+        cp_async_commit();
+        cp_async_wait_pending(1);
+        __syncthreads();
+        if (active) {
+            const float4* xp = reinterpret_cast<const float4*>(Xc + rt * kDw1BigRows);
+            const float4* zp0 = reinterpret_cast<const float4*>(Zc) + ct;
+            const float4* zp1 = reinterpret_cast<const float4*>(Zc) + ct + n_ct;
+            const int xs4 = Dp >> 2, zs4 = Hp >> 2;
+#pragma unroll 2
+            for (int el = 0; el < ne; ++el) {
+                float x[kDw1BigRows];
+#pragma unroll
+                for (int j = 0; j < kDw1BigRows / 4; ++j) {
+                    const float4 v = xp[el * xs4 + j];
+                    x[4 * j] = v.x; x[4 * j + 1] = v.y; x[4 * j + 2] = v.z; x[4 * j + 3] = v.w;
+                }
+                const float4 za = zp0[el * zs4], zb = zp1[el * zs4];
+                const float z[kDw1BigCols] = {za.x, za.y, za.z, za.w, zb.x, zb.y, zb.z, zb.w};
+#pragma unroll
+                for (int r = 0; r < kDw1BigRows; ++r)
+#pragma unroll
+                    for (int cc = 0; cc < kDw1BigCols; ++cc) acc[r][cc] = fmaf(x[r], z[cc], acc[r][cc]);
+            }
+        }
+        __syncthreads();
+    }
+    cp_async_wait_pending(0);
+
+    if (active) {
+        float* out = a.part + (size_t)blockIdx.x * ((size_t)D * H);
+#pragma unroll
+        for (int r = 0; r < kDw1BigRows; ++r) {
+            const int row = rt * kDw1BigRows + r;
+            if (row < D) {
+                if (ct < H4)
+                    reinterpret_cast<float4*>(out + (size_t)row * H)[ct] = make_float4(acc[r][0], acc[r][1], acc[r][2], acc[r][3]);
+                if (ct + n_ct < H4)
+                    reinterpret_cast<float4*>(out + (size_t)row * H)[ct + n_ct] = make_float4(acc[r][4], acc[r][5], acc[r][6], acc[r][7]);
+            }
+        }
+    }
+}
+
+// =============================================================================================
 // K3 — gradient reduction + AdaGrad.  Eight lanes per parameter sum the partials (interleaved,
 // then a fixed xor tree); the leader applies ResourceApplyAdagrad as trainOp does at
 // QDecisionPolicyActor.scala:50, :73:   accum += g*g;  var -= (g*lr) * (1/sqrt(accum)).

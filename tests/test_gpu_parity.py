@@ -497,3 +497,30 @@ def test_first_step_of_full_batch_against_oracle():
     if n_diff == 0:
         _tol.assert_grad_close(g, ref["grad"])
         assert np.abs(p - o.params).max() <= _tol.W_ATOL
+
+
+@pytest.mark.parametrize("n", [19000, 40007])
+def test_large_batch_path_against_oracle(n):
+    """More than 128 episodes per SM: the three-kernel path with the large-batch dW1 kernel (one split
+    per SM, 16 x 8 register tiles).  One teacher-forced step against the oracle."""
+    cfg = O.Config(bookkeeping=O.RLPY, seed=31)
+    prices = O.gen_prices(cfg.seed, 0, 500, 300)
+    soe = (np.arange(n) % 500).astype(np.int32)
+    w = (O.gen_normal(12, 0, cfg.P) * 0.05).astype(np.float32)
+    i = 66
+    o = O.Oracle(cfg, params=w)
+    o.env_create(prices, soe, 1000.0, 1)
+    o.env["step"] = i
+    x = states_of(cfg, prices, soe, i, o.env["budget"], o.env["shares"])
+    ref = o.env_step(1, trace=True, want_grad=True)[0]
+    with make_policy(cfg, params=w) as pol:
+        pol.env_create(prices, soe, 1000.0, 1)
+        assert pol.get_option("fused_active") == 0
+        pol.env_set_state(step=i)
+        tr = {k: a[0] for k, a in pol.env_step_trace(1).items()}
+        g = pol.last_grad()
+        p, _ = pol.get_weights()
+    n_diff = compare_step(cfg, w, x, tr, ref, "large batch")
+    if n_diff == 0:
+        _tol.assert_grad_close(g, ref["grad"])
+        assert np.abs(p - o.params).max() <= _tol.W_ATOL
