@@ -56,7 +56,10 @@ def assert_actions_match(cfg, params, x, act, act_ref, q_ref, what="action"):
     return int(diff.sum())
 
 
-def assert_grad_close(g, g_ref, what="grad"):
+def assert_grad_close(g, g_ref, what="grad", n_terms=1):
+    """n_terms = number of episodes summed.  The oracle adds the per-episode gradients sequentially in
+    fp32, whose rounding error grows ~sqrt(n); beyond the calibrated 4096 episodes the Frobenius bound
+    scales with sqrt(n / 4096) (the device's tree of partial sums is the more accurate of the two)."""
     g = np.asarray(g, np.float64)
     g_ref = np.asarray(g_ref, np.float64)
     m = np.abs(g_ref).max()
@@ -66,5 +69,6 @@ def assert_grad_close(g, g_ref, what="grad"):
     d = np.abs(g - g_ref)
     assert d.max() <= GRAD_RTOL * m, f"{what}: max |dg| {d.max():.4g} > {GRAD_RTOL} * {m:.4g}"
     fro = np.linalg.norm(g - g_ref) / np.linalg.norm(g_ref)
-    assert fro <= GRAD_FRO, f"{what}: relative Frobenius error {fro:.3g} > {GRAD_FRO}"
+    bound = GRAD_FRO * max(1.0, (n_terms / 4096.0) ** 0.5)
+    assert fro <= bound, f"{what}: relative Frobenius error {fro:.3g} > {bound:.3g}"
     return float(fro)

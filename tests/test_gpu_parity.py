@@ -522,5 +522,5 @@ def test_large_batch_path_against_oracle(n):
         p, _ = pol.get_weights()
     n_diff = compare_step(cfg, w, x, tr, ref, "large batch")
     if n_diff == 0:
-        _tol.assert_grad_close(g, ref["grad"])
+        _tol.assert_grad_close(g, ref["grad"], "large batch grad", n_terms=n)
         assert np.abs(p - o.params).max() <= _tol.W_ATOL
