@@ -1293,11 +1293,15 @@ __global__ void __launch_bounds__(kEpMaxThreads, 1) episode_kernel(const Episode
                 // sum the ranks' gradients in rank order (bit-identical on every rank) and apply AdaGrad
                 const size_t boff = (size_t)(sidx & 1) * P;
                 for (int64_t p = ((int64_t)blockIdx.x * nthreads + tid) * 4; p < P; p += total_threads * 4) {
+                    // all peers' loads are issued before the first is consumed: one NVLink round trip, not `world`
+                    float4 pv[8];
+#pragma unroll
+                    for (int r = 0; r < 8; ++r)
+                        pv[r] = (r < ea.world) ? __ldcv(reinterpret_cast<const float4*>(ea.xg[r] + boff + p))
+                                               : make_float4(0.f, 0.f, 0.f, 0.f);
                     float4 gs = make_float4(0.f, 0.f, 0.f, 0.f);
-                    for (int r = 0; r < ea.world; ++r) {
-                        const float4 v = __ldcv(reinterpret_cast<const float4*>(ea.xg[r] + boff + p));
-                        gs.x += v.x; gs.y += v.y; gs.z += v.z; gs.w += v.w;
-                    }
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) { gs.x += pv[r].x; gs.y += pv[r].y; gs.z += pv[r].z; gs.w += pv[r].w; }
                     *reinterpret_cast<float4*>(ea.grad + p) = gs;
                     float4 av = *reinterpret_cast<float4*>(ea.acc + p);
                     float4 wv = *reinterpret_cast<float4*>(ea.params_rw + p);
