@@ -279,7 +279,8 @@ def run_ours(args):
 
     # ---- roofline of the dominant kernel, measured live with CUDA events on the launching stream
     peaks = measured_peaks()
-    fp32_peak = pol.measure_fp32_peak()
+    fp32_uniform_peak = pol.measure_fp32_peak()       # dependency-free FFMA with kernel-uniform multiplicands
+    fp32_peak = pol.measure_fp32_outer_peak()         # three-register outer-product FFMA: what a contraction can issue
     n_prof = 200 if HIDDEN <= 256 else 8
     fused = bool(pol.get_option("fused_active"))
     wide = bool(pol.get_option("wide"))
@@ -305,7 +306,8 @@ def run_ours(args):
             us_per_env_step=ep_us, avg_launch_us=ep_us,
             binding=dict(bound="fp32-fma", achieved=step_flops / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
                          frac=step_flops / dur / 1e12 / fp32_peak if fp32_peak else None,
-                         peak_source="measured live (qp_measure_fp32_peak, dependency-free FFMA)"),
+                         peak_source="measured live: qp_measure_fp32_outer_peak (8x8 outer-product FFMA, three register sources); the "
+                                     f"uniform-operand FFMA stream reaches {fp32_uniform_peak:.1f} TFLOP/s on the same GPU"),
             bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP)
     elif wide:
         pol.env_reset()
@@ -340,7 +342,8 @@ def run_ours(args):
                 peak_source=peaks["source"] + " (burst copy)", avg_launch_us=ep_us, us_per_env_step=ep_us,
                 binding=dict(bound="fp32-fma", achieved=step_flops / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
                              frac=step_flops / dur / 1e12 / fp32_peak if fp32_peak else None,
-                             peak_source="measured live (qp_measure_fp32_peak, dependency-free FFMA)"),
+                             peak_source="measured live: qp_measure_fp32_outer_peak (8x8 outer-product FFMA, three register sources); the "
+                                     f"uniform-operand FFMA stream reaches {fp32_uniform_peak:.1f} TFLOP/s on the same GPU"),
                 bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP)
     elif fused:
         # one persistent kernel runs every env-step of a launch: its duration / steps is the step time
@@ -363,7 +366,8 @@ def run_ours(args):
                          "inside the SM the forward sweep is limited by shared-memory wavefronts (DESIGN.md §4)",
                          achieved=step_flops / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
                          frac=step_flops / dur / 1e12 / fp32_peak if fp32_peak else None,
-                         peak_source="measured live (qp_measure_fp32_peak, dependency-free FFMA)"),
+                         peak_source="measured live: qp_measure_fp32_outer_peak (8x8 outer-product FFMA, three register sources); the "
+                                     f"uniform-operand FFMA stream reaches {fp32_uniform_peak:.1f} TFLOP/s on the same GPU"),
             bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP,
             three_kernel_path_us=dict(zip(names, split_us)),
         )
@@ -389,7 +393,8 @@ def run_ours(args):
             binding=dict(bound="fp32-fma", note="compute-bound at fp32: 227 FLOP/B vs ridge ~11 (SURVEY.md §8d)",
                          achieved=k_flops[dom] / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
                          frac=k_flops[dom] / dur / 1e12 / fp32_peak if fp32_peak else None,
-                         peak_source="measured live (qp_measure_fp32_peak, dependency-free FFMA)"),
+                         peak_source="measured live: qp_measure_fp32_outer_peak (8x8 outer-product FFMA, three register sources); the "
+                                     f"uniform-operand FFMA stream reaches {fp32_uniform_peak:.1f} TFLOP/s on the same GPU"),
             step=dict(us=step_us, hbm_frac=bytes_per_env_step(n_local) * n_local / (step_us * 1e-6) / 1e9 / peaks["hbm_gbs"],
                       fp32_frac=FLOP_PER_ENV_STEP * n_local / (step_us * 1e-6) / 1e12 / fp32_peak if fp32_peak else None,
                       bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP),

@@ -259,6 +259,9 @@ int qp_env_step_timed(qp_handle* h, int32_t n_steps, float* ms_sum);
 /* Measured fp32-FMA throughput of the handle's GPU in TFLOP/s (dependency-free FFMA streams):
  * the roof that binds the fp32 path; MEASURED_PEAKS.json only carries HBM and bf16 tensor peaks. */
 int qp_measure_fp32_peak(qp_handle* h, double* tflops);
+/* The same for the FFMA pattern a register-tiled contraction issues (8 x 8 outer product per step,
+ * three register sources per FFMA): the attainable roof of the fp32 kernels of this library. */
+int qp_measure_fp32_outer_peak(qp_handle* h, double* tflops);
 /* Kernels launched by this handle so far.  Returns the count. */
 int64_t qp_launch_count(const qp_handle* h);
 

@@ -76,6 +76,7 @@ SIGNATURES = {
     "qp_stream": (C.c_void_p, [_H]),
     "qp_env_step_timed": (C.c_int, [_H, C.c_int32, _P]),
     "qp_measure_fp32_peak": (C.c_int, [_H, C.POINTER(C.c_double)]),
+    "qp_measure_fp32_outer_peak": (C.c_int, [_H, C.POINTER(C.c_double)]),
     "qp_launch_count": (C.c_int64, [_H]),
     "qp_last_error": (C.c_char_p, []),
     "qp_version": (C.c_char_p, []),

@@ -1580,6 +1580,27 @@ int qp_measure_fp32_peak(qp_handle* h, double* tflops) {
     return QP_OK;
 }
 
+int qp_measure_fp32_outer_peak(qp_handle* h, double* tflops) {
+    if (!h || !tflops) return fail(QP_EINVAL, "null argument");
+    QP_TRY(use_device(h));
+    const int blocks = h->num_sms * 8, iters = 1 << 12;
+    double best = 0.0;
+    for (int rep = 0; rep < 5; ++rep) {
+        QP_CUDA(cudaEventRecord(h->ev[0], h->stream));
+        fma_outer_kernel<<<blocks, 256, 0, h->stream>>>(h->grad.p, iters);
+        h->launches++;
+        QP_CUDA(cudaGetLastError());
+        QP_CUDA(cudaEventRecord(h->ev[1], h->stream));
+        QP_CUDA(cudaEventSynchronize(h->ev[1]));
+        float ms = 0.0f;
+        QP_CUDA(cudaEventElapsedTime(&ms, h->ev[0], h->ev[1]));
+        const double flops = 2.0 * 64.0 * (double)iters * 256.0 * (double)blocks;
+        if (rep > 0) best = std::max(best, flops / (ms * 1e-3) / 1e12);
+    }
+    *tflops = best;
+    return QP_OK;
+}
+
 int qp_train(qp_handle* h, const float* prices, int64_t series_len, int64_t n_series,
              const int32_t* series_of_env, int64_t n_envs, int64_t env_id_base, double budget0,
              int32_t shares0, double* portfolios_out) {

@@ -1348,6 +1348,33 @@ __global__ void __launch_bounds__(256) fma_peak_kernel(float* out, int iters, fl
     if (s == 123.456f) out[0] = s;  // keeps the loop alive without a store in practice
 }
 
+// Measurement aid: the FFMA pattern register-tiled contractions actually issue — an 8 x 8 outer
+// product per step, every FFMA with three register sources (acc += a[i] * b[j]).  The dependency-free
+// stream above multiplies by kernel-uniform operands, which the hardware can take from the uniform
+// datapath at full rate; this one measures the rate of the three-register form.
+__global__ void __launch_bounds__(256) fma_outer_kernel(float* out, int iters) {
+    float a[8], b[8], acc[8][8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { a[i] = 1.0f + 1e-3f * (float)((threadIdx.x + i) & 15); b[i] = 1.0f - 1e-3f * (float)((threadIdx.x * 3 + i) & 15); }
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) acc[i][j] = 0.0f;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i)
+#pragma unroll
+            for (int j = 0; j < 8; ++j) acc[i][j] = fmaf(a[i], b[j], acc[i][j]);
+        a[it & 7] += 1e-7f;      // keeps the operands live without adding measurable work
+    }
+    float s = 0.0f;
+#pragma unroll
+    for (int i = 0; i < 8; ++i)
+#pragma unroll
+        for (int j = 0; j < 8; ++j) s += acc[i][j];
+    if (s == 123.456f) out[0] = s;
+}
+
 #endif  // __CUDACC__
 
 }  // namespace qp

@@ -328,6 +328,11 @@ class QDecisionPolicy:
         check(self._lib.qp_measure_fp32_peak(self._h, C.byref(t)))
         return t.value
 
+    def measure_fp32_outer_peak(self) -> float:
+        t = C.c_double()
+        check(self._lib.qp_measure_fp32_outer_peak(self._h, C.byref(t)))
+        return t.value
+
     @property
     def stream(self) -> int:
         return int(self._lib.qp_stream(self._h) or 0)
