@@ -5,6 +5,7 @@
 #include "qp_kernels.cuh"
 #include "qp_wide.cuh"
 #include "qp_tc.cuh"
+#include "qp_ep_tc.cuh"
 #include "../../include/qpolicy.h"
 
 #include <dlfcn.h>
@@ -172,6 +173,12 @@ struct qp_handle {
     int64_t iteration = 0;
     std::string snapshot_path;
     int64_t snapshot_every = 500;
+    // persistent kernel with tensor-core contractions (qp_ep_tc.cuh)
+    bool allow_ep_tc = false, ep_tc_ready = false;
+    DevBuf<float> et_w_hi, et_w_lo;
+    CUtensorMap tm_et_hi, tm_et_lo;
+    int et_Kp = 0, et_nkb = 0, et_Np = 0, et_halves = 0;
+    size_t et_smem = 0;
     Geometry geo;
     bool tile_ok = false;               // W1 fits in shared memory: per-tile kernels usable
     bool wide = false;                  // GEMM-organised path (qp_wide.cuh)
@@ -387,12 +394,13 @@ int get_encode_tiled(EncodeTiledFn* out) {
 
 // 2-D fp32 tensor [outer][inner] with row pitch `pitch_bytes`, boxes of 128 rows x 32 elements
 // (128 B), 128-byte swizzle — the layout the K-major UMMA descriptor in qp_tc.cuh expects.
-int make_tmap(CUtensorMap* m, const float* base, uint64_t inner, uint64_t outer, uint64_t pitch_bytes) {
+int make_tmap(CUtensorMap* m, const float* base, uint64_t inner, uint64_t outer, uint64_t pitch_bytes,
+              uint32_t box_rows = kTcBM) {
     EncodeTiledFn enc = nullptr;
     QP_TRY(get_encode_tiled(&enc));
     const cuuint64_t dims[2] = {inner, outer};
     const cuuint64_t strides[1] = {pitch_bytes};
-    const cuuint32_t box[2] = {kTcBK, kTcBM};
+    const cuuint32_t box[2] = {kTcBK, box_rows};
     const cuuint32_t estr[2] = {1, 1};
     const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, (void*)base, dims, strides, box, estr,
                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
@@ -603,6 +611,41 @@ bool use_fused(const qp_handle* h) {
            h->n_envs <= (int64_t)kTileEnvs * h->num_sms;
 }
 
+// Everything the tensor-core persistent kernel needs for the current episodes; leaves ep_tc_ready
+// false (and the FFMA persistent kernel in charge) when a precondition does not hold.
+int ep_tc_prepare(qp_handle* h) {
+    h->ep_tc_ready = false;
+    const Hyper& hp = h->hp;
+    if (!h->tile_ok || !h->geo.ep_ok || hp.H % 4 != 0) return QP_OK;
+    const int Kp = (int)round_up(hp.wn, 32), nkb = Kp / 32, Np = (int)round_up(hp.H, 16), halves = (hp.wn + 127) / 128;
+    const size_t TB = (size_t)Np * 128;
+    const size_t smem = 1024 + (size_t)nkb * 8192 + 4 * TB + (size_t)(hp.wn + 1) * kXStride * 4 + 16 + (size_t)hp.H * 16 +
+                        (size_t)hp.H * 8 + 256 + 576 * 4 + 256 + 8 + 64 + 64;
+    if (Np > 256 || halves > 2 || halves * Np > 512 || (size_t)nkb * 8192 < TB || (size_t)halves * 16384 > 2 * TB ||
+        (int64_t)hp.wn * kTileEnvs > 20LL * kEtThreads || smem > (size_t)h->max_smem)
+        return QP_OK;
+    // the state matrix goes to the tensor core as its tf32 value alone: the prices must be tf32-exact
+    DevBuf<int32_t> flag;
+    QP_TRY(flag.ensure(1));
+    QP_CUDA(cudaMemsetAsync(flag.p, 0, sizeof(int), h->stream));
+    const int64_t n = h->n_series * h->series_len;
+    tc_inexact_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->prices.p, n, flag.p);
+    int inexact = 1;
+    QP_CUDA(cudaMemcpyAsync(&inexact, flag.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
+    QP_CUDA(cudaStreamSynchronize(h->stream));
+    flag.release();
+    h->launches += 1;
+    if (inexact) return QP_OK;
+    QP_TRY(h->et_w_hi.ensure((size_t)hp.H * Kp)); QP_TRY(h->et_w_lo.ensure((size_t)hp.H * Kp));
+    QP_CUDA(cudaMemsetAsync(h->et_w_hi.p, 0, (size_t)hp.H * Kp * sizeof(float), h->stream));
+    QP_CUDA(cudaMemsetAsync(h->et_w_lo.p, 0, (size_t)hp.H * Kp * sizeof(float), h->stream));
+    QP_TRY(make_tmap(&h->tm_et_hi, h->et_w_hi.p, Kp, hp.H, (uint64_t)Kp * sizeof(float), (uint32_t)Np));
+    QP_TRY(make_tmap(&h->tm_et_lo, h->et_w_lo.p, Kp, hp.H, (uint64_t)Kp * sizeof(float), (uint32_t)Np));
+    h->et_Kp = Kp; h->et_nkb = nkb; h->et_Np = Np; h->et_halves = halves; h->et_smem = smem;
+    h->ep_tc_ready = true;
+    return QP_OK;
+}
+
 // n_steps env-steps of every episode in ONE cooperative launch of the persistent episode kernel.
 int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace, int32_t trace_step0,
                             bool apply_in_kernel = true, int32_t step_offset = 0) {
@@ -639,6 +682,17 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
     if (h->want_dbg) {
         QP_TRY(h->dbg.ensure((size_t)n_steps * 8));
         ea.dbg = h->dbg.p;
+    }
+    if (h->allow_ep_tc && h->ep_tc_ready && h->world == 1 && apply_in_kernel) {
+        EpTcArgs x{};
+        x.ea = ea;
+        x.w1T_hi = h->et_w_hi.p; x.w1T_lo = h->et_w_lo.p;
+        x.Kp = h->et_Kp; x.nkb = h->et_nkb; x.Np = h->et_Np; x.halves = h->et_halves;
+        void* targs[] = {&h->tm_et_hi, &h->tm_et_lo, &x};
+        QP_CUDA(cudaLaunchCooperativeKernel((const void*)episode_tc_kernel, dim3(h->num_sms), dim3(kEtThreads),
+                                            targs, h->et_smem, h->stream));
+        h->launches++;
+        return QP_OK;
     }
     void* args[] = {&ea};
     QP_CUDA(cudaLaunchCooperativeKernel((const void*)episode_kernel, dim3(h->num_sms), dim3(h->geo.ep_threads),
@@ -750,6 +804,7 @@ int qp_create(const qp_config* cfg, qp_handle** out) {
     QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_big_kernel<kEnvStep>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_big_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     QP_BAIL_CUDA(cudaFuncSetAttribute(episode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(episode_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     QP_BAIL_CUDA(cudaFuncSetAttribute(wide_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     {
         int coop = 0;
@@ -790,6 +845,7 @@ int qp_destroy(qp_handle* h) {
     h->m_states.release(); h->m_next.release(); h->m_rewards.release(); h->m_steps.release();
     h->m_q.release(); h->m_ids.release(); h->m_actions.release();
     h->wZ1.release(); h->wdZ1.release(); h->wdz2.release(); h->wkn.release();
+    h->et_w_hi.release(); h->et_w_lo.release();
     for (int j = 0; j < 4; ++j) { h->p_hi[j].release(); h->p_lo[j].release(); }
     h->pT_hi.release(); h->pT_lo.release(); h->xe_hi.release(); h->xe_lo.release();
     h->w1T_hi.release(); h->w1T_lo.release(); h->dzT_hi.release(); h->dzT_lo.release();
@@ -929,6 +985,7 @@ int qp_env_create(qp_handle* h, const float* prices, int64_t series_len, int64_t
     h->B0 = budget0; h->N0 = shares0;
     h->has_env = true;
     h->tc_ready = false;
+    QP_TRY(ep_tc_prepare(h));
     if (h->wide || (h->hp.H % 128 == 0 && h->hp.H / 32 <= kWideMaxColsPerLane)) {
         bool identity = n_series == n_envs;
         for (int64_t e = 0; identity && e < n_envs; ++e) identity = series_of_env[e] == e;
@@ -1466,6 +1523,7 @@ int qp_set_option(qp_handle* h, const char* key, int64_t value) {
     if (std::strcmp(key, "fused") == 0) { h->allow_fused = value != 0; return QP_OK; }
     if (std::strcmp(key, "tc") == 0) { h->allow_tc = value != 0; return QP_OK; }
     if (std::strcmp(key, "p2p") == 0) { h->allow_p2p = value != 0; return QP_OK; }
+    if (std::strcmp(key, "ep_tc") == 0) { h->allow_ep_tc = value != 0; return QP_OK; }
     if (std::strcmp(key, "tc_passes") == 0) {
         if (value != 1 && value != 3) return fail(QP_EINVAL, "tc_passes must be 3 (3xTF32) or 1 (TF32)");
         h->tc_passes = (int)value;
@@ -1485,6 +1543,10 @@ int qp_get_option(qp_handle* h, const char* key, int64_t* value) {
     if (!h || !key || !value) return fail(QP_EINVAL, "null argument");
     if (std::strcmp(key, "fused") == 0) { *value = h->allow_fused ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "wide") == 0) { *value = h->wide ? 1 : 0; return QP_OK; }
+    if (std::strcmp(key, "ep_tc_active") == 0) {
+        *value = (h->has_env && use_fused(h) && h->allow_ep_tc && h->ep_tc_ready && h->world == 1) ? 1 : 0;
+        return QP_OK;
+    }
     if (std::strcmp(key, "p2p_active") == 0) { *value = (h->has_env && h->world > 1 && use_fused(h)) ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "tc_a_lo_zero") == 0) { *value = h->tc_a_lo_zero ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "tc_active") == 0) { *value = (h->wide && h->allow_tc && h->tc_ready) ? 1 : 0; return QP_OK; }

@@ -1,0 +1,525 @@
+// qp_ep_tc.cuh — the persistent episode kernel with its two in-CTA contractions on the tcgen05
+// tensor cores (3xTF32), for the reference shape (window 201, hidden 200) and its neighbours.
+//
+// Same life cycle as episode_kernel (qp_kernels.cuh): one cooperative launch, CTA c owns episodes
+// [32c, 32c+32), the price window lives in shared memory and slides one row per step, two grid
+// barriers per step around the gradient sum + AdaGrad.  What changes is phase A:
+//   * forward  Z[64, Np] = X[64, Kp] · W1[Kp, Np]   rows 0..31 = state s, rows 32..63 = state s' of the 32
+//     episodes; issued as M = 128 MMAs (rows 64..127 read whatever follows in shared memory and land in
+//     TMEM lanes nobody reads).  A = X is written by the CTA itself in the K-major SWIZZLE_128B
+//     layout; B = W1^T streams through a 2-stage TMA ring from the tf32 hi/lo copies that phase B
+//     of the previous step left in global memory.
+//   * backward dW1[256, Np] = X^T[256, 32] · dZ1[32, Np]   two M = 128 halves, K = the 32 episodes.
+// Precision: prices must be tf32-exact (checked at qp_env_create; the synthetic quarter-tick walk is)
+// so that X needs no lo part; W1 and dZ1 are hi/lo pairs -> A_hi·B_hi + A_hi·B_lo, fp32-grade.  The
+// budget/shares columns of the state (not tf32-exact) stay on the FFMA path, as in episode_kernel.
+#pragma once
+#include "qp_kernels.cuh"
+#include "qp_tc.cuh"
+
+namespace qp {
+
+constexpr int kEtThreads = 384;
+
+struct EpTcArgs {
+    EpisodeArgs ea;
+    float* w1T_hi; float* w1T_lo;   // [H, Kp] K-major tf32 hi/lo copies of W1[0:wn, :] (rows k >= wn zero)
+    int Kp;                          // wn rounded up to 32
+    int nkb;                         // Kp / 32
+    int Np;                          // hidden rounded up to 16 (MMA N)
+    int halves;                      // ceil(wn / 128): M = 128 tiles of the backward contraction
+};
+
+#ifdef __CUDACC__
+
+// byte offset of element (row, col) of a K-major SWIZZLE_128B tile with 128-byte rows (32 fp32)
+__device__ __forceinline__ uint32_t et_swz(int row, int col) {
+    return (uint32_t)row * 128u + (((uint32_t)(col >> 2) ^ ((uint32_t)row & 7u)) << 4) + ((uint32_t)(col & 3) << 2);
+}
+__device__ __forceinline__ float et_tf32(float x) {
+    uint32_t t;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(t) : "f"(x));
+    return __uint_as_float(t);
+}
+__device__ __forceinline__ void et_fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
+
+__device__ __forceinline__ void et_tmem_ld16(uint32_t taddr, float* v) {
+    uint32_t r[16];
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+    asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+#pragma unroll
+    for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
+}
+
+// W1[0:wn, :] (row-major [k][n]) -> K-major hi/lo copies [n][Kp], for parameters p in a float4 group
+__device__ __forceinline__ void et_publish_w(const EpTcArgs& x, int64_t p, const float4& w, int H, int wn) {
+    const int k = (int)(p / H), n = (int)(p - (int64_t)k * H);
+    if (k >= wn) return;
+    const float ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+        const float hi = et_tf32(ww[q]);
+        x.w1T_hi[(size_t)(n + q) * x.Kp + k] = hi;
+        x.w1T_lo[(size_t)(n + q) * x.Kp + k] = ww[q] - hi;
+    }
+}
+
+__global__ void __launch_bounds__(kEtThreads, 1)
+episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_constant__ CUtensorMap tW_lo, const EpTcArgs x) {
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    extern __shared__ uint8_t et_smem_raw[];
+    const EpisodeArgs& ea = x.ea;
+    const StepArgs& a = ea.s;
+    const Hyper& hp = a.hp;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nthreads = blockDim.x, nwarps = nthreads >> 5;
+    const int D = hp.D, H = hp.H, wn = hp.wn;
+    const int Np = x.Np, nkb = x.nkb, halves = x.halves;
+    const uint32_t TB = (uint32_t)Np * 128u;                   // bytes of one [Np x 32] operand tile
+
+    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(et_smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* Afwd = base;                                       // nkb tiles of [64 x 32] (8 KB each)
+    uint8_t* ring = Afwd + (size_t)nkb * 8192;                  // 2 stages x (hi, lo) of [Np x 32]
+    uint8_t* Abwd = ring;                                       // after the forward: X^T [halves*128 x 32]
+    uint8_t* Bbwd_hi = ring + (size_t)halves * 16384;
+    uint8_t* Bbwd_lo = Bbwd_hi + TB;
+    float* HV = reinterpret_cast<float*>(Afwd);                 // after the forward: h(s)*dz2, [Np][32]
+    float* Xs = reinterpret_cast<float*>(ring + 4 * (size_t)TB);  // master window [(wn+1)][33]
+    float* W2s = Xs + (size_t)(wn + 1) * kXStride;
+    W2s = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(W2s) + 15) & ~(uintptr_t)15);
+    float* Wb = W2s + (size_t)H * 4;
+    float* Ws = Wb + H;
+    float* XE = Ws + H;                                         // [2][32]
+    float* qpart = XE + 64;                                     // [3 parts][2 states][3][32]
+    float* dz2s = qpart + 3 * 2 * 3 * 32;                       // [32]
+    int* kns = reinterpret_cast<int*>(dz2s + 32);               // [32]
+    uint64_t* bars = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(kns + 32) + 7) & ~(uintptr_t)7);
+    uint64_t* full = bars;          // [2]
+    uint64_t* empty = bars + 2;     // [2]
+    uint64_t* tf_fwd = bars + 4;
+    uint64_t* tf_bwd = bars + 5;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 6);
+
+    const int64_t B = a.B;
+    const int64_t n_tiles = (B + kTileEnvs - 1) / kTileEnvs;
+    const bool has_tile = (int64_t)blockIdx.x < n_tiles;
+    const int64_t e = (int64_t)blockIdx.x * kTileEnvs + lane;
+    const bool valid = has_tile && e < B;
+    const int64_t ec = has_tile ? (valid ? e : B - 1) : 0;
+    const float bias = hp.bias;
+    const float* W1g = a.params;
+    const float* W2g = a.params + (size_t)D * H;
+    const int q4 = warp & 3, part = warp >> 2;                  // TMEM lane quarter / column part of this warp
+    const int n_ld = Np >> 4;                                   // 16-column TMEM loads per row
+    const int ld0 = part * n_ld / 3, ld1 = (part + 1) * n_ld / 3;
+    constexpr int kMaxLd = 6;                                   // <= 96 columns per warp (Np <= 288)
+
+    if (tid == 0) {
+        mbar_init(full, 1); mbar_init(full + 1, 1); mbar_init(empty, 1); mbar_init(empty + 1, 1);
+        mbar_init(tf_fwd, 1); mbar_init(tf_bwd, 1);
+        mbar_fence_init();
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
+                         (uint32_t)__cvta_generic_to_shared(tmem_slot)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+    }
+    // zero everything the MMAs may read before it is first written (padding rows / columns)
+    for (size_t i = tid; i < ((size_t)nkb * 8192 + 4 * (size_t)TB) / 16; i += nthreads)
+        reinterpret_cast<float4*>(base)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    double budget = a.budget[ec], share_value = a.share_value[ec];
+    int32_t shares = a.shares[ec];
+    const float* my_row = a.prices + (int64_t)a.series_of_env[ec] * a.T;
+    for (int idx = tid; idx < (wn + 1) * kXStride; idx += nthreads) Xs[idx] = 0.0f;
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    if (has_tile) {
+        const int segs = (wn + 1 + 31) >> 5, items = kTileEnvs * segs;
+        for (int it = warp; it < items; it += nwarps) {
+            const int el = it & 31, k = ((it >> 5) << 5) + lane;
+            const float* src = reinterpret_cast<const float*>(
+                __shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(my_row), el)) + ea.step0;
+            if (k <= wn) cp_async4(Xs + k * kXStride + el, src + k);
+        }
+        cp_async_commit();
+        cp_async_wait_pending(0);
+    }
+    // publish the K-major tf32 hi/lo copies of the current W1 (phase B keeps them current afterwards)
+    {
+        const int64_t P1 = (int64_t)D * H;
+        for (int64_t p = ((int64_t)blockIdx.x * nthreads + tid) * 4; p < P1; p += (int64_t)gridDim.x * nthreads * 4)
+            et_publish_w(x, p, __ldcg(reinterpret_cast<const float4*>(W1g + p)), H, wn);
+    }
+    __threadfence();
+    grid.sync();
+
+    const uint32_t idesc = tc_instr_desc(128, Np);
+    uint32_t ring_it = 0;                                       // k-blocks pushed through the ring so far
+
+    for (int32_t sidx = 0; sidx < ea.n_steps; ++sidx) {
+        const int32_t istep = ea.step0 + sidx;
+        const uint32_t par = (uint32_t)sidx & 1u;
+        float q_s[3] = {0.f, 0.f, 0.f}, q_n[3] = {0.f, 0.f, 0.f};
+        float keep[kMaxLd * 16];                                // q4 == 0: h(s); q4 == 1: window part of z1(s')
+        int action = 0, explored = 0, a_eff = 2, kn = 0;
+        float r32 = 0.0f, target = 0.0f, dz2 = 0.0f, p_next = 0.0f;
+        double nb = budget, p_new = 0.0;
+        int32_t ns = shares;
+
+        if (has_tile) {
+            // ---- S0: A operand of the forward (K-major, swizzled) from the master window; small tables
+            for (int it = warp; it < 64 * nkb; it += nwarps) {          // (row, k-block): lanes over the 32 k of the block
+                const int row = it & 63, kb = it >> 6;
+                const int k = kb * 32 + lane + (row >> 5);              // rows 32..63: state s' = window shifted by one
+                const float v = (k - (row >> 5) < wn && k <= wn) ? Xs[k * kXStride + (row & 31)] : 0.0f;
+                *reinterpret_cast<float*>(Afwd + (size_t)kb * 8192 + et_swz(row, lane)) = v;
+            }
+            for (int j = tid; j < H; j += nthreads) {
+                reinterpret_cast<float4*>(W2s)[j] = make_float4(__ldcg(W2g + j * 3), __ldcg(W2g + j * 3 + 1), __ldcg(W2g + j * 3 + 2), 0.f);
+                Wb[j] = __ldcg(W1g + (size_t)wn * H + j);
+                Ws[j] = __ldcg(W1g + (size_t)(wn + 1) * H + j);
+            }
+            if (warp == 0 && (int64_t)istep + wn + 1 < a.T) p_next = __ldg(my_row + istep + wn + 1);
+            et_fence_async_smem();
+        }
+        __syncthreads();
+
+        if (has_tile) {
+            // ---- S1: forward contraction on the tensor cores
+            if (warp == 0 && lane == 0) {
+                fence_proxy_async();                                    // phase-B writes of W1^T -> TMA reads
+                for (int kb = 0; kb < nkb; ++kb) {
+                    const uint32_t it = ring_it + (uint32_t)kb, s = it & 1u, ph = (it >> 1) & 1u;
+                    tc_wait(empty + s, ph ^ 1u);
+                    uint8_t* st = ring + (size_t)s * 2 * TB;
+                    mbar_arrive_expect_tx(full + s, 2 * TB);
+                    tma_load_2d(st, &tW_hi, kb * 32, 0, full + s);
+                    tma_load_2d(st + TB, &tW_lo, kb * 32, 0, full + s);
+                }
+            } else if (warp == 1 && lane == 0) {
+                for (int kb = 0; kb < nkb; ++kb) {
+                    const uint32_t it = ring_it + (uint32_t)kb, s = it & 1u, ph = (it >> 1) & 1u;
+                    tc_wait(full + s, ph);
+                    tc_fence_after();
+                    uint8_t* st = ring + (size_t)s * 2 * TB;
+                    const uint64_t da = tc_smem_desc(Afwd + (size_t)kb * 8192);
+                    const uint64_t db_hi = tc_smem_desc(st), db_lo = tc_smem_desc(st + TB);
+#pragma unroll
+                    for (int k4 = 0; k4 < 4; ++k4) {
+                        tc_mma_tf32(tmem_base, da + 2 * k4, db_hi + 2 * k4, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+                        tc_mma_tf32(tmem_base, da + 2 * k4, db_lo + 2 * k4, idesc, 1u);
+                    }
+                    tc_commit(empty + s);
+                }
+                tc_commit(tf_fwd);
+            }
+            ring_it += (uint32_t)nkb;
+            tc_wait(tf_fwd, par);
+            tc_fence_after();
+
+            // ---- S2: hidden layer of s (q4 == 0) / window part of s' (q4 == 1) out of TMEM
+            if (q4 < 2) {
+                float pq[3] = {0.f, 0.f, 0.f};
+                const float xb = __double2float_rn(budget), xs = (float)shares;
+#pragma unroll
+                for (int l = 0; l < kMaxLd; ++l) {
+                    if (ld0 + l < ld1) {
+                        float v[16];
+                        et_tmem_ld16(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)((ld0 + l) * 16), v);
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            const int c = (ld0 + l) * 16 + j;
+                            float out = v[j];
+                            if (q4 == 0) {
+                                float h = 0.0f;
+                                if (c < H) {
+                                    const float z = fmaf(xs, Ws[c], fmaf(xb, Wb[c], v[j])) + bias;
+                                    h = z > 0.0f ? z : 0.0f;
+                                    const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
+                                    pq[0] = fmaf(h, w2.x, pq[0]); pq[1] = fmaf(h, w2.y, pq[1]); pq[2] = fmaf(h, w2.z, pq[2]);
+                                }
+                                out = h;
+                            }
+                            keep[l * 16 + j] = out;
+                        }
+                    }
+                }
+                if (q4 == 0) {
+#pragma unroll
+                    for (int t = 0; t < 3; ++t) qpart[((part * 2 + 0) * 3 + t) * 32 + lane] = pq[t];
+                }
+            }
+            tc_fence_before();
+        }
+        __syncthreads();
+
+        if (has_tile) {
+            // ---- S3: SelectionAction, decision, reward (every warp keeps its own copy), then Q(s')
+#pragma unroll
+            for (int t = 0; t < 3; ++t) {
+                float s = 0.0f;
+                for (int pp = 0; pp < 3; ++pp) s += qpart[((pp * 2 + 0) * 3 + t) * 32 + lane];
+                s += bias;
+                q_s[t] = s > 0.0f ? s : 0.0f;
+            }
+            const uint64_t env_id = (uint64_t)(a.env_id_base + e);
+            uint32_t r[4];
+            philox4x32_10((uint32_t)env_id, (uint32_t)(env_id >> 32), (uint32_t)istep, 1u,
+                          (uint32_t)hp.seed, (uint32_t)(hp.seed >> 32), r);
+            const float u = (float)(r[0] >> 8) * (1.0f / 16777216.0f);
+            float thr = __fdiv_rn((float)istep, hp.step_div);
+            if (hp.epsilon < thr) thr = hp.epsilon;
+            if (u < thr) action = argmax3(q_s);
+            else { explored = 1; action = (int)(((uint64_t)r[1] * 3u) >> 32); }
+            p_new = (double)Xs[wn * kXStride + lane];
+            const double cur = __dadd_rn(budget, __dmul_rn((double)shares, share_value));
+            const double base_b = hp.bookkeeping == 0 ? a.B0 : budget;
+            const int32_t base_n = hp.bookkeeping == 0 ? a.N0 : shares;
+            nb = base_b; ns = base_n;
+            if (action == 0 && base_b >= p_new) { nb = __dsub_rn(base_b, p_new); ns = base_n + 1; a_eff = 0; }
+            else if (action == 1 && base_n > 0) { nb = __dadd_rn(base_b, p_new); ns = base_n - 1; a_eff = 1; }
+            const double newp = __dadd_rn(nb, __dmul_rn((double)ns, p_new));
+            r32 = __double2float_rn(__dsub_rn(newp, cur));
+            if (q4 == 1) {
+                const float xnb = __double2float_rn(nb), xns = (float)ns;
+                float pq[3] = {0.f, 0.f, 0.f};
+#pragma unroll
+                for (int l = 0; l < kMaxLd; ++l) {
+                    if (ld0 + l < ld1) {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            const int c = (ld0 + l) * 16 + j;
+                            if (c < H) {
+                                const float z = fmaf(xns, Ws[c], fmaf(xnb, Wb[c], keep[l * 16 + j])) + bias;
+                                const float h = z > 0.0f ? z : 0.0f;
+                                const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
+                                pq[0] = fmaf(h, w2.x, pq[0]); pq[1] = fmaf(h, w2.y, pq[1]); pq[2] = fmaf(h, w2.z, pq[2]);
+                            }
+                        }
+                    }
+                }
+#pragma unroll
+                for (int t = 0; t < 3; ++t) qpart[((part * 2 + 1) * 3 + t) * 32 + lane] = pq[t];
+            }
+        }
+        __syncthreads();
+
+        if (has_tile) {
+            // ---- S4: TD target, dZ1 (hi/lo, K-major over the episodes), h*dz2, X^T operand
+#pragma unroll
+            for (int t = 0; t < 3; ++t) {
+                float s = 0.0f;
+                for (int pp = 0; pp < 3; ++pp) s += qpart[((pp * 2 + 1) * 3 + t) * 32 + lane];
+                s += bias;
+                q_n[t] = s > 0.0f ? s : 0.0f;
+            }
+            kn = argmax3(q_n);
+            const float qn_k = kn == 0 ? q_n[0] : (kn == 1 ? q_n[1] : q_n[2]);
+            const float qs_k = kn == 0 ? q_s[0] : (kn == 1 ? q_s[1] : q_s[2]);
+            target = __fadd_rn(r32, __fmul_rn(hp.gamma, qn_k));
+            const float dq = -__fmul_rn(2.0f, __fsub_rn(target, qs_k));
+            dz2 = (valid && qs_k > 0.0f) ? dq : 0.0f;
+            if (q4 == 0) {
+#pragma unroll
+                for (int l = 0; l < kMaxLd; ++l) {
+                    if (ld0 + l < ld1) {
+#pragma unroll
+                        for (int j = 0; j < 16; ++j) {
+                            const int c = (ld0 + l) * 16 + j;
+                            float d1 = 0.0f, hvv = 0.0f;
+                            if (c < H) {
+                                const float h = keep[l * 16 + j];
+                                const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
+                                const float w2k = kn == 0 ? w2.x : (kn == 1 ? w2.y : w2.z);
+                                d1 = h > 0.0f ? __fmul_rn(dz2, w2k) : 0.0f;
+                                hvv = __fmul_rn(h, dz2);
+                            }
+                            const float hi = et_tf32(d1);
+                            const uint32_t off = et_swz(c, lane);
+                            *reinterpret_cast<float*>(Bbwd_hi + off) = hi;
+                            *reinterpret_cast<float*>(Bbwd_lo + off) = d1 - hi;
+                            HV[c * 32 + lane] = hvv;
+                        }
+                    }
+                }
+            }
+            if (warp == 0) {
+                XE[lane] = __double2float_rn(budget);
+                XE[32 + lane] = (float)shares;
+                kns[lane] = kn;
+                dz2s[lane] = dz2;
+                if (valid) {
+                    const TraceDev& t = a.trace;
+                    const int64_t ti = (int64_t)(istep - a.trace_step0) * B + e;
+                    if (t.action_sel) t.action_sel[ti] = action;
+                    if (t.action_eff) t.action_eff[ti] = a_eff;
+                    if (t.explored) t.explored[ti] = explored;
+                    if (t.k_next) t.k_next[ti] = kn;
+                    if (t.reward) t.reward[ti] = r32;
+                    if (t.target) t.target[ti] = target;
+                    if (t.budget) t.budget[ti] = nb;
+                    if (t.shares) t.shares[ti] = ns;
+                    if (t.q_s) { t.q_s[ti * 3] = q_s[0]; t.q_s[ti * 3 + 1] = q_s[1]; t.q_s[ti * 3 + 2] = q_s[2]; }
+                    if (t.q_n) { t.q_n[ti * 3] = q_n[0]; t.q_n[ti * 3 + 1] = q_n[1]; t.q_n[ti * 3 + 2] = q_n[2]; }
+                }
+            }
+            // X^T operand: row k = window element k of every episode (rows >= wn are zero)
+            for (int k = warp; k < halves * 128; k += nwarps)
+                *reinterpret_cast<float*>(Abwd + et_swz(k, lane)) = k < wn ? Xs[k * kXStride + lane] : 0.0f;
+            budget = nb; shares = ns; share_value = p_new;             // carry (TrainerChildActor.scala:99-102)
+            et_fence_async_smem();
+        }
+        __syncthreads();
+
+        if (has_tile) {
+            // ---- S5: backward contraction on the tensor cores; dW2 and the two extra dW1 rows meanwhile
+            if (warp == 1 && lane == 0) {
+                tc_fence_after();
+                const uint64_t db_hi = tc_smem_desc(Bbwd_hi), db_lo = tc_smem_desc(Bbwd_lo);
+                for (int hf = 0; hf < halves; ++hf) {
+                    const uint64_t da = tc_smem_desc(Abwd + (size_t)hf * 16384);
+#pragma unroll
+                    for (int k4 = 0; k4 < 4; ++k4) {
+                        tc_mma_tf32(tmem_base + (uint32_t)(hf * Np), da + 2 * k4, db_hi + 2 * k4, idesc, k4 > 0 ? 1u : 0u);
+                        tc_mma_tf32(tmem_base + (uint32_t)(hf * Np), da + 2 * k4, db_lo + 2 * k4, idesc, 1u);
+                    }
+                }
+                tc_commit(tf_bwd);
+            }
+            float* out = ea.part1 + (size_t)blockIdx.x * ((size_t)D * H);
+            float* out2 = a.dw2_part + (size_t)blockIdx.x * (3 * H);
+            for (int idx = tid; idx < 3 * H; idx += nthreads) {          // dW2[c][t] = sum_e [kn_e == t] h_e[c] dz2_e
+                const int c = idx / 3, t = idx - c * 3;
+                float s = 0.0f;
+                for (int el = 0; el < kTileEnvs; ++el) s += (kns[el] == t) ? HV[c * 32 + el] : 0.0f;
+                out2[idx] = s;
+            }
+            for (int idx = tid; idx < 2 * H; idx += nthreads) {          // dW1 rows wn (budget), wn + 1 (shares)
+                const int m = idx / H, c = idx - m * H;
+                float s = 0.0f;
+                for (int el = 0; el < kTileEnvs; ++el) {
+                    const uint32_t off = et_swz(c, el);
+                    const float d1 = *reinterpret_cast<const float*>(Bbwd_hi + off) + *reinterpret_cast<const float*>(Bbwd_lo + off);
+                    s = fmaf(XE[m * 32 + el], d1, s);
+                }
+                out[(size_t)(wn + m) * H + c] = s;
+            }
+            tc_wait(tf_bwd, par);
+            tc_fence_after();
+            // ---- S6: dW1 partial out of TMEM
+            for (int hf = 0; hf < halves; ++hf) {
+                const int k = hf * 128 + q4 * 32 + lane;
+#pragma unroll 1
+                for (int l = ld0; l < ld1; ++l) {
+                    float v[16];
+                    et_tmem_ld16(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(hf * Np + l * 16), v);
+                    if (k < wn) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (l * 16 + 4 * j < H)
+                                *reinterpret_cast<float4*>(out + (size_t)k * H + l * 16 + 4 * j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                    }
+                }
+            }
+            tc_fence_before();
+        }
+        __syncthreads();
+        if (!ea.apply_in_kernel) break;
+        // ---- S7: slide the window
+        if (has_tile) {
+            constexpr int kMaxPer = 20;
+            float mv[kMaxPer];
+            const int total = wn * kTileEnvs;
+#pragma unroll
+            for (int j = 0; j < kMaxPer; ++j) {
+                const int idx = tid + j * nthreads;
+                if (idx < total) mv[j] = Xs[((idx >> 5) + 1) * kXStride + (idx & 31)];
+            }
+            __syncthreads();
+#pragma unroll
+            for (int j = 0; j < kMaxPer; ++j) {
+                const int idx = tid + j * nthreads;
+                if (idx < total) Xs[(idx >> 5) * kXStride + (idx & 31)] = mv[j];
+            }
+            if (warp == 0) Xs[wn * kXStride + lane] = p_next;
+        }
+        __threadfence();
+        grid.sync();
+
+        // ---- phase B: gradient sum over the tiles + AdaGrad (as episode_kernel) + tf32 hi/lo of the new W1
+        {
+            const int64_t total_threads = (int64_t)gridDim.x * nthreads;
+            const int64_t P1 = (int64_t)D * H, P = P1 + 3 * (int64_t)H;
+            const int64_t n_tasks = ((P >> 2) * 4 + 31) / 32 * 32;
+            const int n1 = (int)n_tiles;
+            for (int64_t task = (int64_t)blockIdx.x * nthreads + tid; task < n_tasks; task += total_threads) {
+                const int64_t p = (task >> 2) << 2;
+                const int sub = (int)(task & 3);
+                const bool in_range = p < P;
+                float4 gsum = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (in_range) {
+                    const float* src; int64_t stride, off;
+                    if (p < P1) { src = ea.part1; stride = P1; off = p; }
+                    else { src = a.dw2_part; stride = P - P1; off = p - P1; }
+                    for (int j0 = sub; j0 < n1; j0 += 32) {
+                        float4 v[8];
+#pragma unroll
+                        for (int uu = 0; uu < 8; ++uu) {
+                            const int j = j0 + 4 * uu;
+                            v[uu] = (j < n1) ? __ldcg(reinterpret_cast<const float4*>(src + (int64_t)j * stride + off))
+                                             : make_float4(0.f, 0.f, 0.f, 0.f);
+                        }
+#pragma unroll
+                        for (int uu = 0; uu < 8; ++uu) { gsum.x += v[uu].x; gsum.y += v[uu].y; gsum.z += v[uu].z; gsum.w += v[uu].w; }
+                    }
+                }
+#pragma unroll
+                for (int m = 1; m <= 2; m <<= 1) {
+                    gsum.x += __shfl_xor_sync(0xffffffffu, gsum.x, m);
+                    gsum.y += __shfl_xor_sync(0xffffffffu, gsum.y, m);
+                    gsum.z += __shfl_xor_sync(0xffffffffu, gsum.z, m);
+                    gsum.w += __shfl_xor_sync(0xffffffffu, gsum.w, m);
+                }
+                if (in_range && sub == 0) {
+                    *reinterpret_cast<float4*>(ea.grad + p) = gsum;
+                    float4 av = *reinterpret_cast<float4*>(ea.acc + p);
+                    float4 wv = *reinterpret_cast<float4*>(ea.params_rw + p);
+                    const float gg[4] = {gsum.x, gsum.y, gsum.z, gsum.w};
+                    float aa[4] = {av.x, av.y, av.z, av.w};
+                    float ww[4] = {wv.x, wv.y, wv.z, wv.w};
+#pragma unroll
+                    for (int qq = 0; qq < 4; ++qq) {
+                        aa[qq] = __fadd_rn(aa[qq], __fmul_rn(gg[qq], gg[qq]));
+                        ww[qq] = __fsub_rn(ww[qq], __fmul_rn(__fmul_rn(gg[qq], hp.lr), __fdiv_rn(1.0f, __fsqrt_rn(aa[qq]))));
+                    }
+                    const float4 wnew = make_float4(ww[0], ww[1], ww[2], ww[3]);
+                    *reinterpret_cast<float4*>(ea.acc + p) = make_float4(aa[0], aa[1], aa[2], aa[3]);
+                    *reinterpret_cast<float4*>(ea.params_rw + p) = wnew;
+                    if (p < P1) et_publish_w(x, p, wnew, H, wn);
+                }
+            }
+        }
+        __threadfence();
+        grid.sync();
+    }
+
+    if (has_tile && warp == 0 && valid) {
+        a.budget[e] = budget;
+        a.shares[e] = shares;
+        a.share_value[e] = share_value;
+    }
+    if (ea.apply_in_kernel && blockIdx.x == 0 && tid == 0) *ea.d_step_rw = ea.step0 + ea.n_steps;
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 2) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(512u) : "memory");
+}
+
+#endif  // __CUDACC__
+}  // namespace qp

@@ -236,6 +236,15 @@ __global__ void tc_any_nonzero_kernel(const float* __restrict__ x, int64_t n, in
     if (i < n && x[i] != 0.0f) atomicOr(flag, 1);
 }
 
+// flag[0] = 1 if some element is not exactly representable in tf32
+__global__ void tc_inexact_kernel(const float* __restrict__ x, int64_t n, int* flag) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    uint32_t t;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(t) : "f"(x[i]));
+    if (__uint_as_float(t) != x[i]) atomicOr(flag, 1);
+}
+
 // src [R, C] row-major  ->  hiT / loT [C, ldt] (transposed, K-major for the tensor core), zero padding
 // of columns R..ldt-1 is the caller's (buffers are zero-initialised once).
 __global__ void tc_transpose_split_kernel(const float* __restrict__ src, int64_t R, int64_t C, int64_t ld_src,

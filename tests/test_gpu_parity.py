@@ -323,6 +323,72 @@ def test_persistent_kernel_matches_three_kernel_path():
     assert np.abs(wa - wb).max() <= 40 * _tol.W_ATOL
 
 
+@pytest.mark.parametrize("bookkeeping", [O.REFERENCE, O.RLPY])
+@pytest.mark.parametrize("n_envs,N0", [(5, 3), (64, 1), (200, 2)])
+def test_persistent_tensor_core_kernel_teacher_forced(bookkeeping, n_envs, N0):
+    """The persistent kernel with its in-CTA contractions on tcgen05 (3xTF32), reference shape,
+    teacher-forced against the oracle at the same fp32 tolerance."""
+    cfg = O.Config(bookkeeping=bookkeeping, seed=77)
+    n_series = max(1, n_envs // 2)
+    prices = O.gen_prices(cfg.seed, 0, n_series, 400)       # quarter ticks: tf32-exact, as the path requires
+    soe = (np.arange(n_envs) % n_series).astype(np.int32)
+    w0 = (O.gen_normal(21, 0, cfg.P) * 0.05).astype(np.float32)
+    o = O.Oracle(cfg, params=w0)
+    o.env_create(prices, soe, 1000.0, N0, env_id_base=10 ** 10)
+    with make_policy(cfg, fused=1) as pol:
+        pol.set_option("ep_tc", 1)
+        pol.env_create(prices, soe, 1000.0, N0, env_id_base=10 ** 10)
+        assert pol.get_option("ep_tc_active") == 1
+        for i in (0, 1, 57, 150, 198):
+            o.env["step"] = i
+            w, acc = o.params.copy(), o.acc.copy()
+            b, s, v = o.env["budget"].copy(), o.env["shares"].copy(), o.env["share_value"].copy()
+            pol.set_weights(w, acc)
+            pol.env_set_state(b, s, v, step=i)
+            x = states_of(cfg, prices, soe, i, b, s)
+            ref = o.env_step(1, trace=True, want_grad=True)[0]
+            tr = {k: a[0] for k, a in pol.env_step_trace(1).items()}
+            n_diff = compare_step(cfg, w, x, tr, ref, f"ep_tc step {i}")
+            if n_diff == 0:
+                _tol.assert_grad_close(pol.last_grad(), ref["grad"], f"ep_tc step {i} grad")
+                p, a = pol.get_weights()
+                assert np.abs(p - o.params).max() <= _tol.W_ATOL
+                bd, sd, vd = pol.env_state()
+                np.testing.assert_array_equal(bd, o.env["budget"])
+                np.testing.assert_array_equal(sd, o.env["shares"])
+    # prices that are not tf32-exact keep the FFMA persistent kernel
+    with make_policy(cfg, fused=1) as pol:
+        pol.set_option("ep_tc", 1)
+        pol.env_create(prices * np.float32(1.0371), soe, 1000.0, N0)
+        assert pol.get_option("ep_tc_active") == 0 and pol.get_option("fused_active") == 1
+
+
+def test_persistent_tensor_core_kernel_free_running():
+    """40 env-steps in one launch (weights republished as tf32 hi/lo every step inside the kernel),
+    against the FFMA persistent kernel on the same episodes."""
+    cfg = O.Config(bookkeeping=O.RLPY, lr=1e-4, seed=9)
+    n = 300
+    prices = O.gen_prices(cfg.seed, 0, 50, 400)
+    soe = (np.arange(n) % 50).astype(np.int32)
+    w = (O.gen_normal(3, 0, cfg.P) * 0.05).astype(np.float32)
+    res = []
+    for tc in (1, 0):
+        with make_policy(cfg, params=w, fused=1) as pol:
+            pol.set_option("ep_tc", tc)
+            pol.env_create(prices, soe, 1000.0, 1)
+            pol.env_set_state(step=120)
+            assert pol.get_option("ep_tc_active") == tc
+            tr = pol.env_step_trace(25)
+            pol.env_step(15)
+            res.append((tr, pol.get_weights()[0], pol.env_state(), pol.steps_done))
+    (ta, wa, sa, da), (tb, wb, sb, db) = res
+    assert da == db == 160
+    for k in ("action_sel", "action_eff", "explored", "shares", "budget", "reward", "k_next"):
+        np.testing.assert_array_equal(ta[k], tb[k], err_msg=k)
+    np.testing.assert_allclose(ta["q_s"], tb["q_s"], rtol=1e-4, atol=1e-3)
+    assert np.abs(wa - wb).max() <= 40 * _tol.W_ATOL
+
+
 # ------------------------------------------------------------------------------------------------
 # GEMM-organised path (BASELINE.json configs[3]: hist 512 -> window 513, hidden 2048)
 # ------------------------------------------------------------------------------------------------
