@@ -1,0 +1,29 @@
+"""Critical-path breakdown of episode_tc_kernel (clock64 stamps of CTA 0)."""
+import os
+import sys
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import numpy as np
+
+import scala_akka_tensorflow_sharetrade_helper_b200 as q
+from oracle import oracle as O
+
+n, steps = 4096, 60
+prices = O.gen_prices(42, 0, n, 1000)
+with q.QDecisionPolicy(q.PolicyConfig()) as pol:
+    pol.set_option("ep_tc", 1)
+    pol.set_option("phase_clocks", 1)
+    pol.env_create(prices, np.arange(n, dtype=np.int32), 1000.0, 0)
+    pol.env_step(steps)
+    pol.env_step(steps)
+    c = pol.phase_clocks(steps)[5:]
+names = ["S0 operand build (A fwd, tables)", "S1 forward MMA (TMA ring + tcgen05)", "S2 epilogue 1 (h(s), z(s') out of TMEM)",
+         "S3 select, book-keeping, Q(s')", "S4 TD, dZ1 hi/lo, h*dz2, X^T operand", "S5 backward MMA + dW2 + extra rows",
+         "S6 epilogue 2 (dW1 partial out of TMEM)"]
+d = np.diff(c, axis=1).astype(np.float64)
+tot = (c[1:, 0] - c[:-1, 0]).mean()
+for k, nm in enumerate(names):
+    print(f"{nm:48s} {d[:, k].mean():9.0f} cyc  {d[:, k].mean() / tot * 100:5.1f}%")
+rest = (c[1:, 0] - c[:-1, 7]).mean()
+print(f"{'S7 shift, 2 grid.sync, phase B (+W1^T publish)':48s} {rest:9.0f} cyc  {rest / tot * 100:5.1f}%")
+print(f"{'step total':48s} {tot:9.0f} cyc  (~{tot / 1.965e3:.1f} us)")

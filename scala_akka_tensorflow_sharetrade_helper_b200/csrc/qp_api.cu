@@ -174,7 +174,7 @@ struct qp_handle {
     std::string snapshot_path;
     int64_t snapshot_every = 500;
     // persistent kernel with tensor-core contractions (qp_ep_tc.cuh)
-    bool allow_ep_tc = false, ep_tc_ready = false;
+    bool allow_ep_tc = true, ep_tc_ready = false;   // qp_set_option("ep_tc", 0) keeps the FFMA persistent kernel
     DevBuf<float> et_w_hi, et_w_lo;
     CUtensorMap tm_et_hi, tm_et_lo;
     int et_Kp = 0, et_nkb = 0, et_Np = 0, et_halves = 0;
@@ -620,8 +620,8 @@ int ep_tc_prepare(qp_handle* h) {
     const int Kp = (int)round_up(hp.wn, 32), nkb = Kp / 32, Np = (int)round_up(hp.H, 16), halves = (hp.wn + 127) / 128;
     const size_t TB = (size_t)Np * 128;
     const size_t smem = 1024 + (size_t)nkb * 8192 + 4 * TB + (size_t)(hp.wn + 1) * kXStride * 4 + 16 + (size_t)hp.H * 16 +
-                        (size_t)hp.H * 8 + 256 + 576 * 4 + 256 + 8 + 64 + 64;
-    if (Np > 256 || halves > 2 || halves * Np > 512 || (size_t)nkb * 8192 < TB || (size_t)halves * 16384 > 2 * TB ||
+                        (size_t)hp.H * 8 + 256 + 2304 * 4 + 256 + 8 + 64 + 64;
+    if (Np > 256 || halves > 2 || halves * Np > 512 || (size_t)nkb * 8192 < 2 * (size_t)Np * kXStride * 4 || (size_t)halves * 16384 > 2 * TB ||
         (int64_t)hp.wn * kTileEnvs > 20LL * kEtThreads || smem > (size_t)h->max_smem)
         return QP_OK;
     // the state matrix goes to the tensor core as its tf32 value alone: the prices must be tf32-exact

@@ -88,15 +88,16 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     uint8_t* Abwd = ring;                                       // after the forward: X^T [halves*128 x 32]
     uint8_t* Bbwd_hi = ring + (size_t)halves * 16384;
     uint8_t* Bbwd_lo = Bbwd_hi + TB;
-    float* HV = reinterpret_cast<float*>(Afwd);                 // after the forward: h(s)*dz2, [Np][32]
+    float* HS = reinterpret_cast<float*>(Afwd);                 // after the forward: h(s), [Np][33]
+    float* ZN = HS + (size_t)Np * kXStride;                     // after the forward: window part of z1(s'), [Np][33]
     float* Xs = reinterpret_cast<float*>(ring + 4 * (size_t)TB);  // master window [(wn+1)][33]
     float* W2s = Xs + (size_t)(wn + 1) * kXStride;
     W2s = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(W2s) + 15) & ~(uintptr_t)15);
     float* Wb = W2s + (size_t)H * 4;
     float* Ws = Wb + H;
     float* XE = Ws + H;                                         // [2][32]
-    float* qpart = XE + 64;                                     // [3 parts][2 states][3][32]
-    float* dz2s = qpart + 3 * 2 * 3 * 32;                       // [32]
+    float* qpart = XE + 64;                                     // [12 warps][2 states][3][32]
+    float* dz2s = qpart + 12 * 2 * 3 * 32;                      // [32]
     int* kns = reinterpret_cast<int*>(dz2s + 32);               // [32]
     uint64_t* bars = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(kns + 32) + 7) & ~(uintptr_t)7);
     uint64_t* full = bars;          // [2]
@@ -117,7 +118,6 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     const int q4 = warp & 3, part = warp >> 2;                  // TMEM lane quarter / column part of this warp
     const int n_ld = Np >> 4;                                   // 16-column TMEM loads per row
     const int ld0 = part * n_ld / 3, ld1 = (part + 1) * n_ld / 3;
-    constexpr int kMaxLd = 6;                                   // <= 96 columns per warp (Np <= 288)
 
     if (tid == 0) {
         mbar_init(full, 1); mbar_init(full + 1, 1); mbar_init(empty, 1); mbar_init(empty + 1, 1);
@@ -167,21 +167,30 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         const int32_t istep = ea.step0 + sidx;
         const uint32_t par = (uint32_t)sidx & 1u;
         float q_s[3] = {0.f, 0.f, 0.f}, q_n[3] = {0.f, 0.f, 0.f};
-        float keep[kMaxLd * 16];                                // q4 == 0: h(s); q4 == 1: window part of z1(s')
         int action = 0, explored = 0, a_eff = 2, kn = 0;
         float r32 = 0.0f, target = 0.0f, dz2 = 0.0f, p_next = 0.0f;
         double nb = budget, p_new = 0.0;
         int32_t ns = shares;
-
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 0] = clock64();
         if (has_tile) {
-            // ---- S0: A operand of the forward (K-major, swizzled) from the master window; small tables
+            // ---- S0: small tables (global loads issued first), then the A operand of the forward
+            // (K-major, swizzled) from the master window
+            float4 tw2 = make_float4(0.f, 0.f, 0.f, 0.f);
+            float twb = 0.0f, tws = 0.0f;
+            if (tid < H) {
+                tw2 = make_float4(__ldcg(W2g + tid * 3), __ldcg(W2g + tid * 3 + 1), __ldcg(W2g + tid * 3 + 2), 0.f);
+                twb = __ldcg(W1g + (size_t)wn * H + tid);
+                tws = __ldcg(W1g + (size_t)(wn + 1) * H + tid);
+            }
+#pragma unroll 4
             for (int it = warp; it < 64 * nkb; it += nwarps) {          // (row, k-block): lanes over the 32 k of the block
                 const int row = it & 63, kb = it >> 6;
                 const int k = kb * 32 + lane + (row >> 5);              // rows 32..63: state s' = window shifted by one
                 const float v = (k - (row >> 5) < wn && k <= wn) ? Xs[k * kXStride + (row & 31)] : 0.0f;
                 *reinterpret_cast<float*>(Afwd + (size_t)kb * 8192 + et_swz(row, lane)) = v;
             }
-            for (int j = tid; j < H; j += nthreads) {
+            if (tid < H) { reinterpret_cast<float4*>(W2s)[tid] = tw2; Wb[tid] = twb; Ws[tid] = tws; }
+            for (int j = tid + nthreads; j < H; j += nthreads) {       // hidden > 384 (not the reference shape)
                 reinterpret_cast<float4*>(W2s)[j] = make_float4(__ldcg(W2g + j * 3), __ldcg(W2g + j * 3 + 1), __ldcg(W2g + j * 3 + 2), 0.f);
                 Wb[j] = __ldcg(W1g + (size_t)wn * H + j);
                 Ws[j] = __ldcg(W1g + (size_t)(wn + 1) * H + j);
@@ -190,7 +199,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             et_fence_async_smem();
         }
         __syncthreads();
-
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 1] = clock64();
         if (has_tile) {
             // ---- S1: forward contraction on the tensor cores
             if (warp == 0 && lane == 0) {
@@ -224,48 +233,58 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             tc_wait(tf_fwd, par);
             tc_fence_after();
 
-            // ---- S2: hidden layer of s (q4 == 0) / window part of s' (q4 == 1) out of TMEM
+            if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 2] = clock64();
+            // ---- S2: out of TMEM into shared memory: h(s) (lane quarter 0) and the window part of z1(s')
+            // (lane quarter 1); the element-wise work after this runs on all twelve warps
             if (q4 < 2) {
-                float pq[3] = {0.f, 0.f, 0.f};
                 const float xb = __double2float_rn(budget), xs = (float)shares;
+#pragma unroll 1
+                for (int l = ld0; l < ld1; ++l) {
+                    float v[16];
+                    et_tmem_ld16(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(l * 16), v);
 #pragma unroll
-                for (int l = 0; l < kMaxLd; ++l) {
-                    if (ld0 + l < ld1) {
-                        float v[16];
-                        et_tmem_ld16(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)((ld0 + l) * 16), v);
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            const int c = (ld0 + l) * 16 + j;
-                            float out = v[j];
-                            if (q4 == 0) {
-                                float h = 0.0f;
-                                if (c < H) {
-                                    const float z = fmaf(xs, Ws[c], fmaf(xb, Wb[c], v[j])) + bias;
-                                    h = z > 0.0f ? z : 0.0f;
-                                    const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
-                                    pq[0] = fmaf(h, w2.x, pq[0]); pq[1] = fmaf(h, w2.y, pq[1]); pq[2] = fmaf(h, w2.z, pq[2]);
-                                }
-                                out = h;
+                    for (int j = 0; j < 16; ++j) {
+                        const int c = l * 16 + j;
+                        float out = v[j];
+                        if (q4 == 0) {
+                            out = 0.0f;
+                            if (c < H) {
+                                const float z = fmaf(xs, Ws[c], fmaf(xb, Wb[c], v[j])) + bias;
+                                out = z > 0.0f ? z : 0.0f;
                             }
-                            keep[l * 16 + j] = out;
+                            HS[c * kXStride + lane] = out;
+                        } else {
+                            ZN[c * kXStride + lane] = out;
                         }
                     }
-                }
-                if (q4 == 0) {
-#pragma unroll
-                    for (int t = 0; t < 3; ++t) qpart[((part * 2 + 0) * 3 + t) * 32 + lane] = pq[t];
                 }
             }
             tc_fence_before();
         }
         __syncthreads();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 3] = clock64();
 
         if (has_tile) {
-            // ---- S3: SelectionAction, decision, reward (every warp keeps its own copy), then Q(s')
+            // ---- S3: Q(s) (columns dealt round-robin to the warps, fixed order), SelectionAction, decision,
+            // reward (every warp keeps its own copy), then Q(s')
+            {
+                float pq[3] = {0.f, 0.f, 0.f};
+#pragma unroll 4
+                for (int c = warp; c < H; c += nwarps) {
+                    const float h = HS[c * kXStride + lane];
+                    const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
+                    pq[0] = fmaf(h, w2.x, pq[0]); pq[1] = fmaf(h, w2.y, pq[1]); pq[2] = fmaf(h, w2.z, pq[2]);
+                }
+#pragma unroll
+                for (int t = 0; t < 3; ++t) qpart[((warp * 2 + 0) * 3 + t) * 32 + lane] = pq[t];
+            }
+        }
+        __syncthreads();
+        if (has_tile) {
 #pragma unroll
             for (int t = 0; t < 3; ++t) {
                 float s = 0.0f;
-                for (int pp = 0; pp < 3; ++pp) s += qpart[((pp * 2 + 0) * 3 + t) * 32 + lane];
+                for (int w = 0; w < nwarps; ++w) s += qpart[((w * 2 + 0) * 3 + t) * 32 + lane];
                 s += bias;
                 q_s[t] = s > 0.0f ? s : 0.0f;
             }
@@ -287,36 +306,29 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             else if (action == 1 && base_n > 0) { nb = __dadd_rn(base_b, p_new); ns = base_n - 1; a_eff = 1; }
             const double newp = __dadd_rn(nb, __dmul_rn((double)ns, p_new));
             r32 = __double2float_rn(__dsub_rn(newp, cur));
-            if (q4 == 1) {
+            {
                 const float xnb = __double2float_rn(nb), xns = (float)ns;
                 float pq[3] = {0.f, 0.f, 0.f};
-#pragma unroll
-                for (int l = 0; l < kMaxLd; ++l) {
-                    if (ld0 + l < ld1) {
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            const int c = (ld0 + l) * 16 + j;
-                            if (c < H) {
-                                const float z = fmaf(xns, Ws[c], fmaf(xnb, Wb[c], keep[l * 16 + j])) + bias;
-                                const float h = z > 0.0f ? z : 0.0f;
-                                const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
-                                pq[0] = fmaf(h, w2.x, pq[0]); pq[1] = fmaf(h, w2.y, pq[1]); pq[2] = fmaf(h, w2.z, pq[2]);
-                            }
-                        }
-                    }
+#pragma unroll 4
+                for (int c = warp; c < H; c += nwarps) {
+                    const float z = fmaf(xns, Ws[c], fmaf(xnb, Wb[c], ZN[c * kXStride + lane])) + bias;
+                    const float h = z > 0.0f ? z : 0.0f;
+                    const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
+                    pq[0] = fmaf(h, w2.x, pq[0]); pq[1] = fmaf(h, w2.y, pq[1]); pq[2] = fmaf(h, w2.z, pq[2]);
                 }
 #pragma unroll
-                for (int t = 0; t < 3; ++t) qpart[((part * 2 + 1) * 3 + t) * 32 + lane] = pq[t];
+                for (int t = 0; t < 3; ++t) qpart[((warp * 2 + 1) * 3 + t) * 32 + lane] = pq[t];
             }
         }
         __syncthreads();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 4] = clock64();
 
         if (has_tile) {
-            // ---- S4: TD target, dZ1 (hi/lo, K-major over the episodes), h*dz2, X^T operand
+            // ---- S4: TD target; dZ1 as a K-major (episodes contiguous) tf32 hi/lo pair; X^T operand
 #pragma unroll
             for (int t = 0; t < 3; ++t) {
                 float s = 0.0f;
-                for (int pp = 0; pp < 3; ++pp) s += qpart[((pp * 2 + 1) * 3 + t) * 32 + lane];
+                for (int w = 0; w < nwarps; ++w) s += qpart[((w * 2 + 1) * 3 + t) * 32 + lane];
                 s += bias;
                 q_n[t] = s > 0.0f ? s : 0.0f;
             }
@@ -326,29 +338,18 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             target = __fadd_rn(r32, __fmul_rn(hp.gamma, qn_k));
             const float dq = -__fmul_rn(2.0f, __fsub_rn(target, qs_k));
             dz2 = (valid && qs_k > 0.0f) ? dq : 0.0f;
-            if (q4 == 0) {
-#pragma unroll
-                for (int l = 0; l < kMaxLd; ++l) {
-                    if (ld0 + l < ld1) {
-#pragma unroll
-                        for (int j = 0; j < 16; ++j) {
-                            const int c = (ld0 + l) * 16 + j;
-                            float d1 = 0.0f, hvv = 0.0f;
-                            if (c < H) {
-                                const float h = keep[l * 16 + j];
-                                const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
-                                const float w2k = kn == 0 ? w2.x : (kn == 1 ? w2.y : w2.z);
-                                d1 = h > 0.0f ? __fmul_rn(dz2, w2k) : 0.0f;
-                                hvv = __fmul_rn(h, dz2);
-                            }
-                            const float hi = et_tf32(d1);
-                            const uint32_t off = et_swz(c, lane);
-                            *reinterpret_cast<float*>(Bbwd_hi + off) = hi;
-                            *reinterpret_cast<float*>(Bbwd_lo + off) = d1 - hi;
-                            HV[c * 32 + lane] = hvv;
-                        }
-                    }
+#pragma unroll 4
+            for (int c = warp; c < Np; c += nwarps) {
+                float d1 = 0.0f;
+                if (c < H) {
+                    const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
+                    const float w2k = kn == 0 ? w2.x : (kn == 1 ? w2.y : w2.z);
+                    d1 = HS[c * kXStride + lane] > 0.0f ? __fmul_rn(dz2, w2k) : 0.0f;
                 }
+                const float hi = et_tf32(d1);
+                const uint32_t off = et_swz(c, lane);
+                *reinterpret_cast<float*>(Bbwd_hi + off) = hi;
+                *reinterpret_cast<float*>(Bbwd_lo + off) = d1 - hi;
             }
             if (warp == 0) {
                 XE[lane] = __double2float_rn(budget);
@@ -371,12 +372,14 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                 }
             }
             // X^T operand: row k = window element k of every episode (rows >= wn are zero)
+#pragma unroll 4
             for (int k = warp; k < halves * 128; k += nwarps)
                 *reinterpret_cast<float*>(Abwd + et_swz(k, lane)) = k < wn ? Xs[k * kXStride + lane] : 0.0f;
             budget = nb; shares = ns; share_value = p_new;             // carry (TrainerChildActor.scala:99-102)
             et_fence_async_smem();
         }
         __syncthreads();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 5] = clock64();
 
         if (has_tile) {
             // ---- S5: backward contraction on the tensor cores; dW2 and the two extra dW1 rows meanwhile
@@ -395,24 +398,30 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             }
             float* out = ea.part1 + (size_t)blockIdx.x * ((size_t)D * H);
             float* out2 = a.dw2_part + (size_t)blockIdx.x * (3 * H);
-            for (int idx = tid; idx < 3 * H; idx += nthreads) {          // dW2[c][t] = sum_e [kn_e == t] h_e[c] dz2_e
-                const int c = idx / 3, t = idx - c * 3;
-                float s = 0.0f;
-                for (int el = 0; el < kTileEnvs; ++el) s += (kns[el] == t) ? HV[c * 32 + el] : 0.0f;
-                out2[idx] = s;
-            }
-            for (int idx = tid; idx < 2 * H; idx += nthreads) {          // dW1 rows wn (budget), wn + 1 (shares)
-                const int m = idx / H, c = idx - m * H;
-                float s = 0.0f;
+            // dW2[c][t] = sum_e [kn_e == t] h_e[c] dz2_e and the budget / shares rows of dW1: one thread per
+            // hidden column, episodes summed sequentially out of shared memory (fixed order, no shuffles)
+            for (int c = tid; c < H; c += nthreads) {
+                const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
+                float s0 = 0.f, s1 = 0.f, s2 = 0.f, x0 = 0.f, x1 = 0.f;
+#pragma unroll 8
                 for (int el = 0; el < kTileEnvs; ++el) {
-                    const uint32_t off = et_swz(c, el);
-                    const float d1 = *reinterpret_cast<const float*>(Bbwd_hi + off) + *reinterpret_cast<const float*>(Bbwd_lo + off);
-                    s = fmaf(XE[m * 32 + el], d1, s);
+                    const float h = HS[c * kXStride + el];
+                    const float dz = dz2s[el];
+                    const int k = kns[el];
+                    const float hv = __fmul_rn(h, dz);
+                    s0 += k == 0 ? hv : 0.0f; s1 += k == 1 ? hv : 0.0f; s2 += k == 2 ? hv : 0.0f;
+                    const float w2k = k == 0 ? w2.x : (k == 1 ? w2.y : w2.z);
+                    const float d1 = h > 0.0f ? __fmul_rn(dz, w2k) : 0.0f;
+                    x0 = fmaf(XE[el], d1, x0);
+                    x1 = fmaf(XE[32 + el], d1, x1);
                 }
-                out[(size_t)(wn + m) * H + c] = s;
+                out2[c * 3 + 0] = s0; out2[c * 3 + 1] = s1; out2[c * 3 + 2] = s2;
+                out[(size_t)wn * H + c] = x0;
+                out[(size_t)(wn + 1) * H + c] = x1;
             }
             tc_wait(tf_bwd, par);
             tc_fence_after();
+            if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 6] = clock64();
             // ---- S6: dW1 partial out of TMEM
             for (int hf = 0; hf < halves; ++hf) {
                 const int k = hf * 128 + q4 * 32 + lane;
@@ -431,6 +440,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             tc_fence_before();
         }
         __syncthreads();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 7] = clock64();
         if (!ea.apply_in_kernel) break;
         // ---- S7: slide the window
         if (has_tile) {

@@ -31,6 +31,7 @@ def make_policy(cfg: O.Config, params=None, acc=None, fused=None):
         pol.set_weights(params, acc)
     if fused is not None:
         pol.set_option("fused", int(fused))   # 1: persistent episode kernel, 0: three kernels per step
+        pol.set_option("ep_tc", 0)            # the FFMA form; the tcgen05 form has its own tests below
     return pol
 
 
@@ -335,8 +336,7 @@ def test_persistent_tensor_core_kernel_teacher_forced(bookkeeping, n_envs, N0):
     w0 = (O.gen_normal(21, 0, cfg.P) * 0.05).astype(np.float32)
     o = O.Oracle(cfg, params=w0)
     o.env_create(prices, soe, 1000.0, N0, env_id_base=10 ** 10)
-    with make_policy(cfg, fused=1) as pol:
-        pol.set_option("ep_tc", 1)
+    with make_policy(cfg) as pol:                 # defaults: persistent kernel, tensor-core form when eligible
         pol.env_create(prices, soe, 1000.0, N0, env_id_base=10 ** 10)
         assert pol.get_option("ep_tc_active") == 1
         for i in (0, 1, 57, 150, 198):
@@ -357,8 +357,7 @@ def test_persistent_tensor_core_kernel_teacher_forced(bookkeeping, n_envs, N0):
                 np.testing.assert_array_equal(bd, o.env["budget"])
                 np.testing.assert_array_equal(sd, o.env["shares"])
     # prices that are not tf32-exact keep the FFMA persistent kernel
-    with make_policy(cfg, fused=1) as pol:
-        pol.set_option("ep_tc", 1)
+    with make_policy(cfg) as pol:
         pol.env_create(prices * np.float32(1.0371), soe, 1000.0, N0)
         assert pol.get_option("ep_tc_active") == 0 and pol.get_option("fused_active") == 1
 
@@ -373,7 +372,7 @@ def test_persistent_tensor_core_kernel_free_running():
     w = (O.gen_normal(3, 0, cfg.P) * 0.05).astype(np.float32)
     res = []
     for tc in (1, 0):
-        with make_policy(cfg, params=w, fused=1) as pol:
+        with make_policy(cfg, params=w) as pol:
             pol.set_option("ep_tc", tc)
             pol.env_create(prices, soe, 1000.0, 1)
             pol.env_set_state(step=120)
