@@ -357,8 +357,10 @@ def run_ours(args):
         dur = ep_us * 1e-6
         step_bytes = bytes_per_env_step(n_local) * n_local
         step_flops = float(FLOP_PER_ENV_STEP) * n_local
+        ep_tc = bool(pol.get_option("ep_tc_active"))
         roofline = dict(
-            bound="hbm", kernel="episode_kernel (persistent, all env-steps of a launch)",
+            bound="hbm", kernel=("episode_tc_kernel (persistent; in-CTA contractions on tcgen05, 3xTF32)" if ep_tc
+                                 else "episode_kernel (persistent, all env-steps of a launch)"),
             achieved=step_bytes / dur / 1e9, peak=peaks["hbm_gbs"], unit="GB/s",
             frac=step_bytes / dur / 1e9 / peaks["hbm_gbs"], traffic=None,
             peak_source=peaks["source"] + " (burst copy)", avg_launch_us=ep_us * n_prof, us_per_env_step=ep_us,
@@ -371,10 +373,21 @@ def run_ours(args):
             bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP,
             three_kernel_path_us=dict(zip(names, split_us)),
         )
+        if ep_tc:
+            tf32_peak = peaks["bf16_tflops"] / 2.0
+            roofline["tensor"] = dict(achieved=step_flops / dur / 1e12, peak=tf32_peak / 3.0, unit="TFLOP/s",
+                                      frac=step_flops / dur / 1e12 / (tf32_peak / 3.0),
+                                      note="3xTF32-equivalent roof (measured bf16 / 2 / 3); the contractions are ~15 % of the "
+                                           "step, the rest is operand build, epilogues, grid barriers and the gradient sum")
+            pol.set_option("ep_tc", 0)
+            pol.env_reset()
+            pol.env_step(20)
+            roofline["ffma_persistent_kernel_us_per_env_step"] = float(pol.env_step_timed(n_prof)[0]) / n_prof * 1e3
+            pol.set_option("ep_tc", 1)
         # DRAM traffic from the committed ncu --set full capture of a 30-step launch of this kernel
         # (profiles/r1_v2_ncu_episode_kernel_summary.csv: 9.40 MB read + 4.91 MB written), per env-step;
         # far below the algorithmic bytes because windows stay in shared memory and weights/partials in L2
-        if n_local == 4096 and HIDDEN == 200:
+        if n_local == 4096 and HIDDEN == 200 and not ep_tc:
             roofline["traffic"] = (9.397248e6 + 4.906752e6) / 30.0
             roofline["traffic_note"] = "bytes per env-step of 4096 episodes, from profiles/r1_v2_ncu_episode_kernel_summary.csv"
     else:

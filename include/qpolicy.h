@@ -132,9 +132,9 @@ int qp_get_option(qp_handle* h, const char* key, int64_t* value);
  * K must be a multiple of 32*splits.  ms_out (may be NULL) receives the device time of one launch. */
 int qp_debug_tc_gemm(int32_t device, int64_t M, int64_t N, int64_t K, const float* A, const float* B, float* C,
                      int32_t passes, int32_t splits, float* ms_out);
-/* Tuning aid: with option "phase_clocks" = 1 the persistent kernel's CTA 0 stamps clock64() at 8
- * phase boundaries of every env-step of a launch; this copies the [n_steps x 8] stamps of the last
- * launch to out. */
+/* Tuning aid: with option "phase_clocks" = 1 the persistent kernel's CTA 0 stamps clock64() at up
+ * to 16 phase boundaries of every env-step of a launch (unused slots stay 0); this copies the
+ * [n_steps x 16] stamps of the last launch to out. */
 int qp_debug_phase_clocks(qp_handle* h, int32_t n_steps, int64_t* out);
 
 /* Per-step record for parity checks; host arrays of n_steps x n_envs entries (x3 for q_*),

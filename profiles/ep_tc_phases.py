@@ -8,7 +8,7 @@ import numpy as np
 import scala_akka_tensorflow_sharetrade_helper_b200 as q
 from oracle import oracle as O
 
-n, steps = 4096, 60
+n, steps = (int(sys.argv[1]) if len(sys.argv) > 1 else 4096), 60
 prices = O.gen_prices(42, 0, n, 1000)
 with q.QDecisionPolicy(q.PolicyConfig()) as pol:
     pol.set_option("ep_tc", 1)
@@ -20,10 +20,17 @@ with q.QDecisionPolicy(q.PolicyConfig()) as pol:
 names = ["S0 operand build (A fwd, tables)", "S1 forward MMA (TMA ring + tcgen05)", "S2 epilogue 1 (h(s), z(s') out of TMEM)",
          "S3 select, book-keeping, Q(s')", "S4 TD, dZ1 hi/lo, h*dz2, X^T operand", "S5 backward MMA + dW2 + extra rows",
          "S6 epilogue 2 (dW1 partial out of TMEM)"]
-d = np.diff(c, axis=1).astype(np.float64)
+d = np.diff(c[:, :11], axis=1).astype(np.float64)
 tot = (c[1:, 0] - c[:-1, 0]).mean()
 for k, nm in enumerate(names):
     print(f"{nm:48s} {d[:, k].mean():9.0f} cyc  {d[:, k].mean() / tot * 100:5.1f}%")
-rest = (c[1:, 0] - c[:-1, 7]).mean()
-print(f"{'S7 shift, 2 grid.sync, phase B (+W1^T publish)':48s} {rest:9.0f} cyc  {rest / tot * 100:5.1f}%")
+for k, nm in ((7, "S7 window shift"), (8, "grid.sync 1 (wait for the slowest CTA)"), (9, "phase B: sum + AdaGrad + W1^T publish")):
+    print(f"{nm:48s} {d[:, k].mean():9.0f} cyc  {d[:, k].mean() / tot * 100:5.1f}%")
+rest = (c[1:, 0] - c[:-1, 10]).mean()
+print(f"{'grid.sync 2':48s} {rest:9.0f} cyc  {rest / tot * 100:5.1f}%")
 print(f"{'step total':48s} {tot:9.0f} cyc  (~{tot / 1.965e3:.1f} us)")
+
+# finer stamps (relative to the phase starts): S4 internals of warp 0, S6 of warp 11 and warp 0
+f = lambda a, b: (c[:, a] - c[:, b]).mean()
+print(f"S4: q_n sum + dZ1 loop {f(14, 4):.0f}; trace/XE + barrier {f(5, 14):.0f}")
+print(f"S5/S6: warp 11 enters S6 at +{f(11, 5):.0f} after S5 start, spends {f(12, 11):.0f}; warp 0 column loop {f(6, 5):.0f}, its S6 {f(13, 6):.0f}")

@@ -176,7 +176,8 @@ struct qp_handle {
     // persistent kernel with tensor-core contractions (qp_ep_tc.cuh)
     bool allow_ep_tc = true, ep_tc_ready = false;   // qp_set_option("ep_tc", 0) keeps the FFMA persistent kernel
     DevBuf<float> et_w_hi, et_w_lo;
-    CUtensorMap tm_et_hi, tm_et_lo;
+    CUtensorMap tm_et_hi, tm_et_lo, tm_et_part;
+    const float* tm_et_part_ptr = nullptr; int64_t tm_et_part_tiles = 0;   // what tm_et_part was encoded for
     int et_Kp = 0, et_nkb = 0, et_Np = 0, et_halves = 0;
     size_t et_smem = 0;
     Geometry geo;
@@ -409,6 +410,22 @@ int make_tmap(CUtensorMap* m, const float* base, uint64_t inner, uint64_t outer,
     return QP_OK;
 }
 
+// 3-D fp32 tensor [d2][d1][d0] for TMA stores of [32 x 32] boxes (128-byte rows, 128-byte swizzle)
+int make_tmap3_store(CUtensorMap* m, const float* base, uint64_t d0, uint64_t d1, uint64_t d2, uint64_t pitch1_bytes,
+                     uint64_t pitch2_bytes) {
+    EncodeTiledFn enc = nullptr;
+    QP_TRY(get_encode_tiled(&enc));
+    const cuuint64_t dims[3] = {d0, d1, d2};
+    const cuuint64_t strides[2] = {pitch1_bytes, pitch2_bytes};
+    const cuuint32_t box[3] = {32, 32, 1};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, (void*)base, dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(QP_ECUDA, "cuTensorMapEncodeTiled (3-D) failed with code " + std::to_string((int)r));
+    return QP_OK;
+}
+
 int launch_tc_gemm(cudaStream_t st, const CUtensorMap& a_hi, const CUtensorMap& a_lo, const CUtensorMap& b_hi,
                    const CUtensorMap& b_lo, const TcGemmArgs& g, int tiles_m, int tiles_n, int splits) {
     static bool attr_set[64] = {false};
@@ -619,10 +636,13 @@ int ep_tc_prepare(qp_handle* h) {
     if (!h->tile_ok || !h->geo.ep_ok || hp.H % 4 != 0) return QP_OK;
     const int Kp = (int)round_up(hp.wn, 32), nkb = Kp / 32, Np = (int)round_up(hp.H, 16), halves = (hp.wn + 127) / 128;
     const size_t TB = (size_t)Np * 128;
-    const size_t smem = 1024 + (size_t)nkb * 8192 + 4 * TB + (size_t)(hp.wn + 1) * kXStride * 4 + 16 + (size_t)hp.H * 16 +
+    const size_t smem = 1024 + (size_t)nkb * 8192 + 4 * TB + (size_t)halves * 16384 + 16 + (size_t)hp.H * 16 +
                         (size_t)hp.H * 8 + 256 + 2304 * 4 + 256 + 8 + 64 + 64;
-    if (Np > 256 || halves > 2 || halves * Np > 512 || (size_t)nkb * 8192 < 2 * (size_t)Np * kXStride * 4 || (size_t)halves * 16384 > 2 * TB ||
-        (int64_t)hp.wn * kTileEnvs > 20LL * kEtThreads || smem > (size_t)h->max_smem)
+    // the window ring needs one free row beyond the window; the partial's boxes are staged in the ring (12 x 8 KB)
+    if (halves * 128 < hp.wn + 2 || (size_t)12 * 8192 > 4 * TB || ((size_t)hp.H * 4) % 16 != 0 || ((size_t)h->P1 * 4) % 16 != 0)
+        return QP_OK;
+    if (Np > 256 || halves > 2 || halves * Np > 512 || (size_t)nkb * 8192 < 2 * (size_t)Np * kXStride * 4 || 
+        smem > (size_t)h->max_smem)
         return QP_OK;
     // the state matrix goes to the tensor core as its tf32 value alone: the prices must be tf32-exact
     DevBuf<int32_t> flag;
@@ -680,7 +700,7 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
     ea.n_rt = h->geo.ep_n_rt; ea.n_ct = h->geo.ep_n_ct; ea.nwf = h->geo.step_warps;
     ea.dbg = nullptr;
     if (h->want_dbg) {
-        QP_TRY(h->dbg.ensure((size_t)n_steps * 8));
+        QP_TRY(h->dbg.ensure((size_t)n_steps * qp::kDbgSlots));
         ea.dbg = h->dbg.p;
     }
     if (h->allow_ep_tc && h->ep_tc_ready && h->world == 1 && apply_in_kernel) {
@@ -688,7 +708,12 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
         x.ea = ea;
         x.w1T_hi = h->et_w_hi.p; x.w1T_lo = h->et_w_lo.p;
         x.Kp = h->et_Kp; x.nkb = h->et_nkb; x.Np = h->et_Np; x.halves = h->et_halves;
-        void* targs[] = {&h->tm_et_hi, &h->tm_et_lo, &x};
+        if (h->tm_et_part_ptr != h->part1.p || h->tm_et_part_tiles != n_tiles) {
+            QP_TRY(make_tmap3_store(&h->tm_et_part, h->part1.p, (uint64_t)h->hp.H, (uint64_t)h->hp.wn, (uint64_t)n_tiles,
+                                    (uint64_t)h->hp.H * sizeof(float), (uint64_t)h->P1 * sizeof(float)));
+            h->tm_et_part_ptr = h->part1.p; h->tm_et_part_tiles = n_tiles;
+        }
+        void* targs[] = {&h->tm_et_hi, &h->tm_et_lo, &h->tm_et_part, &x};
         QP_CUDA(cudaLaunchCooperativeKernel((const void*)episode_tc_kernel, dim3(h->num_sms), dim3(kEtThreads),
                                             targs, h->et_smem, h->stream));
         h->launches++;
@@ -1510,9 +1535,9 @@ int qp_debug_tc_gemm(int32_t device, int64_t M, int64_t N, int64_t K, const floa
 
 int qp_debug_phase_clocks(qp_handle* h, int32_t n_steps, int64_t* out) {
     if (!h || !out) return fail(QP_EINVAL, "null argument");
-    if (!h->dbg.p || (size_t)n_steps * 8 > h->dbg.cap) return fail(QP_ESTATE, "no phase stamps recorded");
+    if (!h->dbg.p || (size_t)n_steps * qp::kDbgSlots > h->dbg.cap) return fail(QP_ESTATE, "no phase stamps recorded");
     QP_TRY(use_device(h));
-    QP_CUDA(cudaMemcpyAsync(out, h->dbg.p, (size_t)n_steps * 8 * sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
+    QP_CUDA(cudaMemcpyAsync(out, h->dbg.p, (size_t)n_steps * qp::kDbgSlots * sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
     QP_CUDA(cudaStreamSynchronize(h->stream));
     return QP_OK;
 }

@@ -41,6 +41,12 @@ __device__ __forceinline__ float et_tf32(float x) {
     asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(t) : "f"(x));
     return __uint_as_float(t);
 }
+// h = relu(z_window + budget*W1[wn] + shares*W1[wn+1] + 0.1): one definition, so that every phase
+// that re-forms h from the stored window part agrees bit for bit
+__device__ __forceinline__ float et_hidden(float zwin, float xb, float xs, float wb, float ws, float bias) {
+    const float z = fmaf(xs, ws, fmaf(xb, wb, zwin)) + bias;
+    return z > 0.0f ? z : 0.0f;
+}
 __device__ __forceinline__ void et_fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory"); }
 
 __device__ __forceinline__ void et_tmem_ld16(uint32_t taddr, float* v) {
@@ -54,6 +60,35 @@ __device__ __forceinline__ void et_tmem_ld16(uint32_t taddr, float* v) {
 #pragma unroll
     for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
 }
+
+__device__ __forceinline__ void et_tmem_ld16_nowait(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+        : "r"(taddr));
+}
+__device__ __forceinline__ void et_tmem_ld32_nowait(uint32_t taddr, uint32_t* r) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
+          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]),
+          "=r"(r[16]), "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]),
+          "=r"(r[24]), "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+        : "r"(taddr));
+}
+// TMA tensor store (shared -> global) of one box; completion is tracked by the issuing thread's bulk groups
+__device__ __forceinline__ void et_tma_store_3d(const CUtensorMap* tmap, const void* smem_src, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];\n" ::"l"(tmap),
+                 "r"((uint32_t)__cvta_generic_to_shared(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
+__device__ __forceinline__ void et_bulk_commit() { asm volatile("cp.async.bulk.commit_group;\n" ::: "memory"); }
+__device__ __forceinline__ void et_bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;\n" ::: "memory"); }
+__device__ __forceinline__ void et_bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory"); }
+__device__ __forceinline__ void et_tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
+
 
 // W1[0:wn, :] (row-major [k][n]) -> K-major hi/lo copies [n][Kp], for parameters p in a float4 group
 __device__ __forceinline__ void et_publish_w(const EpTcArgs& x, int64_t p, const float4& w, int H, int wn) {
@@ -69,10 +104,11 @@ __device__ __forceinline__ void et_publish_w(const EpTcArgs& x, int64_t p, const
 }
 
 __global__ void __launch_bounds__(kEtThreads, 1)
-episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_constant__ CUtensorMap tW_lo, const EpTcArgs x) {
+episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_constant__ CUtensorMap tW_lo,
+                  const __grid_constant__ CUtensorMap tP, const EpTcArgs x) {
     namespace cg = cooperative_groups;
     cg::grid_group grid = cg::this_grid();
-    extern __shared__ uint8_t et_smem_raw[];
+    extern __shared__ __align__(1024) uint8_t et_smem_raw[];
     const EpisodeArgs& ea = x.ea;
     const StepArgs& a = ea.s;
     const Hyper& hp = a.hp;
@@ -82,24 +118,34 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     const int Np = x.Np, nkb = x.nkb, halves = x.halves;
     const uint32_t TB = (uint32_t)Np * 128u;                   // bytes of one [Np x 32] operand tile
 
-    uint8_t* base = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(et_smem_raw) + 1023) & ~(uintptr_t)1023);
+    // Every pointer below is the __shared__ symbol plus an offset: an integer round trip (the usual
+    // "(addr + 1023) & ~1023") makes the compiler lose the state space and emit generic LD/ST for all
+    // shared-memory traffic of the kernel.  The 1024-byte alignment comes from the declaration.
+    uint8_t* base = et_smem_raw;
+    if (tid == 0 && ((uint32_t)__cvta_generic_to_shared(base) & 1023u) != 0u) __trap();
+    const size_t off_ring = (size_t)nkb * 8192;
+    const size_t off_xs = off_ring + 4 * (size_t)TB;
+    const size_t off_w2s = off_xs + (size_t)halves * 16384;
     uint8_t* Afwd = base;                                       // nkb tiles of [64 x 32] (8 KB each)
-    uint8_t* ring = Afwd + (size_t)nkb * 8192;                  // 2 stages x (hi, lo) of [Np x 32]
-    uint8_t* Abwd = ring;                                       // after the forward: X^T [halves*128 x 32]
-    uint8_t* Bbwd_hi = ring + (size_t)halves * 16384;
+    uint8_t* ring = base + off_ring;                            // 2 stages x (hi, lo) of [Np x 32]
+    uint8_t* Bbwd_hi = ring;                                    // after the forward: dZ1 hi / lo, [Np x 32 episodes]
     uint8_t* Bbwd_lo = Bbwd_hi + TB;
-    float* HS = reinterpret_cast<float*>(Afwd);                 // after the forward: h(s), [Np][33]
+    float* HS = reinterpret_cast<float*>(Afwd);                 // after the forward: window part of z1(s), [Np][33]
     float* ZN = HS + (size_t)Np * kXStride;                     // after the forward: window part of z1(s'), [Np][33]
-    float* Xs = reinterpret_cast<float*>(ring + 4 * (size_t)TB);  // master window [(wn+1)][33]
-    float* W2s = Xs + (size_t)(wn + 1) * kXStride;
-    W2s = reinterpret_cast<float*>((reinterpret_cast<uintptr_t>(W2s) + 15) & ~(uintptr_t)15);
+    // master window, kept as the A operand of the backward contraction: X^T [R = halves*128 rows][32 episodes],
+    // K-major SWIZZLE_128B.  The rows are a ring: at step sidx of the launch window element k is row
+    // (k + sidx) mod R, so sliding the window is writing ONE row (the next price); the rows outside the
+    // window hold stale prices, whose products land in TMEM lanes that are never stored.
+    uint8_t* XT = base + off_xs;
+    const int Rm = halves * 128 - 1;
+    float* W2s = reinterpret_cast<float*>(base + off_w2s);
     float* Wb = W2s + (size_t)H * 4;
     float* Ws = Wb + H;
     float* XE = Ws + H;                                         // [2][32]
     float* qpart = XE + 64;                                     // [12 warps][2 states][3][32]
     float* dz2s = qpart + 12 * 2 * 3 * 32;                      // [32]
     int* kns = reinterpret_cast<int*>(dz2s + 32);               // [32]
-    uint64_t* bars = reinterpret_cast<uint64_t*>((reinterpret_cast<uintptr_t>(kns + 32) + 7) & ~(uintptr_t)7);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(base + ((off_w2s + (size_t)H * 24 + (64 + 12 * 2 * 3 * 32 + 64) * 4 + 7) & ~(size_t)7));
     uint64_t* full = bars;          // [2]
     uint64_t* empty = bars + 2;     // [2]
     uint64_t* tf_fwd = bars + 4;
@@ -135,7 +181,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     double budget = a.budget[ec], share_value = a.share_value[ec];
     int32_t shares = a.shares[ec];
     const float* my_row = a.prices + (int64_t)a.series_of_env[ec] * a.T;
-    for (int idx = tid; idx < (wn + 1) * kXStride; idx += nthreads) Xs[idx] = 0.0f;
+    for (int idx = tid; idx < halves * 4096; idx += nthreads) reinterpret_cast<float*>(XT)[idx] = 0.0f;
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
@@ -146,7 +192,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             const int el = it & 31, k = ((it >> 5) << 5) + lane;
             const float* src = reinterpret_cast<const float*>(
                 __shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(my_row), el)) + ea.step0;
-            if (k <= wn) cp_async4(Xs + k * kXStride + el, src + k);
+            if (k <= wn) cp_async4(XT + et_swz(k, el), src + k);
         }
         cp_async_commit();
         cp_async_wait_pending(0);
@@ -162,6 +208,9 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
 
     const uint32_t idesc = tc_instr_desc(128, Np);
     uint32_t ring_it = 0;                                       // k-blocks pushed through the ring so far
+    // every CTA streams the same W1^T tiles: start each at a different k-block so that the L2 requests
+    // of the grid spread over the whole matrix instead of all landing on one tile at a time
+    const int kb_first = (int)(blockIdx.x % (unsigned)nkb);
 
     for (int32_t sidx = 0; sidx < ea.n_steps; ++sidx) {
         const int32_t istep = ea.step0 + sidx;
@@ -171,7 +220,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         float r32 = 0.0f, target = 0.0f, dz2 = 0.0f, p_next = 0.0f;
         double nb = budget, p_new = 0.0;
         int32_t ns = shares;
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 0] = clock64();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 0] = clock64();
         if (has_tile) {
             // ---- S0: small tables (global loads issued first), then the A operand of the forward
             // (K-major, swizzled) from the master window
@@ -182,12 +231,17 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                 twb = __ldcg(W1g + (size_t)wn * H + tid);
                 tws = __ldcg(W1g + (size_t)(wn + 1) * H + tid);
             }
-#pragma unroll 4
-            for (int it = warp; it < 64 * nkb; it += nwarps) {          // (row, k-block): lanes over the 32 k of the block
-                const int row = it & 63, kb = it >> 6;
-                const int k = kb * 32 + lane + (row >> 5);              // rows 32..63: state s' = window shifted by one
-                const float v = (k - (row >> 5) < wn && k <= wn) ? Xs[k * kXStride + (row & 31)] : 0.0f;
-                *reinterpret_cast<float*>(Afwd + (size_t)kb * 8192 + et_swz(row, lane)) = v;
+#pragma unroll 2
+            for (int it = warp; it < 16 * nkb; it += nwarps) {          // (k-block, 16-byte chunk, state): lanes = episodes
+                const int half = it & 1, chunk = (it >> 1) & 7, kb = it >> 4;
+                const int kk = kb * 32 + chunk * 4;                     // columns kk..kk+3; state s' = window shifted by one
+                float v[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    v[j] = kk + j < wn ? *reinterpret_cast<const float*>(XT + et_swz((kk + j + half + sidx) & Rm, lane)) : 0.0f;
+                const int row = half * 32 + lane;
+                *reinterpret_cast<float4*>(Afwd + (size_t)kb * 8192 + (size_t)row * 128 + ((chunk ^ (row & 7)) << 4)) =
+                    make_float4(v[0], v[1], v[2], v[3]);
             }
             if (tid < H) { reinterpret_cast<float4*>(W2s)[tid] = tw2; Wb[tid] = twb; Ws[tid] = tws; }
             for (int j = tid + nthreads; j < H; j += nthreads) {       // hidden > 384 (not the reference shape)
@@ -199,13 +253,14 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             et_fence_async_smem();
         }
         __syncthreads();
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 1] = clock64();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 1] = clock64();
         if (has_tile) {
             // ---- S1: forward contraction on the tensor cores
             if (warp == 0 && lane == 0) {
                 fence_proxy_async();                                    // phase-B writes of W1^T -> TMA reads
-                for (int kb = 0; kb < nkb; ++kb) {
-                    const uint32_t it = ring_it + (uint32_t)kb, s = it & 1u, ph = (it >> 1) & 1u;
+                for (int kk = 0; kk < nkb; ++kk) {
+                    const int kb = (kk + kb_first) % nkb;
+                    const uint32_t it = ring_it + (uint32_t)kk, s = it & 1u, ph = (it >> 1) & 1u;
                     tc_wait(empty + s, ph ^ 1u);
                     uint8_t* st = ring + (size_t)s * 2 * TB;
                     mbar_arrive_expect_tx(full + s, 2 * TB);
@@ -213,8 +268,9 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                     tma_load_2d(st + TB, &tW_lo, kb * 32, 0, full + s);
                 }
             } else if (warp == 1 && lane == 0) {
-                for (int kb = 0; kb < nkb; ++kb) {
-                    const uint32_t it = ring_it + (uint32_t)kb, s = it & 1u, ph = (it >> 1) & 1u;
+                for (int kk = 0; kk < nkb; ++kk) {
+                    const int kb = (kk + kb_first) % nkb;
+                    const uint32_t it = ring_it + (uint32_t)kk, s = it & 1u, ph = (it >> 1) & 1u;
                     tc_wait(full + s, ph);
                     tc_fence_after();
                     uint8_t* st = ring + (size_t)s * 2 * TB;
@@ -222,7 +278,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                     const uint64_t db_hi = tc_smem_desc(st), db_lo = tc_smem_desc(st + TB);
 #pragma unroll
                     for (int k4 = 0; k4 < 4; ++k4) {
-                        tc_mma_tf32(tmem_base, da + 2 * k4, db_hi + 2 * k4, idesc, (kb > 0 || k4 > 0) ? 1u : 0u);
+                        tc_mma_tf32(tmem_base, da + 2 * k4, db_hi + 2 * k4, idesc, (kk > 0 || k4 > 0) ? 1u : 0u);
                         tc_mma_tf32(tmem_base, da + 2 * k4, db_lo + 2 * k4, idesc, 1u);
                     }
                     tc_commit(empty + s);
@@ -233,45 +289,33 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             tc_wait(tf_fwd, par);
             tc_fence_after();
 
-            if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 2] = clock64();
+            if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 2] = clock64();
             // ---- S2: out of TMEM into shared memory: h(s) (lane quarter 0) and the window part of z1(s')
             // (lane quarter 1); the element-wise work after this runs on all twelve warps
             if (q4 < 2) {
-                const float xb = __double2float_rn(budget), xs = (float)shares;
+                float* dstz = q4 == 0 ? HS : ZN;         // raw window part of z1(s) / z1(s'); h is formed where it is used
 #pragma unroll 1
                 for (int l = ld0; l < ld1; ++l) {
                     float v[16];
                     et_tmem_ld16(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(l * 16), v);
 #pragma unroll
-                    for (int j = 0; j < 16; ++j) {
-                        const int c = l * 16 + j;
-                        float out = v[j];
-                        if (q4 == 0) {
-                            out = 0.0f;
-                            if (c < H) {
-                                const float z = fmaf(xs, Ws[c], fmaf(xb, Wb[c], v[j])) + bias;
-                                out = z > 0.0f ? z : 0.0f;
-                            }
-                            HS[c * kXStride + lane] = out;
-                        } else {
-                            ZN[c * kXStride + lane] = out;
-                        }
-                    }
+                    for (int j = 0; j < 16; ++j) dstz[(l * 16 + j) * kXStride + lane] = v[j];
                 }
             }
             tc_fence_before();
         }
         __syncthreads();
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 3] = clock64();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 3] = clock64();
 
         if (has_tile) {
             // ---- S3: Q(s) (columns dealt round-robin to the warps, fixed order), SelectionAction, decision,
             // reward (every warp keeps its own copy), then Q(s')
             {
                 float pq[3] = {0.f, 0.f, 0.f};
+                const float xb = __double2float_rn(budget), xs = (float)shares;
 #pragma unroll 4
                 for (int c = warp; c < H; c += nwarps) {
-                    const float h = HS[c * kXStride + lane];
+                    const float h = et_hidden(HS[c * kXStride + lane], xb, xs, Wb[c], Ws[c], bias);
                     const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
                     pq[0] = fmaf(h, w2.x, pq[0]); pq[1] = fmaf(h, w2.y, pq[1]); pq[2] = fmaf(h, w2.z, pq[2]);
                 }
@@ -283,8 +327,12 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         if (has_tile) {
 #pragma unroll
             for (int t = 0; t < 3; ++t) {
+                float pw[12];
+#pragma unroll
+                for (int w = 0; w < 12; ++w) pw[w] = w < nwarps ? qpart[((w * 2 + 0) * 3 + t) * 32 + lane] : 0.0f;
                 float s = 0.0f;
-                for (int w = 0; w < nwarps; ++w) s += qpart[((w * 2 + 0) * 3 + t) * 32 + lane];
+#pragma unroll
+                for (int w = 0; w < 12; ++w) s += pw[w];
                 s += bias;
                 q_s[t] = s > 0.0f ? s : 0.0f;
             }
@@ -297,7 +345,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             if (hp.epsilon < thr) thr = hp.epsilon;
             if (u < thr) action = argmax3(q_s);
             else { explored = 1; action = (int)(((uint64_t)r[1] * 3u) >> 32); }
-            p_new = (double)Xs[wn * kXStride + lane];
+            p_new = (double)*reinterpret_cast<const float*>(XT + et_swz((wn + sidx) & Rm, lane));
             const double cur = __dadd_rn(budget, __dmul_rn((double)shares, share_value));
             const double base_b = hp.bookkeeping == 0 ? a.B0 : budget;
             const int32_t base_n = hp.bookkeeping == 0 ? a.N0 : shares;
@@ -311,8 +359,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                 float pq[3] = {0.f, 0.f, 0.f};
 #pragma unroll 4
                 for (int c = warp; c < H; c += nwarps) {
-                    const float z = fmaf(xns, Ws[c], fmaf(xnb, Wb[c], ZN[c * kXStride + lane])) + bias;
-                    const float h = z > 0.0f ? z : 0.0f;
+                    const float h = et_hidden(ZN[c * kXStride + lane], xnb, xns, Wb[c], Ws[c], bias);
                     const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
                     pq[0] = fmaf(h, w2.x, pq[0]); pq[1] = fmaf(h, w2.y, pq[1]); pq[2] = fmaf(h, w2.z, pq[2]);
                 }
@@ -321,14 +368,18 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             }
         }
         __syncthreads();
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 4] = clock64();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 4] = clock64();
 
         if (has_tile) {
             // ---- S4: TD target; dZ1 as a K-major (episodes contiguous) tf32 hi/lo pair; X^T operand
 #pragma unroll
             for (int t = 0; t < 3; ++t) {
+                float pw[12];
+#pragma unroll
+                for (int w = 0; w < 12; ++w) pw[w] = w < nwarps ? qpart[((w * 2 + 1) * 3 + t) * 32 + lane] : 0.0f;
                 float s = 0.0f;
-                for (int w = 0; w < nwarps; ++w) s += qpart[((w * 2 + 1) * 3 + t) * 32 + lane];
+#pragma unroll
+                for (int w = 0; w < 12; ++w) s += pw[w];
                 s += bias;
                 q_n[t] = s > 0.0f ? s : 0.0f;
             }
@@ -338,19 +389,22 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             target = __fadd_rn(r32, __fmul_rn(hp.gamma, qn_k));
             const float dq = -__fmul_rn(2.0f, __fsub_rn(target, qs_k));
             dz2 = (valid && qs_k > 0.0f) ? dq : 0.0f;
+            const float xb_s = __double2float_rn(budget), xs_s = (float)shares;      // state s (carry not yet advanced)
 #pragma unroll 4
-            for (int c = warp; c < Np; c += nwarps) {
-                float d1 = 0.0f;
-                if (c < H) {
-                    const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
-                    const float w2k = kn == 0 ? w2.x : (kn == 1 ? w2.y : w2.z);
-                    d1 = HS[c * kXStride + lane] > 0.0f ? __fmul_rn(dz2, w2k) : 0.0f;
-                }
+            for (int c = warp; c < H; c += nwarps) {
+                const float hcol = et_hidden(HS[c * kXStride + lane], xb_s, xs_s, Wb[c], Ws[c], bias);
+                const float d1 = hcol > 0.0f ? __fmul_rn(dz2, W2s[c * 4 + kn]) : 0.0f;
                 const float hi = et_tf32(d1);
                 const uint32_t off = et_swz(c, lane);
                 *reinterpret_cast<float*>(Bbwd_hi + off) = hi;
                 *reinterpret_cast<float*>(Bbwd_lo + off) = d1 - hi;
             }
+            for (int c = H + warp; c < Np; c += nwarps) {               // padding columns of the MMA
+                const uint32_t off = et_swz(c, lane);
+                *reinterpret_cast<float*>(Bbwd_hi + off) = 0.0f;
+                *reinterpret_cast<float*>(Bbwd_lo + off) = 0.0f;
+            }
+            if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 14] = clock64();
             if (warp == 0) {
                 XE[lane] = __double2float_rn(budget);
                 XE[32 + lane] = (float)shares;
@@ -371,15 +425,12 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                     if (t.q_n) { t.q_n[ti * 3] = q_n[0]; t.q_n[ti * 3 + 1] = q_n[1]; t.q_n[ti * 3 + 2] = q_n[2]; }
                 }
             }
-            // X^T operand: row k = window element k of every episode (rows >= wn are zero)
-#pragma unroll 4
-            for (int k = warp; k < halves * 128; k += nwarps)
-                *reinterpret_cast<float*>(Abwd + et_swz(k, lane)) = k < wn ? Xs[k * kXStride + lane] : 0.0f;
+            if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 15] = clock64();
             budget = nb; shares = ns; share_value = p_new;             // carry (TrainerChildActor.scala:99-102)
             et_fence_async_smem();
         }
         __syncthreads();
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 5] = clock64();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 5] = clock64();
 
         if (has_tile) {
             // ---- S5: backward contraction on the tensor cores; dW2 and the two extra dW1 rows meanwhile
@@ -387,7 +438,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                 tc_fence_after();
                 const uint64_t db_hi = tc_smem_desc(Bbwd_hi), db_lo = tc_smem_desc(Bbwd_lo);
                 for (int hf = 0; hf < halves; ++hf) {
-                    const uint64_t da = tc_smem_desc(Abwd + (size_t)hf * 16384);
+                    const uint64_t da = tc_smem_desc(XT + (size_t)hf * 16384);
 #pragma unroll
                     for (int k4 = 0; k4 < 4; ++k4) {
                         tc_mma_tf32(tmem_base + (uint32_t)(hf * Np), da + 2 * k4, db_hi + 2 * k4, idesc, k4 > 0 ? 1u : 0u);
@@ -402,10 +453,11 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             // hidden column, episodes summed sequentially out of shared memory (fixed order, no shuffles)
             for (int c = tid; c < H; c += nthreads) {
                 const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
+                const float wb = Wb[c], ws = Ws[c];
                 float s0 = 0.f, s1 = 0.f, s2 = 0.f, x0 = 0.f, x1 = 0.f;
 #pragma unroll 8
                 for (int el = 0; el < kTileEnvs; ++el) {
-                    const float h = HS[c * kXStride + el];
+                    const float h = et_hidden(HS[c * kXStride + el], XE[el], XE[32 + el], wb, ws, bias);
                     const float dz = dz2s[el];
                     const int k = kns[el];
                     const float hv = __fmul_rn(h, dz);
@@ -421,47 +473,70 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             }
             tc_wait(tf_bwd, par);
             tc_fence_after();
-            if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 6] = clock64();
-            // ---- S6: dW1 partial out of TMEM
-            for (int hf = 0; hf < halves; ++hf) {
-                const int k = hf * 128 + q4 * 32 + lane;
-#pragma unroll 1
-                for (int l = ld0; l < ld1; ++l) {
-                    float v[16];
-                    et_tmem_ld16(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(hf * Np + l * 16), v);
-                    if (k < wn) {
+            if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 6] = clock64();
+            // ---- S6: dW1 partial out of TMEM.  A TMEM load hands every lane one row of the tile; stored
+            // straight to global memory that is 32 different lines per instruction.  Instead each warp puts
+            // [32 rows x 32 columns] boxes into shared memory (128-byte swizzle, conflict-free) and lane 0
+            // hands them to the TMA engine, which writes whole row segments while the warp fetches the next
+            // box.  Row p of the tile is window element (p - sidx) mod R; the tensor map ends at row wn, so
+            // the rows outside the window are clipped; the one block that wraps stores its wrapped rows itself.
+            if (ea.dbg && blockIdx.x == 0 && tid == 11 * 32) ea.dbg[(size_t)sidx * kDbgSlots + 11] = clock64();
+            {
+                const int ncb = (H + 31) >> 5;
+                uint8_t* stg = ring + (size_t)warp * 8192;              // two boxes per warp; dZ1 is dead by now
+                int n_box = 0;
+                for (int i = part; i < halves * ncb; i += 3) {
+                    const int hf = i / ncb, cb = i - hf * ncb;
+                    const int k0 = (hf * 128 + q4 * 32 - sidx) & Rm;
+                    const bool st_a = k0 < wn, st_b = k0 + 32 > Rm + 1;
+                    if (!st_a && !st_b) continue;
+                    uint32_t r[32];
+                    et_tmem_ld32_nowait(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(hf * Np + cb * 32), r);
+                    if (n_box >= 2) {
+                        if (lane == 0) et_bulk_wait_read1();            // the box two stores back has left its buffer
+                        __syncwarp();
+                    }
+                    et_tmem_wait_ld();
+                    uint8_t* buf = stg + (size_t)(n_box & 1) * 4096;
 #pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            if (l * 16 + 4 * j < H)
-                                *reinterpret_cast<float4*>(out + (size_t)k * H + l * 16 + 4 * j) = make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                    for (int j = 0; j < 8; ++j)
+                        *reinterpret_cast<uint4*>(buf + lane * 128 + ((j ^ (lane & 7)) << 4)) =
+                            make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+                    et_fence_async_smem();
+                    __syncwarp();
+                    if (lane == 0) {
+                        if (st_a) et_tma_store_3d(&tP, buf, cb * 32, k0, (int)blockIdx.x);
+                        et_bulk_commit();
+                    }
+                    ++n_box;
+                    if (st_b) {
+                        // the rows that wrapped around the ring (TMA store coordinates cannot be negative):
+                        // one 32-row block per step, stored row by row from the registers
+                        const int k = k0 + lane - (Rm + 1);
+                        if (k >= 0 && k < wn) {
+#pragma unroll
+                            for (int j = 0; j < 8; ++j)
+                                if (cb * 32 + 4 * j < H)
+                                    *reinterpret_cast<uint4*>(out + (size_t)k * H + cb * 32 + 4 * j) =
+                                        make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+                        }
                     }
                 }
             }
+            if (ea.dbg && blockIdx.x == 0 && tid == 11 * 32) ea.dbg[(size_t)sidx * kDbgSlots + 12] = clock64();
+            if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 13] = clock64();
             tc_fence_before();
         }
         __syncthreads();
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 7] = clock64();
-        if (!ea.apply_in_kernel) break;
-        // ---- S7: slide the window
-        if (has_tile) {
-            constexpr int kMaxPer = 20;
-            float mv[kMaxPer];
-            const int total = wn * kTileEnvs;
-#pragma unroll
-            for (int j = 0; j < kMaxPer; ++j) {
-                const int idx = tid + j * nthreads;
-                if (idx < total) mv[j] = Xs[((idx >> 5) + 1) * kXStride + (idx & 31)];
-            }
-            __syncthreads();
-#pragma unroll
-            for (int j = 0; j < kMaxPer; ++j) {
-                const int idx = tid + j * nthreads;
-                if (idx < total) Xs[(idx >> 5) * kXStride + (idx & 31)] = mv[j];
-            }
-            if (warp == 0) Xs[wn * kXStride + lane] = p_next;
-        }
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 7] = clock64();
+        if (!ea.apply_in_kernel) { et_bulk_wait_all(); break; }
+        // ---- S7: slide the window: one new row of the ring
+        if (has_tile && warp == 0) *reinterpret_cast<float*>(XT + et_swz((wn + 1 + sidx) & Rm, lane)) = p_next;
+        et_bulk_wait_all();                                             // the partial is in global memory
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 8] = clock64();
         __threadfence();
         grid.sync();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 9] = clock64();
 
         // ---- phase B: gradient sum over the tiles + AdaGrad (as episode_kernel) + tf32 hi/lo of the new W1
         {
@@ -516,6 +591,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                 }
             }
         }
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 10] = clock64();
         __threadfence();
         grid.sync();
     }

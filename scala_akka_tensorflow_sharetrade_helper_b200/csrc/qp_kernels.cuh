@@ -28,6 +28,7 @@ constexpr int kDw1MaxThreads = 384;
 constexpr int kDw1ChunkEnvs = 32;  // episodes per pipeline stage of the dW1 kernel
 constexpr int kDw1Stages = 2;
 constexpr int kDw1TileCols = 52;   // target width of one column tile of dW1 (grid.y = ceil(H / 52))
+constexpr int kDbgSlots = 16;      // clock64 stamps per env-step (qp_debug_phase_clocks)
 constexpr int kApplyLanes = 8;     // lanes cooperating on one parameter in the apply kernel
 constexpr int kEpRows = 16;        // persistent kernel: register tile of its dW1 contraction, 16 rows
 constexpr int kEpCols = 8;         //   x 8 columns (float4 groups ct and ct + n_ct)
@@ -921,7 +922,7 @@ __global__ void __launch_bounds__(kEpMaxThreads, 1) episode_kernel(const Episode
     for (int32_t sidx = 0; sidx < ea.n_steps; ++sidx) {
         const int32_t istep = ea.step0 + sidx;
         const uint32_t parity = (uint32_t)sidx & 1u;
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 0] = clock64();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 0] = clock64();
         // ---- current weights into shared memory (written by phase B of the previous step)
         if (has_tile) {
             if (warp == 0) {
@@ -1066,7 +1067,7 @@ __global__ void __launch_bounds__(kEpMaxThreads, 1) episode_kernel(const Episode
             for (int x = 0; x < 3; ++x) qpart[((warp * 2 + 1) * 3 + x) * 32 + lane] = pq[x];
         }
         __syncthreads();     // after this barrier nobody reads W1s any more: the Z tile may overwrite it
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 1] = clock64();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 1] = clock64();
 
         if (has_tile && fwd_warp) {
             // UpdateQ target and output-layer backward (QDecisionPolicyActor.scala:67-73, :49)
@@ -1132,7 +1133,7 @@ __global__ void __launch_bounds__(kEpMaxThreads, 1) episode_kernel(const Episode
             }
         __syncthreads();
 
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 2] = clock64();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 2] = clock64();
         // ---- dW1 partial of this tile: X^T · dZ1 over its 32 episodes, straight from shared memory
         if (has_tile) {
             float* out = ea.part1 + (size_t)blockIdx.x * ((size_t)D * H);
@@ -1181,7 +1182,7 @@ __global__ void __launch_bounds__(kEpMaxThreads, 1) episode_kernel(const Episode
             for (int j = tid; j < 3 * H; j += nthreads) dst2[j] = dw2acc[j];
         }
         __syncthreads();
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 3] = clock64();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 3] = clock64();
         if (!ea.apply_in_kernel) break;     // grid-uniform: single-step launch, the host continues with apply_kernel
         // ---- slide the window: row k <- row k + 1 (k < wn), row wn <- the new price
         if (has_tile) {
@@ -1201,10 +1202,10 @@ __global__ void __launch_bounds__(kEpMaxThreads, 1) episode_kernel(const Episode
             }
             if (warp == 0) Xs[wn * kXStride + lane] = p_next;
         }
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 4] = clock64();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 4] = clock64();
         __threadfence();
         grid.sync();
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 5] = clock64();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 5] = clock64();
 
         // ---- phase B: gradient sum over the tiles (fixed order) + AdaGrad, all CTAs.
         // Four lanes share one float4 of parameters; each lane loads its partials (j = sub, sub+4, ...)
@@ -1318,10 +1319,10 @@ __global__ void __launch_bounds__(kEpMaxThreads, 1) episode_kernel(const Episode
                 }
             }
         }
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 6] = clock64();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 6] = clock64();
         __threadfence();
         grid.sync();
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * 8 + 7] = clock64();
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 7] = clock64();
     }
 
     if (has_tile && warp == 0 && valid) {

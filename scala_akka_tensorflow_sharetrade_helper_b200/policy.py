@@ -221,7 +221,7 @@ class QDecisionPolicy:
         return int(v.value)
 
     def phase_clocks(self, n_steps):
-        out = np.zeros((n_steps, 8), np.int64)
+        out = np.zeros((n_steps, 16), np.int64)
         check(self._lib.qp_debug_phase_clocks(self._h, int(n_steps), _ptr(out)))
         return out
 
