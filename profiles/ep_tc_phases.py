@@ -32,5 +32,5 @@ print(f"{'step total':48s} {tot:9.0f} cyc  (~{tot / 1.965e3:.1f} us)")
 
 # finer stamps (relative to the phase starts): S4 internals of warp 0, S6 of warp 11 and warp 0
 f = lambda a, b: (c[:, a] - c[:, b]).mean()
-print(f"S4: q_n sum + dZ1 loop {f(14, 4):.0f}; trace/XE + barrier {f(5, 14):.0f}")
-print(f"S5/S6: warp 11 enters S6 at +{f(11, 5):.0f} after S5 start, spends {f(12, 11):.0f}; warp 0 column loop {f(6, 5):.0f}, its S6 {f(13, 6):.0f}")
+print(f"phase B: all groups summed after {f(14, 9):.0f}; AdaGrad + publish {f(10, 15):.0f}")
+print(f"S5/S6: warp 0 column loop {f(6, 5):.0f}, its S6 {f(13, 6):.0f}")

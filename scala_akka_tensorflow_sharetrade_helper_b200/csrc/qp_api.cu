@@ -158,7 +158,9 @@ struct qp_handle {
     ncclComm_t comm = nullptr;
     int rank = 0, world = 1;
     // in-kernel all-reduce over NVLink peer memory (persistent kernel, world > 1)
-    void* p2p_block = nullptr;          // [256 B of flags | 2 * P floats] exported to the other ranks
+    // exported to the other ranks: [256 B of flags | 2 * P floats] for episode_kernel, then, for episode_tc_kernel,
+    // [2 x 8 x p_pad {value, tag} pairs] (p2p_tc_offset / p2p_pad below)
+    void* p2p_block = nullptr;
     void* p2p_peer_block[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     bool p2p_ready = false, allow_p2p = true;
     unsigned int p2p_flag_base = 0;
@@ -178,6 +180,7 @@ struct qp_handle {
     DevBuf<float> et_w_hi, et_w_lo;
     CUtensorMap tm_et_hi, tm_et_lo, tm_et_part;
     const float* tm_et_part_ptr = nullptr; int64_t tm_et_part_tiles = 0;   // what tm_et_part was encoded for
+    DevBuf<unsigned long long> et_published;    // split grid barrier of episode_tc_kernel
     int et_Kp = 0, et_nkb = 0, et_Np = 0, et_halves = 0;
     size_t et_smem = 0;
     Geometry geo;
@@ -621,6 +624,9 @@ int wide_prepare_tc(qp_handle* h) {
     return QP_OK;
 }
 
+size_t p2p_tc_offset(const qp_handle* h) { return (size_t)round_up(256 + (int64_t)2 * h->P * (int64_t)sizeof(float), 256); }
+size_t p2p_pad(const qp_handle* h) { return (size_t)round_up(h->P, 64); }
+
 bool use_fused(const qp_handle* h) {
     const bool single = h->world == 1;
     const bool peers = h->world > 1 && h->world <= 8 && h->p2p_ready && h->allow_p2p;
@@ -637,7 +643,7 @@ int ep_tc_prepare(qp_handle* h) {
     const int Kp = (int)round_up(hp.wn, 32), nkb = Kp / 32, Np = (int)round_up(hp.H, 16), halves = (hp.wn + 127) / 128;
     const size_t TB = (size_t)Np * 128;
     const size_t smem = 1024 + (size_t)nkb * 8192 + 4 * TB + (size_t)halves * 16384 + 16 + (size_t)hp.H * 16 +
-                        (size_t)hp.H * 8 + 256 + 2304 * 4 + 256 + 8 + 64 + 64;
+                        (size_t)hp.H * 8 + 256 + 2304 * 4 + 256 + 8 + 256;
     // the window ring needs one free row beyond the window; the partial's boxes are staged in the ring (12 x 8 KB)
     if (halves * 128 < hp.wn + 2 || (size_t)12 * 8192 > 4 * TB || ((size_t)hp.H * 4) % 16 != 0 || ((size_t)h->P1 * 4) % 16 != 0)
         return QP_OK;
@@ -703,11 +709,17 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
         QP_TRY(h->dbg.ensure((size_t)n_steps * qp::kDbgSlots));
         ea.dbg = h->dbg.p;
     }
-    if (h->allow_ep_tc && h->ep_tc_ready && h->world == 1 && apply_in_kernel) {
+    if (h->allow_ep_tc && h->ep_tc_ready && apply_in_kernel) {
         EpTcArgs x{};
         x.ea = ea;
         x.w1T_hi = h->et_w_hi.p; x.w1T_lo = h->et_w_lo.p;
         x.Kp = h->et_Kp; x.nkb = h->et_nkb; x.Np = h->et_Np; x.halves = h->et_halves;
+        QP_TRY(h->et_published.ensure(1));
+        x.published = h->et_published.p;
+        x.p_pad = (int64_t)p2p_pad(h);
+        for (int r = 0; r < ea.world && ea.world > 1; ++r) {
+            x.pdata[r] = reinterpret_cast<uint2*>(reinterpret_cast<char*>(h->p2p_peer_block[r]) + p2p_tc_offset(h));
+        }
         if (h->tm_et_part_ptr != h->part1.p || h->tm_et_part_tiles != n_tiles) {
             QP_TRY(make_tmap3_store(&h->tm_et_part, h->part1.p, (uint64_t)h->hp.H, (uint64_t)h->hp.wn, (uint64_t)n_tiles,
                                     (uint64_t)h->hp.H * sizeof(float), (uint64_t)h->P1 * sizeof(float)));
@@ -870,7 +882,7 @@ int qp_destroy(qp_handle* h) {
     h->m_states.release(); h->m_next.release(); h->m_rewards.release(); h->m_steps.release();
     h->m_q.release(); h->m_ids.release(); h->m_actions.release();
     h->wZ1.release(); h->wdZ1.release(); h->wdz2.release(); h->wkn.release();
-    h->et_w_hi.release(); h->et_w_lo.release();
+    h->et_w_hi.release(); h->et_w_lo.release(); h->et_published.release();
     for (int j = 0; j < 4; ++j) { h->p_hi[j].release(); h->p_lo[j].release(); }
     h->pT_hi.release(); h->pT_lo.release(); h->xe_hi.release(); h->xe_lo.release();
     h->w1T_hi.release(); h->w1T_lo.release(); h->dzT_hi.release(); h->dzT_lo.release();
@@ -1569,7 +1581,7 @@ int qp_get_option(qp_handle* h, const char* key, int64_t* value) {
     if (std::strcmp(key, "fused") == 0) { *value = h->allow_fused ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "wide") == 0) { *value = h->wide ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "ep_tc_active") == 0) {
-        *value = (h->has_env && use_fused(h) && h->allow_ep_tc && h->ep_tc_ready && h->world == 1) ? 1 : 0;
+        *value = (h->has_env && use_fused(h) && h->allow_ep_tc && h->ep_tc_ready) ? 1 : 0;
         return QP_OK;
     }
     if (std::strcmp(key, "p2p_active") == 0) { *value = (h->has_env && h->world > 1 && use_fused(h)) ? 1 : 0; return QP_OK; }
@@ -1608,7 +1620,7 @@ int qp_dist_p2p_export(qp_handle* h, void* out, size_t out_bytes) {
     static_assert(sizeof(cudaIpcMemHandle_t) == QP_DIST_IPC_BYTES, "IPC handle size");
     QP_TRY(use_device(h));
     if (!h->p2p_block) {
-        const size_t bytes = 256 + (size_t)2 * h->P * sizeof(float);
+        const size_t bytes = p2p_tc_offset(h) + (size_t)2 * 8 * p2p_pad(h) * sizeof(uint2);
         QP_CUDA(cudaMalloc(&h->p2p_block, bytes));
         QP_CUDA(cudaMemset(h->p2p_block, 0, bytes));
         QP_CUDA(cudaDeviceSynchronize());
@@ -1632,8 +1644,7 @@ int qp_dist_p2p_import(qp_handle* h, const void* handles, int32_t world) {
         QP_CUDA(cudaIpcOpenMemHandle(&ptr, hd, cudaIpcMemLazyEnablePeerAccess));
         h->p2p_peer_block[r] = ptr;
     }
-    h->p2p_ready = true;
-    h->p2p_flag_base = 0;
+    h->p2p_ready = true;      // (p2p_flag_base keeps counting: the tags left in the blocks stay in the past)
     return QP_OK;
 }
 

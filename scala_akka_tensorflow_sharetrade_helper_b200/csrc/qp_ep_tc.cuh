@@ -28,6 +28,10 @@ struct EpTcArgs {
     int nkb;                         // Kp / 32
     int Np;                          // hidden rounded up to 16 (MMA N)
     int halves;                      // ceil(wn / 128): M = 128 tiles of the backward contraction
+    unsigned long long* published;   // CTAs that have finished phase B, summed over the steps of the launch
+    // several GPUs (ea.world > 1): every rank's exchange block, mapped into this process (CUDA IPC)
+    uint2* pdata[8];                 // [parity][src rank][p_pad] {value, step tag} of the ranks' shares of the gradient
+    int64_t p_pad;
 };
 
 #ifdef __CUDACC__
@@ -87,6 +91,17 @@ __device__ __forceinline__ void et_tma_store_3d(const CUtensorMap* tmap, const v
 __device__ __forceinline__ void et_bulk_commit() { asm volatile("cp.async.bulk.commit_group;\n" ::: "memory"); }
 __device__ __forceinline__ void et_bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;\n" ::: "memory"); }
 __device__ __forceinline__ void et_bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory"); }
+// Dataflow synchronisation between the CTAs of the (co-resident) grid.  Bounded: a flag that never
+// arrives traps the kernel instead of hanging the GPU.
+__device__ __forceinline__ void et_wait_count(const unsigned long long* c, unsigned long long want) {
+    unsigned long long v;
+    for (unsigned int spin = 0;; ++spin) {
+        asm volatile("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(c) : "memory");
+        if (v >= want) return;
+        if (spin > 64u) __nanosleep(32);
+        if (spin > (1u << 24)) __trap();
+    }
+}
 __device__ __forceinline__ void et_tmem_wait_ld() { asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory"); }
 
 
@@ -150,7 +165,9 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     uint64_t* empty = bars + 2;     // [2]
     uint64_t* tf_fwd = bars + 4;
     uint64_t* tf_bwd = bars + 5;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 6);
+    uint64_t* pb_bar = bars + 6;    // [4] phase B: a group of 32 partial segments has landed
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+
 
     const int64_t B = a.B;
     const int64_t n_tiles = (B + kTileEnvs - 1) / kTileEnvs;
@@ -168,6 +185,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     if (tid == 0) {
         mbar_init(full, 1); mbar_init(full + 1, 1); mbar_init(empty, 1); mbar_init(empty + 1, 1);
         mbar_init(tf_fwd, 1); mbar_init(tf_bwd, 1);
+        for (int g = 0; g < 4; ++g) mbar_init(pb_bar + g, 1);
         mbar_fence_init();
     }
     if (warp == 2) {
@@ -203,11 +221,26 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         for (int64_t p = ((int64_t)blockIdx.x * nthreads + tid) * 4; p < P1; p += (int64_t)gridDim.x * nthreads * 4)
             et_publish_w(x, p, __ldcg(reinterpret_cast<const float4*>(W1g + p)), H, wn);
     }
+    // phase B's division of the parameters over the CTAs (see there), and who publishes into which k-block
+    const int64_t P1 = (int64_t)D * H, P = P1 + 3 * (int64_t)H;
+    const int n1 = (int)n_tiles;
+    const int n_w1_ctas = max(1, (int)gridDim.x - 2);
+    const int chunk = (int)(((P1 + n_w1_ctas - 1) / n_w1_ctas + 3) & ~(int64_t)3);
+    const int chunk2 = ((3 * H + 1) / 2 + 3) & ~3;
+    const int pitch = max(chunk, chunk2);
+    const int rows_cap = min(128, (int)(off_xs / ((size_t)pitch * 4)) & ~3);   // a multiple of 4: see the running sums
+    // flow: the grid barrier after phase B is split.  A CTA that has published its share of the new
+    // weights adds one to a counter and moves on; only warp 0 of each CTA waits for the counter (before it
+    // starts the W1^T stream) while the other warps already build the A operand of the next step.
+    const bool flow = gridDim.x >= 8 && pitch <= nthreads && rows_cap >= 4 && x.published != nullptr;
+    const int n_publishers = (int)((P1 + chunk - 1) / chunk) + 2;
+    if (flow && blockIdx.x == 0 && tid == 0) *x.published = 0ull;
     __threadfence();
     grid.sync();
 
     const uint32_t idesc = tc_instr_desc(128, Np);
     uint32_t ring_it = 0;                                       // k-blocks pushed through the ring so far
+    uint32_t pb_phase = 0;
     // every CTA streams the same W1^T tiles: start each at a different k-block so that the L2 requests
     // of the grid spread over the whole matrix instead of all landing on one tile at a time
     const int kb_first = (int)(blockIdx.x % (unsigned)nkb);
@@ -221,30 +254,47 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         double nb = budget, p_new = 0.0;
         int32_t ns = shares;
         if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 0] = clock64();
+        // producer side of the W1^T ring: k-block number kk of this step into its stage
+        auto push_w_tiles = [&](int kk) {
+            const int kb = (kk + kb_first) % nkb;
+            const uint32_t it = ring_it + (uint32_t)kk, s = it & 1u, ph = (it >> 1) & 1u;
+            tc_wait(empty + s, ph ^ 1u);
+            uint8_t* st = ring + (size_t)s * 2 * TB;
+            mbar_arrive_expect_tx(full + s, 2 * TB);
+            tma_load_2d(st, &tW_hi, kb * 32, 0, full + s);
+            tma_load_2d(st + TB, &tW_lo, kb * 32, 0, full + s);
+        };
+        if (tid == 0) {
+            // the new weights are complete once every publisher of the previous step is through
+            if (flow && sidx > 0) et_wait_count(x.published, (unsigned long long)sidx * (unsigned long long)n_publishers);
+            // both stages are free: start the stream now, so that the first tiles travel while the warps
+            // build the A operand
+            fence_proxy_async();                                        // phase-B writes of W1^T -> TMA reads
+            if (has_tile)
+                for (int kk = 0; kk < min(2, nkb); ++kk) push_w_tiles(kk);
+        }
         if (has_tile) {
-            // ---- S0: small tables (global loads issued first), then the A operand of the forward
-            // (K-major, swizzled) from the master window
-            float4 tw2 = make_float4(0.f, 0.f, 0.f, 0.f);
-            float twb = 0.0f, tws = 0.0f;
-            if (tid < H) {
-                tw2 = make_float4(__ldcg(W2g + tid * 3), __ldcg(W2g + tid * 3 + 1), __ldcg(W2g + tid * 3 + 2), 0.f);
-                twb = __ldcg(W1g + (size_t)wn * H + tid);
-                tws = __ldcg(W1g + (size_t)(wn + 1) * H + tid);
-            }
+            // ---- S0: the A operand of the forward (K-major, swizzled) from the master window — it does not
+            // depend on the update in flight — then the small tables, once their publishers are through
+            const int w_first = flow ? 1 : 0;                           // (flow: warp 0 is busy feeding the ring)
+            if (warp >= w_first) {
 #pragma unroll 2
-            for (int it = warp; it < 16 * nkb; it += nwarps) {          // (k-block, 16-byte chunk, state): lanes = episodes
-                const int half = it & 1, chunk = (it >> 1) & 7, kb = it >> 4;
-                const int kk = kb * 32 + chunk * 4;                     // columns kk..kk+3; state s' = window shifted by one
-                float v[4];
+                for (int it = warp - w_first; it < 16 * nkb; it += nwarps - w_first) {   // (k-block, 16-byte chunk, state): lanes = episodes
+                    const int half = it & 1, chunk16 = (it >> 1) & 7, kb = it >> 4;
+                    const int kk = kb * 32 + chunk16 * 4;               // columns kk..kk+3; state s' = window shifted by one
+                    float v[4];
 #pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    v[j] = kk + j < wn ? *reinterpret_cast<const float*>(XT + et_swz((kk + j + half + sidx) & Rm, lane)) : 0.0f;
-                const int row = half * 32 + lane;
-                *reinterpret_cast<float4*>(Afwd + (size_t)kb * 8192 + (size_t)row * 128 + ((chunk ^ (row & 7)) << 4)) =
-                    make_float4(v[0], v[1], v[2], v[3]);
+                    for (int j = 0; j < 4; ++j)
+                        v[j] = kk + j < wn ? *reinterpret_cast<const float*>(XT + et_swz((kk + j + half + sidx) & Rm, lane)) : 0.0f;
+                    const int row = half * 32 + lane;
+                    *reinterpret_cast<float4*>(Afwd + (size_t)kb * 8192 + (size_t)row * 128 + ((chunk16 ^ (row & 7)) << 4)) =
+                        make_float4(v[0], v[1], v[2], v[3]);
+                }
             }
-            if (tid < H) { reinterpret_cast<float4*>(W2s)[tid] = tw2; Wb[tid] = twb; Ws[tid] = tws; }
-            for (int j = tid + nthreads; j < H; j += nthreads) {       // hidden > 384 (not the reference shape)
+        }
+        if (flow) __syncthreads();                                      // warp 0 has seen the counter: the tables are final
+        if (has_tile) {
+            for (int j = tid; j < H; j += nthreads) {
                 reinterpret_cast<float4*>(W2s)[j] = make_float4(__ldcg(W2g + j * 3), __ldcg(W2g + j * 3 + 1), __ldcg(W2g + j * 3 + 2), 0.f);
                 Wb[j] = __ldcg(W1g + (size_t)wn * H + j);
                 Ws[j] = __ldcg(W1g + (size_t)(wn + 1) * H + j);
@@ -257,16 +307,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         if (has_tile) {
             // ---- S1: forward contraction on the tensor cores
             if (warp == 0 && lane == 0) {
-                fence_proxy_async();                                    // phase-B writes of W1^T -> TMA reads
-                for (int kk = 0; kk < nkb; ++kk) {
-                    const int kb = (kk + kb_first) % nkb;
-                    const uint32_t it = ring_it + (uint32_t)kk, s = it & 1u, ph = (it >> 1) & 1u;
-                    tc_wait(empty + s, ph ^ 1u);
-                    uint8_t* st = ring + (size_t)s * 2 * TB;
-                    mbar_arrive_expect_tx(full + s, 2 * TB);
-                    tma_load_2d(st, &tW_hi, kb * 32, 0, full + s);
-                    tma_load_2d(st + TB, &tW_lo, kb * 32, 0, full + s);
-                }
+                for (int kk = 2; kk < nkb; ++kk) push_w_tiles(kk);      // (the first two went out before S0)
             } else if (warp == 1 && lane == 0) {
                 for (int kk = 0; kk < nkb; ++kk) {
                     const int kb = (kk + kb_first) % nkb;
@@ -404,7 +445,6 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                 *reinterpret_cast<float*>(Bbwd_hi + off) = 0.0f;
                 *reinterpret_cast<float*>(Bbwd_lo + off) = 0.0f;
             }
-            if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 14] = clock64();
             if (warp == 0) {
                 XE[lane] = __double2float_rn(budget);
                 XE[32 + lane] = (float)shares;
@@ -425,7 +465,6 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                     if (t.q_n) { t.q_n[ti * 3] = q_n[0]; t.q_n[ti * 3 + 1] = q_n[1]; t.q_n[ti * 3 + 2] = q_n[2]; }
                 }
             }
-            if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 15] = clock64();
             budget = nb; shares = ns; share_value = p_new;             // carry (TrainerChildActor.scala:99-102)
             et_fence_async_smem();
         }
@@ -523,7 +562,6 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                     }
                 }
             }
-            if (ea.dbg && blockIdx.x == 0 && tid == 11 * 32) ea.dbg[(size_t)sidx * kDbgSlots + 12] = clock64();
             if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 13] = clock64();
             tc_fence_before();
         }
@@ -538,13 +576,124 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         grid.sync();
         if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 9] = clock64();
 
-        // ---- phase B: gradient sum over the tiles + AdaGrad (as episode_kernel) + tf32 hi/lo of the new W1
-        {
+        // ---- phase B: gradient sum over the tiles + AdaGrad (as episode_kernel) + tf32 hi/lo of the new W1.
+        // W1: CTA c owns `chunk` consecutive parameters; their n_tiles partial segments come in as bulk
+        // copies (all in flight at once, one mbarrier), then one thread per parameter sums them out of
+        // shared memory in the order of the FFMA kernel: four interleaved running sums, (0+1)+(2+3).
+        // W2 (3*H parameters, its own partial buffer) is the last two CTAs' share, handled the same way.
+        if (flow) {
+            const bool w2_cta = (int)blockIdx.x >= (int)gridDim.x - 2;
+            const float* src = w2_cta ? a.dw2_part : ea.part1;
+            const int64_t stride = w2_cta ? 3 * (int64_t)H : P1;
+            const int64_t off = w2_cta ? (int64_t)((int)blockIdx.x - ((int)gridDim.x - 2)) * chunk2 : (int64_t)blockIdx.x * chunk;
+            const int64_t p0 = w2_cta ? P1 + off : off;
+            const int len = (int)max((int64_t)0, min((int64_t)(w2_cta ? chunk2 : chunk), stride - off));
+            if (len > 0) {
+                float* stage = reinterpret_cast<float*>(base);          // [rows][pitch], over the operand regions
+                const int64_t p = p0 + tid;
+                float av = 0.0f, wv = 0.0f;
+                if (tid < len) { av = ea.acc[p]; wv = ea.params_rw[p]; }
+                float s4[4] = {0.f, 0.f, 0.f, 0.f};
+                for (int r0 = 0; r0 < n1; r0 += rows_cap) {
+                    const int rows = min(rows_cap, n1 - r0), ngrp = (rows + 31) >> 5;
+                    if (tid < ngrp) mbar_arrive_expect_tx(pb_bar + tid, (uint32_t)min(32, rows - tid * 32) * (uint32_t)len * 4u);
+                    __syncthreads();
+                    if (tid < rows) {
+                        fence_proxy_async();
+                        bulk_g2s(stage + (size_t)tid * pitch, src + (size_t)(r0 + tid) * stride + off, (uint32_t)len * 4u,
+                                 pb_bar + (tid >> 5));
+                    }
+                    for (int g = 0; g < ngrp; ++g) {
+                        mbar_wait(pb_bar + g, (pb_phase >> g) & 1u);
+                        if (tid < len) {
+                            // r0 and the group starts are multiples of 4, so j mod 4 is the tile index mod 4
+                            const int j1 = min(rows, g * 32 + 32);
+                            int j = g * 32;
+#pragma unroll 2
+                            for (; j + 3 < j1; j += 4) {
+                                s4[0] += stage[(size_t)(j + 0) * pitch + tid];
+                                s4[1] += stage[(size_t)(j + 1) * pitch + tid];
+                                s4[2] += stage[(size_t)(j + 2) * pitch + tid];
+                                s4[3] += stage[(size_t)(j + 3) * pitch + tid];
+                            }
+                            for (; j < j1; ++j) s4[j & 3] += stage[(size_t)j * pitch + tid];
+                        }
+                    }
+                    pb_phase ^= (1u << ngrp) - 1u;
+                    if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 14] = clock64();
+                    __syncthreads();                                    // the stage is free for the next pass
+                }
+                if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 15] = clock64();
+                float g = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+                if (ea.world > 1 && tid < len) {
+                    // ---- gradient all-reduce over NVLink peer memory, share by share and without a fence:
+                    // every value travels as one 8-byte store {value, step tag} into the slot this rank owns in
+                    // every peer's exchange block (posted writes, one NVLink crossing); the receiver spins on its
+                    // LOCAL slots until the tag is this step's, then adds the values in rank order — the same
+                    // bits on every rank.  Two buffers by step parity: a rank cannot send step t+2 before it has
+                    // received this rank's step t+1, which is sent after step t has been read.
+                    const unsigned int want = ea.flag_base + (unsigned int)sidx + 1u;
+                    const size_t slot = (size_t)(sidx & 1) * (size_t)ea.world;
+                    const uint2 mine = make_uint2(__float_as_uint(g), want);
+#pragma unroll
+                    for (int r = 0; r < 8; ++r)
+                        if (r < ea.world && r != ea.rank)
+                            asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(x.pdata[r] + (slot + (size_t)ea.rank) * (size_t)x.p_pad + p),
+                                         "r"(mine.x), "r"(mine.y) : "memory");
+                    const uint2* local = x.pdata[ea.rank];
+                    float pv[8];
+                    unsigned long long t0 = 0;
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) {
+                        pv[r] = 0.0f;
+                        if (r < ea.world) {
+                            if (r == ea.rank) { pv[r] = g; continue; }
+                            const uint2* src = local + (slot + (size_t)r) * (size_t)x.p_pad + p;
+                            for (unsigned int spins = 0;; ++spins) {
+                                uint2 v;
+                                asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(src) : "memory");
+                                if (v.y == want) { pv[r] = __uint_as_float(v.x); break; }
+                                if ((spins & 4095u) == 4095u) {
+                                    unsigned long long t;
+                                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                                    if (t0 == 0) t0 = t;
+                                    else if (t - t0 > 20000000000ull) __trap();   // a rank never arrived: fail instead of hanging
+                                }
+                            }
+                        }
+                    }
+                    g = 0.0f;
+#pragma unroll
+                    for (int r = 0; r < 8; ++r) g += pv[r];
+                }
+                if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 12] = clock64();
+                if (tid < len) {
+                    ea.grad[p] = g;
+                    av = __fadd_rn(av, __fmul_rn(g, g));
+                    wv = __fsub_rn(wv, __fmul_rn(__fmul_rn(g, hp.lr), __fdiv_rn(1.0f, __fsqrt_rn(av))));
+                    ea.acc[p] = av;
+                    ea.params_rw[p] = wv;
+                    const int k = (int)(p / H), n = (int)(p - (int64_t)k * H);
+                    if (k < wn) {                                       // (W2 and the budget / shares rows: k >= wn)
+                        const float hi = et_tf32(wv);
+                        x.w1T_hi[(size_t)n * x.Kp + k] = hi;
+                        x.w1T_lo[(size_t)n * x.Kp + k] = wv - hi;
+                    }
+                }
+                // tell the consumers
+                __syncthreads();
+                if (tid == 0) {
+                    __threadfence();
+                    atomicAdd(x.published, 1ull);
+                }
+            }
+        } else {
+            // shapes the bulk scheme does not cover: four lanes per float4 group, straight from global memory
+            const int cta_lo = 0;
             const int64_t total_threads = (int64_t)gridDim.x * nthreads;
-            const int64_t P1 = (int64_t)D * H, P = P1 + 3 * (int64_t)H;
-            const int64_t n_tasks = ((P >> 2) * 4 + 31) / 32 * 32;
-            const int n1 = (int)n_tiles;
-            for (int64_t task = (int64_t)blockIdx.x * nthreads + tid; task < n_tasks; task += total_threads) {
+            const int64_t task_lo = 0;
+            // whole warps stay in the loop (shuffles below): the bound is on the warp's first task
+            for (int64_t task = task_lo + (int64_t)((int)blockIdx.x - cta_lo) * nthreads + tid; task - lane < P; task += total_threads) {
                 const int64_t p = (task >> 2) << 2;
                 const int sub = (int)(task & 3);
                 const bool in_range = p < P;
@@ -592,8 +741,10 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             }
         }
         if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 10] = clock64();
-        __threadfence();
-        grid.sync();
+        if (!flow) {
+            __threadfence();
+            grid.sync();
+        }
     }
 
     if (has_tile && warp == 0 && valid) {
