@@ -73,53 +73,82 @@ def measured_peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
-    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md).  One
+    nvidia-smi process (rank 0) watches every GPU of the job; it is started before the warm-up because its
+    own start-up takes longer than a short timed region, and only the samples whose timestamp falls inside
+    [mark_begin, mark_end] are kept."""
+    Q = ("timestamp,index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index: int):
-        self.gpu = gpu_index
+    def __init__(self, gpu_indices):
+        self.gpus = list(gpu_indices)
         self.proc = None
         self.path = None
+        self.t0 = self.t1 = None
 
     def start(self):
+        if not self.gpus:
+            return
         try:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             os.close(fd)
             self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "50",
-                 "-i", str(self.gpu)], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
+                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "20",
+                 "-i", ",".join(str(g) for g in self.gpus)], stdout=open(self.path, "w"), stderr=subprocess.DEVNULL)
         except Exception:
             self.proc = None
 
+    def mark_begin(self):
+        self.t0 = time.time()
+
+    def mark_end(self):
+        self.t1 = time.time()
+
     def stop(self):
+        import datetime
         out = dict(sm_mhz=None, sm_max_mhz=None, reasons=[], samples=0)
         if self.proc is None:
             return out
+        for _ in range(40):                 # nvidia-smi's own start-up can outlast a short region: wait for one sample
+            try:
+                if os.path.getsize(self.path) > 0:
+                    break
+            except OSError:
+                break
+            time.sleep(0.05)
         self.proc.terminate()
         try:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-        sm, mx, reasons = [], [], set()
+        rows = []
         try:
             for line in open(self.path):
                 f = [x.strip() for x in line.split(",")]
-                if len(f) < 8:
+                if len(f) < 9:
                     continue
                 try:
-                    sm.append(float(f[1])); mx.append(float(f[2]))
+                    ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                    rows.append((ts, float(f[2]), float(f[3]), f[5:9]))
                 except ValueError:
                     continue
-                for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[4:8]):
-                    if v == "Active":
-                        reasons.add(name)
             os.unlink(self.path)
         except Exception:
             pass
-        if sm:
-            out.update(sm_mhz=statistics.median(sm), sm_max_mhz=max(mx), samples=len(sm))
+        inside = [r for r in rows if self.t0 is not None and self.t1 is not None and self.t0 <= r[0] <= self.t1 + 0.02]
+        window = "timed region"
+        if not inside:                      # region shorter than the sampling period / nvidia-smi's start-up
+            inside, window = rows, "nearest samples (warm-up before / idle after a timed region shorter than the sampler's start-up)"
+        reasons = set()
+        for r in inside:
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), r[3]):
+                if v == "Active":
+                    reasons.add(name)
+        if inside:
+            sm = [r[1] for r in inside]
+            out.update(sm_mhz=statistics.median(sm), sm_min_mhz=min(sm), sm_max_mhz=max(r[2] for r in inside),
+                       samples=len(inside), gpus=len(self.gpus), window=window)
         out["reasons"] = sorted(reasons)
         return out
 
@@ -247,13 +276,15 @@ def run_ours(args):
     pol.env_create(prices_np, soe_np, BUDGET0, SHARES0, env_id_base=rank * n_local)
 
     def timed(fn, k, w):
+        # rank 0 watches the clocks of every GPU of the job
+        sampler = ClockSampler(([local] if world == 1 else range(world)) if rank == 0 else [])
+        sampler.start()
         for _ in range(w):
             fn()
         barrier()
-        sampler = ClockSampler(local)
-        sampler.start()
         l0 = pol.launch_count
         ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        sampler.mark_begin()
         t0 = time.perf_counter()
         with torch.cuda.stream(stream):
             ev0.record()
@@ -263,6 +294,7 @@ def run_ours(args):
             ev1.record()
         barrier()
         wall = time.perf_counter() - t0
+        sampler.mark_end()
         clocks = sampler.stop()
         ms = ev0.elapsed_time(ev1)
         launches = pol.launch_count - l0
@@ -358,32 +390,62 @@ def run_ours(args):
         step_bytes = bytes_per_env_step(n_local) * n_local
         step_flops = float(FLOP_PER_ENV_STEP) * n_local
         ep_tc = bool(pol.get_option("ep_tc_active"))
-        roofline = dict(
-            bound="hbm", kernel=("episode_tc_kernel (persistent; in-CTA contractions on tcgen05, 3xTF32)" if ep_tc
-                                 else "episode_kernel (persistent, all env-steps of a launch)"),
-            achieved=step_bytes / dur / 1e9, peak=peaks["hbm_gbs"], unit="GB/s",
-            frac=step_bytes / dur / 1e9 / peaks["hbm_gbs"], traffic=None,
-            peak_source=peaks["source"] + " (burst copy)", avg_launch_us=ep_us * n_prof, us_per_env_step=ep_us,
-            binding=dict(bound="fp32-fma", note="compute-bound at fp32: 227 FLOP/B vs ridge ~11 (SURVEY.md §8d); "
-                         "inside the SM the forward sweep is limited by shared-memory wavefronts (DESIGN.md §4)",
-                         achieved=step_flops / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
-                         frac=step_flops / dur / 1e12 / fp32_peak if fp32_peak else None,
-                         peak_source="measured live: qp_measure_fp32_outer_peak (8x8 outer-product FFMA, three register sources); the "
-                                     f"uniform-operand FFMA stream reaches {fp32_uniform_peak:.1f} TFLOP/s on the same GPU"),
-            bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP,
-            three_kernel_path_us=dict(zip(names, split_us)),
-        )
+        hbm = dict(achieved=step_bytes / dur / 1e9, peak=peaks["hbm_gbs"], unit="GB/s",
+                   frac=step_bytes / dur / 1e9 / peaks["hbm_gbs"], peak_source=peaks["source"] + " (burst copy)")
+        fma = dict(bound="fp32-fma", achieved=step_flops / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
+                   frac=step_flops / dur / 1e12 / fp32_peak if fp32_peak else None,
+                   peak_source="measured live: qp_measure_fp32_outer_peak (8x8 outer-product FFMA, three register sources); the "
+                               f"uniform-operand FFMA stream reaches {fp32_uniform_peak:.1f} TFLOP/s on the same GPU")
         if ep_tc:
-            tf32_peak = peaks["bf16_tflops"] / 2.0
-            roofline["tensor"] = dict(achieved=step_flops / dur / 1e12, peak=tf32_peak / 3.0, unit="TFLOP/s",
-                                      frac=step_flops / dur / 1e12 / (tf32_peak / 3.0),
-                                      note="3xTF32-equivalent roof (measured bf16 / 2 / 3); the contractions are ~15 % of the "
-                                           "step, the rest is operand build, epilogues, grid barriers and the gradient sum")
+            # contractions on tcgen05 kind::tf32; prices are tf32-exact, W1 / dZ1 are hi+lo pairs: two MMAs per product
+            tc_peak = peaks["bf16_tflops"] / 2.0 / 2.0
+            roofline = dict(
+                bound="tensor", kernel="episode_tc_kernel (persistent, all env-steps of a launch; contractions on tcgen05, 2 x TF32 per product)",
+                achieved=step_flops / dur / 1e12, peak=tc_peak, unit="TFLOP/s", frac=step_flops / dur / 1e12 / tc_peak,
+                traffic=None, peak_source=peaks["source"] + " bf16 burst / 2 (tf32) / 2 (hi and lo part of W1 / dZ1)",
+                avg_launch_us=ep_us * n_prof, us_per_env_step=ep_us,
+                note="achieved counts the algorithmic FLOPs of the whole env-step.  The step is a chain of dependent phases inside "
+                     "one persistent kernel (operand build, W1^T stream + MMA, TMEM epilogues, element-wise TD work, partial "
+                     "store, grid barrier, gradient sum + AdaGrad): see phase_cycles and DESIGN.md §4",
+                hbm=hbm, fp32_fma_equivalent=fma,
+                bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP,
+                three_kernel_path_us=dict(zip(names, split_us)))
+            # L2 traffic of one env-step by construction: every CTA streams W1^T hi+lo, writes its dW1/dW2
+            # partial, and the partials are read once by the gradient sum
+            n_tiles = (n_local + 31) // 32
+            kp, npad = -(-WINDOW // 32) * 32, -(-HIDDEN // 16) * 16
+            l2_bytes = n_tiles * (2.0 * kp * npad * 4 + 2.0 * 4 * P)
+            roofline["l2"] = dict(achieved=l2_bytes / dur / 1e9, unit="GB/s", bytes_per_step=l2_bytes,
+                                  note="by construction, not measured; the microarchitecture guide's L2 cap is ~6300 B/clk")
+            try:
+                pol.set_option("phase_clocks", 1)
+                pol.env_reset()
+                pol.env_step(40)
+                c = pol.phase_clocks(40)[5:]
+                pol.set_option("phase_clocks", 0)
+                labels = ["S0 A-operand build + tables", "S1 W1^T stream + forward MMA", "S2 z out of TMEM", "S3 Q(s), select, book-keeping, Q(s')",
+                          "S4 TD target, dZ1 hi/lo", "S5 backward MMA, dW2, budget/shares rows", "S6 dW1 partial: TMEM -> TMA store",
+                          "S7 window row + store completion", "grid barrier", "phase B: bulk-copy sum, AdaGrad, W1^T publish"]
+                d = np.diff(c[:, :11], axis=1).astype(np.float64).mean(axis=0)
+                tot = float((c[1:, 0] - c[:-1, 0]).mean())
+                roofline["phase_cycles"] = dict({k: float(v) for k, v in zip(labels, d)}, step_total=tot,
+                                                note="clock64 stamps of CTA 0, mean over 35 env-steps")
+            except Exception as exc:  # stamps are a tuning aid, never fatal for the bench line
+                roofline["phase_cycles"] = dict(error=str(exc))
             pol.set_option("ep_tc", 0)
             pol.env_reset()
             pol.env_step(20)
             roofline["ffma_persistent_kernel_us_per_env_step"] = float(pol.env_step_timed(n_prof)[0]) / n_prof * 1e3
             pol.set_option("ep_tc", 1)
+        else:
+            roofline = dict(
+                bound="hbm", kernel="episode_kernel (persistent, all env-steps of a launch)",
+                achieved=hbm["achieved"], peak=hbm["peak"], unit="GB/s", frac=hbm["frac"], traffic=None,
+                peak_source=hbm["peak_source"], avg_launch_us=ep_us * n_prof, us_per_env_step=ep_us,
+                binding=dict(fma, note="compute-bound at fp32: 227 FLOP/B vs ridge ~11 (SURVEY.md §8d); "
+                             "inside the SM the forward sweep is limited by shared-memory wavefronts (DESIGN.md §4)"),
+                bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP,
+                three_kernel_path_us=dict(zip(names, split_us)))
         # DRAM traffic from the committed ncu --set full capture of a 30-step launch of this kernel
         # (profiles/r1_v2_ncu_episode_kernel_summary.csv: 9.40 MB read + 4.91 MB written), per env-step;
         # far below the algorithmic bytes because windows stay in shared memory and weights/partials in L2

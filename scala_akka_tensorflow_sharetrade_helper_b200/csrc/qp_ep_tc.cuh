@@ -630,36 +630,39 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                     // every value travels as one 8-byte store {value, step tag} into the slot this rank owns in
                     // every peer's exchange block (posted writes, one NVLink crossing); the receiver spins on its
                     // LOCAL slots until the tag is this step's, then adds the values in rank order — the same
-                    // bits on every rank.  Two buffers by step parity: a rank cannot send step t+2 before it has
+                    // bits on every rank.  Two buffers by (global) step parity: a rank cannot send step t+2 before it has
                     // received this rank's step t+1, which is sent after step t has been read.
                     const unsigned int want = ea.flag_base + (unsigned int)sidx + 1u;
-                    const size_t slot = (size_t)(sidx & 1) * (size_t)ea.world;
+                    const size_t slot = (size_t)(want & 1u) * (size_t)ea.world;     // (global step parity: alternates across launches too)
                     const uint2 mine = make_uint2(__float_as_uint(g), want);
 #pragma unroll
                     for (int r = 0; r < 8; ++r)
                         if (r < ea.world && r != ea.rank)
                             asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(x.pdata[r] + (slot + (size_t)ea.rank) * (size_t)x.p_pad + p),
                                          "r"(mine.x), "r"(mine.y) : "memory");
-                    const uint2* local = x.pdata[ea.rank];
+                    const uint2* local = x.pdata[ea.rank] + slot * (size_t)x.p_pad + p;
                     float pv[8];
-                    unsigned long long t0 = 0;
 #pragma unroll
-                    for (int r = 0; r < 8; ++r) {
-                        pv[r] = 0.0f;
-                        if (r < ea.world) {
-                            if (r == ea.rank) { pv[r] = g; continue; }
-                            const uint2* src = local + (slot + (size_t)r) * (size_t)x.p_pad + p;
-                            for (unsigned int spins = 0;; ++spins) {
-                                uint2 v;
-                                asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v.x), "=r"(v.y) : "l"(src) : "memory");
-                                if (v.y == want) { pv[r] = __uint_as_float(v.x); break; }
-                                if ((spins & 4095u) == 4095u) {
-                                    unsigned long long t;
-                                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-                                    if (t0 == 0) t0 = t;
-                                    else if (t - t0 > 20000000000ull) __trap();   // a rank never arrived: fail instead of hanging
-                                }
-                            }
+                    for (int r = 0; r < 8; ++r) pv[r] = 0.0f;
+                    pv[ea.rank & 7] = g;
+                    unsigned int pending = ((1u << ea.world) - 1u) & ~(1u << ea.rank);
+                    unsigned long long t0 = 0;
+                    for (unsigned int spins = 0; pending != 0u; ++spins) {
+                        // all outstanding slots are read in one go (independent loads), then inspected
+                        uint2 v[8];
+#pragma unroll
+                        for (int r = 0; r < 8; ++r)
+                            if ((pending >> r) & 1u)
+                                asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v[r].x), "=r"(v[r].y)
+                                             : "l"(local + (size_t)r * (size_t)x.p_pad) : "memory");
+#pragma unroll
+                        for (int r = 0; r < 8; ++r)
+                            if (((pending >> r) & 1u) && v[r].y == want) { pv[r] = __uint_as_float(v[r].x); pending &= ~(1u << r); }
+                        if ((spins & 4095u) == 4095u) {
+                            unsigned long long t;
+                            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                            if (t0 == 0) t0 = t;
+                            else if (t - t0 > 20000000000ull) __trap();   // a rank never arrived: fail instead of hanging
                         }
                     }
                     g = 0.0f;
