@@ -432,6 +432,12 @@ def run_ours(args):
                                                 note="clock64 stamps of CTA 0, mean over 35 env-steps")
             except Exception as exc:  # stamps are a tuning aid, never fatal for the bench line
                 roofline["phase_cycles"] = dict(error=str(exc))
+            if n_local == 4096 and HIDDEN == 200:
+                # dram__bytes_read.sum + dram__bytes_write.sum of the committed ncu --set full capture of one 30-step
+                # launch of this kernel, per env-step; far below the algorithmic bytes because the windows stay in
+                # shared memory and weights / partials in L2
+                roofline["traffic"] = (4.756736e6 + 1.551104e6) / 30.0
+                roofline["traffic_note"] = "bytes per env-step of 4096 episodes, from profiles/r1_v5_ncu_episode_tc_kernel_summary.csv"
             pol.set_option("ep_tc", 0)
             pol.env_reset()
             pol.env_step(20)
