@@ -388,6 +388,75 @@ def test_persistent_tensor_core_kernel_free_running():
     assert np.abs(wa - wb).max() <= 40 * _tol.W_ATOL
 
 
+@pytest.mark.parametrize("shape", [(200, 192), (220, 180)])
+def test_persistent_tensor_core_kernel_other_shapes(shape):
+    """The edges of the shapes the tensor-core kernel accepts: hidden = 192 (the smallest N whose operand ring
+    holds the epilogue's staging boxes; Np == H, no padding columns) and window 220 / hidden 180 (12 padding
+    columns in the MMA's N, the last 32-column box of the partial clipped by the tensor map at column 180),
+    teacher-forced against the oracle."""
+    cfg = O.Config(wn=shape[0], hidden=shape[1], bookkeeping=O.RLPY, seed=5)
+    n_envs = 70
+    prices = O.gen_prices(cfg.seed, 0, 35, cfg.wn + 60)
+    soe = (np.arange(n_envs) % 35).astype(np.int32)
+    w0 = (O.gen_normal(8, 0, cfg.P) * 0.05).astype(np.float32)
+    o = O.Oracle(cfg, params=w0)
+    o.env_create(prices, soe, 1000.0, 1)
+    with make_policy(cfg) as pol:
+        pol.env_create(prices, soe, 1000.0, 1)
+        assert pol.get_option("ep_tc_active") == 1, "shape not taken by the tensor-core kernel"
+        for i in (0, 31, 58):
+            o.env["step"] = i
+            w, acc = o.params.copy(), o.acc.copy()
+            b, s, v = o.env["budget"].copy(), o.env["shares"].copy(), o.env["share_value"].copy()
+            pol.set_weights(w, acc)
+            pol.env_set_state(b, s, v, step=i)
+            x = states_of(cfg, prices, soe, i, b, s)
+            ref = o.env_step(1, trace=True, want_grad=True)[0]
+            tr = {k: a[0] for k, a in pol.env_step_trace(1).items()}
+            if compare_step(cfg, w, x, tr, ref, f"ep_tc {shape} step {i}") == 0:
+                _tol.assert_grad_close(pol.last_grad(), ref["grad"], f"ep_tc {shape} step {i} grad")
+                assert np.abs(pol.get_weights()[0] - o.params).max() <= _tol.W_ATOL
+
+
+def test_persistent_tensor_core_kernel_ring_wraps():
+    """330 env-steps in ONE launch: the window ring (256 rows) wraps more than once, every row block of the
+    dW1 partial takes the wrapped-store path in turn.  step_div is huge, so the ε-greedy threshold stays 0 and
+    every action is the Philox draw (independent of Q): the book-keeping trajectory is then identical for the
+    tensor-core kernel, the FFMA kernel and the oracle, and Q / weights can be compared all the way."""
+    cfg = O.Config(bookkeeping=O.RLPY, lr=1e-5, seed=31, step_div=1e12)      # (lr small enough to keep the ReLUs alive)
+    n, T, steps = 96, 201 + 340, 330
+    prices = O.gen_prices(cfg.seed, 0, n, T)
+    soe = np.arange(n, dtype=np.int32)
+    w = (O.gen_normal(4, 0, cfg.P) * 0.05).astype(np.float32)
+    res = []
+    for tc in (1, 0):
+        with make_policy(cfg, params=w) as pol:
+            pol.set_option("ep_tc", tc)
+            pol.env_create(prices, soe, 1000.0, 2)
+            assert pol.get_option("ep_tc_active") == tc
+            tr = pol.env_step_trace(steps)
+            res.append((tr, pol.get_weights()[0], pol.last_grad()))
+    (ta, wa, ga), (tb, wb, gb) = res
+    assert ta["explored"].all()
+    for k in ("action_sel", "action_eff", "shares", "budget", "reward"):
+        np.testing.assert_array_equal(ta[k], tb[k], err_msg=k)
+    scale = np.maximum(1.0, np.abs(tb["q_s"]).max(axis=2, keepdims=True))
+    assert (np.abs(ta["q_s"] - tb["q_s"]) <= 2e-3 * scale).all(), "Q(s) of the two persistent kernels drifted apart"
+    assert np.abs(wa - wb).max() <= steps * _tol.W_ATOL
+    d = np.linalg.norm(ga - gb) / np.linalg.norm(gb)
+    assert d <= 2e-3, f"last gradient: relative Frobenius distance {d:.3g}"
+    # and the oracle, over the whole stretch
+    o = O.Oracle(cfg, params=w)
+    o.env_create(prices, soe, 1000.0, 2)
+    ref = o.env_step(steps, trace=True)
+    for k in ("action_sel", "action_eff", "shares", "budget", "reward"):
+        np.testing.assert_array_equal(ta[k], np.stack([r[k] for r in ref]), err_msg=f"oracle {k}")
+    q_ref = np.stack([r["q_s"] for r in ref])
+    scale = np.maximum(1.0, np.abs(q_ref).max(axis=2, keepdims=True))
+    assert (np.abs(ta["q_s"] - q_ref) <= 5e-3 * scale).all(), "Q(s) drifted away from the oracle"
+    assert np.abs(wa - o.params).max() <= steps * _tol.W_ATOL
+
+
 # ------------------------------------------------------------------------------------------------
 # GEMM-organised path (BASELINE.json configs[3]: hist 512 -> window 513, hidden 2048)
 # ------------------------------------------------------------------------------------------------
