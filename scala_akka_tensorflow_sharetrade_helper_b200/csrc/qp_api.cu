@@ -643,9 +643,12 @@ int ep_tc_prepare(qp_handle* h) {
     const int Kp = (int)round_up(hp.wn, 32), nkb = Kp / 32, Np = (int)round_up(hp.H, 16), halves = (hp.wn + 127) / 128;
     const size_t TB = (size_t)Np * 128;
     const size_t smem = 1024 + (size_t)nkb * 8192 + 4 * TB + (size_t)halves * 16384 + 16 + (size_t)hp.H * 16 +
-                        (size_t)hp.H * 8 + 256 + 2304 * 4 + 256 + 8 + 256;
-    // the window ring needs one free row beyond the window; the partial's boxes are staged in the ring (12 x 8 KB)
-    if (halves * 128 < hp.wn + 2 || (size_t)12 * 8192 > 4 * TB || ((size_t)hp.H * 4) % 16 != 0 || ((size_t)h->P1 * 4) % 16 != 0)
+                        (size_t)hp.H * 8 + 256 + (size_t)kEtWarps * 192 * 4 + 256 + 8 + 256;
+    // the window ring needs one free row beyond the window; the partial's boxes are staged in the operand ring
+    // (8 KB per warp) and, for the warps that do not fit there, behind h(s) in the A-operand region (4 KB each)
+    const size_t n_ring = std::min<size_t>(kEtWarps, 4 * TB / 8192);
+    const size_t stage_end = round_up((int64_t)Np * kXStride * 4, 1024) + (kEtWarps - n_ring) * 4096;
+    if (halves * 128 < hp.wn + 2 || stage_end > (size_t)nkb * 8192 || ((size_t)hp.H * 4) % 16 != 0 || ((size_t)h->P1 * 4) % 16 != 0)
         return QP_OK;
     if (Np > 256 || halves > 2 || halves * Np > 512 || (size_t)nkb * 8192 < 2 * (size_t)Np * kXStride * 4 || 
         smem > (size_t)h->max_smem)

@@ -19,7 +19,9 @@
 
 namespace qp {
 
-constexpr int kEtThreads = 384;
+constexpr int kEtThreads = 384;    // 12 warps; 16 were measured slower (47.3 K vs 45.3 K cycles per step: the per-warp redundant select / book-keeping grows)
+constexpr int kEtWarps = kEtThreads / 32;
+constexpr int kEtParts = kEtWarps / 4;     // warps per TMEM lane quarter (a warp can only read quarter warp % 4)
 
 struct EpTcArgs {
     EpisodeArgs ea;
@@ -90,6 +92,7 @@ __device__ __forceinline__ void et_tma_store_3d(const CUtensorMap* tmap, const v
 }
 __device__ __forceinline__ void et_bulk_commit() { asm volatile("cp.async.bulk.commit_group;\n" ::: "memory"); }
 __device__ __forceinline__ void et_bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;\n" ::: "memory"); }
+__device__ __forceinline__ void et_bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory"); }
 __device__ __forceinline__ void et_bulk_wait_all() { asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory"); }
 // Dataflow synchronisation between the CTAs of the (co-resident) grid.  Bounded: a flag that never
 // arrives traps the kernel instead of hanging the GPU.
@@ -157,10 +160,10 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     float* Wb = W2s + (size_t)H * 4;
     float* Ws = Wb + H;
     float* XE = Ws + H;                                         // [2][32]
-    float* qpart = XE + 64;                                     // [12 warps][2 states][3][32]
-    float* dz2s = qpart + 12 * 2 * 3 * 32;                      // [32]
+    float* qpart = XE + 64;                                     // [warps][2 states][3][32]
+    float* dz2s = qpart + kEtWarps * 2 * 3 * 32;                // [32]
     int* kns = reinterpret_cast<int*>(dz2s + 32);               // [32]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(base + ((off_w2s + (size_t)H * 24 + (64 + 12 * 2 * 3 * 32 + 64) * 4 + 7) & ~(size_t)7));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(base + ((off_w2s + (size_t)H * 24 + (64 + kEtWarps * 2 * 3 * 32 + 64) * 4 + 7) & ~(size_t)7));
     uint64_t* full = bars;          // [2]
     uint64_t* empty = bars + 2;     // [2]
     uint64_t* tf_fwd = bars + 4;
@@ -180,7 +183,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     const float* W2g = a.params + (size_t)D * H;
     const int q4 = warp & 3, part = warp >> 2;                  // TMEM lane quarter / column part of this warp
     const int n_ld = Np >> 4;                                   // 16-column TMEM loads per row
-    const int ld0 = part * n_ld / 3, ld1 = (part + 1) * n_ld / 3;
+    const int ld0 = part * n_ld / kEtParts, ld1 = (part + 1) * n_ld / kEtParts;
 
     if (tid == 0) {
         mbar_init(full, 1); mbar_init(full + 1, 1); mbar_init(empty, 1); mbar_init(empty + 1, 1);
@@ -368,12 +371,12 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         if (has_tile) {
 #pragma unroll
             for (int t = 0; t < 3; ++t) {
-                float pw[12];
+                float pw[kEtWarps];
 #pragma unroll
-                for (int w = 0; w < 12; ++w) pw[w] = w < nwarps ? qpart[((w * 2 + 0) * 3 + t) * 32 + lane] : 0.0f;
+                for (int w = 0; w < kEtWarps; ++w) pw[w] = w < nwarps ? qpart[((w * 2 + 0) * 3 + t) * 32 + lane] : 0.0f;
                 float s = 0.0f;
 #pragma unroll
-                for (int w = 0; w < 12; ++w) s += pw[w];
+                for (int w = 0; w < kEtWarps; ++w) s += pw[w];
                 s += bias;
                 q_s[t] = s > 0.0f ? s : 0.0f;
             }
@@ -415,12 +418,12 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             // ---- S4: TD target; dZ1 as a K-major (episodes contiguous) tf32 hi/lo pair; X^T operand
 #pragma unroll
             for (int t = 0; t < 3; ++t) {
-                float pw[12];
+                float pw[kEtWarps];
 #pragma unroll
-                for (int w = 0; w < 12; ++w) pw[w] = w < nwarps ? qpart[((w * 2 + 1) * 3 + t) * 32 + lane] : 0.0f;
+                for (int w = 0; w < kEtWarps; ++w) pw[w] = w < nwarps ? qpart[((w * 2 + 1) * 3 + t) * 32 + lane] : 0.0f;
                 float s = 0.0f;
 #pragma unroll
-                for (int w = 0; w < 12; ++w) s += pw[w];
+                for (int w = 0; w < kEtWarps; ++w) s += pw[w];
                 s += bias;
                 q_n[t] = s > 0.0f ? s : 0.0f;
             }
@@ -522,21 +525,26 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             if (ea.dbg && blockIdx.x == 0 && tid == 11 * 32) ea.dbg[(size_t)sidx * kDbgSlots + 11] = clock64();
             {
                 const int ncb = (H + 31) >> 5;
-                uint8_t* stg = ring + (size_t)warp * 8192;              // two boxes per warp; dZ1 is dead by now
+                // two boxes per warp in the operand ring (dZ1 is dead by now) as far as it reaches; the last
+                // warps get one box each behind h(s) in the A-operand region
+                const int n_ring = min(kEtWarps, (int)(4 * (size_t)TB / 8192));
+                const int nbuf = warp < n_ring ? 2 : 1;
+                uint8_t* stg = warp < n_ring ? ring + (size_t)warp * 8192
+                                             : base + (((size_t)Np * kXStride * 4 + 1023) & ~(size_t)1023) + (size_t)(warp - n_ring) * 4096;
                 int n_box = 0;
-                for (int i = part; i < halves * ncb; i += 3) {
+                for (int i = part; i < halves * ncb; i += kEtParts) {
                     const int hf = i / ncb, cb = i - hf * ncb;
                     const int k0 = (hf * 128 + q4 * 32 - sidx) & Rm;
                     const bool st_a = k0 < wn, st_b = k0 + 32 > Rm + 1;
                     if (!st_a && !st_b) continue;
                     uint32_t r[32];
                     et_tmem_ld32_nowait(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(hf * Np + cb * 32), r);
-                    if (n_box >= 2) {
-                        if (lane == 0) et_bulk_wait_read1();            // the box two stores back has left its buffer
+                    if (n_box >= nbuf) {                                // the buffer's previous box has left it
+                        if (lane == 0) { if (nbuf == 2) et_bulk_wait_read1(); else et_bulk_wait_read0(); }
                         __syncwarp();
                     }
                     et_tmem_wait_ld();
-                    uint8_t* buf = stg + (size_t)(n_box & 1) * 4096;
+                    uint8_t* buf = stg + (size_t)(n_box & (nbuf - 1)) * 4096;
 #pragma unroll
                     for (int j = 0; j < 8; ++j)
                         *reinterpret_cast<uint4*>(buf + lane * 128 + ((j ^ (lane & 7)) << 4)) =
