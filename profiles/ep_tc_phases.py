@@ -33,4 +33,5 @@ print(f"{'step total':48s} {tot:9.0f} cyc  (~{tot / 1.965e3:.1f} us)")
 # finer stamps (relative to the phase starts): S4 internals of warp 0, S6 of warp 11 and warp 0
 f = lambda a, b: (c[:, a] - c[:, b]).mean()
 print(f"phase B: all groups summed after {f(14, 9):.0f}; AdaGrad + publish {f(10, 15):.0f}")
-print(f"S5/S6: warp 0 column loop {f(6, 5):.0f}, its S6 {f(13, 6):.0f}")
+if n > 148 * 32:
+    print(f"last wave of CTA 0: carry load + window reload {f(13, 11):.0f}; S0 {f(1, 13):.0f}; S1..S6 {f(7, 1):.0f}")

@@ -1,5 +1,6 @@
 """configs[2]/configs[4] per-GPU shape: 131 072 episodes on one GPU (512 tickers x 256 episodes each, or
-131 072 distinct series), three-kernels-per-step path.  Usage: python profiles/fanout_workload.py [tickers] [steps]"""
+131 072 distinct series): the tensor-core persistent kernel in waves (default) and the three-kernels-per-step
+path (fused = 0).  Usage: python profiles/fanout_workload.py [tickers] [steps]"""
 import os
 import sys
 import time
@@ -15,13 +16,15 @@ steps = int(sys.argv[2]) if len(sys.argv) > 2 else 40
 n = 131072
 prices = O.gen_prices(42, 0, tickers, 1000)
 soe = (np.arange(n) // (n // tickers)).astype(np.int32)
-with q.QDecisionPolicy(q.PolicyConfig()) as pol:
-    pol.env_create(prices, soe, 1000.0, 0)
-    assert pol.get_option("fused_active") == 0
-    pol.env_step(10)
-    t0 = time.perf_counter()
-    pol.env_step(steps)
-    dt = time.perf_counter() - t0
-    kms = pol.env_step_timed(steps) / steps * 1e3
-    print(f"tickers {tickers} episodes {n}: {dt / steps * 1e6:.1f} us/env-step -> {n * steps / dt:.4g} env-steps/s; "
-          f"kernels us {kms.tolist()}")
+for fused in (1, 0):
+    with q.QDecisionPolicy(q.PolicyConfig()) as pol:
+        pol.set_option("fused", fused)
+        pol.env_create(prices, soe, 1000.0, 0)
+        assert pol.get_option("fused_active") == fused and pol.get_option("ep_tc_active") == fused
+        pol.env_step(10)
+        t0 = time.perf_counter()
+        pol.env_step(steps)
+        dt = time.perf_counter() - t0
+        kms = pol.env_step_timed(steps) / steps * 1e3
+        print(f"{'tensor-core kernel in waves' if fused else 'three kernels per step'}: tickers {tickers} episodes {n}: "
+              f"{dt / steps * 1e6:.1f} us/env-step -> {n * steps / dt:.4g} env-steps/s; kernels us {kms.tolist()}")

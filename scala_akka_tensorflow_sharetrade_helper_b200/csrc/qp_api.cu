@@ -630,8 +630,10 @@ size_t p2p_pad(const qp_handle* h) { return (size_t)round_up(h->P, 64); }
 bool use_fused(const qp_handle* h) {
     const bool single = h->world == 1;
     const bool peers = h->world > 1 && h->world <= 8 && h->p2p_ready && h->allow_p2p;
-    return !h->wide && h->allow_fused && h->coop_launch && (single || peers) && h->geo.ep_ok &&
-           h->n_envs <= (int64_t)kTileEnvs * h->num_sms;
+    // one tile per SM for the FFMA kernel; the tensor-core kernel runs any number of tiles in waves
+    const bool fits = h->n_envs <= (int64_t)kTileEnvs * h->num_sms;
+    const bool tc = h->allow_ep_tc && h->ep_tc_ready;
+    return !h->wide && h->allow_fused && h->coop_launch && (single || peers) && h->geo.ep_ok && (fits || tc);
 }
 
 // Everything the tensor-core persistent kernel needs for the current episodes; leaves ep_tc_ready
@@ -639,7 +641,7 @@ bool use_fused(const qp_handle* h) {
 int ep_tc_prepare(qp_handle* h) {
     h->ep_tc_ready = false;
     const Hyper& hp = h->hp;
-    if (!h->tile_ok || !h->geo.ep_ok || hp.H % 4 != 0) return QP_OK;
+    if (!h->tile_ok || !h->geo.ep_ok || hp.H % 4 != 0 || hp.H > kEtThreads) return QP_OK;
     const int Kp = (int)round_up(hp.wn, 32), nkb = Kp / 32, Np = (int)round_up(hp.H, 16), halves = (hp.wn + 127) / 128;
     const size_t TB = (size_t)Np * 128;
     const size_t smem = 1024 + (size_t)nkb * 8192 + 4 * TB + (size_t)halves * 16384 + 16 + (size_t)hp.H * 16 +

@@ -90,6 +90,13 @@ __device__ __forceinline__ void et_tma_store_3d(const CUtensorMap* tmap, const v
                  "r"((uint32_t)__cvta_generic_to_shared(smem_src)), "r"(c0), "r"(c1), "r"(c2)
                  : "memory");
 }
+// the same box ADDED to what global memory holds (fp32 add performed by the memory system).  Used only by the
+// CTA that owns the destination, one wave after the other: the order of the additions is fixed.
+__device__ __forceinline__ void et_tma_reduce_add_3d(const CUtensorMap* tmap, const void* smem_src, int c0, int c1, int c2) {
+    asm volatile("cp.reduce.async.bulk.tensor.3d.global.shared::cta.add.tile.bulk_group [%0, {%2, %3, %4}], [%1];\n" ::"l"(tmap),
+                 "r"((uint32_t)__cvta_generic_to_shared(smem_src)), "r"(c0), "r"(c1), "r"(c2)
+                 : "memory");
+}
 __device__ __forceinline__ void et_bulk_commit() { asm volatile("cp.async.bulk.commit_group;\n" ::: "memory"); }
 __device__ __forceinline__ void et_bulk_wait_read1() { asm volatile("cp.async.bulk.wait_group.read 1;\n" ::: "memory"); }
 __device__ __forceinline__ void et_bulk_wait_read0() { asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory"); }
@@ -201,7 +208,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         reinterpret_cast<float4*>(base)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     double budget = a.budget[ec], share_value = a.share_value[ec];
     int32_t shares = a.shares[ec];
-    const float* my_row = a.prices + (int64_t)a.series_of_env[ec] * a.T;
+    const float* my_row = a.prices + (int64_t)a.series_of_env[ec] * a.T;       // (per wave when there are several)
     for (int idx = tid; idx < halves * 4096; idx += nthreads) reinterpret_cast<float*>(XT)[idx] = 0.0f;
     tc_fence_before();
     __syncthreads();
@@ -226,7 +233,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     }
     // phase B's division of the parameters over the CTAs (see there), and who publishes into which k-block
     const int64_t P1 = (int64_t)D * H, P = P1 + 3 * (int64_t)H;
-    const int n1 = (int)n_tiles;
+    const int n1 = (int)min(n_tiles, (int64_t)gridDim.x);      // one partial per CTA that has tiles
     const int n_w1_ctas = max(1, (int)gridDim.x - 2);
     const int chunk = (int)(((P1 + n_w1_ctas - 1) / n_w1_ctas + 3) & ~(int64_t)3);
     const int chunk2 = ((3 * H + 1) / 2 + 3) & ~3;
@@ -247,16 +254,39 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     // every CTA streams the same W1^T tiles: start each at a different k-block so that the L2 requests
     // of the grid spread over the whole matrix instead of all landing on one tile at a time
     const int kb_first = (int)(blockIdx.x % (unsigned)nkb);
+    // More tiles than CTAs: every step runs in waves.  CTA c does tiles c, c + G, c + 2G, ...; the window and
+    // the carry of a tile are then reloaded from global memory for every wave (no ring, no registers across
+    // steps); the first wave stores its dW1 partial, the later ones add theirs to it (TMA reduce-add by the CTA
+    // that owns the partial, in wave order), so the gradient sum over the CTAs is shared by all waves.  (TMEM has
+    // no room to accumulate over the waves: forward 208 + backward 416 columns > 512.)
+    const int n_waves = (int)((n_tiles + gridDim.x - 1) / gridDim.x);
+    const bool multi = n_waves > 1;
+    uint32_t mma_it = 0;                                        // tiles this CTA has pushed through the MMAs
 
     for (int32_t sidx = 0; sidx < ea.n_steps; ++sidx) {
         const int32_t istep = ea.step0 + sidx;
-        const uint32_t par = (uint32_t)sidx & 1u;
+        const int roff = multi ? 0 : sidx;                              // ring offset of the window
+        float p_next = 0.0f;
+        float acc5[5] = {0.f, 0.f, 0.f, 0.f, 0.f};                      // this thread's column of dW2 and of the budget / shares rows
+        float* out = ea.part1 + (size_t)blockIdx.x * ((size_t)D * H);
+        float* out2 = a.dw2_part + (size_t)blockIdx.x * (3 * H);
+        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 0] = clock64();
+      for (int wave = 0; wave < n_waves; ++wave) {
+        const int64_t tile = (int64_t)wave * gridDim.x + blockIdx.x;
+        const bool has_tile = tile < n_tiles;
+        const int64_t e = tile * kTileEnvs + lane;
+        const bool valid = has_tile && e < B;
+        const uint32_t par = mma_it & 1u;
+        if (multi) {
+            const int64_t ecw = has_tile ? (valid ? e : B - 1) : 0;
+            budget = a.budget[ecw]; share_value = a.share_value[ecw]; shares = a.shares[ecw];
+            my_row = a.prices + (int64_t)a.series_of_env[ecw] * a.T;
+        }
         float q_s[3] = {0.f, 0.f, 0.f}, q_n[3] = {0.f, 0.f, 0.f};
         int action = 0, explored = 0, a_eff = 2, kn = 0;
-        float r32 = 0.0f, target = 0.0f, dz2 = 0.0f, p_next = 0.0f;
+        float r32 = 0.0f, target = 0.0f, dz2 = 0.0f;
         double nb = budget, p_new = 0.0;
         int32_t ns = shares;
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 0] = clock64();
         // producer side of the W1^T ring: k-block number kk of this step into its stage
         auto push_w_tiles = [&](int kk) {
             const int kb = (kk + kb_first) % nkb;
@@ -269,13 +299,30 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         };
         if (tid == 0) {
             // the new weights are complete once every publisher of the previous step is through
-            if (flow && sidx > 0) et_wait_count(x.published, (unsigned long long)sidx * (unsigned long long)n_publishers);
+            if (flow && sidx > 0 && wave == 0) et_wait_count(x.published, (unsigned long long)sidx * (unsigned long long)n_publishers);
             // both stages are free: start the stream now, so that the first tiles travel while the warps
             // build the A operand
             fence_proxy_async();                                        // phase-B writes of W1^T -> TMA reads
             if (has_tile)
                 for (int kk = 0; kk < min(2, nkb); ++kk) push_w_tiles(kk);
         }
+        if (ea.dbg && blockIdx.x == 0 && tid == 0 && wave == n_waves - 1) ea.dbg[(size_t)sidx * kDbgSlots + 11] = clock64();
+        if (multi) {
+            // this wave's window: element k of episode el at row k (the previous wave's MMAs are through)
+            if (has_tile) {
+                const int segs = (wn + 1 + 31) >> 5, items = kTileEnvs * segs;
+                for (int it = warp; it < items; it += nwarps) {
+                    const int el = it & 31, k = ((it >> 5) << 5) + lane;
+                    const float* src = reinterpret_cast<const float*>(
+                        __shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(my_row), el)) + istep;
+                    if (k <= wn) cp_async4(XT + et_swz(k, el), src + k);
+                }
+                cp_async_commit();
+                cp_async_wait_pending(0);
+            }
+            __syncthreads();
+        }
+        if (ea.dbg && blockIdx.x == 0 && tid == 0 && wave == n_waves - 1) ea.dbg[(size_t)sidx * kDbgSlots + 13] = clock64();
         if (has_tile) {
             // ---- S0: the A operand of the forward (K-major, swizzled) from the master window — it does not
             // depend on the update in flight — then the small tables, once their publishers are through
@@ -288,21 +335,25 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                     float v[4];
 #pragma unroll
                     for (int j = 0; j < 4; ++j)
-                        v[j] = kk + j < wn ? *reinterpret_cast<const float*>(XT + et_swz((kk + j + half + sidx) & Rm, lane)) : 0.0f;
+                        v[j] = kk + j < wn ? *reinterpret_cast<const float*>(XT + et_swz((kk + j + half + roff) & Rm, lane)) : 0.0f;
                     const int row = half * 32 + lane;
                     *reinterpret_cast<float4*>(Afwd + (size_t)kb * 8192 + (size_t)row * 128 + ((chunk16 ^ (row & 7)) << 4)) =
                         make_float4(v[0], v[1], v[2], v[3]);
                 }
             }
         }
-        if (flow) __syncthreads();                                      // warp 0 has seen the counter: the tables are final
-        if (has_tile) {
-            for (int j = tid; j < H; j += nthreads) {
-                reinterpret_cast<float4*>(W2s)[j] = make_float4(__ldcg(W2g + j * 3), __ldcg(W2g + j * 3 + 1), __ldcg(W2g + j * 3 + 2), 0.f);
-                Wb[j] = __ldcg(W1g + (size_t)wn * H + j);
-                Ws[j] = __ldcg(W1g + (size_t)(wn + 1) * H + j);
+        if (wave == 0) {                                                // the small tables serve every wave of the step
+            if (flow) __syncthreads();                                  // warp 0 has seen the counter: the tables are final
+            if (has_tile) {
+                for (int j = tid; j < H; j += nthreads) {
+                    reinterpret_cast<float4*>(W2s)[j] = make_float4(__ldcg(W2g + j * 3), __ldcg(W2g + j * 3 + 1), __ldcg(W2g + j * 3 + 2), 0.f);
+                    Wb[j] = __ldcg(W1g + (size_t)wn * H + j);
+                    Ws[j] = __ldcg(W1g + (size_t)(wn + 1) * H + j);
+                }
             }
-            if (warp == 0 && (int64_t)istep + wn + 1 < a.T) p_next = __ldg(my_row + istep + wn + 1);
+        }
+        if (has_tile) {
+            if (!multi && warp == 0 && (int64_t)istep + wn + 1 < a.T) p_next = __ldg(my_row + istep + wn + 1);
             et_fence_async_smem();
         }
         __syncthreads();
@@ -389,7 +440,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             if (hp.epsilon < thr) thr = hp.epsilon;
             if (u < thr) action = argmax3(q_s);
             else { explored = 1; action = (int)(((uint64_t)r[1] * 3u) >> 32); }
-            p_new = (double)*reinterpret_cast<const float*>(XT + et_swz((wn + sidx) & Rm, lane));
+            p_new = (double)*reinterpret_cast<const float*>(XT + et_swz((wn + roff) & Rm, lane));
             const double cur = __dadd_rn(budget, __dmul_rn((double)shares, share_value));
             const double base_b = hp.bookkeeping == 0 ? a.B0 : budget;
             const int32_t base_n = hp.bookkeeping == 0 ? a.N0 : shares;
@@ -469,6 +520,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                 }
             }
             budget = nb; shares = ns; share_value = p_new;             // carry (TrainerChildActor.scala:99-102)
+            if (multi && warp == 0 && valid) { a.budget[e] = budget; a.shares[e] = shares; a.share_value[e] = share_value; }
             et_fence_async_smem();
         }
         __syncthreads();
@@ -489,14 +541,14 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                 }
                 tc_commit(tf_bwd);
             }
-            float* out = ea.part1 + (size_t)blockIdx.x * ((size_t)D * H);
-            float* out2 = a.dw2_part + (size_t)blockIdx.x * (3 * H);
             // dW2[c][t] = sum_e [kn_e == t] h_e[c] dz2_e and the budget / shares rows of dW1: one thread per
-            // hidden column, episodes summed sequentially out of shared memory (fixed order, no shuffles)
-            for (int c = tid; c < H; c += nthreads) {
+            // hidden column (H <= blockDim), episodes summed sequentially out of shared memory (fixed order, no
+            // shuffles), wave after wave into the same five registers
+            if (tid < H) {
+                const int c = tid;
                 const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
                 const float wb = Wb[c], ws = Ws[c];
-                float s0 = 0.f, s1 = 0.f, s2 = 0.f, x0 = 0.f, x1 = 0.f;
+                float s0 = acc5[0], s1 = acc5[1], s2 = acc5[2], x0 = acc5[3], x1 = acc5[4];
 #pragma unroll 8
                 for (int el = 0; el < kTileEnvs; ++el) {
                     const float h = et_hidden(HS[c * kXStride + el], XE[el], XE[32 + el], wb, ws, bias);
@@ -509,12 +561,11 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                     x0 = fmaf(XE[el], d1, x0);
                     x1 = fmaf(XE[32 + el], d1, x1);
                 }
-                out2[c * 3 + 0] = s0; out2[c * 3 + 1] = s1; out2[c * 3 + 2] = s2;
-                out[(size_t)wn * H + c] = x0;
-                out[(size_t)(wn + 1) * H + c] = x1;
+                acc5[0] = s0; acc5[1] = s1; acc5[2] = s2; acc5[3] = x0; acc5[4] = x1;
             }
             tc_wait(tf_bwd, par);
             tc_fence_after();
+            ++mma_it;
             if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 6] = clock64();
             // ---- S6: dW1 partial out of TMEM.  A TMEM load hands every lane one row of the tile; stored
             // straight to global memory that is 32 different lines per instruction.  Instead each warp puts
@@ -522,7 +573,6 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             // hands them to the TMA engine, which writes whole row segments while the warp fetches the next
             // box.  Row p of the tile is window element (p - sidx) mod R; the tensor map ends at row wn, so
             // the rows outside the window are clipped; the one block that wraps stores its wrapped rows itself.
-            if (ea.dbg && blockIdx.x == 0 && tid == 11 * 32) ea.dbg[(size_t)sidx * kDbgSlots + 11] = clock64();
             {
                 const int ncb = (H + 31) >> 5;
                 // two boxes per warp in the operand ring (dZ1 is dead by now) as far as it reaches; the last
@@ -534,7 +584,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                 int n_box = 0;
                 for (int i = part; i < halves * ncb; i += kEtParts) {
                     const int hf = i / ncb, cb = i - hf * ncb;
-                    const int k0 = (hf * 128 + q4 * 32 - sidx) & Rm;
+                    const int k0 = (hf * 128 + q4 * 32 - roff) & Rm;
                     const bool st_a = k0 < wn, st_b = k0 + 32 > Rm + 1;
                     if (!st_a && !st_b) continue;
                     uint32_t r[32];
@@ -552,7 +602,10 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                     et_fence_async_smem();
                     __syncwarp();
                     if (lane == 0) {
-                        if (st_a) et_tma_store_3d(&tP, buf, cb * 32, k0, (int)blockIdx.x);
+                        if (st_a) {                                     // later waves add to what the first one stored
+                            if (wave == 0) et_tma_store_3d(&tP, buf, cb * 32, k0, (int)blockIdx.x);
+                            else et_tma_reduce_add_3d(&tP, buf, cb * 32, k0, (int)blockIdx.x);
+                        }
                         et_bulk_commit();
                     }
                     ++n_box;
@@ -570,14 +623,21 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                     }
                 }
             }
-            if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 13] = clock64();
+            // the next wave reuses the staging buffers and overwrites the partial's boxes in order: wait here
+            if (wave + 1 < n_waves) et_bulk_wait_all();
             tc_fence_before();
         }
         __syncthreads();
+      }   // waves
+        if (has_tile && tid < H) {                                      // (has_tile: the CTA's first tile; it has at least that one)
+            out2[tid * 3 + 0] = acc5[0]; out2[tid * 3 + 1] = acc5[1]; out2[tid * 3 + 2] = acc5[2];
+            out[(size_t)wn * H + tid] = acc5[3];
+            out[(size_t)(wn + 1) * H + tid] = acc5[4];
+        }
         if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 7] = clock64();
         if (!ea.apply_in_kernel) { et_bulk_wait_all(); break; }
         // ---- S7: slide the window: one new row of the ring
-        if (has_tile && warp == 0) *reinterpret_cast<float*>(XT + et_swz((wn + 1 + sidx) & Rm, lane)) = p_next;
+        if (!multi && has_tile && warp == 0) *reinterpret_cast<float*>(XT + et_swz((wn + 1 + sidx) & Rm, lane)) = p_next;
         et_bulk_wait_all();                                             // the partial is in global memory
         if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 8] = clock64();
         __threadfence();
@@ -758,7 +818,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         }
     }
 
-    if (has_tile && warp == 0 && valid) {
+    if (!multi && has_tile && warp == 0 && valid) {
         a.budget[e] = budget;
         a.shares[e] = shares;
         a.share_value[e] = share_value;

@@ -633,10 +633,13 @@ def test_first_step_of_full_batch_against_oracle():
         assert np.abs(p - o.params).max() <= _tol.W_ATOL
 
 
+@pytest.mark.parametrize("fused", [0, 1])
 @pytest.mark.parametrize("n", [19000, 40007])
-def test_large_batch_path_against_oracle(n):
-    """More than 128 episodes per SM: the three-kernel path with the large-batch dW1 kernel (one split
-    per SM, 16 x 8 register tiles).  One teacher-forced step against the oracle."""
+def test_large_batch_path_against_oracle(n, fused):
+    """More than 128 episodes per SM.  fused = 0: the three-kernel path with the large-batch dW1 kernel (one
+    split per SM, 16 x 8 register tiles); fused = 1: the tensor-core persistent kernel in waves (5 / 9 tiles per
+    CTA, the last wave ragged, the last tile partly filled), whose backward MMAs accumulate over the waves.  One
+    teacher-forced step against the oracle, then state after three more free-running steps."""
     cfg = O.Config(bookkeeping=O.RLPY, seed=31)
     prices = O.gen_prices(cfg.seed, 0, 500, 300)
     soe = (np.arange(n) % 500).astype(np.int32)
@@ -648,12 +651,19 @@ def test_large_batch_path_against_oracle(n):
     x = states_of(cfg, prices, soe, i, o.env["budget"], o.env["shares"])
     ref = o.env_step(1, trace=True, want_grad=True)[0]
     with make_policy(cfg, params=w) as pol:
+        pol.set_option("fused", fused)
         pol.env_create(prices, soe, 1000.0, 1)
-        assert pol.get_option("fused_active") == 0
+        assert pol.get_option("fused_active") == fused and pol.get_option("ep_tc_active") == fused
         pol.env_set_state(step=i)
         tr = {k: a[0] for k, a in pol.env_step_trace(1).items()}
         g = pol.last_grad()
         p, _ = pol.get_weights()
+        # the carry of every wave's tiles went back to global memory: the state the API returns is the traced one
+        bd, sd, _ = pol.env_state()
+        np.testing.assert_array_equal(bd, tr["budget"])
+        np.testing.assert_array_equal(sd, tr["shares"])
+        pol.env_step(3)
+        assert pol.steps_done == i + 4
     n_diff = compare_step(cfg, w, x, tr, ref, "large batch")
     if n_diff == 0:
         _tol.assert_grad_close(g, ref["grad"], "large batch grad", n_terms=n)
