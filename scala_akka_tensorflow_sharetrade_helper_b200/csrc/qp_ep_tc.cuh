@@ -582,6 +582,9 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                 uint8_t* stg = warp < n_ring ? ring + (size_t)warp * 8192
                                              : base + (((size_t)Np * kXStride * 4 + 1023) & ~(size_t)1023) + (size_t)(warp - n_ring) * 4096;
                 int n_box = 0;
+                // the additions below must find the previous wave's store / additions complete (they are, a whole
+                // wave later; this makes it a guarantee)
+                if (wave > 0) et_bulk_wait_all();
                 for (int i = part; i < halves * ncb; i += kEtParts) {
                     const int hf = i / ncb, cb = i - hf * ncb;
                     const int k0 = (hf * 128 + q4 * 32 - roff) & Rm;
@@ -623,8 +626,8 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                     }
                 }
             }
-            // the next wave reuses the staging buffers and overwrites the partial's boxes in order: wait here
-            if (wave + 1 < n_waves) et_bulk_wait_all();
+            // the next wave's W1^T tiles land on the staging buffers: the TMA engine must have read them
+            if (wave + 1 < n_waves) et_bulk_wait_read0();
             tc_fence_before();
         }
         __syncthreads();

@@ -457,6 +457,29 @@ def test_persistent_tensor_core_kernel_ring_wraps():
     assert np.abs(wa - o.params).max() <= steps * _tol.W_ATOL
 
 
+def test_wave_mode_is_bit_reproducible():
+    """The tensor-core kernel in waves (several tiles per CTA): the later waves ADD their dW1 partial to the first
+    wave's through the memory system (TMA reduce-add).  Only the CTA that owns a partial adds to it, one wave
+    after the other, so the sum has a fixed order: two runs give the same bits."""
+    cfg = O.Config(bookkeeping=O.RLPY, seed=3)
+    n = 15000
+    prices = O.gen_prices(cfg.seed, 0, 300, 260)
+    soe = (np.arange(n) % 300).astype(np.int32)
+    w = (O.gen_normal(5, 0, cfg.P) * 0.05).astype(np.float32)
+    res = []
+    for _ in range(2):
+        with make_policy(cfg, params=w) as pol:
+            pol.env_create(prices, soe, 1000.0, 1)
+            assert pol.get_option("ep_tc_active") == 1
+            pol.env_step(6)
+            res.append((pol.get_weights()[0], pol.last_grad(), pol.env_state()))
+    np.testing.assert_array_equal(res[0][0], res[1][0])
+    np.testing.assert_array_equal(res[0][1], res[1][1])
+    for a_, b_ in zip(res[0][2], res[1][2]):
+        np.testing.assert_array_equal(a_, b_)
+    assert np.abs(res[0][1]).max() > 0
+
+
 # ------------------------------------------------------------------------------------------------
 # GEMM-organised path (BASELINE.json configs[3]: hist 512 -> window 513, hidden 2048)
 # ------------------------------------------------------------------------------------------------
