@@ -313,7 +313,7 @@ def run_ours(args):
     peaks = measured_peaks()
     fp32_uniform_peak = pol.measure_fp32_peak()       # dependency-free FFMA with kernel-uniform multiplicands
     fp32_peak = pol.measure_fp32_outer_peak()         # three-register outer-product FFMA: what a contraction can issue
-    n_prof = 200 if HIDDEN <= 256 else 8
+    n_prof = (200 if n_local <= 32 * 148 else 24) if HIDDEN <= 256 else 8
     fused = bool(pol.get_option("fused_active"))
     wide = bool(pol.get_option("wide"))
 
@@ -417,7 +417,11 @@ def run_ours(args):
             l2_bytes = n_tiles * (2.0 * kp * npad * 4 + 2.0 * 4 * P)
             roofline["l2"] = dict(achieved=l2_bytes / dur / 1e9, unit="GB/s", bytes_per_step=l2_bytes,
                                   note="by construction, not measured; the microarchitecture guide's L2 cap is ~6300 B/clk")
+            single_wave = n_local <= 32 * 148
             try:
+                if not single_wave:
+                    raise RuntimeError("several tiles per CTA (waves): the per-phase stamps describe the last wave only; "
+                                       "see profiles/ep_tc_phases.py")
                 pol.set_option("phase_clocks", 1)
                 pol.env_reset()
                 pol.env_step(40)
@@ -438,11 +442,14 @@ def run_ours(args):
                 # shared memory and weights / partials in L2
                 roofline["traffic"] = (4.756736e6 + 1.551104e6) / 30.0
                 roofline["traffic_note"] = "bytes per env-step of 4096 episodes, from profiles/r1_v5_ncu_episode_tc_kernel_summary.csv"
-            pol.set_option("ep_tc", 0)
-            pol.env_reset()
-            pol.env_step(20)
-            roofline["ffma_persistent_kernel_us_per_env_step"] = float(pol.env_step_timed(n_prof)[0]) / n_prof * 1e3
-            pol.set_option("ep_tc", 1)
+            if single_wave:
+                pol.set_option("ep_tc", 0)
+                pol.env_reset()
+                pol.env_step(20)
+                roofline["ffma_persistent_kernel_us_per_env_step"] = float(pol.env_step_timed(n_prof)[0]) / n_prof * 1e3
+                pol.set_option("ep_tc", 1)
+            else:
+                roofline["kernel"] += f"; {-(-((n_local + 31) // 32) // 148)} waves per step"
         else:
             roofline = dict(
                 bound="hbm", kernel="episode_kernel (persistent, all env-steps of a launch)",
