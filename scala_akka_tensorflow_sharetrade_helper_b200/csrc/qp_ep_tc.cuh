@@ -155,7 +155,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     uint8_t* ring = base + off_ring;                            // 2 stages x (hi, lo) of [Np x 32]
     uint8_t* Bbwd_hi = ring;                                    // after the forward: dZ1 hi / lo, [Np x 32 episodes]
     uint8_t* Bbwd_lo = Bbwd_hi + TB;
-    float* HS = reinterpret_cast<float*>(Afwd);                 // after the forward: window part of z1(s), [Np][33]
+    float* HS = reinterpret_cast<float*>(Afwd);                 // after the forward: window part of z1(s), then h(s), [Np][33]
     float* ZN = HS + (size_t)Np * kXStride;                     // after the forward: window part of z1(s'), [Np][33]
     // master window, kept as the A operand of the backward contraction: X^T [R = halves*128 rows][32 episodes],
     // K-major SWIZZLE_128B.  The rows are a ring: at step sidx of the launch window element k is row
@@ -285,8 +285,9 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         float q_s[3] = {0.f, 0.f, 0.f}, q_n[3] = {0.f, 0.f, 0.f};
         int action = 0, explored = 0, a_eff = 2, kn = 0;
         float r32 = 0.0f, target = 0.0f, dz2 = 0.0f;
-        double nb = budget, p_new = 0.0;
+        double nb = budget, p_new = 0.0, cur = 0.0;
         int32_t ns = shares;
+        uint32_t rnd[4] = {0u, 0u, 0u, 0u};
         // producer side of the W1^T ring: k-block number kk of this step into its stage
         auto push_w_tiles = [&](int kk) {
             const int kb = (kk + kb_first) % nkb;
@@ -381,6 +382,14 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                 tc_commit(tf_fwd);
             }
             ring_it += (uint32_t)nkb;
+            // while the tensor core works: everything of the decision that does not depend on Q
+            {
+                const uint64_t env_id = (uint64_t)(a.env_id_base + e);
+                philox4x32_10((uint32_t)env_id, (uint32_t)(env_id >> 32), (uint32_t)istep, 1u,
+                              (uint32_t)hp.seed, (uint32_t)(hp.seed >> 32), rnd);
+                p_new = (double)*reinterpret_cast<const float*>(XT + et_swz((wn + roff) & Rm, lane));
+                cur = __dadd_rn(budget, __dmul_rn((double)shares, share_value));
+            }
             tc_wait(tf_fwd, par);
             tc_fence_after();
 
@@ -411,6 +420,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
 #pragma unroll 4
                 for (int c = warp; c < H; c += nwarps) {
                     const float h = et_hidden(HS[c * kXStride + lane], xb, xs, Wb[c], Ws[c], bias);
+                    HS[c * kXStride + lane] = h;                        // from here on the tile holds h(s)
                     const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
                     pq[0] = fmaf(h, w2.x, pq[0]); pq[1] = fmaf(h, w2.y, pq[1]); pq[2] = fmaf(h, w2.z, pq[2]);
                 }
@@ -431,17 +441,11 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                 s += bias;
                 q_s[t] = s > 0.0f ? s : 0.0f;
             }
-            const uint64_t env_id = (uint64_t)(a.env_id_base + e);
-            uint32_t r[4];
-            philox4x32_10((uint32_t)env_id, (uint32_t)(env_id >> 32), (uint32_t)istep, 1u,
-                          (uint32_t)hp.seed, (uint32_t)(hp.seed >> 32), r);
-            const float u = (float)(r[0] >> 8) * (1.0f / 16777216.0f);
+            const float u = (float)(rnd[0] >> 8) * (1.0f / 16777216.0f);
             float thr = __fdiv_rn((float)istep, hp.step_div);
             if (hp.epsilon < thr) thr = hp.epsilon;
             if (u < thr) action = argmax3(q_s);
-            else { explored = 1; action = (int)(((uint64_t)r[1] * 3u) >> 32); }
-            p_new = (double)*reinterpret_cast<const float*>(XT + et_swz((wn + roff) & Rm, lane));
-            const double cur = __dadd_rn(budget, __dmul_rn((double)shares, share_value));
+            else { explored = 1; action = (int)(((uint64_t)rnd[1] * 3u) >> 32); }
             const double base_b = hp.bookkeeping == 0 ? a.B0 : budget;
             const int32_t base_n = hp.bookkeeping == 0 ? a.N0 : shares;
             nb = base_b; ns = base_n;
@@ -484,11 +488,9 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             target = __fadd_rn(r32, __fmul_rn(hp.gamma, qn_k));
             const float dq = -__fmul_rn(2.0f, __fsub_rn(target, qs_k));
             dz2 = (valid && qs_k > 0.0f) ? dq : 0.0f;
-            const float xb_s = __double2float_rn(budget), xs_s = (float)shares;      // state s (carry not yet advanced)
 #pragma unroll 4
             for (int c = warp; c < H; c += nwarps) {
-                const float hcol = et_hidden(HS[c * kXStride + lane], xb_s, xs_s, Wb[c], Ws[c], bias);
-                const float d1 = hcol > 0.0f ? __fmul_rn(dz2, W2s[c * 4 + kn]) : 0.0f;
+                const float d1 = HS[c * kXStride + lane] > 0.0f ? __fmul_rn(dz2, W2s[c * 4 + kn]) : 0.0f;
                 const float hi = et_tf32(d1);
                 const uint32_t off = et_swz(c, lane);
                 *reinterpret_cast<float*>(Bbwd_hi + off) = hi;
@@ -547,11 +549,10 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             if (tid < H) {
                 const int c = tid;
                 const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
-                const float wb = Wb[c], ws = Ws[c];
                 float s0 = acc5[0], s1 = acc5[1], s2 = acc5[2], x0 = acc5[3], x1 = acc5[4];
 #pragma unroll 8
                 for (int el = 0; el < kTileEnvs; ++el) {
-                    const float h = et_hidden(HS[c * kXStride + el], XE[el], XE[32 + el], wb, ws, bias);
+                    const float h = HS[c * kXStride + el];
                     const float dz = dz2s[el];
                     const int k = kns[el];
                     const float hv = __fmul_rn(h, dz);
