@@ -120,11 +120,19 @@ int qp_env_step(qp_handle* h, int32_t n_steps);
 int qp_env_step_async(qp_handle* h, int32_t n_steps);
 int qp_sync(qp_handle* h);
 
-/* Execution options (no reference counterpart).  "fused" (default 1): when the episodes fit one
- * 32-episode tile per SM and a single GPU is used, qp_env_step* run as ONE persistent cooperative
- * kernel for all requested steps (price windows stay in shared memory, two grid barriers per
- * step); 0 forces the three-kernels-per-step path that larger batches and multi-GPU runs use.
- * Read-only: "fused_active" = 1 if the next qp_env_step would take the persistent kernel. */
+/* Execution options (no reference counterpart); all default to 1.
+ *   "fused"   qp_env_step* run as ONE persistent cooperative kernel for all requested steps (price windows
+ *             stay in shared memory); 0 forces the three-kernels-per-step path.
+ *   "ep_tc"   the persistent kernel does its two contractions on the tcgen05 tensor cores (hi/lo TF32 pairs,
+ *             fp32-grade).  Taken when the prices are tf32-exact (checked at qp_env_create) and the shape fits
+ *             (window 193..203 at hidden 200); any number of episodes (waves).  Otherwise, and
+ *             with 0, the FFMA form of the kernel runs, which needs the episodes to fit one 32-episode tile per SM.
+ *   "p2p"     several GPUs: gradient exchange inside the persistent kernel over NVLink peer memory
+ *             (qp_dist_p2p_export / qp_dist_p2p_import); 0: one fused step kernel per env-step + NCCL all-reduce.
+ *   "wide", "tc", "tc_passes"   the GEMM-organised path for policies whose W1 does not fit in shared memory.
+ *   "phase_clocks"  tuning aid, see qp_debug_phase_clocks.
+ * Read-only: "fused_active", "ep_tc_active", "p2p_active", "fused_step_active", "tc_active", "tc_a_lo_zero":
+ * what the next qp_env_step would take. */
 int qp_set_option(qp_handle* h, const char* key, int64_t value);
 int qp_get_option(qp_handle* h, const char* key, int64_t* value);
 /* Test hook for the tcgen05 tensor-core GEMM of the GEMM-organised path, on its own:

@@ -1,18 +1,25 @@
 // qp_ep_tc.cuh — the persistent episode kernel with its two in-CTA contractions on the tcgen05
-// tensor cores (3xTF32), for the reference shape (window 201, hidden 200) and its neighbours.
+// tensor cores, for the reference shape (window 201, hidden 200) and its neighbours.  DESIGN.md §4 (i-tc).
 //
-// Same life cycle as episode_kernel (qp_kernels.cuh): one cooperative launch, CTA c owns episodes
-// [32c, 32c+32), the price window lives in shared memory and slides one row per step, two grid
-// barriers per step around the gradient sum + AdaGrad.  What changes is phase A:
-//   * forward  Z[64, Np] = X[64, Kp] · W1[Kp, Np]   rows 0..31 = state s, rows 32..63 = state s' of the 32
-//     episodes; issued as M = 128 MMAs (rows 64..127 read whatever follows in shared memory and land in
-//     TMEM lanes nobody reads).  A = X is written by the CTA itself in the K-major SWIZZLE_128B
-//     layout; B = W1^T streams through a 2-stage TMA ring from the tf32 hi/lo copies that phase B
-//     of the previous step left in global memory.
-//   * backward dW1[256, Np] = X^T[256, 32] · dZ1[32, Np]   two M = 128 halves, K = the 32 episodes.
-// Precision: prices must be tf32-exact (checked at qp_env_create; the synthetic quarter-tick walk is)
-// so that X needs no lo part; W1 and dZ1 are hi/lo pairs -> A_hi·B_hi + A_hi·B_lo, fp32-grade.  The
-// budget/shares columns of the state (not tf32-exact) stay on the FFMA path, as in episode_kernel.
+// Life cycle as episode_kernel (qp_kernels.cuh): one cooperative launch runs every requested env-step;
+// CTA c owns episodes [32c, 32c+32) (or, with more tiles than CTAs, tiles c, c+G, ... in waves).
+//   * state     the price window of the tile lives in shared memory in the layout of the backward A operand
+//               (X^T, K-major SWIZZLE_128B) as a ring of rows: sliding it is writing one row per step
+//   * forward   Z[64, Np] = X[64, Kp] · W1[Kp, Np]: rows 0..31 = state s, rows 32..63 = state s'; issued as M = 128
+//               MMAs (rows 64..127 read whatever follows in shared memory and land in TMEM lanes nobody reads).
+//               A = X is written by the CTA; B = W1^T streams through a 2-stage TMA ring from the tf32 hi/lo
+//               copies that phase B of the previous step left in global memory
+//   * glue      raw z out of TMEM into shared-memory tiles; Q(s), select, book-keeping, Q(s'), TD target and dZ1
+//               on all warps; dZ1 goes straight into the backward B operand as a tf32 hi/lo pair
+//   * backward  dW1[256, Np] = X^T[256, 32] · dZ1[32, Np], two M = 128 halves, K = the 32 episodes; the partial
+//               leaves TMEM through swizzled boxes and TMA tensor stores (reduce-add from the second wave on)
+//   * update    grid barrier; every CTA owns a share of the parameters: the tiles' partial segments arrive as
+//               bulk copies and are summed in shared memory; with several GPUs the shares are exchanged over
+//               NVLink peer memory ({value, tag} stores, no fence); AdaGrad; tf32 hi/lo of the new W1 published;
+//               split barrier (publishers count up, warp 0 of each CTA waits at the top of the next step)
+// Precision: prices must be tf32-exact (checked at qp_env_create; the synthetic quarter-tick walk is) so that
+// X needs no lo part; W1 and dZ1 are hi/lo pairs -> A·B_hi + A·B_lo, fp32-grade.  The budget/shares columns
+// of the state (not tf32-exact) stay on the FFMA pipe, as in episode_kernel.
 #pragma once
 #include "qp_kernels.cuh"
 #include "qp_tc.cuh"
