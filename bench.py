@@ -428,7 +428,7 @@ def run_ours(args):
                 c = pol.phase_clocks(40)[5:]
                 pol.set_option("phase_clocks", 0)
                 labels = ["S0 A-operand build + tables", "S1 W1^T stream + forward MMA", "S2 z out of TMEM", "S3 Q(s), select, book-keeping, Q(s')",
-                          "S4 TD target, dZ1 hi/lo", "S5 backward MMA, dW2, budget/shares rows", "S6 dW1 partial: TMEM -> TMA store",
+                          "S4 TD target, dZ1 hi/lo", "S5 backward MMA, dW2, budget/shares rows", "S6 dW1 partial: TMEM -> TMA store, extra rows",
                           "S7 window row + store completion", "grid barrier", "phase B: bulk-copy sum, AdaGrad, W1^T publish"]
                 d = np.diff(c[:, :11], axis=1).astype(np.float64).mean(axis=0)
                 tot = float((c[1:, 0] - c[:-1, 0]).mean())
@@ -440,8 +440,8 @@ def run_ours(args):
                 # dram__bytes_read.sum + dram__bytes_write.sum of the committed ncu --set full capture of one 30-step
                 # launch of this kernel, per env-step; far below the algorithmic bytes because the windows stay in
                 # shared memory and weights / partials in L2
-                roofline["traffic"] = (4.756736e6 + 1.551104e6) / 30.0
-                roofline["traffic_note"] = "bytes per env-step of 4096 episodes, from profiles/r1_v5_ncu_episode_tc_kernel_summary.csv"
+                roofline["traffic"] = (4.754944e6 + 1.326592e6) / 30.0
+                roofline["traffic_note"] = "bytes per env-step of 4096 episodes, from profiles/r1_v6_ncu_episode_tc_kernel_summary.csv"
             if single_wave:
                 pol.set_option("ep_tc", 0)
                 pol.env_reset()
