@@ -723,7 +723,7 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
         x.published = h->et_published.p;
         x.p_pad = (int64_t)p2p_pad(h);
         for (int r = 0; r < ea.world && ea.world > 1; ++r) {
-            x.pdata[r] = reinterpret_cast<uint2*>(reinterpret_cast<char*>(h->p2p_peer_block[r]) + p2p_tc_offset(h));
+            x.pdata[r] = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(h->p2p_peer_block[r]) + p2p_tc_offset(h));
         }
         if (h->tm_et_part_ptr != h->part1.p || h->tm_et_part_tiles != n_tiles) {
             QP_TRY(make_tmap3_store(&h->tm_et_part, h->part1.p, (uint64_t)h->hp.H, (uint64_t)h->hp.wn, (uint64_t)n_tiles,
@@ -1625,7 +1625,7 @@ int qp_dist_p2p_export(qp_handle* h, void* out, size_t out_bytes) {
     static_assert(sizeof(cudaIpcMemHandle_t) == QP_DIST_IPC_BYTES, "IPC handle size");
     QP_TRY(use_device(h));
     if (!h->p2p_block) {
-        const size_t bytes = p2p_tc_offset(h) + (size_t)2 * 8 * p2p_pad(h) * sizeof(uint2);
+        const size_t bytes = p2p_tc_offset(h) + (size_t)2 * 8 * p2p_pad(h) * sizeof(unsigned long long);
         QP_CUDA(cudaMalloc(&h->p2p_block, bytes));
         QP_CUDA(cudaMemset(h->p2p_block, 0, bytes));
         QP_CUDA(cudaDeviceSynchronize());

@@ -39,7 +39,7 @@ struct EpTcArgs {
     int halves;                      // ceil(wn / 128): M = 128 tiles of the backward contraction
     unsigned long long* published;   // CTAs that have finished phase B, summed over the steps of the launch
     // several GPUs (ea.world > 1): every rank's exchange block, mapped into this process (CUDA IPC)
-    uint2* pdata[8];                 // [parity][src rank][p_pad] {value, step tag} of the ranks' shares of the gradient
+    unsigned long long* pdata[8];    // [parity][src rank][p_pad] (step tag << 32 | value bits) of the ranks' shares of the gradient
     int64_t p_pad;
 };
 
@@ -713,13 +713,15 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                     // received this rank's step t+1, which is sent after step t has been read.
                     const unsigned int want = ea.flag_base + (unsigned int)sidx + 1u;
                     const size_t slot = (size_t)(want & 1u) * (size_t)ea.world;     // (global step parity: alternates across launches too)
-                    const uint2 mine = make_uint2(__float_as_uint(g), want);
+                    // ONE 64-bit scalar store per value (tag in the upper half): single-copy atomic by the memory model,
+                    // which a two-element vector store is not
+                    const unsigned long long mine = ((unsigned long long)want << 32) | (unsigned long long)__float_as_uint(g);
 #pragma unroll
                     for (int r = 0; r < 8; ++r)
                         if (r < ea.world && r != ea.rank)
-                            asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(x.pdata[r] + (slot + (size_t)ea.rank) * (size_t)x.p_pad + p),
-                                         "r"(mine.x), "r"(mine.y) : "memory");
-                    const uint2* local = x.pdata[ea.rank] + slot * (size_t)x.p_pad + p;
+                            asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(x.pdata[r] + (slot + (size_t)ea.rank) * (size_t)x.p_pad + p),
+                                         "l"(mine) : "memory");
+                    const unsigned long long* local = x.pdata[ea.rank] + slot * (size_t)x.p_pad + p;
                     float pv[8];
 #pragma unroll
                     for (int r = 0; r < 8; ++r) pv[r] = 0.0f;
@@ -728,15 +730,18 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                     unsigned long long t0 = 0;
                     for (unsigned int spins = 0; pending != 0u; ++spins) {
                         // all outstanding slots are read in one go (independent loads), then inspected
-                        uint2 v[8];
+                        unsigned long long v[8];
 #pragma unroll
                         for (int r = 0; r < 8; ++r)
                             if ((pending >> r) & 1u)
-                                asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(v[r].x), "=r"(v[r].y)
+                                asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v[r])
                                              : "l"(local + (size_t)r * (size_t)x.p_pad) : "memory");
 #pragma unroll
                         for (int r = 0; r < 8; ++r)
-                            if (((pending >> r) & 1u) && v[r].y == want) { pv[r] = __uint_as_float(v[r].x); pending &= ~(1u << r); }
+                            if (((pending >> r) & 1u) && (unsigned int)(v[r] >> 32) == want) {
+                                pv[r] = __uint_as_float((unsigned int)v[r]);
+                                pending &= ~(1u << r);
+                            }
                         if ((spins & 4095u) == 4095u) {
                             unsigned long long t;
                             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
