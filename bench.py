@@ -37,6 +37,7 @@ D = WINDOW + 2
 P = D * HIDDEN + 3 * HIDDEN
 FLOP_PER_ENV_STEP = 6 * D * HIDDEN + 16 * HIDDEN          # 246 800
 ROLLOUT = SERIES_LEN - WINDOW                             # env-steps per bench step
+SCALING = "weak"                                          # per-GPU episodes fixed as N grows (configs[1], configs[2])
 METRIC = "env-steps/sec (act+TD update)"
 UNIT = "env-steps/s"
 WORKLOAD_NAME = "configs[1]"
@@ -45,7 +46,7 @@ WORKLOAD_NAME = "configs[1]"
 def set_workload(name: str, args):
     """configs[1] (default): 4096 episodes, window 201, hidden 200.  'wide' = configs[3]: hist 512
     (window 513), hidden 2048, batch 65 536 on one GPU; a bench step is then a 16-env-step slice."""
-    global WINDOW, HIDDEN, D, P, FLOP_PER_ENV_STEP, ROLLOUT, WORKLOAD_NAME
+    global WINDOW, HIDDEN, D, P, FLOP_PER_ENV_STEP, ROLLOUT, WORKLOAD_NAME, SCALING
     if name == "wide":
         WINDOW, HIDDEN, WORKLOAD_NAME = 513, 2048, "configs[3] (wide policy)"
         D = WINDOW + 2
@@ -53,7 +54,8 @@ def set_workload(name: str, args):
         FLOP_PER_ENV_STEP = 6 * D * HIDDEN + 16 * HIDDEN
         ROLLOUT = args.rollout_steps or 16
         if args.envs_per_gpu == 4096:
-            args.envs_per_gpu = 65536 // max(1, args.gpus)
+            args.envs_per_gpu = 65536 // max(1, args.gpus)     # the config names the total batch: strong scaling
+            SCALING = "strong"
     elif args.rollout_steps:
         ROLLOUT = args.rollout_steps
 
@@ -490,7 +492,7 @@ def run_ours(args):
 
     line = dict(
         metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
-        ms_per_step=ms / args.steps, higher_is_better=True, scaling="weak", vs_baseline=None, dtype="fp32",
+        ms_per_step=ms / args.steps, higher_is_better=True, scaling=SCALING, vs_baseline=None, dtype="fp32",
         data="synthetic", config=workload_config(args, n_total), clocks=clocks,
         e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=int(prices_np.nbytes + soe_np.nbytes),
                  d2h_bytes_per_step=int(n_local * 8), ms_per_step=e2e_wall / args.steps * 1e3, clocks=e2e_clocks,
