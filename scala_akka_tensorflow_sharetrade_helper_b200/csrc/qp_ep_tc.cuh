@@ -74,13 +74,6 @@ __device__ __forceinline__ void et_tmem_ld16(uint32_t taddr, float* v) {
     for (int j = 0; j < 16; ++j) v[j] = __uint_as_float(r[j]);
 }
 
-__device__ __forceinline__ void et_tmem_ld16_nowait(uint32_t taddr, uint32_t* r) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];\n"
-        : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]),
-          "=r"(r[8]), "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
-        : "r"(taddr));
-}
 __device__ __forceinline__ void et_tmem_ld32_nowait(uint32_t taddr, uint32_t* r) {
     asm volatile(
         "tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
@@ -238,7 +231,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         for (int64_t p = ((int64_t)blockIdx.x * nthreads + tid) * 4; p < P1; p += (int64_t)gridDim.x * nthreads * 4)
             et_publish_w(x, p, __ldcg(reinterpret_cast<const float4*>(W1g + p)), H, wn);
     }
-    // phase B's division of the parameters over the CTAs (see there), and who publishes into which k-block
+    // phase B's division of the parameters over the CTAs (see there)
     const int64_t P1 = (int64_t)D * H, P = P1 + 3 * (int64_t)H;
     const int n1 = (int)min(n_tiles, (int64_t)gridDim.x);      // one partial per CTA that has tiles
     const int n_w1_ctas = max(1, (int)gridDim.x - 2);
@@ -477,7 +470,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 4] = clock64();
 
         if (has_tile) {
-            // ---- S4: TD target; dZ1 as a K-major (episodes contiguous) tf32 hi/lo pair; X^T operand
+            // ---- S4: TD target; dZ1 as a K-major (episodes contiguous) tf32 hi/lo pair = B operand of the backward
 #pragma unroll
             for (int t = 0; t < 3; ++t) {
                 float pw[kEtWarps];
@@ -657,7 +650,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
 
         // ---- phase B: gradient sum over the tiles + AdaGrad (as episode_kernel) + tf32 hi/lo of the new W1.
         // W1: CTA c owns `chunk` consecutive parameters; their n_tiles partial segments come in as bulk
-        // copies (all in flight at once, one mbarrier), then one thread per parameter sums them out of
+        // copies (all in flight at once, one mbarrier per group of 32), then one thread per parameter sums them out of
         // shared memory in the order of the FFMA kernel: four interleaved running sums, (0+1)+(2+3).
         // W2 (3*H parameters, its own partial buffer) is the last two CTAs' share, handled the same way.
         if (flow) {
