@@ -201,6 +201,7 @@ struct qp_handle {
     bool allow_fused = true;            // qp_set_option("fused", 0) forces the three-kernel path
     DevBuf<long long> dbg;              // phase stamps of the persistent kernel (qp_debug_phase_clocks)
     bool want_dbg = false;
+    bool want_cta_ns = false;           // "phase_clocks" = 2: globaltimer stamps of every CTA instead (tensor-core kernel)
     bool coop_launch = false;
 };
 
@@ -645,7 +646,7 @@ int ep_tc_prepare(qp_handle* h) {
     const int Kp = (int)round_up(hp.wn, 32), nkb = Kp / 32, Np = (int)round_up(hp.H, 16), halves = (hp.wn + 127) / 128;
     const size_t TB = (size_t)Np * 128;
     const size_t smem = 1024 + (size_t)nkb * 8192 + 4 * TB + (size_t)halves * 16384 + 16 + (size_t)hp.H * 16 +
-                        (size_t)hp.H * 8 + 256 + (size_t)kEtWarps * 192 * 4 + 256 + 8 + 256;
+                        (size_t)hp.H * 8 + 256 + (size_t)kEtWarps * 384 * 4 + 256 + 8 + 256;
     // the window ring needs one free row beyond the window; the partial's boxes are staged in the operand ring
     // (8 KB per warp) and, for the warps that do not fit there, behind h(s) in the A-operand region (4 KB each)
     const size_t n_ring = std::min<size_t>(kEtWarps, 4 * TB / 8192);
@@ -719,6 +720,11 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
         x.ea = ea;
         x.w1T_hi = h->et_w_hi.p; x.w1T_lo = h->et_w_lo.p;
         x.Kp = h->et_Kp; x.nkb = h->et_nkb; x.Np = h->et_Np; x.halves = h->et_halves;
+        if (h->want_cta_ns) {        // the stamps share the dbg buffer: [n_steps][grid][4] instead of [n_steps][kDbgSlots]
+            QP_TRY(h->dbg.ensure((size_t)n_steps * h->num_sms * 4));
+            x.ea.dbg = nullptr;
+            x.cta_ns = h->dbg.p;
+        }
         QP_TRY(h->et_published.ensure(1));
         x.published = h->et_published.p;
         x.p_pad = (int64_t)p2p_pad(h);
@@ -1561,7 +1567,7 @@ int qp_debug_phase_clocks(qp_handle* h, int32_t n_steps, int64_t* out) {
 
 int qp_set_option(qp_handle* h, const char* key, int64_t value) {
     if (!h || !key) return fail(QP_EINVAL, "null argument");
-    if (std::strcmp(key, "phase_clocks") == 0) { h->want_dbg = value != 0; return QP_OK; }
+    if (std::strcmp(key, "phase_clocks") == 0) { h->want_dbg = value != 0; h->want_cta_ns = value == 2; return QP_OK; }
     if (std::strcmp(key, "fused") == 0) { h->allow_fused = value != 0; return QP_OK; }
     if (std::strcmp(key, "tc") == 0) { h->allow_tc = value != 0; return QP_OK; }
     if (std::strcmp(key, "p2p") == 0) { h->allow_p2p = value != 0; return QP_OK; }

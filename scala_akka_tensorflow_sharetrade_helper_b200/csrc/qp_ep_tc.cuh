@@ -41,6 +41,7 @@ struct EpTcArgs {
     // several GPUs (ea.world > 1): every rank's exchange block, mapped into this process (CUDA IPC)
     unsigned long long* pdata[8];    // [parity][src rank][p_pad] (step tag << 32 | value bits) of the ranks' shares of the gradient
     int64_t p_pad;
+    long long* cta_ns;               // tuning aid ("phase_clocks" = 2): [n_steps][gridDim][4] globaltimer stamps of every CTA
 };
 
 #ifdef __CUDACC__
@@ -167,10 +168,10 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     float* Wb = W2s + (size_t)H * 4;
     float* Ws = Wb + H;
     float* XE = Ws + H;                                         // [2][32]
-    float* qpart = XE + 64;                                     // [warps][2 states][3][32]
-    float* dz2s = qpart + kEtWarps * 2 * 3 * 32;                // [32]
+    float* qpart = XE + 64;                                     // [warps][Q(s), Q(s') after Buy / Sell / Hold][3][32]
+    float* dz2s = qpart + kEtWarps * 4 * 3 * 32;                // [32]
     int* kns = reinterpret_cast<int*>(dz2s + 32);               // [32]
-    uint64_t* bars = reinterpret_cast<uint64_t*>(base + ((off_w2s + (size_t)H * 24 + (64 + kEtWarps * 2 * 3 * 32 + 64) * 4 + 7) & ~(size_t)7));
+    uint64_t* bars = reinterpret_cast<uint64_t*>(base + ((off_w2s + (size_t)H * 24 + (64 + kEtWarps * 4 * 3 * 32 + 64) * 4 + 7) & ~(size_t)7));
     uint64_t* full = bars;          // [2]
     uint64_t* empty = bars + 2;     // [2]
     uint64_t* tf_fwd = bars + 4;
@@ -271,6 +272,14 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         float* out = ea.part1 + (size_t)blockIdx.x * ((size_t)D * H);
         float* out2 = a.dw2_part + (size_t)blockIdx.x * (3 * H);
         if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 0] = clock64();
+        auto cta_stamp = [&](int i) {
+            if (x.cta_ns && tid == 0) {
+                unsigned long long t;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                x.cta_ns[((size_t)sidx * gridDim.x + blockIdx.x) * 4 + i] = (long long)t;
+            }
+        };
+        cta_stamp(0);
       for (int wave = 0; wave < n_waves; ++wave) {
         const int64_t tile = (int64_t)wave * gridDim.x + blockIdx.x;
         const bool has_tile = tile < n_tiles;
@@ -394,6 +403,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             tc_fence_after();
 
             if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 2] = clock64();
+            cta_stamp(1);
             // ---- S2: out of TMEM into shared memory: h(s) (lane quarter 0) and the window part of z1(s')
             // (lane quarter 1); the element-wise work after this runs on all twelve warps
             if (q4 < 2) {
@@ -411,21 +421,41 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         __syncthreads();
         if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 3] = clock64();
 
+        // the three states s' the decision can lead to (index = effective action: 0 Buy, 1 Sell, 2 Hold; an
+        // action that is not affordable is demoted to Hold, TrainerChildActor.scala:118-123) — known before Q is
+        const double base_b = hp.bookkeeping == 0 ? a.B0 : budget;
+        const int32_t base_n = hp.bookkeeping == 0 ? a.N0 : shares;
+        const bool can_buy = base_b >= p_new, can_sell = base_n > 0;
+        const double nbc[3] = {can_buy ? __dsub_rn(base_b, p_new) : base_b, can_sell ? __dadd_rn(base_b, p_new) : base_b, base_b};
+        const int32_t nsc[3] = {can_buy ? base_n + 1 : base_n, can_sell ? base_n - 1 : base_n, base_n};
         if (has_tile) {
-            // ---- S3: Q(s) (columns dealt round-robin to the warps, fixed order), SelectionAction, decision,
-            // reward (every warp keeps its own copy), then Q(s')
+            // ---- S3: ONE pass over the hidden columns (dealt round-robin to the warps, fixed order) forms h(s) and
+            // the partial sums of Q(s) and of Q(s') for all three outcomes; then SelectionAction, decision, reward
+            // (every warp keeps its own copy) pick the outcome.  (Two passes with the decision in between cost a
+            // barrier and a third more shared-memory traffic.)
             {
-                float pq[3] = {0.f, 0.f, 0.f};
+                float pq[4][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}};
                 const float xb = __double2float_rn(budget), xs = (float)shares;
-#pragma unroll 4
+                const float xnb[3] = {__double2float_rn(nbc[0]), __double2float_rn(nbc[1]), __double2float_rn(nbc[2])};
+                const float xns[3] = {(float)nsc[0], (float)nsc[1], (float)nsc[2]};
+#pragma unroll 2
                 for (int c = warp; c < H; c += nwarps) {
-                    const float h = et_hidden(HS[c * kXStride + lane], xb, xs, Wb[c], Ws[c], bias);
-                    HS[c * kXStride + lane] = h;                        // from here on the tile holds h(s)
+                    const float wb = Wb[c], ws = Ws[c], zn = ZN[c * kXStride + lane];
                     const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
-                    pq[0] = fmaf(h, w2.x, pq[0]); pq[1] = fmaf(h, w2.y, pq[1]); pq[2] = fmaf(h, w2.z, pq[2]);
+                    const float h = et_hidden(HS[c * kXStride + lane], xb, xs, wb, ws, bias);
+                    HS[c * kXStride + lane] = h;                        // from here on the tile holds h(s)
+                    pq[0][0] = fmaf(h, w2.x, pq[0][0]); pq[0][1] = fmaf(h, w2.y, pq[0][1]); pq[0][2] = fmaf(h, w2.z, pq[0][2]);
+#pragma unroll
+                    for (int j = 0; j < 3; ++j) {
+                        const float hn = et_hidden(zn, xnb[j], xns[j], wb, ws, bias);
+                        pq[1 + j][0] = fmaf(hn, w2.x, pq[1 + j][0]); pq[1 + j][1] = fmaf(hn, w2.y, pq[1 + j][1]);
+                        pq[1 + j][2] = fmaf(hn, w2.z, pq[1 + j][2]);
+                    }
                 }
 #pragma unroll
-                for (int t = 0; t < 3; ++t) qpart[((warp * 2 + 0) * 3 + t) * 32 + lane] = pq[t];
+                for (int j = 0; j < 4; ++j)
+#pragma unroll
+                    for (int t = 0; t < 3; ++t) qpart[((warp * 4 + j) * 3 + t) * 32 + lane] = pq[j][t];
             }
         }
         __syncthreads();
@@ -434,7 +464,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             for (int t = 0; t < 3; ++t) {
                 float pw[kEtWarps];
 #pragma unroll
-                for (int w = 0; w < kEtWarps; ++w) pw[w] = w < nwarps ? qpart[((w * 2 + 0) * 3 + t) * 32 + lane] : 0.0f;
+                for (int w = 0; w < kEtWarps; ++w) pw[w] = w < nwarps ? qpart[((w * 4 + 0) * 3 + t) * 32 + lane] : 0.0f;
                 float s = 0.0f;
 #pragma unroll
                 for (int w = 0; w < kEtWarps; ++w) s += pw[w];
@@ -446,36 +476,21 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             if (hp.epsilon < thr) thr = hp.epsilon;
             if (u < thr) action = argmax3(q_s);
             else { explored = 1; action = (int)(((uint64_t)rnd[1] * 3u) >> 32); }
-            const double base_b = hp.bookkeeping == 0 ? a.B0 : budget;
-            const int32_t base_n = hp.bookkeeping == 0 ? a.N0 : shares;
-            nb = base_b; ns = base_n;
-            if (action == 0 && base_b >= p_new) { nb = __dsub_rn(base_b, p_new); ns = base_n + 1; a_eff = 0; }
-            else if (action == 1 && base_n > 0) { nb = __dadd_rn(base_b, p_new); ns = base_n - 1; a_eff = 1; }
+            if (action == 0 && can_buy) a_eff = 0;
+            else if (action == 1 && can_sell) a_eff = 1;
+            nb = a_eff == 0 ? nbc[0] : (a_eff == 1 ? nbc[1] : nbc[2]);
+            ns = a_eff == 0 ? nsc[0] : (a_eff == 1 ? nsc[1] : nsc[2]);
             const double newp = __dadd_rn(nb, __dmul_rn((double)ns, p_new));
             r32 = __double2float_rn(__dsub_rn(newp, cur));
-            {
-                const float xnb = __double2float_rn(nb), xns = (float)ns;
-                float pq[3] = {0.f, 0.f, 0.f};
-#pragma unroll 4
-                for (int c = warp; c < H; c += nwarps) {
-                    const float h = et_hidden(ZN[c * kXStride + lane], xnb, xns, Wb[c], Ws[c], bias);
-                    const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
-                    pq[0] = fmaf(h, w2.x, pq[0]); pq[1] = fmaf(h, w2.y, pq[1]); pq[2] = fmaf(h, w2.z, pq[2]);
-                }
-#pragma unroll
-                for (int t = 0; t < 3; ++t) qpart[((warp * 2 + 1) * 3 + t) * 32 + lane] = pq[t];
-            }
-        }
-        __syncthreads();
-        if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 4] = clock64();
+            if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 4] = clock64();
 
-        if (has_tile) {
-            // ---- S4: TD target; dZ1 as a K-major (episodes contiguous) tf32 hi/lo pair = B operand of the backward
+            // ---- S4: Q(s') of the outcome taken, TD target; dZ1 as a K-major (episodes contiguous) tf32 hi/lo pair = B
+            // operand of the backward
 #pragma unroll
             for (int t = 0; t < 3; ++t) {
                 float pw[kEtWarps];
 #pragma unroll
-                for (int w = 0; w < kEtWarps; ++w) pw[w] = w < nwarps ? qpart[((w * 2 + 1) * 3 + t) * 32 + lane] : 0.0f;
+                for (int w = 0; w < kEtWarps; ++w) pw[w] = w < nwarps ? qpart[((w * 4 + 1 + a_eff) * 3 + t) * 32 + lane] : 0.0f;
                 float s = 0.0f;
 #pragma unroll
                 for (int w = 0; w < kEtWarps; ++w) s += pw[w];
@@ -644,6 +659,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         if (!multi && has_tile && warp == 0) *reinterpret_cast<float*>(XT + et_swz((wn + 1 + sidx) & Rm, lane)) = p_next;
         et_bulk_wait_all();                                             // the partial is in global memory
         if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 8] = clock64();
+        cta_stamp(2);
         __threadfence();
         grid.sync();
         if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 9] = clock64();
@@ -821,6 +837,7 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             }
         }
         if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + 10] = clock64();
+        cta_stamp(3);
         if (!flow) {
             __threadfence();
             grid.sync();
