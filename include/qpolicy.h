@@ -181,7 +181,9 @@ int qp_train(qp_handle* h, const float* prices, int64_t series_len, int64_t n_se
 /* ---- batching front-end for the router fan-out (TrainerRouterActor.scala:60-66, :88): many child
  * actors, on any threads, queue their SelectionAction / UpdateQ messages; one qp_flush answers all
  * queued selects with ONE launch (using the weights as they are at the flush) and then turns all
- * queued updates into ONE gradient-SUM step.  Enqueue calls are thread-safe and never touch the GPU;
+ * queued updates into ONE gradient-SUM step.  Enqueue calls are thread-safe and never launch GPU work: a message is one atomic slot
+ * reservation plus a copy straight into the pinned staging buffer the flush uploads from (a queue that
+ * has to grow allocates pinned host memory);
  * the size guards of QDecisionPolicyActor.scala:56-57, :64-65 apply at enqueue time (QP_EINVAL).
  * qp_take_action returns the action of a ticket from the most recent flush that held selects. */
 int qp_enqueue_select(qp_handle* h, const float* state, int64_t state_len, float step, int64_t env_id,

@@ -17,7 +17,9 @@
 #include <cerrno>
 #include <cstdlib>
 #include <map>
+#include <atomic>
 #include <mutex>
+#include <shared_mutex>
 #include <string>
 #include <vector>
 
@@ -165,12 +167,21 @@ struct qp_handle {
     bool p2p_ready = false, allow_p2p = true;
     unsigned int p2p_flag_base = 0;
     // batching front-end (config 5): child actors enqueue rows, one flush = one GPU launch per kind
-    std::mutex qmu;
-    std::vector<float> q_states, q_steps, u_states, u_rewards, u_next;
-    std::vector<int64_t> q_ids;
+    // batching front-end: two generations of queued messages per kind, in pinned host memory.  Actors reserve a slot
+    // with one atomic add under a SHARED lock and copy their message straight into the staging buffer the flush
+    // uploads from; the exclusive lock is taken only to grow a queue or to hand a generation to the flush.
+    struct FrontQueue {
+        float* states = nullptr; float* next = nullptr; float* scalars = nullptr; int64_t* ids = nullptr;
+        int64_t cap = 0;                  // messages the buffers hold
+        std::atomic<int64_t> count{0};    // slots handed out (may overshoot cap: those callers grow the queue and retry)
+    };
+    FrontQueue q_sel[2], q_upd[2];
+    int cur_sel = 0, cur_upd = 0;       // generation the actors write to
+    std::shared_mutex qrw;
+    std::mutex flush_mu;                // flushes are serialised
     std::vector<int32_t> q_results;
     int64_t ticket_base = 0;            // ticket of q_results[0]
-    int64_t next_ticket = 0;
+    int64_t sel_first_ticket = 0;       // ticket of slot 0 of the current select generation
     // UpdateQ counter and snapshot hook (QDecisionPolicyActor.scala:74, :76)
     int64_t iteration = 0;
     std::string snapshot_path;
@@ -894,6 +905,13 @@ int qp_destroy(qp_handle* h) {
     h->m_q.release(); h->m_ids.release(); h->m_actions.release();
     h->wZ1.release(); h->wdZ1.release(); h->wdz2.release(); h->wkn.release();
     h->et_w_hi.release(); h->et_w_lo.release(); h->et_published.release();
+    for (int g = 0; g < 2; ++g)
+        for (qp_handle::FrontQueue* fq : {&h->q_sel[g], &h->q_upd[g]}) {
+            if (fq->states) cudaFreeHost(fq->states);
+            if (fq->scalars) cudaFreeHost(fq->scalars);
+            if (fq->next) cudaFreeHost(fq->next);
+            if (fq->ids) cudaFreeHost(fq->ids);
+        }
     for (int j = 0; j < 4; ++j) { h->p_hi[j].release(); h->p_lo[j].release(); }
     h->pT_hi.release(); h->pT_lo.release(); h->xe_hi.release(); h->xe_lo.release();
     h->w1T_hi.release(); h->w1T_lo.release(); h->dzT_hi.release(); h->dzT_lo.release();
@@ -1267,18 +1285,62 @@ int qp_env_portfolio_stats(qp_handle* h, double* mean, double* stddev) {
 }
 
 // ---- batching front-end -------------------------------------------------------------------------
+namespace {
+
+// grows a queue to at least `need` messages (exclusive lock held: no writer is inside)
+int front_grow(qp_handle* h, qp_handle::FrontQueue& q, bool update_kind, int64_t need) {
+    // writers that found the queue full have pushed count past cap; every slot below cap is completely written
+    if (q.count.load() > q.cap) q.count.store(q.cap);
+    if (need <= q.cap) return QP_OK;
+    QP_TRY(use_device(h));
+    const int64_t D = h->hp.D, cap = std::max<int64_t>(std::max<int64_t>(1024, 2 * q.cap), need);
+    float *st = nullptr, *nx = nullptr, *sc = nullptr;
+    int64_t* ids = nullptr;
+    QP_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&st), (size_t)cap * D * sizeof(float), cudaHostAllocDefault));
+    QP_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&sc), (size_t)cap * sizeof(float), cudaHostAllocDefault));
+    if (update_kind) QP_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&nx), (size_t)cap * D * sizeof(float), cudaHostAllocDefault));
+    else QP_CUDA(cudaHostAlloc(reinterpret_cast<void**>(&ids), (size_t)cap * sizeof(int64_t), cudaHostAllocDefault));
+    const int64_t n = std::min<int64_t>(q.count.load(), q.cap);
+    if (n > 0) {
+        std::memcpy(st, q.states, (size_t)n * D * sizeof(float));
+        std::memcpy(sc, q.scalars, (size_t)n * sizeof(float));
+        if (update_kind) std::memcpy(nx, q.next, (size_t)n * D * sizeof(float));
+        else std::memcpy(ids, q.ids, (size_t)n * sizeof(int64_t));
+    }
+    if (q.states) cudaFreeHost(q.states);
+    if (q.scalars) cudaFreeHost(q.scalars);
+    if (q.next) cudaFreeHost(q.next);
+    if (q.ids) cudaFreeHost(q.ids);
+    q.states = st; q.next = nx; q.scalars = sc; q.ids = ids; q.cap = cap;
+    return QP_OK;
+}
+
+}  // namespace
+
 int qp_enqueue_select(qp_handle* h, const float* state, int64_t state_len, float step, int64_t env_id,
                       int64_t* ticket) {
     if (!h || !state || !ticket) return fail(QP_EINVAL, "null argument");
     if (state_len != h->hp.D)
         return fail(QP_EINVAL, "SelectionAction: tensorflow input size(" + std::to_string(h->hp.D) +
                                    ") and state(" + std::to_string(state_len) + ") size do not match");
-    std::lock_guard<std::mutex> lock(h->qmu);
-    h->q_states.insert(h->q_states.end(), state, state + state_len);
-    h->q_steps.push_back(step);
-    h->q_ids.push_back(env_id);
-    *ticket = h->next_ticket++;
-    return QP_OK;
+    const size_t D = (size_t)h->hp.D;
+    for (;;) {
+        {
+            std::shared_lock<std::shared_mutex> lock(h->qrw);
+            qp_handle::FrontQueue& q = h->q_sel[h->cur_sel];
+            const int64_t slot = q.count.fetch_add(1);
+            if (slot < q.cap) {
+                std::memcpy(q.states + (size_t)slot * D, state, D * sizeof(float));
+                q.scalars[slot] = step;
+                q.ids[slot] = env_id;
+                *ticket = h->sel_first_ticket + slot;
+                return QP_OK;
+            }
+        }
+        std::unique_lock<std::shared_mutex> lock(h->qrw);     // full: grow (the first to get here does it), then retry
+        qp_handle::FrontQueue& q = h->q_sel[h->cur_sel];
+        QP_TRY(front_grow(h, q, false, std::min<int64_t>(q.count.load(), q.cap) + 1));
+    }
 }
 
 int qp_enqueue_update(qp_handle* h, const float* state, int64_t state_len, float reward,
@@ -1288,35 +1350,55 @@ int qp_enqueue_update(qp_handle* h, const float* state, int64_t state_len, float
         return fail(QP_EINVAL, "update q: tensorflow input size(" + std::to_string(h->hp.D) +
                                    ") and state(or nextState) size(" + std::to_string(state_len) + ", " +
                                    std::to_string(next_state_len) + ") do not match");
-    std::lock_guard<std::mutex> lock(h->qmu);
-    h->u_states.insert(h->u_states.end(), state, state + state_len);
-    h->u_next.insert(h->u_next.end(), next_state, next_state + next_state_len);
-    h->u_rewards.push_back(reward);
-    return QP_OK;
+    const size_t D = (size_t)h->hp.D;
+    for (;;) {
+        {
+            std::shared_lock<std::shared_mutex> lock(h->qrw);
+            qp_handle::FrontQueue& q = h->q_upd[h->cur_upd];
+            const int64_t slot = q.count.fetch_add(1);
+            if (slot < q.cap) {
+                std::memcpy(q.states + (size_t)slot * D, state, D * sizeof(float));
+                std::memcpy(q.next + (size_t)slot * D, next_state, D * sizeof(float));
+                q.scalars[slot] = reward;
+                return QP_OK;
+            }
+        }
+        std::unique_lock<std::shared_mutex> lock(h->qrw);
+        qp_handle::FrontQueue& q = h->q_upd[h->cur_upd];
+        QP_TRY(front_grow(h, q, true, std::min<int64_t>(q.count.load(), q.cap) + 1));
+    }
 }
 
 int qp_flush(qp_handle* h, int64_t* n_selects, int64_t* n_updates) {
     if (!h) return fail(QP_EINVAL, "null handle");
-    // take the queues under the lock, run the GPU work outside it so that actors keep enqueuing
-    std::vector<float> qs, qst, us, ur, un;
-    std::vector<int64_t> qi;
-    int64_t first_ticket = 0;
+    std::lock_guard<std::mutex> one_flush(h->flush_mu);
+    // hand the current generations to this flush and let the actors continue into the other pair
+    qp_handle::FrontQueue *qs, *qu;
+    int64_t ns, nu, first_ticket;
     {
-        std::lock_guard<std::mutex> lock(h->qmu);
-        qs.swap(h->q_states); qst.swap(h->q_steps); qi.swap(h->q_ids);
-        us.swap(h->u_states); ur.swap(h->u_rewards); un.swap(h->u_next);
-        first_ticket = h->next_ticket - (int64_t)qst.size();
+        std::unique_lock<std::shared_mutex> lock(h->qrw);
+        qs = &h->q_sel[h->cur_sel]; qu = &h->q_upd[h->cur_upd];
+        ns = std::min<int64_t>(qs->count.load(), qs->cap);
+        nu = std::min<int64_t>(qu->count.load(), qu->cap);
+        qs->count.store(ns); qu->count.store(nu);
+        first_ticket = h->sel_first_ticket;
+        h->sel_first_ticket += ns;
+        h->cur_sel ^= 1; h->cur_upd ^= 1;
     }
-    const int64_t ns = (int64_t)qst.size(), nu = (int64_t)ur.size();
+    int st = QP_OK;
     if (ns > 0) {   // every queued SelectionAction is answered with the weights as they are now ...
         std::vector<int32_t> res((size_t)ns, 0);
-        QP_TRY(qp_select_action(h, qs.data(), h->hp.D, qst.data(), qi.data(), res.data(), nullptr, ns));
-        std::lock_guard<std::mutex> lock(h->qmu);
-        h->q_results.swap(res);
-        h->ticket_base = first_ticket;
+        st = qp_select_action(h, qs->states, h->hp.D, qs->scalars, qs->ids, res.data(), nullptr, ns);
+        if (st == QP_OK) {
+            std::unique_lock<std::shared_mutex> lock(h->qrw);
+            h->q_results.swap(res);
+            h->ticket_base = first_ticket;
+        }
     }
-    if (nu > 0)     // ... then every queued UpdateQ becomes one gradient-SUM step
-        QP_TRY(qp_update_q(h, us.data(), h->hp.D, ur.data(), un.data(), h->hp.D, nu));
+    if (st == QP_OK && nu > 0)     // ... then every queued UpdateQ becomes one gradient-SUM step
+        st = qp_update_q(h, qu->states, h->hp.D, qu->scalars, qu->next, h->hp.D, nu);
+    qs->count.store(0); qu->count.store(0);      // (nobody writes to the generation being flushed)
+    if (st != QP_OK) return st;
     if (n_selects) *n_selects = ns;
     if (n_updates) *n_updates = nu;
     return QP_OK;
@@ -1324,8 +1406,8 @@ int qp_flush(qp_handle* h, int64_t* n_selects, int64_t* n_updates) {
 
 int qp_take_action(qp_handle* h, int64_t ticket, int32_t* action) {
     if (!h || !action) return fail(QP_EINVAL, "null argument");
-    std::lock_guard<std::mutex> lock(h->qmu);
-    if (ticket >= h->next_ticket - (int64_t)h->q_steps.size() && ticket < h->next_ticket)
+    std::shared_lock<std::shared_mutex> lock(h->qrw);
+    if (ticket >= h->sel_first_ticket)
         return fail(QP_ESTATE, "ticket " + std::to_string(ticket) + " is still queued: call qp_flush first");
     const int64_t idx = ticket - h->ticket_base;
     if (idx < 0 || idx >= (int64_t)h->q_results.size())
@@ -1336,8 +1418,9 @@ int qp_take_action(qp_handle* h, int64_t ticket, int32_t* action) {
 
 int64_t qp_pending(qp_handle* h) {
     if (!h) return 0;
-    std::lock_guard<std::mutex> lock(h->qmu);
-    return (int64_t)h->q_steps.size() + (int64_t)h->u_rewards.size();
+    std::shared_lock<std::shared_mutex> lock(h->qrw);
+    const qp_handle::FrontQueue &qa = h->q_sel[h->cur_sel], &qb = h->q_upd[h->cur_upd];
+    return std::min<int64_t>(qa.count.load(), qa.cap) + std::min<int64_t>(qb.count.load(), qb.cap);
 }
 
 // ---- checkpoint (fills the reference's saveSnapshot stub, QDecisionPolicyActor.scala:74, :91-93) -----
