@@ -58,6 +58,58 @@ def test_enqueue_flush_equals_direct_batch():
         assert front.pending == 0 and front.flush() == (0, 0)
 
 
+def test_front_end_queues_grow_and_alternate():
+    """The queues are two generations of pinned staging buffers that grow by doubling while other threads keep
+    reserving slots: 3 200 selects from eight threads (1 024 -> 4 096 slots, twice: once per generation), tickets
+    stay unique and consecutive across flushes, every action is the one a direct batch gives, and a ticket of an
+    older flush is refused."""
+    q = q_mod()
+    cfg = O.Config(seed=5)
+    n_threads, per = 8, 400
+    n = n_threads * per
+    rng = np.random.default_rng(1)
+    w = (O.gen_normal(6, 0, cfg.P) * 0.05).astype(np.float32)
+    with make_policy(cfg, params=w) as direct, make_policy(cfg, params=w) as batched:
+        front = q.BatchingPolicy(batched)
+        first_round_ticket = None
+        for rnd in range(2):
+            s = rng.uniform(50, 150, (n, cfg.D)).astype(np.float32)
+            steps = rng.integers(0, 1200, n).astype(np.float32)
+            a_ref = direct.select_action(s, steps, np.arange(n))
+            tickets = [None] * n
+
+            def child(t):
+                for j in range(t * per, (t + 1) * per):
+                    tickets[j] = front.enqueue_select(s[j], float(steps[j]), j)
+
+            th = [threading.Thread(target=child, args=(t,)) for t in range(n_threads)]
+            [x.start() for x in th]
+            [x.join() for x in th]
+            assert front.pending == n
+            assert sorted(tickets) == list(range(rnd * n, (rnd + 1) * n))
+            assert front.flush() == (n, 0)
+            got = np.array([int(front.action(tickets[j])) for j in range(n)])
+            np.testing.assert_array_equal(got, a_ref)
+            if rnd == 0:
+                first_round_ticket = tickets[0]
+        with pytest.raises(q.IllegalArgumentException, match="most recent flush"):
+            front.action(first_round_ticket)
+        # updates through the grown queues: one gradient-SUM step over all of them
+        s2 = s + rng.uniform(-1, 1, (n, cfg.D)).astype(np.float32)
+        r = rng.uniform(-5, 5, n).astype(np.float32)
+        direct.update_q(s, r, s2)
+
+        def child_u(t):
+            for j in range(t * per, (t + 1) * per):
+                front.enqueue_update(s[j], float(r[j]), s2[j])
+
+        th = [threading.Thread(target=child_u, args=(t,)) for t in range(n_threads)]
+        [x.start() for x in th]
+        [x.join() for x in th]
+        assert front.flush() == (0, n)
+        _tol.assert_grad_close(batched.last_grad(), direct.last_grad())
+
+
 def test_router_fanout_in_lockstep():
     """Tickers x episodes through the front-end, stepping in lock-step: equals the fused episode path."""
     q = q_mod()
