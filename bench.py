@@ -108,10 +108,8 @@ class ClockSampler:
         self.t1 = time.time()
 
     def stop(self):
-        import datetime
-        out = dict(sm_mhz=None, sm_max_mhz=None, reasons=[], samples=0)
         if self.proc is None:
-            return out
+            return dict(sm_mhz=None, sm_max_mhz=None, reasons=[], samples=0)
         for _ in range(40):                 # nvidia-smi's own start-up can outlast a short region: wait for one sample
             try:
                 if os.path.getsize(self.path) > 0:
@@ -124,21 +122,30 @@ class ClockSampler:
             self.proc.wait(timeout=5)
         except Exception:
             self.proc.kill()
-        rows = []
         try:
-            for line in open(self.path):
-                f = [x.strip() for x in line.split(",")]
-                if len(f) < 9:
-                    continue
-                try:
-                    ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
-                    rows.append((ts, float(f[2]), float(f[3]), f[5:9]))
-                except ValueError:
-                    continue
+            lines = open(self.path).read().splitlines()
             os.unlink(self.path)
         except Exception:
-            pass
-        inside = [r for r in rows if self.t0 is not None and self.t1 is not None and self.t0 <= r[0] <= self.t1 + 0.02]
+            lines = []
+        return self.summarise(lines, self.t0, self.t1, len(self.gpus))
+
+    @staticmethod
+    def summarise(lines, t0, t1, n_gpus):
+        """nvidia-smi CSV lines (the query in Q) -> the `clocks` object of the bench line; only samples whose
+        timestamp lies in [t0, t1] count, unless there are none."""
+        import datetime
+        out = dict(sm_mhz=None, sm_max_mhz=None, reasons=[], samples=0)
+        rows = []
+        for line in lines:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                ts = datetime.datetime.strptime(f[0], "%Y/%m/%d %H:%M:%S.%f").timestamp()
+                rows.append((ts, float(f[2]), float(f[3]), f[5:9]))
+            except ValueError:
+                continue
+        inside = [r for r in rows if t0 is not None and t1 is not None and t0 <= r[0] <= t1 + 0.02]
         window = "timed region"
         if not inside:                      # region shorter than the sampling period / nvidia-smi's start-up
             inside, window = rows, "nearest samples (warm-up before / idle after a timed region shorter than the sampler's start-up)"
@@ -150,7 +157,7 @@ class ClockSampler:
         if inside:
             sm = [r[1] for r in inside]
             out.update(sm_mhz=statistics.median(sm), sm_min_mhz=min(sm), sm_max_mhz=max(r[2] for r in inside),
-                       samples=len(inside), gpus=len(self.gpus), window=window)
+                       samples=len(inside), gpus=n_gpus, window=window)
         out["reasons"] = sorted(reasons)
         return out
 
