@@ -778,10 +778,8 @@ episode_tc_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                 }
                 // tell the consumers
                 __syncthreads();
-                if (tid == 0) {
-                    __threadfence();
-                    atomicAdd(x.published, 1ull);
-                }
+                if (tid == 0)     // release at GPU scope: cumulative over the CTA's stores the barrier above has ordered
+                    asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(x.published), "l"(1ull) : "memory");
             }
         } else {
             // shapes the bulk scheme does not cover: four lanes per float4 group, straight from global memory
