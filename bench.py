@@ -318,6 +318,36 @@ def run_ours(args):
     e2e_ms, e2e_wall, e2e_clocks, _ = timed(e2e_pass, args.steps, 1)
     e2e_value = args.steps * n_env_steps * n_total / (e2e_wall)
 
+    # ---- result check, outside the timed regions: the last e2e pass left a finished run on every rank.
+    # REFERENCE book-keeping from (1000, 0) never changes a portfolio's value, and every rank applied
+    # the same all-reduced gradient sums, so the replicas' weights must be bit-identical.
+    import hashlib
+    ports_now = pol.portfolios()
+    params_now, _ = pol.get_weights()
+    digest = hashlib.blake2b(params_now.tobytes(), digest_size=8).hexdigest()
+    digests = [digest]
+    problems = []
+    if dist is not None:
+        digests = [None] * world
+        dist.all_gather_object(digests, digest)
+    if not (ports_now == BUDGET0).all():
+        problems.append(f"rank {rank}: {(ports_now != BUDGET0).sum()} portfolios differ from {BUDGET0}")
+    if not np.isfinite(params_now).all():
+        problems.append(f"rank {rank}: non-finite weights")
+    if len(set(digests)) != 1:
+        problems.append(f"replicas' weights differ across ranks: {digests}")
+    if dist is not None:
+        allp = [None] * world
+        dist.all_gather_object(allp, problems)
+        problems = [x for pr in allp for x in pr]
+    result_check = "ok" if not problems else "FAILED: " + "; ".join(sorted(set(problems)))
+    data_plane = dict(fused_active=int(pol.get_option("fused_active")), ep_tc_active=int(pol.get_option("ep_tc_active")),
+                      p2p_active=int(pol.get_option("p2p_active")), fused_step_active=int(pol.get_option("fused_step_active")),
+                      tiles_per_sm=-(-((n_local + 31) // 32) // 148), params_digest=digest,
+                      gradient_exchange=("none (one GPU)" if world == 1 else
+                                         ("in-kernel all-to-all over NVLink peer memory (tagged 64-bit stores), no NCCL call in the step"
+                                          if pol.get_option("p2p_active") else "ncclAllReduce between kernels")))
+
     # ---- roofline of the dominant kernel, measured live with CUDA events on the launching stream
     peaks = measured_peaks()
     fp32_uniform_peak = pol.measure_fp32_peak()       # dependency-free FFMA with kernel-uniform multiplicands
@@ -497,14 +527,20 @@ def run_ours(args):
                       bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP),
         )
 
+    if data_plane["ep_tc_active"]:
+        dtype = "fp32 (contractions on tcgen05 as 2xTF32: tf32-exact prices x tf32 hi/lo weight pairs, fp32 accumulate in TMEM; element-wise fp32, book-keeping fp64)"
+    elif wide and pol.get_option("tc_active"):
+        dtype = "fp32 (GEMMs on tcgen05 as 3xTF32 hi/lo splits, fp32 accumulate in TMEM; element-wise fp32, book-keeping fp64)"
+    else:
+        dtype = "fp32 (FFMA contractions; book-keeping fp64)"
     line = dict(
         metric=METRIC, value=value, unit=UNIT, n_gpus=world, steps=args.steps, warmup=max(args.warmup, 3),
-        ms_per_step=ms / args.steps, higher_is_better=True, scaling=SCALING, vs_baseline=None, dtype="fp32",
+        ms_per_step=ms / args.steps, higher_is_better=True, scaling=SCALING, vs_baseline=None, dtype=dtype,
         data="synthetic", config=workload_config(args, n_total), clocks=clocks,
         e2e=dict(value=e2e_value, unit=UNIT, h2d_bytes_per_step=int(prices_np.nbytes + soe_np.nbytes),
                  d2h_bytes_per_step=int(n_local * 8), ms_per_step=e2e_wall / args.steps * 1e3, clocks=e2e_clocks,
                  api="qp_train (TrainerChildActor.train): pinned host prices in, portfolios out"),
-        gpu_launches=int(launches), roofline=roofline, wall_s=wall,
+        gpu_launches=int(launches), roofline=roofline, wall_s=wall, result_check=result_check, data_plane=data_plane,
     )
 
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -226,9 +226,15 @@ int qp_dist_nccl_version(int32_t* version);
  * episode kernel over NVLink peer memory instead of NCCL launches between kernels.  Each rank exports a
  * 64-byte CUDA IPC handle of its exchange buffer (qp_dist_p2p_export), the host gathers the world's
  * handles in rank order and gives them to every rank (qp_dist_p2p_import).  Per env-step every rank
- * then publishes its gradient, raises a flag in each peer's memory, and sums all ranks' gradients in
- * rank order before AdaGrad — bit-identical on every rank.  All ranks must step in lock-step with
- * the same n_steps.  If either call fails (no peer access) the NCCL path stays in use. */
+ * then sends its share of the gradient sum into every peer's buffer and adds all ranks' shares in rank
+ * order before AdaGrad — bit-identical on every rank.  Tensor-core kernel (the default): each value
+ * travels with its step tag as ONE 64-bit store, the receiver polls its local slots, no fence and no
+ * flag; FFMA kernel: whole-gradient buffers, a system fence and one flag per rank.  All ranks must step
+ * in lock-step with the same n_steps.  If either call fails (no peer access) the NCCL path stays in use.
+ * Call order with several GPUs: qp_dist_init, the p2p calls and every qp_set_option BEFORE qp_env_create —
+ * qp_env_create is collective (one small NCCL MIN all-reduce) and fixes the execution path from what ALL
+ * ranks can do (tf32-exact prices, tiles per SM, peer access), because the three multi-GPU step
+ * protocols do not interoperate. */
 #define QP_DIST_IPC_BYTES 64
 int qp_dist_p2p_export(qp_handle* h, void* out, size_t out_bytes);
 int qp_dist_p2p_import(qp_handle* h, const void* handles, int32_t world);
@@ -252,9 +258,11 @@ int qp_dist_p2p_import(qp_handle* h, const void* handles, int32_t world);
  * on the same GPU (different streams or threads) race: serialise them.  Contents left by one call
  * are never read by the next — every word consumed is rewritten first — so nothing needs clearing.
  * The first call on each device also does that device's one-time set-up (it resolves the array's
- * device address and raises the kernels' shared-memory limit); make that first call before any
- * stream capture begins.  `stream` is a cudaStream_t (NULL = default stream); the call returns
- * after the work on it has finished. */
+ * device address and raises the kernels' shared-memory limit).  `stream` is a cudaStream_t (NULL =
+ * default stream); the call synchronises that stream before it returns, so it cannot be part of a
+ * stream capture.  Alignment: d_params 16 bytes (the kernels fetch W1 in 16-byte granules), every
+ * other pointer 4 bytes; anything else is refused with QP_EINVAL.  The calling thread's current
+ * device is the same after the call as before it. */
 int qp_td_grad_noalloc(int32_t device, const qp_config* cfg, const float* d_params,
                        const float* d_states, const float* d_rewards, const float* d_next_states,
                        int64_t B, float* d_grad_out, void* stream);

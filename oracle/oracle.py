@@ -32,6 +32,10 @@ class _Trace(C.Structure):
                 ("action_sel", "action_eff", "explored", "k_next", "reward", "q_s", "q_n", "target")]
 
 
+class _Force(C.Structure):
+    _fields_ = [("action", C.c_void_p), ("k_next", C.c_void_p)]
+
+
 class _EnvState(C.Structure):
     _fields_ = [("budget", C.c_void_p), ("shares", C.c_void_p), ("share_value", C.c_void_p)]
 
@@ -215,8 +219,18 @@ class Oracle:
     def n_steps_total(self):
         return self.env["prices"].shape[1] - self.cfg.wn  # TrainerChildActor.scala:67
 
-    def env_step(self, n_steps=1, trace=False, mode=0, want_grad=False, threads=0):
+    def env_step(self, n_steps=1, trace=False, mode=0, want_grad=False, threads=0, force_action=None,
+                 force_knext=None):
+        """force_action / force_knext: int32 per episode, entries >= 0 replace the oracle's own choice of
+        the selected action / of argmax q(s') for that episode (teacher hook of the parity tests, used only
+        where the unforced run showed the differing choice to lie inside the stated tolerance)."""
         ev = self.env
+        fc = None
+        if force_action is not None or force_knext is not None:
+            assert n_steps == 1 and not threads
+            fa = None if force_action is None else np.ascontiguousarray(force_action, np.int32)
+            fk = None if force_knext is None else np.ascontiguousarray(force_knext, np.int32)
+            fc = _Force(_p(fa), _p(fk))
         n = ev["n"]
         traces = []
         g = np.empty(self.cfg.P, self.dtype) if want_grad else None
@@ -244,11 +258,12 @@ class Oracle:
                                          C.c_int64(ev["base"]), C.c_int32(i), C.c_double(ev["B0"]),
                                          C.c_int32(ev["N0"]), C.byref(st), C.c_int(threads), _p(partials))
             else:
-                self.lib.qpo_env_step(C.byref(cc), _p(self.params), _p(self.acc), _p(ev["prices"]),
-                                      C.c_int32(ev["prices"].shape[1]), _p(ev["soe"]), C.c_int64(n),
-                                      C.c_int64(ev["base"]), C.c_int32(i), C.c_double(ev["B0"]),
-                                      C.c_int32(ev["N0"]), C.byref(st),
-                                      C.byref(tr) if tr is not None else None, C.c_int(mode), _p(g))
+                self.lib.qpo_env_step_forced(C.byref(cc), _p(self.params), _p(self.acc), _p(ev["prices"]),
+                                             C.c_int32(ev["prices"].shape[1]), _p(ev["soe"]), C.c_int64(n),
+                                             C.c_int64(ev["base"]), C.c_int32(i), C.c_double(ev["B0"]),
+                                             C.c_int32(ev["N0"]), C.byref(st),
+                                             C.byref(tr) if tr is not None else None, C.c_int(mode), _p(g),
+                                             C.byref(fc) if fc is not None else None)
             ev["step"] = i + 1
             if rec is not None:
                 rec["budget"] = ev["budget"].copy()

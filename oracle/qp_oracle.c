@@ -199,7 +199,7 @@ typedef struct {
 } qpo_td_info;
 
 static void td_grad(const qpo_config* c, const real* params, const real* s, real reward,
-                    const real* s2, real* g, real* scratch, qpo_td_info* info) {
+                    const real* s2, real* g, real* scratch, qpo_td_info* info, int force_k) {
     const int D = c->wn + 2, H = c->hidden;
     const real* W1 = params;
     const real* W2 = params + (size_t)D * H;
@@ -210,7 +210,9 @@ static void td_grad(const qpo_config* c, const real* params, const real* s, real
     real q[QPO_ACTIONS], qn[QPO_ACTIONS];
     forward(c, W1, W2, s, z, h, q);
     forward(c, W1, W2, s2, z, h2, qn);
-    const int k = argmax3(qn);
+    /* force_k >= 0: a test imposes the index (used where the top-two gap of q(s') is inside the
+     * stated tolerance and the implementation under test legitimately chose the other one) */
+    const int k = force_k >= 0 ? force_k : argmax3(qn);
     const real target = reward + (real)c->gamma * qn[k];
     /* d/dq (y-q)^2 = -2 (y-q); ReluGrad passes where the output is strictly positive */
     const real dq = -((real)2 * (target - q[k]));
@@ -257,7 +259,7 @@ void qpo_td_grad_batch(const qpo_config* c, const real* params, const real* s, c
     memset(g, 0, sizeof(real) * (size_t)P);
     for (int64_t b = 0; b < B; ++b) {
         qpo_td_info info;
-        td_grad(c, params, s + b * D, (real)reward[b], s2 + b * D, g, scratch, &info);
+        td_grad(c, params, s + b * D, (real)reward[b], s2 + b * D, g, scratch, &info, -1);
         for (int a = 0; a < QPO_ACTIONS; ++a) {
             if (q_s) q_s[b * QPO_ACTIONS + a] = info.q_s[a];
             if (q_n) q_n[b * QPO_ACTIONS + a] = info.q_n[a];
@@ -294,6 +296,14 @@ typedef struct {
     real* target;
 } qpo_trace;
 
+/* Teacher hook of the parity tests (all optional): entries >= 0 replace the oracle's own choice for
+ * that env.  Only used after the unforced run has shown that the differing choice lies inside the
+ * stated tolerance, so that gradient, weights and carry can still be compared in every case. */
+typedef struct {
+    const int32_t* action;   /* replaces the index SelectionAction returns */
+    const int32_t* k_next;   /* replaces argmax q(s') in UpdateQ */
+} qpo_force;
+
 typedef struct {
     double* budget;       /* carry._1 */
     int32_t* shares;      /* carry._2 */
@@ -302,7 +312,7 @@ typedef struct {
 
 static void env_one(const qpo_config* c, const real* params, const float* p, int32_t i,
                     double B0, int32_t N0, int64_t e, uint64_t env_id, qpo_env_state* st,
-                    const qpo_trace* tr, real* g, real* scratch, real* s, real* s2) {
+                    const qpo_trace* tr, real* g, real* scratch, real* s, real* s2, const qpo_force* fc) {
     const int wn = c->wn, D = wn + 2, H = c->hidden;
     const double budget = st->budget[e];
     const int32_t shares = st->shares[e];
@@ -316,7 +326,8 @@ static void env_one(const qpo_config* c, const real* params, const float* p, int
     real q[QPO_ACTIONS];
     forward(c, params, params + (size_t)D * H, s, scratch, scratch + H, q);
     int explored = 0;
-    const int a = select_action(c, q, (float)i, env_id, (uint32_t)i, &explored);
+    int a = select_action(c, q, (float)i, env_id, (uint32_t)i, &explored);
+    if (fc && fc->action && fc->action[e] >= 0) a = fc->action[e];
     /* new share value — :94 */
     const double p_new = (double)p[i + wn];
     /* decision — :118-123 (Q1: REFERENCE mode decides from the constructor's position) */
@@ -336,7 +347,7 @@ static void env_one(const qpo_config* c, const real* params, const float* p, int
     s2[wn + 1] = (real)(float)ns;
     /* ask UpdateQ — :97 */
     qpo_td_info info;
-    td_grad(c, params, s, (real)r32, s2, g, scratch, &info);
+    td_grad(c, params, s, (real)r32, s2, g, scratch, &info, (fc && fc->k_next) ? fc->k_next[e] : -1);
     /* carry — :99-102 */
     st->budget[e] = nb;
     st->shares[e] = ns;
@@ -360,10 +371,10 @@ static void env_one(const qpo_config* c, const real* params, const float* p, int
  * mode 0 = batched SUM (the build's rule), mode 1 = sequential per-sample (the reference's
  * one-mailbox order: env 0 select+update, then env 1 with the updated weights, ...).
  * env_id_base offsets the RNG counter so that a rank's shard draws the global env's numbers. */
-void qpo_env_step(const qpo_config* c, real* params, real* acc, const float* prices, int32_t T,
-                  const int32_t* series_of_env, int64_t n_envs, int64_t env_id_base, int32_t i,
-                  double B0, int32_t N0, qpo_env_state* st, const qpo_trace* tr, int mode,
-                  real* g_out) {
+void qpo_env_step_forced(const qpo_config* c, real* params, real* acc, const float* prices, int32_t T,
+                         const int32_t* series_of_env, int64_t n_envs, int64_t env_id_base, int32_t i,
+                         double B0, int32_t N0, qpo_env_state* st, const qpo_trace* tr, int mode,
+                         real* g_out, const qpo_force* fc) {
     const int D = c->wn + 2, H = c->hidden;
     const int64_t P = (int64_t)D * H + (int64_t)H * QPO_ACTIONS;
     real* g = g_out ? g_out : (real*)malloc(sizeof(real) * (size_t)P);
@@ -373,7 +384,7 @@ void qpo_env_step(const qpo_config* c, real* params, real* acc, const float* pri
     memset(g, 0, sizeof(real) * (size_t)P);
     for (int64_t e = 0; e < n_envs; ++e) {
         const float* p = prices + (int64_t)series_of_env[e] * T;
-        env_one(c, params, p, i, B0, N0, e, (uint64_t)(env_id_base + e), st, tr, g, scratch, s, s2);
+        env_one(c, params, p, i, B0, N0, e, (uint64_t)(env_id_base + e), st, tr, g, scratch, s, s2, fc);
         if (mode == 1) {
             qpo_adagrad(c, params, acc, g, P);
             memset(g, 0, sizeof(real) * (size_t)P);
@@ -382,6 +393,13 @@ void qpo_env_step(const qpo_config* c, real* params, real* acc, const float* pri
     if (mode == 0) qpo_adagrad(c, params, acc, g, P);
     free(scratch);
     if (!g_out) free(g);
+}
+
+void qpo_env_step(const qpo_config* c, real* params, real* acc, const float* prices, int32_t T,
+                  const int32_t* series_of_env, int64_t n_envs, int64_t env_id_base, int32_t i,
+                  double B0, int32_t N0, qpo_env_state* st, const qpo_trace* tr, int mode,
+                  real* g_out) {
+    qpo_env_step_forced(c, params, acc, prices, T, series_of_env, n_envs, env_id_base, i, B0, N0, st, tr, mode, g_out, NULL);
 }
 
 /* Multi-threaded batched-SUM step used only as the timed CPU baseline ("all host cores").
@@ -407,7 +425,7 @@ static void* mt_worker(void* arg) {
     for (int64_t e = lo; e < hi; ++e) {
         const float* p = j->prices + (int64_t)j->series_of_env[e] * j->T;
         env_one(c, j->params, p, j->i, j->B0, j->N0, e, (uint64_t)(j->env_id_base + e), j->st, NULL,
-                g, scratch, s, s2);
+                g, scratch, s, s2, NULL);
     }
     free(scratch);
     return NULL;

@@ -71,7 +71,7 @@ int64_t round_up(int64_t v, int64_t m) { return (v + m - 1) / m * m; }
 typedef struct ncclComm* ncclComm_t;
 typedef struct { char internal[128]; } ncclUniqueId;
 typedef int ncclResult_t;
-constexpr int kNcclFloat32 = 7, kNcclSum = 0;   // ncclDataType_t / ncclRedOp_t values of nccl.h
+constexpr int kNcclFloat32 = 7, kNcclInt32 = 2, kNcclSum = 0, kNcclMin = 3;   // ncclDataType_t / ncclRedOp_t values of nccl.h
 
 struct NcclApi {
     void* lib = nullptr;
@@ -188,6 +188,11 @@ struct qp_handle {
     int64_t snapshot_every = 500;
     // persistent kernel with tensor-core contractions (qp_ep_tc.cuh)
     bool allow_ep_tc = true, ep_tc_ready = false;   // qp_set_option("ep_tc", 0) keeps the FFMA persistent kernel
+    bool et_flow_ok = false;            // the shape takes phase B's bulk-copy branch (the only one with the NVLink exchange)
+    // several GPUs: what ALL ranks can do (MIN over the ranks at qp_env_create); a rank never picks a path alone
+    bool agree_valid = false, agree_ep_tc = false, agree_fits = false, agree_fused = false, agree_p2p = false;
+    DevBuf<int32_t> flags4;             // small device scratch (tf32-exactness flag, rank agreement)
+    int32_t* host_flag = nullptr;       // pinned: the flag's copy back rides on a synchronisation that happens anyway
     DevBuf<float> et_w_hi, et_w_lo;
     CUtensorMap tm_et_hi, tm_et_lo, tm_et_part;
     const float* tm_et_part_ptr = nullptr; int64_t tm_et_part_tiles = 0;   // what tm_et_part was encoded for
@@ -639,19 +644,29 @@ int wide_prepare_tc(qp_handle* h) {
 size_t p2p_tc_offset(const qp_handle* h) { return (size_t)round_up(256 + (int64_t)2 * h->P * (int64_t)sizeof(float), 256); }
 size_t p2p_pad(const qp_handle* h) { return (size_t)round_up(h->P, 64); }
 
+bool ep_tc_usable(const qp_handle* h) {
+    const bool local = h->allow_ep_tc && h->ep_tc_ready && (h->world == 1 || h->et_flow_ok);
+    return h->world == 1 ? local : (local && h->agree_valid && h->agree_ep_tc);
+}
+
+// Which kernels serve qp_env_step.  With several GPUs every input of the decision is a fact ALL ranks share
+// (agreed at qp_env_create): the three multi-GPU step protocols do not interoperate.
 bool use_fused(const qp_handle* h) {
     const bool single = h->world == 1;
-    const bool peers = h->world > 1 && h->world <= 8 && h->p2p_ready && h->allow_p2p;
+    const bool peers = h->world > 1 && h->world <= 8 && h->p2p_ready && h->allow_p2p && h->agree_valid && h->agree_p2p;
     // one tile per SM for the FFMA kernel; the tensor-core kernel runs any number of tiles in waves
-    const bool fits = h->n_envs <= (int64_t)kTileEnvs * h->num_sms;
-    const bool tc = h->allow_ep_tc && h->ep_tc_ready;
-    return !h->wide && h->allow_fused && h->coop_launch && (single || peers) && h->geo.ep_ok && (fits || tc);
+    const bool fits_local = h->n_envs <= (int64_t)kTileEnvs * h->num_sms;
+    const bool fits = single ? fits_local : (fits_local && h->agree_fits);
+    const bool fused_ok = !h->wide && h->allow_fused && h->coop_launch && h->geo.ep_ok && (single || h->agree_fused);
+    return fused_ok && (single || peers) && (fits || ep_tc_usable(h));
 }
 
 // Everything the tensor-core persistent kernel needs for the current episodes; leaves ep_tc_ready
 // false (and the FFMA persistent kernel in charge) when a precondition does not hold.
-int ep_tc_prepare(qp_handle* h) {
+int ep_tc_prepare(qp_handle* h, bool* flag_pending) {
     h->ep_tc_ready = false;
+    h->et_flow_ok = false;
+    *flag_pending = false;
     const Hyper& hp = h->hp;
     if (!h->tile_ok || !h->geo.ep_ok || hp.H % 4 != 0 || hp.H > kEtThreads) return QP_OK;
     const int Kp = (int)round_up(hp.wn, 32), nkb = Kp / 32, Np = (int)round_up(hp.H, 16), halves = (hp.wn + 127) / 128;
@@ -667,25 +682,56 @@ int ep_tc_prepare(qp_handle* h) {
     if (Np > 256 || halves > 2 || halves * Np > 512 || (size_t)nkb * 8192 < 2 * (size_t)Np * kXStride * 4 || 
         smem > (size_t)h->max_smem)
         return QP_OK;
-    // the state matrix goes to the tensor core as its tf32 value alone: the prices must be tf32-exact
-    DevBuf<int32_t> flag;
-    QP_TRY(flag.ensure(1));
-    QP_CUDA(cudaMemsetAsync(flag.p, 0, sizeof(int), h->stream));
+    // the state matrix goes to the tensor core as its tf32 value alone: the prices must be tf32-exact.  The flag lives
+    // in a handle-owned buffer (no allocation here) and its read-back rides on the synchronisation qp_env_reset makes
+    // anyway: see ep_tc_finish.
+    QP_CUDA(cudaMemsetAsync(h->flags4.p, 0, 4 * sizeof(int32_t), h->stream));
     const int64_t n = h->n_series * h->series_len;
-    tc_inexact_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->prices.p, n, flag.p);
-    int inexact = 1;
-    QP_CUDA(cudaMemcpyAsync(&inexact, flag.p, sizeof(int), cudaMemcpyDeviceToHost, h->stream));
-    QP_CUDA(cudaStreamSynchronize(h->stream));
-    flag.release();
+    tc_inexact_kernel<<<(unsigned)((n + 255) / 256), 256, 0, h->stream>>>(h->prices.p, n, h->flags4.p);
     h->launches += 1;
-    if (inexact) return QP_OK;
+    *h->host_flag = 1;
+    QP_CUDA(cudaMemcpyAsync(h->host_flag, h->flags4.p, sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
+    *flag_pending = true;
+    {   // phase B's bulk-copy branch ("flow") is the one that carries the NVLink exchange: same arithmetic as the kernel
+        const int64_t P1 = h->P1;
+        const int n_w1 = std::max(1, h->num_sms - 2);
+        const int chunk = (int)(((P1 + n_w1 - 1) / n_w1 + 3) & ~(int64_t)3);
+        const int chunk2 = ((3 * hp.H + 1) / 2 + 3) & ~3;
+        const int pitch = std::max(chunk, chunk2);
+        const size_t off_xs = (size_t)nkb * 8192 + 4 * TB;
+        const int rows_cap = std::min(128, (int)(off_xs / ((size_t)pitch * 4)) & ~3);
+        h->et_flow_ok = h->num_sms >= 8 && pitch <= kEtThreads && rows_cap >= 4;
+    }
     QP_TRY(h->et_w_hi.ensure((size_t)hp.H * Kp)); QP_TRY(h->et_w_lo.ensure((size_t)hp.H * Kp));
     QP_CUDA(cudaMemsetAsync(h->et_w_hi.p, 0, (size_t)hp.H * Kp * sizeof(float), h->stream));
     QP_CUDA(cudaMemsetAsync(h->et_w_lo.p, 0, (size_t)hp.H * Kp * sizeof(float), h->stream));
     QP_TRY(make_tmap(&h->tm_et_hi, h->et_w_hi.p, Kp, hp.H, (uint64_t)Kp * sizeof(float), (uint32_t)Np));
     QP_TRY(make_tmap(&h->tm_et_lo, h->et_w_lo.p, Kp, hp.H, (uint64_t)Kp * sizeof(float), (uint32_t)Np));
     h->et_Kp = Kp; h->et_nkb = nkb; h->et_Np = Np; h->et_halves = halves; h->et_smem = smem;
-    h->ep_tc_ready = true;
+    h->ep_tc_ready = true;      // provisional: ep_tc_finish takes it back if a price is not tf32-exact
+    return QP_OK;
+}
+
+// Second half of the preparation, called once the stream has been synchronised (qp_env_reset does that for
+// everything qp_env_create enqueued): read the exactness flag, and (several GPUs) agree on the execution path
+// with the other ranks.
+int ep_tc_finish(qp_handle* h, bool flag_pending) {
+    if (flag_pending && *h->host_flag != 0) h->ep_tc_ready = false;
+    h->agree_valid = false;
+    if (h->world > 1 && h->comm) {
+        const int32_t mine[4] = {
+            (h->allow_ep_tc && h->ep_tc_ready && h->et_flow_ok) ? 1 : 0,
+            (h->n_envs <= (int64_t)kTileEnvs * h->num_sms) ? 1 : 0,
+            (!h->wide && h->allow_fused && h->coop_launch && h->geo.ep_ok) ? 1 : 0,
+            (h->p2p_ready && h->allow_p2p) ? 1 : 0};
+        int32_t all[4] = {0, 0, 0, 0};
+        QP_CUDA(cudaMemcpyAsync(h->flags4.p, mine, sizeof mine, cudaMemcpyHostToDevice, h->stream));
+        QP_NCCL(g_nccl.AllReduce(h->flags4.p, h->flags4.p, 4, kNcclInt32, kNcclMin, h->comm, h->stream));
+        QP_CUDA(cudaMemcpyAsync(all, h->flags4.p, sizeof all, cudaMemcpyDeviceToHost, h->stream));
+        QP_CUDA(cudaStreamSynchronize(h->stream));
+        h->agree_ep_tc = all[0] != 0; h->agree_fits = all[1] != 0; h->agree_fused = all[2] != 0; h->agree_p2p = all[3] != 0;
+        h->agree_valid = true;
+    }
     return QP_OK;
 }
 
@@ -726,7 +772,7 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
         QP_TRY(h->dbg.ensure((size_t)n_steps * qp::kDbgSlots));
         ea.dbg = h->dbg.p;
     }
-    if (h->allow_ep_tc && h->ep_tc_ready && apply_in_kernel) {
+    if (ep_tc_usable(h) && apply_in_kernel) {
         EpTcArgs x{};
         x.ea = ea;
         x.w1T_hi = h->et_w_hi.p; x.w1T_lo = h->et_w_lo.p;
@@ -873,8 +919,10 @@ int qp_create(const qp_config* cfg, qp_handle** out) {
     QP_BAIL_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     for (auto& e : h->ev) QP_BAIL_CUDA(cudaEventCreate(&e));
 #undef QP_BAIL_CUDA
-    if (h->params.ensure(h->P) || h->acc.ensure(h->P) || h->grad.ensure(h->P) || h->d_step.ensure(1))
+    if (h->params.ensure(h->P) || h->acc.ensure(h->P) || h->grad.ensure(h->P) || h->d_step.ensure(1) || h->flags4.ensure(4))
         return bail(QP_ECUDA);
+    if (cudaHostAlloc(reinterpret_cast<void**>(&h->host_flag), sizeof(int32_t), cudaHostAllocDefault) != cudaSuccess)
+        return bail(fail(QP_ECUDA, "cudaHostAlloc failed"));
 
     std::vector<float> w(h->P);
     gen_normal(cfg->seed, h->P, w.data());
@@ -917,7 +965,8 @@ int qp_destroy(qp_handle* h) {
     h->w1T_hi.release(); h->w1T_lo.release(); h->dzT_hi.release(); h->dzT_lo.release();
     h->prices.release(); h->series_of_env.release(); h->shares.release();
     h->budget.release(); h->share_value.release(); h->portfolio.release(); h->blocksum.release();
-    h->d_step.release(); h->dbg.release();
+    h->d_step.release(); h->dbg.release(); h->flags4.release();
+    if (h->host_flag) cudaFreeHost(h->host_flag);
     for (auto& e : h->ev) if (e) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
     delete h;
@@ -1019,10 +1068,14 @@ int qp_update_q(qp_handle* h, const float* states, int64_t state_len, const floa
     QP_CUDA(cudaStreamSynchronize(h->stream));
     // if (iteration % 500 == 0 && iteration != 0) saveSnapshot(...)  — QDecisionPolicyActor.scala:74;
     // the reference's saveSnapshot is an empty stub (:91-93), here it writes a checkpoint if a path is set
-    if (!h->snapshot_path.empty() && h->snapshot_every > 0 && h->iteration != 0 &&
-        h->iteration % h->snapshot_every == 0)
+    // The trigger is the reference's (the iteration number this message was handled with); the checkpoint header
+    // stores the number of updates the saved weights CONTAIN, so that a resumed policy neither repeats the
+    // snapshot nor lags by one.
+    const int64_t handled_with = h->iteration;
+    h->iteration = handled_with + 1;     // context.become(iterateUpdate(session, iteration + 1)) (:76)
+    if (!h->snapshot_path.empty() && h->snapshot_every > 0 && handled_with != 0 &&
+        handled_with % h->snapshot_every == 0)
         QP_TRY(qp_save_checkpoint(h, h->snapshot_path.c_str()));
-    h->iteration += 1;                   // context.become(iterateUpdate(session, iteration + 1)) (:76)
     return QP_OK;
 }
 
@@ -1051,7 +1104,8 @@ int qp_env_create(qp_handle* h, const float* prices, int64_t series_len, int64_t
     h->B0 = budget0; h->N0 = shares0;
     h->has_env = true;
     h->tc_ready = false;
-    QP_TRY(ep_tc_prepare(h));
+    bool flag_pending = false;
+    QP_TRY(ep_tc_prepare(h, &flag_pending));
     if (h->wide || (h->hp.H % 128 == 0 && h->hp.H / 32 <= kWideMaxColsPerLane)) {
         bool identity = n_series == n_envs;
         for (int64_t e = 0; identity && e < n_envs; ++e) identity = series_of_env[e] == e;
@@ -1059,7 +1113,8 @@ int qp_env_create(qp_handle* h, const float* prices, int64_t series_len, int64_t
         // needs episode e <-> series e and 16-byte row pitches
         if (identity && series_len % 4 == 0) QP_TRY(wide_prepare_tc(h));
     }
-    return qp_env_reset(h);
+    QP_TRY(qp_env_reset(h));                       // (synchronises the stream)
+    return ep_tc_finish(h, flag_pending);
 }
 
 int qp_env_reset(qp_handle* h) {
@@ -1675,7 +1730,7 @@ int qp_get_option(qp_handle* h, const char* key, int64_t* value) {
     if (std::strcmp(key, "fused") == 0) { *value = h->allow_fused ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "wide") == 0) { *value = h->wide ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "ep_tc_active") == 0) {
-        *value = (h->has_env && use_fused(h) && h->allow_ep_tc && h->ep_tc_ready) ? 1 : 0;
+        *value = (h->has_env && use_fused(h) && ep_tc_usable(h)) ? 1 : 0;
         return QP_OK;
     }
     if (std::strcmp(key, "p2p_active") == 0) { *value = (h->has_env && h->world > 1 && use_fused(h)) ? 1 : 0; return QP_OK; }
@@ -1872,6 +1927,19 @@ extern "C" int qp_td_grad_noalloc(int32_t device, const qp_config* cfg, const fl
     if (cfg->window < 1 || cfg->hidden < 4 || cfg->hidden % 4)
         return fail(QP_EINVAL, "window >= 1 and hidden a multiple of 4 (>= 4) required");
     if (B < 1) return fail(QP_EINVAL, "B < 1");
+    // The kernels fetch W1 with bulk copies (16-byte granules) and the rows with 4-byte loads: a pointer carved out
+    // of somebody else's pool at an odd offset would fault inside the kernel, so it is refused here instead.
+    if ((reinterpret_cast<uintptr_t>(d_params) & 15u) != 0)
+        return fail(QP_EINVAL, "qp_td_grad_noalloc: d_params must be 16-byte aligned");
+    if (((reinterpret_cast<uintptr_t>(d_states) | reinterpret_cast<uintptr_t>(d_rewards) |
+          reinterpret_cast<uintptr_t>(d_next_states) | reinterpret_cast<uintptr_t>(d_grad_out)) & 3u) != 0)
+        return fail(QP_EINVAL, "qp_td_grad_noalloc: device pointers must be 4-byte aligned");
+    // the caller's current device is put back on every way out
+    struct DeviceGuard {
+        int prev = -1;
+        ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    } guard;
+    if (cudaGetDevice(&guard.prev) != cudaSuccess) guard.prev = -1;
     QP_CUDA(cudaSetDevice(device));
     StaticDevice* dev = nullptr;
     QP_TRY(static_setup(device, &dev));

@@ -1,5 +1,6 @@
-"""Two-GPU test of the sharded path through the C ABI: qp_dist_init + the per-step NCCL gradient
-all-reduce.  Needs >= 2 GPUs (skipped on the 1-GPU box; run with `gpurun --gpus 2`)."""
+"""Multi-GPU tests (2, 4 and 8 ranks) of the sharded path through the C ABI: qp_dist_init + the per-step gradient
+all-reduce (in-kernel over NVLink peer memory, or NCCL between kernels).  A case is skipped on a box with fewer GPUs
+than it needs; run with `gpurun --gpus 2|4|8` (logs of those runs: profiles/)."""
 import os
 import socket
 
@@ -55,16 +56,21 @@ def _worker(rank, world, port, out_dir, p2p, ep_tc, n_local):
     dist.destroy_process_group()
 
 
-@pytest.mark.skipif(_n_gpus() < 2, reason="needs two GPUs")
-@pytest.mark.parametrize("p2p,ep_tc,n_local", [(1, 1, N_LOCAL), (1, 0, N_LOCAL), (0, 0, N_LOCAL), (1, 1, 5000)])
-def test_two_gpus_match_one_gpu(tmp_path, p2p, ep_tc, n_local):
-    """p2p = 1: gradient all-reduce inside the persistent kernel over NVLink peer memory (ep_tc = 1: the
+CASES = [(2, 1, 1, N_LOCAL), (2, 1, 0, N_LOCAL), (2, 0, 0, N_LOCAL), (2, 1, 1, 5000),
+         (4, 1, 1, N_LOCAL), (4, 0, 0, N_LOCAL), (8, 1, 1, N_LOCAL), (8, 1, 0, N_LOCAL), (8, 1, 1, 5000)]
+
+
+@pytest.mark.parametrize("world,p2p,ep_tc,n_local", CASES)
+def test_n_gpus_match_one_gpu(tmp_path, world, p2p, ep_tc, n_local):
+    """world ranks, one per GPU (skipped on boxes with fewer), against one GPU holding every episode.
+    p2p = 1: gradient all-reduce inside the persistent kernel over NVLink peer memory (ep_tc = 1: the
     tensor-core kernel, share-by-share exchange; ep_tc = 0: the FFMA kernel, whole-gradient exchange);
     p2p = 0: one fused step kernel per env-step + NCCL all-reduce between kernels.
     n_local = 5000: more than one tile per SM, the tensor-core kernel runs in waves on both sides."""
+    if _n_gpus() < world:
+        pytest.skip(f"needs {world} GPUs")
     import torch.multiprocessing as mp
     import scala_akka_tensorflow_sharetrade_helper_b200 as q
-    world = 2
     with socket.socket() as s:
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
@@ -79,9 +85,10 @@ def test_two_gpus_match_one_gpu(tmp_path, p2p, ep_tc, n_local):
     assert all(int(p["p2p_active"]) == p2p for p in parts), "peer-memory path not taken as requested"
     assert all(int(p["ep_tc_active"]) == ep_tc for p in parts), "tensor-core kernel not (de)selected as requested"
     # replicas bit-identical: same all-reduced sum, same AdaGrad arithmetic
-    np.testing.assert_array_equal(parts[0]["params"], parts[1]["params"])
-    np.testing.assert_array_equal(parts[0]["acc"], parts[1]["acc"])
-    np.testing.assert_array_equal(parts[0]["grad"], parts[1]["grad"])
+    for r in range(1, world):
+        np.testing.assert_array_equal(parts[0]["params"], parts[r]["params"], err_msg=f"rank {r} params")
+        np.testing.assert_array_equal(parts[0]["acc"], parts[r]["acc"], err_msg=f"rank {r} acc")
+        np.testing.assert_array_equal(parts[0]["grad"], parts[r]["grad"], err_msg=f"rank {r} grad")
     # against one GPU holding every episode
     cfg = O.Config(bookkeeping=O.RLPY)
     n = n_local * world
@@ -101,9 +108,9 @@ def test_two_gpus_match_one_gpu(tmp_path, p2p, ep_tc, n_local):
     for k in ("shares", "budget", "action_sel"):
         np.testing.assert_array_equal(np.concatenate([p[k] for p in parts], axis=1), tr[k], err_msg=k)
     np.testing.assert_array_equal(np.concatenate([p["shares2"] for p in parts], axis=1), tr2["shares"])
-    _tol.assert_grad_close(parts[0]["grad_first"], g1_first, "2-GPU vs 1-GPU gradient of the first step", n_terms=n)
+    _tol.assert_grad_close(parts[0]["grad_first"], g1_first, f"{world}-GPU vs 1-GPU gradient of the first step", n_terms=n)
     # ten updates later the two runs stand at slightly different weights (different summation orders, and the
     # tensor-core kernel on one side only): the last gradients agree to the drift of the weights, not to rounding
     d = np.linalg.norm(parts[0]["grad"] - g1) / np.linalg.norm(g1)
-    assert d <= 2e-4, f"2-GPU vs 1-GPU gradient of the last step: relative Frobenius error {d:.3g}"
+    assert d <= 2e-4, f"{world}-GPU vs 1-GPU gradient of the last step: relative Frobenius error {d:.3g}"
     assert np.abs(parts[0]["params"] - p1).max() <= (N_STEPS + 5) * _tol.W_ATOL

@@ -192,4 +192,8 @@ def test_snapshot_every_n_updates(tmp_path):
         with make_policy(cfg) as other:
             other.load_checkpoint(path)
             np.testing.assert_array_equal(other.get_weights()[0], w_now)
-            assert other.iteration == 4
+            assert other.iteration == 5 == pol.iteration     # the snapshot's weights contain five updates
+            path.unlink()
+            other.set_snapshot(path, every=4)
+            other.update_q(s, 1.0, s)                        # handled with iteration 5: no repeat of the snapshot
+            assert not path.exists() and other.iteration == 6

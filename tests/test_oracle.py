@@ -239,3 +239,38 @@ def test_fp32_vs_fp64_twin():
         _tol.assert_grad_close(t32["grad"], t64["grad"])
         assert np.abs(o32.params - o64.params).max() <= _tol.W_ATOL
     assert worst < 0.5, f"fp32 oracle uses {worst:.2f} of the tolerance; it should sit well inside"
+
+
+def test_teacher_hook_imposes_choices_and_nothing_else():
+    """oracle.env_step(force_action=, force_knext=): entries < 0 leave the oracle's own choice; imposing the
+    oracle's own choices reproduces the unforced run bit for bit; imposing another action changes exactly that
+    episode's decision (TrainerChildActor.scala:118-123) and the TD index enters the gradient column."""
+    cfg = O.Config(wn=8, hidden=16, bookkeeping=O.RLPY, seed=3)
+    prices = O.gen_prices(cfg.seed, 0, 6, 40)
+    soe = np.arange(6, dtype=np.int32)
+    w = (np.abs(O.gen_normal(1, 0, cfg.P)) * 0.05).astype(np.float32)      # all-positive: every ReLU alive
+
+    def run(fa=None, fk=None):
+        o = O.Oracle(cfg, params=w)
+        o.env_create(prices, soe, 500.0, 1)
+        o.env["step"] = 5
+        return o.env_step(1, trace=True, want_grad=True, force_action=fa, force_knext=fk)[0], o
+
+    ref, o0 = run()
+    same, o1 = run(ref["action_sel"], ref["k_next"])
+    for k in ref:
+        np.testing.assert_array_equal(ref[k], same[k], err_msg=k)
+    np.testing.assert_array_equal(o0.params, o1.params)
+    none, _ = run(np.full(6, -1, np.int32), np.full(6, -1, np.int32))
+    np.testing.assert_array_equal(ref["grad"], none["grad"])
+    fa = np.full(6, -1, np.int32)
+    fa[2] = (ref["action_sel"][2] + 1) % 3
+    alt, _ = run(fa)
+    assert alt["action_sel"][2] == fa[2]
+    others = np.arange(6) != 2
+    np.testing.assert_array_equal(alt["action_sel"][others], ref["action_sel"][others])
+    np.testing.assert_array_equal(alt["budget"][others], ref["budget"][others])
+    fk = np.full(6, -1, np.int32)
+    fk[4] = (ref["k_next"][4] + 1) % 3
+    altk, _ = run(None, fk)
+    assert altk["k_next"][4] == fk[4] and not np.array_equal(altk["grad"], ref["grad"])

@@ -85,3 +85,23 @@ def test_noalloc_rejects_sizes_beyond_the_built_in_scratch():
     assert st == 0, _capi.last_error()
     st = lib.qp_td_grad_noalloc(0, C.byref(c), g.data_ptr(), z.data_ptr(), z.data_ptr(), z.data_ptr(), 1793, g.data_ptr(), None)
     assert st == _capi.QP_EINVAL
+
+
+def test_noalloc_refuses_a_misaligned_weight_pointer():
+    """A caller that carves its buffers out of another runtime's pool may hand over a pointer at an odd offset; the
+    kernels fetch W1 in 16-byte granules, so such a pointer is refused up front instead of faulting on the GPU."""
+    import torch
+    from scala_akka_tensorflow_sharetrade_helper_b200 import _capi
+    lib = _capi.lib()
+    cfg = O.Config()
+    dev = torch.device("cuda", 0)
+    pool = torch.zeros(cfg.P + 8, dtype=torch.float32, device=dev)
+    z = torch.zeros(4 * cfg.D, dtype=torch.float32, device=dev)
+    g = torch.zeros(cfg.P, dtype=torch.float32, device=dev)
+    c = _capi.QpConfig()
+    lib.qp_config_default(C.byref(c))
+    st = lib.qp_td_grad_noalloc(0, C.byref(c), pool.data_ptr() + 4, z.data_ptr(), z.data_ptr(), z.data_ptr(), 4, g.data_ptr(), None)
+    assert st == _capi.QP_EINVAL and "16-byte" in _capi.last_error()
+    st = lib.qp_td_grad_noalloc(0, C.byref(c), pool.data_ptr() + 16, z.data_ptr(), z.data_ptr(), z.data_ptr(), 4, g.data_ptr(), None)
+    assert st == 0, _capi.last_error()
+    torch.cuda.synchronize()
