@@ -6,6 +6,7 @@
 #include "qp_wide.cuh"
 #include "qp_tc.cuh"
 #include "qp_ep_tc.cuh"
+#include "qp_probe.cuh"
 #include "../../include/qpolicy.h"
 
 #include <dlfcn.h>
@@ -1690,6 +1691,42 @@ int qp_debug_tc_gemm(int32_t device, int64_t M, int64_t N, int64_t K, const floa
         return QP_OK;
     };
     st = run();
+    rel();
+    return st;
+}
+
+// Test hook: single tcgen05.mma instructions on operand images a test lays out byte by byte (qp_probe.cuh).
+int qp_debug_umma(int32_t device, const void* a_img, int64_t a_bytes, const void* b_img, int64_t b_bytes,
+                  uint64_t desc_a, uint64_t desc_b, uint32_t idesc, int32_t n_mma, uint32_t a_step, uint32_t b_step,
+                  uint32_t d_col, uint32_t d_lane, int32_t n_cols, float fill, float* out) {
+    if (!a_img || !b_img || !out) return fail(QP_EINVAL, "null argument");
+    if (a_bytes < 16 || b_bytes < 16 || a_bytes % 16 || b_bytes % 16 || n_cols < 16 || n_cols > 512 || n_cols % 16 || n_mma < 1 ||
+        d_col + (uint32_t)0 > 512)
+        return fail(QP_EINVAL, "image sizes must be multiples of 16 bytes, n_cols a multiple of 16 in [16, 512]");
+    const size_t smem = (((size_t)a_bytes + 1023) & ~(size_t)1023) + (size_t)b_bytes;
+    QP_CUDA(cudaSetDevice(device));
+    int max_smem = 0;
+    QP_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
+    if (smem + 1024 > (size_t)max_smem) return fail(QP_EINVAL, "operand images do not fit in shared memory");
+    QP_CUDA(cudaFuncSetAttribute(umma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+    DevBuf<uint8_t> da, db;
+    DevBuf<float> dout;
+    QP_TRY(da.ensure(a_bytes)); QP_TRY(db.ensure(b_bytes)); QP_TRY(dout.ensure((size_t)128 * n_cols));
+    auto rel = [&]() { da.release(); db.release(); dout.release(); };
+    auto run = [&]() -> int {
+        QP_CUDA(cudaMemcpy(da.p, a_img, a_bytes, cudaMemcpyHostToDevice));
+        QP_CUDA(cudaMemcpy(db.p, b_img, b_bytes, cudaMemcpyHostToDevice));
+        UmmaProbeArgs g{};
+        g.a_img = da.p; g.a_bytes = (uint32_t)a_bytes; g.b_img = db.p; g.b_bytes = (uint32_t)b_bytes;
+        g.desc_a = desc_a; g.desc_b = desc_b; g.idesc = idesc; g.n_mma = n_mma; g.a_step = a_step; g.b_step = b_step;
+        g.d_col = d_col; g.d_lane = d_lane; g.n_cols = n_cols; g.fill = fill; g.out = dout.p;
+        umma_probe_kernel<<<1, 128, smem>>>(g);
+        QP_CUDA(cudaGetLastError());
+        QP_CUDA(cudaDeviceSynchronize());
+        QP_CUDA(cudaMemcpy(out, dout.p, (size_t)128 * n_cols * sizeof(float), cudaMemcpyDeviceToHost));
+        return QP_OK;
+    };
+    const int st = run();
     rel();
     return st;
 }
