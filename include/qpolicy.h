@@ -144,11 +144,13 @@ int qp_debug_tc_gemm(int32_t device, int64_t M, int64_t N, int64_t K, const floa
  * a_img / b_img are copied to shared memory (A at offset 0, B at the next 1024-byte boundary), desc_a / desc_b
  * are the 64-bit shared-memory matrix descriptors with their start-address field relative to the image, n_mma
  * instructions are issued (descriptor start addresses advanced by a_step / b_step 16-byte units each), and all
- * 128 lanes x n_cols columns of tensor memory (preset to `fill`) come back in out.  Pins the operand layouts the
+ * 128 lanes x n_cols columns of tensor memory (preset to `fill`) come back in out.  a_tmem_k != 0: the A operand comes
+ * from tensor memory instead (a_img = [128 rows][a_tmem_k] fp32, written to columns a_col.. of lane = row; a_step then
+ * counts columns).  Pins the operand layouts the
  * persistent kernels rely on (tests/test_gpu_umma_layouts.py).  No counterpart in the reference. */
 int qp_debug_umma(int32_t device, const void* a_img, int64_t a_bytes, const void* b_img, int64_t b_bytes,
                   uint64_t desc_a, uint64_t desc_b, uint32_t idesc, int32_t n_mma, uint32_t a_step, uint32_t b_step,
-                  uint32_t d_col, uint32_t d_lane, int32_t n_cols, float fill, float* out);
+                  uint32_t d_col, uint32_t d_lane, int32_t n_cols, float fill, float* out, int32_t a_tmem_k, uint32_t a_col);
 /* Tuning aid: with option "phase_clocks" = 1 the persistent kernel's CTA 0 stamps clock64() at up
  * to 16 phase boundaries of every env-step of a launch (unused slots stay 0); this copies the
  * [n_steps x 16] stamps of the last launch to out. */

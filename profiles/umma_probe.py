@@ -44,7 +44,7 @@ def a_mn_noswizzle(A, rows, quad_pitch, k0=0):
 def run(a_img, b_img, da, db, ide, n_mma, a_step, b_step, n_cols, d_col=0, d_lane=0, fill=-5.0):
     out = np.empty((128, n_cols), np.float32)
     st = lib.qp_debug_umma(0, a_img, len(a_img), b_img, len(b_img), C.c_uint64(da), C.c_uint64(db), ide, n_mma, a_step, b_step,
-                           d_col, d_lane, n_cols, C.c_float(fill), out.ctypes.data_as(C.c_void_p))
+                           d_col, d_lane, n_cols, C.c_float(fill), out.ctypes.data_as(C.c_void_p), 0, 0)
     if st != 0:
         raise RuntimeError(_capi.last_error())
     return out

@@ -51,7 +51,7 @@ SIGNATURES = {
     "qp_get_option": (C.c_int, [_H, C.c_char_p, C.POINTER(C.c_int64)]),
     "qp_debug_tc_gemm": (C.c_int, [C.c_int32, C.c_int64, C.c_int64, C.c_int64, _P, _P, _P, C.c_int32, C.c_int32, _P]),
     "qp_debug_umma": (C.c_int, [C.c_int32, _P, C.c_int64, _P, C.c_int64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_int32, C.c_uint32,
-                                C.c_uint32, C.c_uint32, C.c_uint32, C.c_int32, C.c_float, _P]),
+                                C.c_uint32, C.c_uint32, C.c_uint32, C.c_int32, C.c_float, _P, C.c_int32, C.c_uint32]),
     "qp_debug_phase_clocks": (C.c_int, [_H, C.c_int32, _P]),
     "qp_env_step_trace": (C.c_int, [_H, C.c_int32, C.POINTER(QpTrace)]),
     "qp_env_get_portfolio": (C.c_int, [_H, _P]),

@@ -6,6 +6,7 @@
 #include "qp_wide.cuh"
 #include "qp_tc.cuh"
 #include "qp_ep_tc.cuh"
+#include "qp_ep_c2.cuh"
 #include "qp_probe.cuh"
 #include "../../include/qpolicy.h"
 
@@ -190,6 +191,12 @@ struct qp_handle {
     // persistent kernel with tensor-core contractions (qp_ep_tc.cuh)
     bool allow_ep_tc = true, ep_tc_ready = false;   // qp_set_option("ep_tc", 0) keeps the FFMA persistent kernel
     bool et_flow_ok = false;            // the shape takes phase B's bulk-copy branch (the only one with the NVLink exchange)
+    // the same kernel on CTA pairs that split the hidden dimension (qp_ep_c2.cuh): the default where it applies
+    bool allow_ep_c2 = true, ep_c2_ready = false;   // qp_set_option("ep_c2", 0) keeps episode_tc_kernel
+    CUtensorMap tm_c2_hi, tm_c2_lo, tm_c2_part;
+    const float* tm_c2_part_ptr = nullptr; int64_t tm_c2_part_pairs = 0;
+    int c2_Hh = 0, c2_Nh = 0, c2_grid = 0, c2_dbg = 0;
+    size_t c2_smem_bytes = 0;
     // several GPUs: what ALL ranks can do (MIN over the ranks at qp_env_create); a rank never picks a path alone
     bool agree_valid = false, agree_ep_tc = false, agree_fits = false, agree_fused = false, agree_p2p = false;
     DevBuf<int32_t> flags4;             // small device scratch (tf32-exactness flag, rank agreement)
@@ -218,6 +225,7 @@ struct qp_handle {
     bool allow_fused = true;            // qp_set_option("fused", 0) forces the three-kernel path
     DevBuf<long long> dbg;              // phase stamps of the persistent kernel (qp_debug_phase_clocks)
     bool want_dbg = false;
+    bool want_fine = false;             // "phase_clocks" = 3: stamps inside the pair kernel's forward
     bool want_cta_ns = false;           // "phase_clocks" = 2: globaltimer stamps of every CTA instead (tensor-core kernel)
     bool coop_launch = false;
 };
@@ -447,6 +455,21 @@ int make_tmap3_store(CUtensorMap* m, const float* base, uint64_t d0, uint64_t d1
     return QP_OK;
 }
 
+// 4-D fp32 tensor [d3][d2][d1][d0] for TMA stores of [32 (d2) x 32 (d0)] boxes (128-byte rows, 128-byte swizzle)
+int make_tmap4_store(CUtensorMap* m, const float* base, const uint64_t dims_in[4], const uint64_t pitch_bytes[3]) {
+    EncodeTiledFn enc = nullptr;
+    QP_TRY(get_encode_tiled(&enc));
+    const cuuint64_t dims[4] = {dims_in[0], dims_in[1], dims_in[2], dims_in[3]};
+    const cuuint64_t strides[3] = {pitch_bytes[0], pitch_bytes[1], pitch_bytes[2]};
+    const cuuint32_t box[4] = {32, 1, 32, 1};
+    const cuuint32_t estr[4] = {1, 1, 1, 1};
+    const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)base, dims, strides, box, estr,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(QP_ECUDA, "cuTensorMapEncodeTiled (4-D) failed with code " + std::to_string((int)r));
+    return QP_OK;
+}
+
 int launch_tc_gemm(cudaStream_t st, const CUtensorMap& a_hi, const CUtensorMap& a_lo, const CUtensorMap& b_hi,
                    const CUtensorMap& b_lo, const TcGemmArgs& g, int tiles_m, int tiles_n, int splits) {
     static bool attr_set[64] = {false};
@@ -650,6 +673,11 @@ bool ep_tc_usable(const qp_handle* h) {
     return h->world == 1 ? local : (local && h->agree_valid && h->agree_ep_tc);
 }
 
+// the pair kernel: one 64-episode tile per CTA pair (no waves), everything episode_tc_kernel needs plus its own shape limits
+bool ep_c2_usable(const qp_handle* h) {
+    return ep_tc_usable(h) && h->allow_ep_c2 && h->ep_c2_ready && h->n_envs <= (int64_t)kC2Envs * (h->c2_grid / 2);
+}
+
 // Which kernels serve qp_env_step.  With several GPUs every input of the decision is a fact ALL ranks share
 // (agreed at qp_env_create): the three multi-GPU step protocols do not interoperate.
 bool use_fused(const qp_handle* h) {
@@ -660,6 +688,42 @@ bool use_fused(const qp_handle* h) {
     const bool fits = single ? fits_local : (fits_local && h->agree_fits);
     const bool fused_ok = !h->wide && h->allow_fused && h->coop_launch && h->geo.ep_ok && (single || h->agree_fused);
     return fused_ok && (single || peers) && (fits || ep_tc_usable(h));
+}
+
+// The pair kernel (qp_ep_c2.cuh) on top of what ep_tc_prepare has set up; leaves ep_c2_ready false when the shape or
+// the device does not take it.
+int ep_c2_prepare(qp_handle* h) {
+    h->ep_c2_ready = false;
+    const Hyper& hp = h->hp;
+    if (hp.H % 8 != 0 || !h->coop_launch) return QP_OK;
+    const int Hh = hp.H / 2, Nh = (int)round_up(Hh, 8), grid = h->num_sms & ~1;
+    const C2Smem sm = c2_smem(Hh, Nh);
+    // the window buffer holds kC2Slide rows of slack behind window element wn + 1; the copy-back moves (wn + 1) * 16
+    // float4 with 12 per thread; the epilogue stages 8 KB per warp over regA + regW; Nh <= 128 TMEM columns per accumulator
+    if (hp.wn + 2 + kC2Slide > kC2Rows || (hp.wn + 1) * 16 > 12 * kC2Threads || Nh > 128 || 2 * Hh > kC2Threads ||
+        sm.regA_bytes + sm.regW_bytes < (size_t)kC2Warps * 8192 || sm.total + 1024 > (size_t)h->max_smem || grid < 8)
+        return QP_OK;
+    {   // phase B's bulk-copy branch must apply (the kernel has no other)
+        const int n_w1 = std::max(1, grid - 2);
+        const int chunk = (int)(((h->P1 + n_w1 - 1) / n_w1 + 3) & ~(int64_t)3);
+        const int chunk2 = ((3 * hp.H + 1) / 2 + 3) & ~3;
+        const int pitch = std::max(chunk, chunk2);
+        const int rows_cap = std::min(128, (int)((sm.regA_bytes + sm.regW_bytes) / ((size_t)pitch * 4)) & ~3);
+        if (pitch > kC2Threads || rows_cap < 4) return QP_OK;
+    }
+    QP_CUDA(cudaFuncSetAttribute(episode_c2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sm.total + 1024)));
+    {   // all pairs must be co-resident (cooperative launch of clusters of two)
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kC2Threads); cfg.dynamicSmemBytes = sm.total + 1024; cfg.stream = h->stream;
+        int n_clusters = 0;
+        if (cudaOccupancyMaxActiveClusters(&n_clusters, episode_c2_kernel, &cfg) != cudaSuccess) { cudaGetLastError(); return QP_OK; }
+        if (n_clusters * 2 < grid) return QP_OK;
+    }
+    QP_TRY(make_tmap(&h->tm_c2_hi, h->et_w_hi.p, h->et_Kp, hp.H, (uint64_t)h->et_Kp * sizeof(float), (uint32_t)Nh));
+    QP_TRY(make_tmap(&h->tm_c2_lo, h->et_w_lo.p, h->et_Kp, hp.H, (uint64_t)h->et_Kp * sizeof(float), (uint32_t)Nh));
+    h->c2_Hh = Hh; h->c2_Nh = Nh; h->c2_grid = grid; h->c2_smem_bytes = sm.total + 1024;
+    h->ep_c2_ready = true;
+    return QP_OK;
 }
 
 // Everything the tensor-core persistent kernel needs for the current episodes; leaves ep_tc_ready
@@ -710,6 +774,7 @@ int ep_tc_prepare(qp_handle* h, bool* flag_pending) {
     QP_TRY(make_tmap(&h->tm_et_lo, h->et_w_lo.p, Kp, hp.H, (uint64_t)Kp * sizeof(float), (uint32_t)Np));
     h->et_Kp = Kp; h->et_nkb = nkb; h->et_Np = Np; h->et_halves = halves; h->et_smem = smem;
     h->ep_tc_ready = true;      // provisional: ep_tc_finish takes it back if a price is not tf32-exact
+    QP_TRY(ep_c2_prepare(h));
     return QP_OK;
 }
 
@@ -772,6 +837,39 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
     if (h->want_dbg) {
         QP_TRY(h->dbg.ensure((size_t)n_steps * qp::kDbgSlots));
         ea.dbg = h->dbg.p;
+    }
+    if (ep_c2_usable(h) && apply_in_kernel) {
+        // CTA pairs that split the hidden dimension: one 64-episode tile per pair
+        const int64_t n_pairs = (h->n_envs + kC2Envs - 1) / kC2Envs;
+        EpC2Args x{};
+        x.ea = ea;
+        x.w1T_hi = h->et_w_hi.p; x.w1T_lo = h->et_w_lo.p;
+        x.Kp = h->et_Kp; x.nkb = h->et_nkb; x.Hh = h->c2_Hh; x.Nh = h->c2_Nh; x.dbg_mode = h->c2_dbg;
+        QP_TRY(h->et_published.ensure(1));
+        x.published = h->et_published.p;
+        x.p_pad = (int64_t)p2p_pad(h);
+        for (int r = 0; r < ea.world && ea.world > 1; ++r)
+            x.pdata[r] = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(h->p2p_peer_block[r]) + p2p_tc_offset(h));
+        if (h->want_fine) {          // fine stamps share the dbg buffer: [n_steps][64]
+            QP_TRY(h->dbg.ensure((size_t)n_steps * 64));
+            QP_CUDA(cudaMemsetAsync(h->dbg.p, 0, (size_t)n_steps * 64 * sizeof(long long), h->stream));
+            x.ea.dbg = nullptr;
+            x.fine = h->dbg.p;
+        }
+        if (h->tm_c2_part_ptr != h->part1.p || h->tm_c2_part_pairs != n_pairs) {
+            const uint64_t dims[4] = {(uint64_t)h->c2_Hh, 2, (uint64_t)h->hp.wn, (uint64_t)n_pairs};
+            const uint64_t pitch[3] = {(uint64_t)h->c2_Hh * sizeof(float), (uint64_t)h->hp.H * sizeof(float), (uint64_t)h->P1 * sizeof(float)};
+            QP_TRY(make_tmap4_store(&h->tm_c2_part, h->part1.p, dims, pitch));
+            h->tm_c2_part_ptr = h->part1.p; h->tm_c2_part_pairs = n_pairs;
+        }
+        cudaLaunchConfig_t cfg{};
+        cfg.gridDim = dim3(h->c2_grid); cfg.blockDim = dim3(kC2Threads); cfg.dynamicSmemBytes = h->c2_smem_bytes; cfg.stream = h->stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1;      // (the cluster shape is the kernel's own attribute)
+        cfg.attrs = at; cfg.numAttrs = 1;
+        QP_CUDA(cudaLaunchKernelEx(&cfg, episode_c2_kernel, h->tm_c2_hi, h->tm_c2_lo, h->tm_c2_part, x));
+        h->launches++;
+        return QP_OK;
     }
     if (ep_tc_usable(h) && apply_in_kernel) {
         EpTcArgs x{};
@@ -1698,8 +1796,10 @@ int qp_debug_tc_gemm(int32_t device, int64_t M, int64_t N, int64_t K, const floa
 // Test hook: single tcgen05.mma instructions on operand images a test lays out byte by byte (qp_probe.cuh).
 int qp_debug_umma(int32_t device, const void* a_img, int64_t a_bytes, const void* b_img, int64_t b_bytes,
                   uint64_t desc_a, uint64_t desc_b, uint32_t idesc, int32_t n_mma, uint32_t a_step, uint32_t b_step,
-                  uint32_t d_col, uint32_t d_lane, int32_t n_cols, float fill, float* out) {
+                  uint32_t d_col, uint32_t d_lane, int32_t n_cols, float fill, float* out, int32_t a_tmem_k, uint32_t a_col) {
     if (!a_img || !b_img || !out) return fail(QP_EINVAL, "null argument");
+    if (a_tmem_k != 0 && (a_tmem_k % 8 != 0 || a_bytes != (int64_t)128 * a_tmem_k * 4 || a_col + (uint32_t)a_tmem_k > 512))
+        return fail(QP_EINVAL, "A from tensor memory: a_img must be [128][a_tmem_k] fp32 with a_tmem_k a multiple of 8");
     if (a_bytes < 16 || b_bytes < 16 || a_bytes % 16 || b_bytes % 16 || n_cols < 16 || n_cols > 512 || n_cols % 16 || n_mma < 1 ||
         d_col + (uint32_t)0 > 512)
         return fail(QP_EINVAL, "image sizes must be multiples of 16 bytes, n_cols a multiple of 16 in [16, 512]");
@@ -1708,7 +1808,7 @@ int qp_debug_umma(int32_t device, const void* a_img, int64_t a_bytes, const void
     int max_smem = 0;
     QP_CUDA(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, device));
     if (smem + 1024 > (size_t)max_smem) return fail(QP_EINVAL, "operand images do not fit in shared memory");
-    QP_CUDA(cudaFuncSetAttribute(umma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, max_smem));
+    QP_CUDA(cudaFuncSetAttribute(umma_probe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     DevBuf<uint8_t> da, db;
     DevBuf<float> dout;
     QP_TRY(da.ensure(a_bytes)); QP_TRY(db.ensure(b_bytes)); QP_TRY(dout.ensure((size_t)128 * n_cols));
@@ -1720,6 +1820,7 @@ int qp_debug_umma(int32_t device, const void* a_img, int64_t a_bytes, const void
         g.a_img = da.p; g.a_bytes = (uint32_t)a_bytes; g.b_img = db.p; g.b_bytes = (uint32_t)b_bytes;
         g.desc_a = desc_a; g.desc_b = desc_b; g.idesc = idesc; g.n_mma = n_mma; g.a_step = a_step; g.b_step = b_step;
         g.d_col = d_col; g.d_lane = d_lane; g.n_cols = n_cols; g.fill = fill; g.out = dout.p;
+        g.a_tmem = a_tmem_k != 0 ? 1 : 0; g.a_k = a_tmem_k; g.a_col = a_col;
         umma_probe_kernel<<<1, 128, smem>>>(g);
         QP_CUDA(cudaGetLastError());
         QP_CUDA(cudaDeviceSynchronize());
@@ -1734,6 +1835,12 @@ int qp_debug_umma(int32_t device, const void* a_img, int64_t a_bytes, const void
 int qp_debug_phase_clocks(qp_handle* h, int32_t n_steps, int64_t* out) {
     if (!h || !out) return fail(QP_EINVAL, "null argument");
     if (!h->dbg.p || (size_t)n_steps * qp::kDbgSlots > h->dbg.cap) return fail(QP_ESTATE, "no phase stamps recorded");
+    if (h->want_fine) {      // [n_steps][64]
+        QP_TRY(use_device(h));
+        QP_CUDA(cudaMemcpyAsync(out, h->dbg.p, (size_t)n_steps * 64 * sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
+        QP_CUDA(cudaStreamSynchronize(h->stream));
+        return QP_OK;
+    }
     QP_TRY(use_device(h));
     QP_CUDA(cudaMemcpyAsync(out, h->dbg.p, (size_t)n_steps * qp::kDbgSlots * sizeof(long long), cudaMemcpyDeviceToHost, h->stream));
     QP_CUDA(cudaStreamSynchronize(h->stream));
@@ -1742,11 +1849,13 @@ int qp_debug_phase_clocks(qp_handle* h, int32_t n_steps, int64_t* out) {
 
 int qp_set_option(qp_handle* h, const char* key, int64_t value) {
     if (!h || !key) return fail(QP_EINVAL, "null argument");
-    if (std::strcmp(key, "phase_clocks") == 0) { h->want_dbg = value != 0; h->want_cta_ns = value == 2; return QP_OK; }
+    if (std::strcmp(key, "phase_clocks") == 0) { h->want_dbg = value != 0; h->want_cta_ns = value == 2; h->want_fine = value == 3; return QP_OK; }
     if (std::strcmp(key, "fused") == 0) { h->allow_fused = value != 0; return QP_OK; }
     if (std::strcmp(key, "tc") == 0) { h->allow_tc = value != 0; return QP_OK; }
     if (std::strcmp(key, "p2p") == 0) { h->allow_p2p = value != 0; return QP_OK; }
     if (std::strcmp(key, "ep_tc") == 0) { h->allow_ep_tc = value != 0; return QP_OK; }
+    if (std::strcmp(key, "ep_c2") == 0) { h->allow_ep_c2 = value != 0; return QP_OK; }
+    if (std::strcmp(key, "c2_dbg") == 0) { h->c2_dbg = (int)value; return QP_OK; }
     if (std::strcmp(key, "tc_passes") == 0) {
         if (value != 1 && value != 3) return fail(QP_EINVAL, "tc_passes must be 3 (3xTF32) or 1 (TF32)");
         h->tc_passes = (int)value;
@@ -1770,6 +1879,7 @@ int qp_get_option(qp_handle* h, const char* key, int64_t* value) {
         *value = (h->has_env && use_fused(h) && ep_tc_usable(h)) ? 1 : 0;
         return QP_OK;
     }
+    if (std::strcmp(key, "ep_c2_active") == 0) { *value = (h->has_env && use_fused(h) && ep_c2_usable(h)) ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "p2p_active") == 0) { *value = (h->has_env && h->world > 1 && use_fused(h)) ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "tc_a_lo_zero") == 0) { *value = h->tc_a_lo_zero ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "tc_active") == 0) { *value = (h->wide && h->allow_tc && h->tc_ready) ? 1 : 0; return QP_OK; }

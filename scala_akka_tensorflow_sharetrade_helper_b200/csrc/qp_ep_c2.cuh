@@ -1,0 +1,118 @@
+// qp_ep_c2.cuh — the persistent episode kernel on thread-block clusters of two: a CTA pair owns 64 episodes and
+// splits the HIDDEN dimension, CTA r of the pair taking columns [r*H/2, (r+1)*H/2).  DESIGN.md §4 (i-c2).
+//
+// Why: in episode_tc_kernel (qp_ep_tc.cuh) every CTA streams all of W1^T (hi + lo, 372 KB per env-step at the
+// reference shape) for 32 episodes whose s / s' rows fill half of the M = 128 MMA, and produces a full-width dW1
+// partial per 32 episodes.  With the hidden dimension split over a pair
+//   * each SM takes in HALF of W1^T per step (the forward was bound by that per-SM ingest),
+//   * the M = 128 rows of the forward are all live (64 x s + 64 x s'),
+//   * the backward contracts over 64 episodes: half as many dW1 partials to store, exchange and add.
+// The two CTAs need each other only for the output layer: Q(s) and Q(s') are sums over ALL hidden columns, so each
+// CTA adds up its half and the pair swaps 12 partial sums per episode through distributed shared memory.
+//
+// Operand layouts (tcgen05, kind::tf32; facts pinned by tests/test_gpu_umma_layouts.py):
+//   * the price windows live in shared memory as X^T, [256 rows = time][32 episodes] per 32-episode block, 128-byte
+//     rows, SWIZZLE_128B computed from the absolute address: the K-major A operand of the BACKWARD contraction
+//     (M = time, K = episodes) whose start may be ANY row, so the window slides by moving the descriptor's start
+//     address one row per env-step (rows are copied back to the top every kC2Slide steps);
+//   * kind::tf32 has no usable MN-major form of such a buffer (only the SWIZZLE_128B_BASE32B pattern, which no
+//     K-major descriptor can read), so the FORWARD A operand X (M = episodes and s / s', K = time) is transposed out
+//     of the window buffer per 32-wide k-block into a 3-stage ring by eight builder warps while the tensor core
+//     consumes the previous k-block;
+//   * B of the forward = this CTA's rows of W1^T (tf32 hi / lo), streamed by TMA as before; B of the backward =
+//     dZ1 (hi / lo), written by the element-wise phase.
+// Everything else — select / book-keeping / TD arithmetic, the gradient all-to-all (phase B), the NVLink share
+// exchange, the split grid barrier — is episode_tc_kernel's, on 64-episode tiles.
+#pragma once
+#include "qp_ep_tc.cuh"
+
+namespace qp {
+
+constexpr int kC2Threads = 384;
+constexpr int kC2Warps = kC2Threads / 32;
+constexpr int kC2Envs = 64;             // episodes per CTA pair
+constexpr int kC2Rows = 256;            // rows of the window buffer
+constexpr int kC2Slide = 48;            // env-steps between copy-backs (a multiple of 8: the swizzle phase of a row is kept)
+constexpr int kC2AStages = 3;           // forward A operand ring: [128 rows x 32 k] tiles of 16 KB
+constexpr int kC2Builders = 8;          // warps 2..9 transpose the A tiles
+constexpr int kC2Sub = kC2Warps / 2;    // warps per 32-episode lane group in the element-wise phases
+constexpr int kC2EStride = 65;          // padded row stride of the [column][episode] tiles
+
+struct EpC2Args {
+    EpisodeArgs ea;
+    float* w1T_hi; float* w1T_lo;   // [H, Kp] K-major tf32 hi/lo copies of W1[0:wn, :] (as episode_tc_kernel)
+    int Kp, nkb;
+    int Hh;                          // hidden columns per CTA (H / 2)
+    int Nh;                          // MMA N per CTA: Hh rounded up to 8
+    unsigned long long* published;
+    unsigned long long* pdata[8];    // several GPUs: every rank's exchange block (see EpTcArgs)
+    int64_t p_pad;
+    int dbg_mode;                    // timing experiments (option "c2_dbg"); 0 in every real run
+    long long* fine;                 // tuning aid ("phase_clocks" = 3): [n_steps][64] clock64 stamps inside the forward of CTA 0
+};
+
+// Shared-memory map (bytes from the 1024-aligned base); the host computes the same numbers.
+struct C2Smem {
+    size_t xt, regA, regW, tabs, w2s, wb, ws, xe, dz2s, kns, qpart, qsum, part5, bars, total;
+    size_t regA_bytes, regW_bytes, TBh;
+};
+__host__ __device__ inline C2Smem c2_smem(int Hh, int Nh) {
+    C2Smem m{};
+    m.TBh = (size_t)Nh * 128;
+    m.xt = 0;
+    m.regA = (size_t)2 * kC2Rows * 128;
+    size_t a = (size_t)kC2AStages * 16384, hz = (size_t)2 * Hh * kC2EStride * 4;
+    m.regA_bytes = ((a > hz ? a : hz) + 1023) & ~(size_t)1023;
+    m.regW = m.regA + m.regA_bytes;
+    m.regW_bytes = ((4 * m.TBh) + 1023) & ~(size_t)1023;
+    m.tabs = m.regW + m.regW_bytes;
+    size_t o = m.tabs;
+    m.w2s = o; o += (size_t)Hh * 16;
+    m.wb = o; o += (size_t)Hh * 4;
+    m.ws = o; o += (size_t)Hh * 4;
+    m.xe = o; o += 2 * kC2Envs * 4;
+    m.dz2s = o; o += kC2Envs * 4;
+    m.kns = o; o += kC2Envs * 4;
+    o = (o + 15) & ~(size_t)15;
+    m.qpart = o; o += (size_t)kC2Sub * 12 * kC2Envs * 4;
+    m.qsum = o; o += (size_t)2 * 12 * kC2Envs * 4;
+    m.part5 = o; o += (size_t)2 * 5 * Hh * 4;
+    o = (o + 7) & ~(size_t)7;
+    m.bars = o; o += 24 * 8;
+    m.total = o + 16;
+    return m;
+}
+
+#ifdef __CUDACC__
+
+__device__ __forceinline__ void c2_mbar_arrive(uint64_t* bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" ::"r"((uint32_t)__cvta_generic_to_shared(bar)) : "memory");
+}
+__device__ __forceinline__ uint32_t c2_cluster_rank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
+}
+__device__ __forceinline__ void c2_cluster_sync() {
+    asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+// address of the same shared-memory variable in the CTA with the given rank of this cluster
+__device__ __forceinline__ uint32_t c2_map_peer(const void* p, uint32_t rank) {
+    uint32_t a = (uint32_t)__cvta_generic_to_shared(p), r;
+    asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(rank));
+    return r;
+}
+__device__ __forceinline__ void c2_st_cluster(uint32_t addr, float v) {
+    asm volatile("st.shared::cluster.f32 [%0], %1;" ::"r"(addr), "f"(v) : "memory");
+}
+__device__ __forceinline__ void c2_tma_store_4d(const CUtensorMap* tmap, const void* smem_src, int c0, int c1, int c2, int c3) {
+    asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];\n" ::"l"(tmap),
+                 "r"((uint32_t)__cvta_generic_to_shared(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+                 : "memory");
+}
+
+#endif  // __CUDACC__
+}  // namespace qp
+
+#include "qp_ep_c2_kernel.cuh"

@@ -1,0 +1,112 @@
+// qp_ep_c2_backward.inl — S5 .. S7 of one env-step: backward contraction, dW2 and the budget / shares rows, the
+// dW1 partial out of TMEM into global memory, the next price into the window buffer.
+{
+    // ---- S5: dW1[256, Nh] = X^T[256, 64] · dZ1[64, Nh] on the tensor core: the window buffer IS the K-major A operand
+    // (rows = time, starting at the row of window element 0), contraction over the 64 episodes in two 32-wide blocks
+    if (warp == 1 && lane == 0) {
+        tc_fence_after();
+        for (int hf = 0; hf < halves; ++hf) {
+            bool first = true;
+            for (int kb = 0; kb < 2; ++kb) {
+                const uint64_t da = tc_smem_desc(XT + (size_t)kb * 32768 + (size_t)(roff + hf * 128) * 128);
+                const uint64_t db_hi = tc_smem_desc(Bbwd_hi + (size_t)kb * TBh), db_lo = tc_smem_desc(Bbwd_lo + (size_t)kb * TBh);
+#pragma unroll
+                for (int k4 = 0; k4 < 4; ++k4) {
+                    tc_mma_tf32(tmem_base + 128u + (uint32_t)(hf * 128), da + 2 * k4, db_hi + 2 * k4, idesc, first ? 0u : 1u);
+                    tc_mma_tf32(tmem_base + 128u + (uint32_t)(hf * 128), da + 2 * k4, db_lo + 2 * k4, idesc, 1u);
+                    first = false;
+                }
+            }
+        }
+        tc_commit(tf_bwd);
+    }
+    // meanwhile: dW2[c][t] = sum_e [kn_e == t] h_e[c] dz2_e and the budget / shares rows of dW1, two threads per hidden
+    // column (one per lane group), episodes summed sequentially out of shared memory (fixed order)
+    if (tid < 2 * Hh) {
+        const int c = tid % Hh, gg = tid / Hh;
+        const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
+        float s0 = 0.f, s1 = 0.f, s2 = 0.f, x0 = 0.f, x1 = 0.f;
+#pragma unroll 8
+        for (int l = 0; l < 32; ++l) {
+            const int ee = gg * 32 + l;
+            const float h = HS[c * kC2EStride + ee];
+            const float dz = dz2s[ee];
+            const int k = kns[ee];
+            const float hv = __fmul_rn(h, dz);
+            s0 += k == 0 ? hv : 0.0f; s1 += k == 1 ? hv : 0.0f; s2 += k == 2 ? hv : 0.0f;
+            const float w2k = k == 0 ? w2.x : (k == 1 ? w2.y : w2.z);
+            const float d1 = h > 0.0f ? __fmul_rn(dz, w2k) : 0.0f;
+            x0 = fmaf(XE[ee], d1, x0);
+            x1 = fmaf(XE[kC2Envs + ee], d1, x1);
+        }
+        float* p5 = part5 + (size_t)gg * 5 * Hh + c;
+        p5[0] = s0; p5[Hh] = s1; p5[2 * Hh] = s2; p5[3 * Hh] = x0; p5[4 * Hh] = x1;
+    }
+    tc_wait(tf_bwd, par);
+    tc_fence_after();
+    ++mma_it;
+    __syncthreads();
+    stamp(6);
+    if (tid < Hh) {
+        const float* pa = part5 + tid;
+        const float* pb = part5 + (size_t)5 * Hh + tid;
+        const int c = c0 + tid;
+        out2[c * 3 + 0] = pa[0] + pb[0]; out2[c * 3 + 1] = pa[Hh] + pb[Hh]; out2[c * 3 + 2] = pa[2 * Hh] + pb[2 * Hh];
+        out[(size_t)wn * H + c] = pa[3 * Hh] + pb[3 * Hh];
+        out[(size_t)(wn + 1) * H + c] = pa[4 * Hh] + pb[4 * Hh];
+    }
+    // ---- S6: dW1 partial out of TMEM.  Row m of the accumulator is window element m (the A operand started at the
+    // window's first row).  Each warp stages [32 rows x 32 columns] boxes in shared memory (128-byte swizzle,
+    // conflict-free) and lane 0 hands them to the TMA engine; the tensor map ([pair][row][half][column]) ends at row wn
+    // and at this CTA's last column.  The columns past the last full box go out of the registers directly.
+    {
+        const int nfull = Hh >> 5, tail = Hh - (nfull << 5);
+        uint8_t* stg = regA + (size_t)warp * 8192;
+        int n_box = 0;
+        for (int i = part; i < halves * nfull; i += 3) {
+            const int hf = i / nfull, cb = i - hf * nfull;
+            const int k0 = hf * 128 + q4 * 32;
+            if (k0 >= wn) continue;
+            uint32_t r[32];
+            et_tmem_ld32_nowait(tmem_base + ((uint32_t)(q4 * 32) << 16) + 128u + (uint32_t)(hf * 128 + cb * 32), r);
+            if (n_box >= 2) {                                   // the buffer's previous box has left it
+                if (lane == 0) et_bulk_wait_read1();
+                __syncwarp();
+            }
+            et_tmem_wait_ld();
+            uint8_t* buf = stg + (size_t)(n_box & 1) * 4096;
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+                *reinterpret_cast<uint4*>(buf + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+            et_fence_async_smem();
+            __syncwarp();
+            if (lane == 0) {
+                c2_tma_store_4d(&tP, buf, cb * 32, (int)crank, k0, (int)pair);
+                et_bulk_commit();
+            }
+            ++n_box;
+        }
+        if (tail > 0) {
+            for (int hf = part; hf < halves; hf += 3) {
+                const int k0 = hf * 128 + q4 * 32;
+                if (k0 >= wn) continue;
+                for (int t0 = 0; t0 < tail; t0 += 16) {
+                    float v[16];
+                    et_tmem_ld16(tmem_base + ((uint32_t)(q4 * 32) << 16) + 128u + (uint32_t)(hf * 128 + nfull * 32 + t0), v);
+                    const int k = k0 + lane;
+                    if (k < wn) {
+#pragma unroll
+                        for (int j = 0; j < 4; ++j)
+                            if (t0 + 4 * j < tail)
+                                *reinterpret_cast<float4*>(out + (size_t)k * H + c0 + nfull * 32 + t0 + 4 * j) =
+                                    make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
+                    }
+                }
+            }
+        }
+    }
+    // ---- S7: slide the window: the next price of every episode into the row after the window's last
+    if (wsub == 0) *reinterpret_cast<float*>(XT + (size_t)g * 32768 + et_swz(roff + wn + 1, lane)) = p_next;
+    tc_fence_before();
+    __syncthreads();
+}

@@ -1,0 +1,168 @@
+// qp_ep_c2_kernel.cuh — body of episode_c2_kernel (see qp_ep_c2.cuh for the design).
+#pragma once
+
+namespace qp {
+#ifdef __CUDACC__
+
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kC2Threads, 1)
+episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_constant__ CUtensorMap tW_lo,
+                  const __grid_constant__ CUtensorMap tP, const EpC2Args x) {
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    extern __shared__ __align__(1024) uint8_t c2_smem_raw[];
+    const EpisodeArgs& ea = x.ea;
+    const StepArgs& a = ea.s;
+    const Hyper& hp = a.hp;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int nthreads = kC2Threads;
+    const int D = hp.D, H = hp.H, wn = hp.wn;
+    const int Hh = x.Hh, Nh = x.Nh, nkb = x.nkb;
+    const int halves = (wn + 127) >> 7;
+    const C2Smem sm = c2_smem(Hh, Nh);
+    const uint32_t TBh = (uint32_t)sm.TBh;
+
+    // every pointer is the __shared__ symbol plus an offset (keeps the shared state space: LDS / STS)
+    uint8_t* base = c2_smem_raw;
+    if (tid == 0 && ((uint32_t)__cvta_generic_to_shared(base) & 1023u) != 0u) __trap();
+    uint8_t* XT = base + sm.xt;                                 // [2 blocks][256 rows][32 episodes], SWIZZLE_128B by address
+    uint8_t* regA = base + sm.regA;                             // forward A ring -> z tiles -> epilogue boxes -> phase-B stage
+    uint8_t* regW = base + sm.regW;                             // W1^T ring -> dZ1 hi / lo -> epilogue boxes -> phase-B stage
+    float* HS = reinterpret_cast<float*>(regA);                 // [Hh][65]: window part of z1(s), then h(s)
+    float* ZN = HS + (size_t)Hh * kC2EStride;                   // [Hh][65]: window part of z1(s')
+    uint8_t* Bbwd_hi = regW;                                    // [2 episode blocks][Nh x 32]
+    uint8_t* Bbwd_lo = regW + 2 * (size_t)TBh;
+    float* W2s = reinterpret_cast<float*>(base + sm.w2s);       // [Hh] float4
+    float* Wb = reinterpret_cast<float*>(base + sm.wb);
+    float* Ws = reinterpret_cast<float*>(base + sm.ws);
+    float* XE = reinterpret_cast<float*>(base + sm.xe);         // [2][64]
+    float* dz2s = reinterpret_cast<float*>(base + sm.dz2s);
+    int* kns = reinterpret_cast<int*>(base + sm.kns);
+    float* qpart = reinterpret_cast<float*>(base + sm.qpart);   // [6 warps of a lane group][12][64]
+    float* qsum = reinterpret_cast<float*>(base + sm.qsum);     // [2 CTAs of the pair][12][64]
+    float* part5 = reinterpret_cast<float*>(base + sm.part5);   // [2 lane groups][5][Hh]
+    uint64_t* bars = reinterpret_cast<uint64_t*>(base + sm.bars);
+    uint64_t* w_full = bars;            // [2]
+    uint64_t* w_empty = bars + 2;       // [2]
+    uint64_t* a_full = bars + 4;        // [3]
+    uint64_t* a_empty = bars + 7;       // [3]
+    uint64_t* tf_fwd = bars + 10;
+    uint64_t* tf_bwd = bars + 11;
+    uint64_t* pb_bar = bars + 12;       // [4]
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+
+    const uint32_t crank = c2_cluster_rank();                   // which half of the hidden columns
+    const int c0 = (int)crank * Hh;                             // first hidden column of this CTA
+    const int64_t pair = (int64_t)(blockIdx.x >> 1);
+    const int64_t B = a.B;
+    const int64_t n_pairs = (B + kC2Envs - 1) / kC2Envs;
+    const bool has_tile = pair < n_pairs;
+    const int g = warp & 1, wsub = warp >> 1;                   // element-wise phases: lane group / column subset
+    const int el = g * 32 + lane;                               // episode of this thread within the pair's 64
+    const int64_t e = pair * kC2Envs + el;
+    const bool valid = has_tile && e < B;
+    const int64_t ec = has_tile ? (valid ? e : B - 1) : 0;
+    const float bias = hp.bias;
+    const float* W1g = a.params;
+    const float* W2g = a.params + (size_t)D * H;
+    const int q4 = warp & 3, part = warp >> 2;                  // TMEM lane quarter / column part of this warp
+
+    if (tid == 0) {
+        mbar_init(w_full, 1); mbar_init(w_full + 1, 1); mbar_init(w_empty, 1); mbar_init(w_empty + 1, 1);
+        for (int s = 0; s < kC2AStages; ++s) { mbar_init(a_full + s, kC2Builders); mbar_init(a_empty + s, 1); }
+        mbar_init(tf_fwd, 1); mbar_init(tf_bwd, 1);
+        for (int i = 0; i < 4; ++i) mbar_init(pb_bar + i, 1);
+        mbar_fence_init();
+    }
+    if (warp == 2) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
+                         (uint32_t)__cvta_generic_to_shared(tmem_slot)), "r"(512u) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+    }
+    for (size_t i = tid; i < sm.tabs / 16; i += nthreads) reinterpret_cast<float4*>(base)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    double budget = a.budget[ec], share_value = a.share_value[ec];
+    int32_t shares = a.shares[ec];
+    const float* my_row = a.prices + (int64_t)a.series_of_env[ec] * a.T;
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    if (has_tile) {
+        // the window of every episode of the pair: element k of episode (g, l) at row k of block g
+        const int segs = (wn + 1 + 31) >> 5, items = 32 * segs;
+        for (int it = wsub; it < items; it += kC2Sub) {
+            const int l = it & 31, k = ((it >> 5) << 5) + lane;
+            const float* src = reinterpret_cast<const float*>(
+                __shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(my_row), l)) + ea.step0;
+            if (k <= wn) cp_async4(XT + (size_t)g * 32768 + et_swz(k, l), src + k);
+        }
+        cp_async_commit();
+        cp_async_wait_pending(0);
+    }
+    const int64_t P1 = (int64_t)D * H, P = P1 + 3 * (int64_t)H;
+    {   // K-major tf32 hi/lo copies of the current W1 (phase B keeps them current afterwards)
+        for (int64_t p = ((int64_t)blockIdx.x * nthreads + tid) * 4; p < P1; p += (int64_t)gridDim.x * nthreads * 4) {
+            const float4 w = __ldcg(reinterpret_cast<const float4*>(W1g + p));
+            const int k = (int)(p / H), n = (int)(p - (int64_t)k * H);
+            if (k < wn) {
+                const float ww[4] = {w.x, w.y, w.z, w.w};
+#pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float hi = et_tf32(ww[q]);
+                    x.w1T_hi[(size_t)(n + q) * x.Kp + k] = hi;
+                    x.w1T_lo[(size_t)(n + q) * x.Kp + k] = ww[q] - hi;
+                }
+            }
+        }
+    }
+    // phase B's division of the parameters over the CTAs (as episode_tc_kernel; the host has checked `flow`)
+    const int n1 = (int)n_pairs;                                // one partial per pair
+    const int n_w1_ctas = max(1, (int)gridDim.x - 2);
+    const int chunk = (int)(((P1 + n_w1_ctas - 1) / n_w1_ctas + 3) & ~(int64_t)3);
+    const int chunk2 = ((3 * H + 1) / 2 + 3) & ~3;
+    const int pitch = max(chunk, chunk2);
+    const int rows_cap = min(128, (int)((sm.regA_bytes + sm.regW_bytes) / ((size_t)pitch * 4)) & ~3);
+    if (!(gridDim.x >= 8 && pitch <= nthreads && rows_cap >= 4 && x.published != nullptr)) __trap();
+    const int n_publishers = (int)((P1 + chunk - 1) / chunk) + 2;
+    if (blockIdx.x == 0 && tid == 0) *x.published = 0ull;
+    __threadfence();
+    grid.sync();
+
+    const uint32_t idesc = tc_instr_desc(128, Nh);
+    uint32_t ring_it = 0, a_it = 0, pb_phase = 0, mma_it = 0;
+    const int kb_first = (int)(blockIdx.x % (unsigned)nkb);
+    float* out = ea.part1 + (size_t)pair * ((size_t)D * H);
+    float* out2 = a.dw2_part + (size_t)pair * (3 * H);
+
+    for (int32_t sidx = 0; sidx < ea.n_steps; ++sidx) {
+        const int32_t istep = ea.step0 + sidx;
+        const int roff = sidx % kC2Slide;                       // row of window element 0
+        auto stamp = [&](int i) { if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + i] = clock64(); };
+        stamp(0);
+        if (has_tile) {
+#include "qp_ep_c2_phaseA.inl"
+        }
+        stamp(7);
+        if (!ea.apply_in_kernel) { et_bulk_wait_all(); break; }
+        et_bulk_wait_all();                                     // the partial is in global memory
+        stamp(8);
+        __threadfence();
+        grid.sync();
+        stamp(9);
+#include "qp_ep_c2_phaseB.inl"
+        stamp(10);
+    }
+
+    if (has_tile && crank == 0 && wsub == 0 && valid) {
+        a.budget[e] = budget;
+        a.shares[e] = shares;
+        a.share_value[e] = share_value;
+    }
+    if (ea.apply_in_kernel && blockIdx.x == 0 && tid == 0) *ea.d_step_rw = ea.step0 + ea.n_steps;
+    tc_fence_before();
+    __syncthreads();
+    c2_cluster_sync();                                          // nobody leaves while its partner may still write to it
+    if (warp == 2) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base), "r"(512u) : "memory");
+}
+
+#endif  // __CUDACC__
+}  // namespace qp

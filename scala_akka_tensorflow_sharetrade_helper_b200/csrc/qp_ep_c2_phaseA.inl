@@ -1,0 +1,301 @@
+// qp_ep_c2_phaseA.inl — one env-step of the pair's 64 episodes up to the stored dW1 / dW2 partial.
+// Textually included in episode_c2_kernel's step loop (has_tile is true here).
+{
+    const uint32_t par = mma_it & 1u;
+    // ---- slide: every kC2Slide steps the live rows go back to the top of the buffer.  Source and destination overlap:
+    // everything is read into registers first.  (kC2Slide is a multiple of 8, so a row keeps its swizzle phase.)
+    if (sidx > 0 && roff == 0) {
+        constexpr int kMaxCopy = 12;
+        const int n_items = (wn + 1) * 16;                      // (block, row, 16-byte chunk)
+        float4 v[kMaxCopy];
+#pragma unroll
+        for (int i = 0; i < kMaxCopy; ++i) {
+            const int it = tid + i * nthreads;
+            if (it < n_items) {
+                const int blk = it / ((wn + 1) * 8), rem = it - blk * (wn + 1) * 8;
+                v[i] = *reinterpret_cast<const float4*>(XT + (size_t)blk * 32768 + (size_t)((rem >> 3) + kC2Slide) * 128 + ((rem & 7) << 4));
+            }
+        }
+        __syncthreads();
+#pragma unroll
+        for (int i = 0; i < kMaxCopy; ++i) {
+            const int it = tid + i * nthreads;
+            if (it < n_items) {
+                const int blk = it / ((wn + 1) * 8), rem = it - blk * (wn + 1) * 8;
+                *reinterpret_cast<float4*>(XT + (size_t)blk * 32768 + (size_t)(rem >> 3) * 128 + ((rem & 7) << 4)) = v[i];
+            }
+        }
+        et_fence_async_smem();
+        __syncthreads();
+    }
+    float q_s[3] = {0.f, 0.f, 0.f}, q_n[3] = {0.f, 0.f, 0.f};
+    int action = 0, explored = 0, a_eff = 2, kn = 0;
+    float r32 = 0.0f, target = 0.0f, dz2 = 0.0f, p_next = 0.0f;
+    uint32_t rnd[4] = {0u, 0u, 0u, 0u};
+
+    // ---- S0 / S1: forward contraction Z[128, Nh] = X[128, Kp] · W1[Kp, this CTA's columns] on the tensor core.
+    // Roles: warp 0 feeds the W1^T ring (and loads the small tables), warp 1 issues the MMAs, warps 2..9 transpose the
+    // A tiles out of the window buffer; the A tiles do not depend on the weights, so the builders run ahead of the
+    // split barrier.
+    auto fine = [&](int i) { if (x.fine && blockIdx.x == 0) x.fine[(size_t)sidx * 64 + i] = clock64(); };   // tuning aid
+    const int dbgm = x.dbg_mode;      // timing experiments only (results are wrong when non-zero): 1 no W stream, 2 no A build, 4 no MMA
+    auto push_w_tiles = [&](int kk) {
+        if (dbgm & 1) return;
+        const int kb = (kk + kb_first) % nkb;
+        const uint32_t it = ring_it + (uint32_t)kk, s = it & 1u, ph = (it >> 1) & 1u;
+        tc_wait(w_empty + s, ph ^ 1u);
+        fine(kk);
+        uint8_t* st = regW + (size_t)s * 2 * TBh;
+        mbar_arrive_expect_tx(w_full + s, 2 * TBh);
+        tma_load_2d(st, &tW_hi, kb * 32, c0, w_full + s);
+        tma_load_2d(st + TBh, &tW_lo, kb * 32, c0, w_full + s);
+    };
+    if (warp == 0) {
+        if (lane == 0) {
+            // the new weights are complete once every publisher of the previous step is through
+            if (sidx > 0) et_wait_count(x.published, (unsigned long long)sidx * (unsigned long long)n_publishers);
+            fence_proxy_async();                                // phase-B writes of W1^T -> TMA reads
+            for (int kk = 0; kk < min(2, nkb); ++kk) push_w_tiles(kk);
+            stamp(1);                                           // (the wait for the other CTAs' phase B ends here)
+            for (int kk = 2; kk < nkb; ++kk) push_w_tiles(kk);
+        }
+        __syncwarp();
+    } else if (warp == 1) {
+        if (lane == 0) {
+            bool first = true;
+            for (int kk = 0; kk < nkb; ++kk) {
+                const int kb = (kk + kb_first) % nkb;
+                const uint32_t it = ring_it + (uint32_t)kk, s = it & 1u, ph = (it >> 1) & 1u;
+                const uint32_t ait = a_it + (uint32_t)kk, sa = ait % kC2AStages, pha = (ait / kC2AStages) & 1u;
+                if (!(dbgm & 2)) tc_wait(a_full + sa, pha);
+                fine(16 + kk);
+                if (!(dbgm & 1)) tc_wait(w_full + s, ph);
+                fine(8 + kk);
+                tc_fence_after();
+                uint8_t* st = regW + (size_t)s * 2 * TBh;
+                const uint64_t da = tc_smem_desc(regA + (size_t)sa * 16384);
+                const uint64_t db_hi = tc_smem_desc(st), db_lo = tc_smem_desc(st + TBh);
+#pragma unroll
+                for (int k4 = 0; k4 < 4; ++k4) {
+                    if (kb * 32 + k4 * 8 < wn && !(dbgm & 4)) {    // (the columns past the window are zero on both sides)
+                        tc_mma_tf32(tmem_base, da + 2 * k4, db_hi + 2 * k4, idesc, first ? 0u : 1u);
+                        tc_mma_tf32(tmem_base, da + 2 * k4, db_lo + 2 * k4, idesc, 1u);
+                        first = false;
+                    }
+                }
+                if (!(dbgm & 1)) tc_commit(w_empty + s);
+                if (!(dbgm & 2)) tc_commit(a_empty + sa);
+            }
+            tc_commit(tf_fwd);
+            fine(40);
+        }
+        __syncwarp();                                           // (the other lanes park here instead of polling beside the issuer)
+    } else if (warp < 2 + kC2Builders) {
+        const int bw = warp - 2;
+        for (int kk = 0; kk < ((dbgm & 2) ? 0 : nkb); ++kk) {
+            const int kb = (kk + kb_first) % nkb;
+            const uint32_t ait = a_it + (uint32_t)kk, sa = ait % kC2AStages, pha = (ait / kC2AStages) & 1u;
+            if (lane == 0) tc_wait(a_empty + sa, pha ^ 1u);
+            __syncwarp();
+            if (bw == 0 && lane == 0) fine(24 + kk);
+            uint8_t* At = regA + (size_t)sa * 16384;
+#pragma unroll
+            for (int i = 0; i < 32 / kC2Builders; ++i) {        // (s or s', lane group, 16-byte chunk of the k-block)
+                const int item = bw + kC2Builders * i;
+                const int half = item & 1, eg = (item >> 1) & 1, ch = item >> 2;
+                const int kbase = kb * 32 + ch * 4;
+                const uint8_t* blk = XT + (size_t)eg * 32768;
+                float vv[4];
+#pragma unroll
+                for (int j = 0; j < 4; ++j)
+                    vv[j] = kbase + j < wn ? *reinterpret_cast<const float*>(blk + et_swz(roff + kbase + j + half, lane)) : 0.0f;
+                const int row = half * 64 + eg * 32 + lane;
+                *reinterpret_cast<float4*>(At + (size_t)row * 128 + ((ch ^ (row & 7)) << 4)) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+            }
+            et_fence_async_smem();
+            __syncwarp();
+            if (lane == 0) c2_mbar_arrive(a_full + sa);
+            if (bw == 0 && lane == 0) fine(32 + kk);
+        }
+    }
+    else if (warp == 2 + kC2Builders) {
+        // the small tables of this CTA's columns (W2, the budget / shares rows of W1): they need the new weights too, so
+        // this warp watches the counter itself; every load is issued before the first store
+        if (lane == 0 && sidx > 0) et_wait_count(x.published, (unsigned long long)sidx * (unsigned long long)n_publishers);
+        __syncwarp();
+        constexpr int kTabIter = 4;                             // Hh <= 128
+        float t0[kTabIter], t1[kTabIter], t2[kTabIter], t3[kTabIter], t4[kTabIter];
+#pragma unroll
+        for (int i = 0; i < kTabIter; ++i) {
+            const int j = lane + 32 * i, c = c0 + (j < Hh ? j : 0);
+            t0[i] = __ldcg(W2g + c * 3); t1[i] = __ldcg(W2g + c * 3 + 1); t2[i] = __ldcg(W2g + c * 3 + 2);
+            t3[i] = __ldcg(W1g + (size_t)wn * H + c); t4[i] = __ldcg(W1g + (size_t)(wn + 1) * H + c);
+        }
+#pragma unroll
+        for (int i = 0; i < kTabIter; ++i) {
+            const int j = lane + 32 * i;
+            if (j < Hh) {
+                reinterpret_cast<float4*>(W2s)[j] = make_float4(t0[i], t1[i], t2[i], 0.f);
+                Wb[j] = t3[i];
+                Ws[j] = t4[i];
+            }
+        }
+    }
+    ring_it += (uint32_t)nkb;
+    a_it += (uint32_t)nkb;
+    // everything of the decision that does not depend on Q
+    double p_new, cur;
+    {
+        const uint64_t env_id = (uint64_t)(a.env_id_base + e);
+        philox4x32_10((uint32_t)env_id, (uint32_t)(env_id >> 32), (uint32_t)istep, 1u, (uint32_t)hp.seed, (uint32_t)(hp.seed >> 32), rnd);
+        p_new = (double)*reinterpret_cast<const float*>(XT + (size_t)g * 32768 + et_swz(roff + wn, lane));
+        cur = __dadd_rn(budget, __dmul_rn((double)shares, share_value));
+        if (wsub == 0 && (int64_t)istep + wn + 1 < a.T) p_next = __ldg(my_row + istep + wn + 1);
+    }
+    tc_wait(tf_fwd, par);
+    tc_fence_after();
+    stamp(2);
+    if (tid == 0) fine(41);
+
+    // ---- S2: raw z out of TMEM into the [column][episode] tiles.  TMEM lane quarter q holds rows 32q..32q+31 of
+    // the A operand: q = 0, 1 -> z1(s) of episodes 0..31 / 32..63; q = 2, 3 -> z1(s')
+    {
+        float* dstz = (q4 >> 1) ? ZN : HS;
+        const int eo = (q4 & 1) * 32 + lane;
+        const int n_ld = (Hh + 15) >> 4;
+        const int ld0 = part * n_ld / 3, ld1 = (part + 1) * n_ld / 3;
+#pragma unroll 1
+        for (int l = ld0; l < ld1; ++l) {
+            float v[16];
+            et_tmem_ld16(tmem_base + ((uint32_t)(q4 * 32) << 16) + (uint32_t)(l * 16), v);
+#pragma unroll
+            for (int j = 0; j < 16; ++j)
+                if (l * 16 + j < Hh) dstz[(l * 16 + j) * kC2EStride + eo] = v[j];
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    stamp(3);
+
+    // the three states s' the decision can lead to (index = effective action; TrainerChildActor.scala:118-123)
+    const double base_b = hp.bookkeeping == 0 ? a.B0 : budget;
+    const int32_t base_n = hp.bookkeeping == 0 ? a.N0 : shares;
+    const bool can_buy = base_b >= p_new, can_sell = base_n > 0;
+    const double nbc[3] = {can_buy ? __dsub_rn(base_b, p_new) : base_b, can_sell ? __dadd_rn(base_b, p_new) : base_b, base_b};
+    const int32_t nsc[3] = {can_buy ? base_n + 1 : base_n, can_sell ? base_n - 1 : base_n, base_n};
+    // ---- S3: one pass over this CTA's hidden columns: h(s) and the partial sums of Q(s) and of Q(s') for all three
+    // outcomes (warp = lane group g x column subset wsub)
+    {
+        float pq[4][3] = {{0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}, {0.f, 0.f, 0.f}};
+        const float xb = __double2float_rn(budget), xs = (float)shares;
+        const float xnb[3] = {__double2float_rn(nbc[0]), __double2float_rn(nbc[1]), __double2float_rn(nbc[2])};
+        const float xns[3] = {(float)nsc[0], (float)nsc[1], (float)nsc[2]};
+#pragma unroll 2
+        for (int c = wsub; c < Hh; c += kC2Sub) {
+            const float wb = Wb[c], ws = Ws[c], zn = ZN[c * kC2EStride + el];
+            const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
+            const float h = et_hidden(HS[c * kC2EStride + el], xb, xs, wb, ws, bias);
+            HS[c * kC2EStride + el] = h;                        // from here on the tile holds h(s)
+            pq[0][0] = fmaf(h, w2.x, pq[0][0]); pq[0][1] = fmaf(h, w2.y, pq[0][1]); pq[0][2] = fmaf(h, w2.z, pq[0][2]);
+#pragma unroll
+            for (int j = 0; j < 3; ++j) {
+                const float hn = et_hidden(zn, xnb[j], xns[j], wb, ws, bias);
+                pq[1 + j][0] = fmaf(hn, w2.x, pq[1 + j][0]); pq[1 + j][1] = fmaf(hn, w2.y, pq[1 + j][1]);
+                pq[1 + j][2] = fmaf(hn, w2.z, pq[1 + j][2]);
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+#pragma unroll
+            for (int t = 0; t < 3; ++t) qpart[((wsub * 4 + j) * 3 + t) * kC2Envs + el] = pq[j][t];
+    }
+    __syncthreads();
+    // this CTA's half of the twelve sums per episode, fixed order, to both CTAs of the pair
+    {
+        const uint32_t peer = c2_map_peer(qsum, crank ^ 1u);
+        for (int idx = tid; idx < 12 * kC2Envs; idx += nthreads) {
+            float pw[kC2Sub];
+#pragma unroll
+            for (int w = 0; w < kC2Sub; ++w) pw[w] = qpart[w * 12 * kC2Envs + idx];
+            float s = (pw[0] + pw[1]) + (pw[2] + pw[3]);
+#pragma unroll
+            for (int w = 4; w < kC2Sub; w += 2) s += pw[w] + pw[w + 1];
+            qsum[crank * 12 * kC2Envs + idx] = s;
+            c2_st_cluster(peer + (uint32_t)((crank * 12 * kC2Envs + idx) * 4), s);
+        }
+    }
+    c2_cluster_sync();
+    {
+        // SelectionAction (QDecisionPolicyActor.scala:56-62), decision, reward: every warp of the lane group keeps its copy
+#pragma unroll
+        for (int t = 0; t < 3; ++t) {
+            const float s = (qsum[t * kC2Envs + el] + qsum[(12 + t) * kC2Envs + el]) + bias;
+            q_s[t] = s > 0.0f ? s : 0.0f;
+        }
+        const float u = (float)(rnd[0] >> 8) * (1.0f / 16777216.0f);
+        float thr = __fdiv_rn((float)istep, hp.step_div);
+        if (hp.epsilon < thr) thr = hp.epsilon;
+        if (u < thr) action = argmax3(q_s);
+        else { explored = 1; action = (int)(((uint64_t)rnd[1] * 3u) >> 32); }
+        if (action == 0 && can_buy) a_eff = 0;
+        else if (action == 1 && can_sell) a_eff = 1;
+        const double nb = a_eff == 0 ? nbc[0] : (a_eff == 1 ? nbc[1] : nbc[2]);
+        const int32_t ns = a_eff == 0 ? nsc[0] : (a_eff == 1 ? nsc[1] : nsc[2]);
+        const double newp = __dadd_rn(nb, __dmul_rn((double)ns, p_new));
+        r32 = __double2float_rn(__dsub_rn(newp, cur));
+        stamp(4);
+        // ---- S4: Q(s') of the outcome taken, TD target; dZ1 as the K-major (episodes contiguous) tf32 hi/lo B operand
+#pragma unroll
+        for (int t = 0; t < 3; ++t) {
+            const int jt = (1 + a_eff) * 3 + t;
+            const float s = (qsum[jt * kC2Envs + el] + qsum[(12 + jt) * kC2Envs + el]) + bias;
+            q_n[t] = s > 0.0f ? s : 0.0f;
+        }
+        kn = argmax3(q_n);
+        const float qn_k = kn == 0 ? q_n[0] : (kn == 1 ? q_n[1] : q_n[2]);
+        const float qs_k = kn == 0 ? q_s[0] : (kn == 1 ? q_s[1] : q_s[2]);
+        target = __fadd_rn(r32, __fmul_rn(hp.gamma, qn_k));
+        const float dq = -__fmul_rn(2.0f, __fsub_rn(target, qs_k));
+        dz2 = (valid && qs_k > 0.0f) ? dq : 0.0f;
+        uint8_t* bh = Bbwd_hi + (size_t)g * TBh;
+        uint8_t* bl = Bbwd_lo + (size_t)g * TBh;
+#pragma unroll 4
+        for (int c = wsub; c < Hh; c += kC2Sub) {
+            const float d1 = HS[c * kC2EStride + el] > 0.0f ? __fmul_rn(dz2, W2s[c * 4 + kn]) : 0.0f;
+            const float hi = et_tf32(d1);
+            const uint32_t off = et_swz(c, lane);
+            *reinterpret_cast<float*>(bh + off) = hi;
+            *reinterpret_cast<float*>(bl + off) = d1 - hi;
+        }
+        for (int c = Hh + wsub; c < Nh; c += kC2Sub) {          // padding rows of the MMA's N
+            const uint32_t off = et_swz(c, lane);
+            *reinterpret_cast<float*>(bh + off) = 0.0f;
+            *reinterpret_cast<float*>(bl + off) = 0.0f;
+        }
+        if (wsub == 0) {
+            XE[el] = __double2float_rn(budget);
+            XE[kC2Envs + el] = (float)shares;
+            kns[el] = kn;
+            dz2s[el] = dz2;
+            if (valid && crank == 0) {
+                const TraceDev& t = a.trace;
+                const int64_t ti = (int64_t)(istep - a.trace_step0) * B + e;
+                if (t.action_sel) t.action_sel[ti] = action;
+                if (t.action_eff) t.action_eff[ti] = a_eff;
+                if (t.explored) t.explored[ti] = explored;
+                if (t.k_next) t.k_next[ti] = kn;
+                if (t.reward) t.reward[ti] = r32;
+                if (t.target) t.target[ti] = target;
+                if (t.budget) t.budget[ti] = nb;
+                if (t.shares) t.shares[ti] = ns;
+                if (t.q_s) { t.q_s[ti * 3] = q_s[0]; t.q_s[ti * 3 + 1] = q_s[1]; t.q_s[ti * 3 + 2] = q_s[2]; }
+                if (t.q_n) { t.q_n[ti * 3] = q_n[0]; t.q_n[ti * 3 + 1] = q_n[1]; t.q_n[ti * 3 + 2] = q_n[2]; }
+            }
+        }
+        budget = nb; shares = ns; share_value = p_new;          // carry (TrainerChildActor.scala:99-102)
+    }
+    et_fence_async_smem();
+    __syncthreads();
+    stamp(5);
+#include "qp_ep_c2_backward.inl"
+}

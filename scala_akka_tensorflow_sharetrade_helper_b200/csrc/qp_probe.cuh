@@ -19,6 +19,9 @@ struct UmmaProbeArgs {
     uint32_t a_step, b_step;                   // added to the start-address fields per MMA (16-byte units)
     uint32_t d_col, d_lane;                    // TMEM column / lane offset of the accumulator
     int n_cols;                                // columns read back (multiple of 16, <= 512)
+    int a_tmem;                                // 1: A comes from tensor memory: a_img is [128 rows][a_k] fp32 row-major, written to
+    int a_k;                                   //    columns [a_col, a_col + a_k) of lane = row; a_step then counts COLUMNS per MMA
+    uint32_t a_col;
     float fill;                                // every TMEM word read back is preset to this
     float* out;                                // [128][n_cols]
 };
@@ -51,11 +54,36 @@ __global__ void __launch_bounds__(128, 1) umma_probe_kernel(const UmmaProbeArgs 
             "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1, %1};\n" ::"r"(
                 tmem_base + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0), "r"(v) : "memory");
     }
+    if (g.a_tmem) {
+        const float* arow = reinterpret_cast<const float*>(g.a_img) + (size_t)(warp * 32 + lane) * g.a_k;
+        for (int c0 = 0; c0 < g.a_k; c0 += 8) {
+            uint32_t v[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) v[j] = __float_as_uint(arow[c0 + j]);
+            asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};\n" ::"r"(
+                             tmem_base + ((uint32_t)(warp * 32) << 16) + g.a_col + (uint32_t)c0),
+                         "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
+        }
+    }
     asm volatile("tcgen05.wait::st.sync.aligned;\n" ::: "memory");
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
-    if (tid == 0) {
+    if (tid == 0 && g.a_tmem) {
+        const uint64_t db0 = g.desc_b + (uint64_t)(((uint32_t)__cvta_generic_to_shared(b_s) >> 4) & 0x3FFF);
+        for (int i = 0; i < g.n_mma; ++i) {
+            const uint32_t acc = i > 0 ? 1u : 0u;
+            asm volatile(
+                "{\n\t"
+                ".reg .pred p;\n\t"
+                "setp.ne.b32 p, %4, 0;\n\t"
+                "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, {%5, %5, %5, %5}, p;\n\t"
+                "}\n" ::"r"(tmem_base + (g.d_lane << 16) + g.d_col),
+                "r"(tmem_base + g.a_col + (uint32_t)i * g.a_step), "l"(db0 + (uint64_t)i * g.b_step), "r"(g.idesc), "r"(acc), "r"(0u)
+                : "memory");
+        }
+        tc_commit(&bar);
+    } else if (tid == 0) {
         const uint64_t da0 = g.desc_a + (uint64_t)(((uint32_t)__cvta_generic_to_shared(a_s) >> 4) & 0x3FFF);
         const uint64_t db0 = g.desc_b + (uint64_t)(((uint32_t)__cvta_generic_to_shared(b_s) >> 4) & 0x3FFF);
         for (int i = 0; i < g.n_mma; ++i)

@@ -31,6 +31,8 @@ class Tally:
         self.forced_actions = 0
         self.forced_knext = 0
         self.grad_checked = 0
+        self.kink_columns = 0
+        self.grad_err_vs_twin = []      # (device, fp32 oracle) relative Frobenius distance from the fp64 twin
 
     def assert_mostly_unforced(self, max_frac=0.02):
         assert self.steps > 0 and self.grad_checked == self.steps, "a teacher-forced step was not compared in full"
@@ -91,7 +93,45 @@ def teacher_forced_step(cfg, o, pol, prices, soe, i, what, tally=None, n_terms=1
 
     # ---- gradient sum, AdaGrad (QDecisionPolicyActor.scala:49-50, :73), carry
     g = pol.last_grad()
-    _tol.assert_grad_close(g, ref["grad"], what + " grad", n_terms=n_terms)
+    # The gradient is discontinuous where a hidden unit sits on its ReLU kink (ReluGrad passes where the output is
+    # strictly positive): a unit whose pre-activation is within fp32 rounding of zero for some episode may be masked
+    # differently by two correct implementations, which moves that column of dW1 by a whole episode's contribution.
+    # Such columns (rare; counted) are left out of the gradient comparison.
+    D, H = cfg.D, cfg.hidden
+    x64 = x.astype(np.float64)
+    W1 = w[:D * H].astype(np.float64).reshape(D, H)
+    z = x64 @ W1 + cfg.bias
+    zc = np.abs(x64) @ np.abs(W1) + abs(cfg.bias)
+    kink = (np.abs(z) <= 1e-6 * zc).any(axis=0)
+    keep = np.ones(cfg.P, bool)
+    keep[:D * H] = np.tile(~kink, D)
+    assert kink.sum() <= max(2, H // 50), f"{what}: {kink.sum()} hidden units on their ReLU kink"
+    g_cmp, ref_cmp = np.where(keep, g, 0.0), np.where(keep, ref["grad"], 0.0)
+    if n_terms >= 2048:
+        # Thousands of episodes: the oracle adds the episodes' gradients one after the other in fp32 (the device adds
+        # in a tree), and with the reference's unscaled N(0,1) weights dq = 2 (q - target) inherits the fp32 rounding of
+        # Q itself (|Q| ~ 1e4 from terms of 1e6).  What "fp32-grade" means for such a sum is therefore MEASURED: the
+        # fp32 oracle against its fp64 twin (same imposed choices); the device must be within the stated tolerance of
+        # the twin, or within twice the fp32 oracle's own distance from it.
+        o64 = O.Oracle(cfg, dtype=np.float64, params=w, acc=acc)
+        ev = o.env
+        o64.env_create(ev["prices"], ev["soe"], ev["B0"], ev["N0"], env_id_base=ev["base"])
+        o64.env["budget"][:], o64.env["shares"][:], o64.env["share_value"][:], o64.env["step"] = b, s, v, i
+        r64 = o64.env_step(1, trace=True, want_grad=True, force_action=tr["action_sel"], force_knext=tr["k_next"])[0]
+        g64 = np.where(keep, r64["grad"], 0.0)
+        nrm, m64 = np.linalg.norm(g64), np.abs(g64).max()
+        e32_fro = np.linalg.norm(ref_cmp - g64) / nrm
+        e32_max = np.abs(ref_cmp - g64).max()
+        dev_fro = np.linalg.norm(g_cmp - g64) / nrm
+        dev_max = np.abs(g_cmp - g64).max()
+        assert dev_fro <= max(_tol.GRAD_FRO, 2 * e32_fro), \
+            f"{what} grad vs fp64 twin: relative Frobenius error {dev_fro:.3g} (fp32 oracle: {e32_fro:.3g})"
+        assert dev_max <= max(_tol.GRAD_RTOL * m64, 2 * e32_max), \
+            f"{what} grad vs fp64 twin: max |dg| {dev_max:.3g} (fp32 oracle: {e32_max:.3g}, max |g| {m64:.3g})"
+        if tally is not None:
+            tally.grad_err_vs_twin.append((float(dev_fro), float(e32_fro)))
+    else:
+        _tol.assert_grad_close(g_cmp, ref_cmp, what + " grad", n_terms=n_terms)
     p, a = pol.get_weights()
     # (1) the device's AdaGrad step applied to the device's own gradient sum: the oracle's arithmetic bit for bit
     chk = O.Oracle(cfg, params=w, acc=acc)
@@ -101,7 +141,7 @@ def teacher_forced_step(cfg, o, pol, prices, soe, i, what, tally=None, n_terms=1
     # (2) against the oracle's weights, where the sign of the gradient element is beyond doubt (with the
     # reference's 1e-8 initial accumulator the first step is lr * sign(g), whatever the magnitude of g)
     m = np.abs(ref["grad"]).max()
-    stable = np.abs(ref["grad"]) > 10 * _tol.GRAD_RTOL * m
+    stable = (np.abs(ref["grad"]) > 10 * _tol.GRAD_RTOL * m) & keep
     if stable.any():
         assert np.abs(p[stable] - o.params[stable]).max() <= _tol.W_ATOL, what + " weights"
     if check_state:
@@ -115,4 +155,5 @@ def teacher_forced_step(cfg, o, pol, prices, soe, i, what, tally=None, n_terms=1
         tally.forced_actions += int(n_act)
         tally.forced_knext += int(n_k)
         tally.grad_checked += 1
+        tally.kink_columns += int(kink.sum())
     return tr, ref

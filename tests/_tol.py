@@ -13,7 +13,12 @@ import numpy as np
 Q_RTOL = 1e-4
 Q_COND = 1e-7
 GRAD_RTOL = 1e-4     # per element, relative to max|g| of the update
-GRAD_FRO = 1e-5      # relative Frobenius norm of the gradient difference
+GRAD_FRO = 3e-5      # relative Frobenius norm of the gradient difference.  Calibration (tests/test_gpu_parity.py::
+                     # test_bench_regime_unscaled_weights_teacher_forced prints it): against the fp64 twin the fp32 oracle sits at
+                     # 0.6e-6 .. 1.5e-6; the FFMA kernels at the same level; the tcgen05 kernels at 0.9e-6 .. 1.1e-5 with the
+                     # reference's unscaled N(0,1) weights (the tensor core's fp32 accumulation truncates instead of rounding, and
+                     # dq = 2 (q - target) carries Q's relative error straight into the gradient).  The bound is 3x the worst seen
+                     # and 3x inside what the Q tolerance (1e-4 relative) already concedes.
 W_ATOL = 2e-5        # weights after one AdaGrad step (lr 0.01: a full step is 1e-2)
 
 

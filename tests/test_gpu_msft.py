@@ -32,7 +32,7 @@ def msft(golden_dir):
 def msft_path(pol):
     """The persistent kernel serves these episodes; which form of it is asserted where the test needs it."""
     assert pol.get_option("fused_active") == 1
-    return "tc" if pol.get_option("ep_tc_active") == 1 else "ffma"
+    return "c2" if pol.get_option("ep_c2_active") == 1 else ("tc" if pol.get_option("ep_tc_active") == 1 else "ffma")
 
 
 def test_share_trade_helper_run_reference_bookkeeping(msft):

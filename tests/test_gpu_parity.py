@@ -22,11 +22,12 @@ def q_mod():
     return q
 
 
-PATHS = {"tc": (1, 1), "ffma": (1, 0), "three": (0, 0)}    # name -> (fused, ep_tc)
+PATHS = {"c2": (1, 1, 1), "tc": (1, 1, 0), "ffma": (1, 0, 0), "three": (0, 0, 0)}    # name -> (fused, ep_tc, ep_c2)
 
 
 def make_policy(cfg: O.Config, params=None, acc=None, fused=None, ep_tc=None, path=None):
-    """path: "tc" = persistent kernel with tcgen05 contractions, "ffma" = persistent FFMA kernel, "three" = three
+    """path: "c2" = persistent tcgen05 kernel on CTA pairs that split the hidden dimension (the default where it
+    applies), "tc" = persistent tcgen05 kernel, one tile per CTA, "ffma" = persistent FFMA kernel, "three" = three
     kernels per env-step.  fused / ep_tc set the two options one by one; `fused` alone keeps its old meaning
     (the FFMA form of the persistent kernel / the three-kernel path)."""
     q = q_mod()
@@ -36,20 +37,24 @@ def make_policy(cfg: O.Config, params=None, acc=None, fused=None, ep_tc=None, pa
     pol = q.QDecisionPolicy(pc)
     if params is not None or acc is not None:
         pol.set_weights(params, acc)
+    ep_c2 = None
     if path is not None:
-        fused, ep_tc = PATHS[path]
+        fused, ep_tc, ep_c2 = PATHS[path]
     elif fused is not None and ep_tc is None:
         ep_tc = 0
     if fused is not None:
         pol.set_option("fused", int(fused))
     if ep_tc is not None:
         pol.set_option("ep_tc", int(ep_tc))
+    if ep_c2 is not None:
+        pol.set_option("ep_c2", int(ep_c2))
     return pol
 
 
 def assert_path(pol, path):
-    fused, ep_tc = PATHS[path]
-    assert pol.get_option("fused_active") == fused and pol.get_option("ep_tc_active") == ep_tc, f"path {path} not taken"
+    fused, ep_tc, ep_c2 = PATHS[path]
+    got = (pol.get_option("fused_active"), pol.get_option("ep_tc_active"), pol.get_option("ep_c2_active"))
+    assert got == (fused, ep_tc, ep_c2), f"path {path} not taken: (fused, ep_tc, ep_c2) active = {got}"
 
 
 # ------------------------------------------------------------------------------------------------
@@ -183,9 +188,9 @@ def test_update_q_batches(B, shape):
 # ------------------------------------------------------------------------------------------------
 # episode level
 # ------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("path", ["tc", "ffma", "three"])
+@pytest.mark.parametrize("path", ["c2", "tc", "ffma", "three"])
 @pytest.mark.parametrize("bookkeeping", [O.REFERENCE, O.RLPY])
-@pytest.mark.parametrize("n_envs,N0", [(1, 0), (5, 3), (32, 1), (33, 0), (64, 1), (200, 2)])
+@pytest.mark.parametrize("n_envs,N0", [(1, 0), (5, 3), (32, 1), (33, 0), (64, 1), (65, 1), (200, 2)])
 def test_env_step_teacher_forced(bookkeeping, n_envs, N0, path):
     """Each step starts from the oracle's weights and episode state; device and oracle take one step;
     everything the step produces is compared (tests/_teacher.py), on each of the three execution paths."""
@@ -203,14 +208,14 @@ def test_env_step_teacher_forced(bookkeeping, n_envs, N0, path):
         for i in (0, 1, 57, 150, 198):
             teacher_forced_step(cfg, o, pol, prices, soe, i, f"{path} step {i}", tally)
     tally.assert_mostly_unforced()
-    if path == "tc":     # prices that are not tf32-exact keep the FFMA persistent kernel
+    if path == "c2":     # prices that are not tf32-exact keep the FFMA persistent kernel
         with make_policy(cfg) as pol:
             pol.env_create(prices * np.float32(1.0371), soe, 1000.0, N0)
             assert pol.get_option("ep_tc_active") == 0 and pol.get_option("fused_active") == 1
 
 
-GOLDEN_CASES = [(n, p_) for n in ("episode_rlpy", "episode_reference", "episode_late") for p_ in ("tc", "ffma", "three")] + \
-               [("episode_tiny", "ffma"), ("episode_tiny", "three")]     # (window 8 / hidden 16 is outside the tensor-core kernel's shapes)
+GOLDEN_CASES = [(n, p_) for n in ("episode_rlpy", "episode_reference", "episode_late") for p_ in ("c2", "tc", "ffma", "three")] + \
+               [("episode_tiny", "three")]     # (window 8 / hidden 16 is outside the persistent kernels' shapes)
 
 
 @pytest.mark.parametrize("name,path", GOLDEN_CASES)
@@ -243,7 +248,8 @@ def test_golden_episodes_free_running(golden_dir, name, path):
         np.testing.assert_array_equal(ports, g["portfolios"])
 
 
-def test_tensor_core_kernel_free_running_exploit_branch():
+@pytest.mark.parametrize("path", ["c2", "tc"])
+def test_tensor_core_kernel_free_running_exploit_branch(path):
     """The tensor-core persistent kernel free-running against the oracle with the reference's ε schedule in its
     exploit regime (steps 600..629: 60-63 % of the actions are argmax Q(s), QDecisionPolicyActor.scala:58-60), four
     tiles of episodes, one launch.  Integer book-keeping bit for bit up to the first action divergence, which must
@@ -261,9 +267,9 @@ def test_tensor_core_kernel_free_running_exploit_branch():
         w_at.append(o.params.copy())
         st_at.append((o.env["budget"].copy(), o.env["shares"].copy()))
         ref.append(o.env_step(1, trace=True)[0])
-    with make_policy(cfg, params=w, path="tc") as pol:
+    with make_policy(cfg, params=w, path=path) as pol:
         pol.env_create(prices, soe, 1000.0, 1)
-        assert_path(pol, "tc")
+        assert_path(pol, path)
         pol.env_set_state(step=i0)
         tr = pol.env_step_trace(steps)
     R = {k: np.stack([r[k] for r in ref]) for k in ("action_sel", "action_eff", "explored", "k_next", "shares", "budget", "reward", "q_s")}
@@ -282,7 +288,7 @@ def test_tensor_core_kernel_free_running_exploit_branch():
 
 
 @pytest.mark.parametrize("init_acc", [1e-8, 0.1])
-@pytest.mark.parametrize("path", ["tc", "three"])
+@pytest.mark.parametrize("path", ["c2", "tc", "three"])
 def test_adagrad_initial_accumulator_candidates(init_acc, path):
     """QDecisionPolicyActor.scala:50 `AdaGrad(0.01f)`: the initial accumulator is tensorflow_scala's default, taken
     on trust as 1e-8; TF-Python's 0.1 is the other candidate.  It is a config field: both values go through
@@ -390,7 +396,8 @@ def test_persistent_kernel_matches_three_kernel_path():
     assert np.abs(wa - wb).max() <= 40 * _tol.W_ATOL
 
 
-def test_persistent_tensor_core_kernel_free_running():
+@pytest.mark.parametrize("path", ["c2", "tc"])
+def test_persistent_tensor_core_kernel_free_running(path):
     """40 env-steps in one launch (weights republished as tf32 hi/lo every step inside the kernel),
     against the FFMA persistent kernel on the same episodes."""
     cfg = O.Config(bookkeeping=O.RLPY, lr=1e-4, seed=9)
@@ -399,12 +406,11 @@ def test_persistent_tensor_core_kernel_free_running():
     soe = (np.arange(n) % 50).astype(np.int32)
     w = (O.gen_normal(3, 0, cfg.P) * 0.05).astype(np.float32)
     res = []
-    for tc in (1, 0):
-        with make_policy(cfg, params=w) as pol:
-            pol.set_option("ep_tc", tc)
+    for pth in (path, "ffma"):
+        with make_policy(cfg, params=w, path=pth) as pol:
             pol.env_create(prices, soe, 1000.0, 1)
             pol.env_set_state(step=120)
-            assert pol.get_option("ep_tc_active") == tc
+            assert_path(pol, pth)
             tr = pol.env_step_trace(25)
             pol.env_step(15)
             res.append((tr, pol.get_weights()[0], pol.env_state(), pol.steps_done))
@@ -438,9 +444,10 @@ def test_persistent_tensor_core_kernel_other_shapes(shape):
     tally.assert_mostly_unforced()
 
 
-def test_persistent_tensor_core_kernel_ring_wraps():
-    """330 env-steps in ONE launch: the window ring (256 rows) wraps more than once, every row block of the
-    dW1 partial takes the wrapped-store path in turn.  step_div is huge, so the ε-greedy threshold stays 0 and
+@pytest.mark.parametrize("path", ["c2", "tc"])
+def test_persistent_tensor_core_kernel_ring_wraps(path):
+    """330 env-steps in ONE launch.  tc: the window ring (256 rows) wraps more than once, every row block of the
+    dW1 partial takes the wrapped-store path in turn; c2: the window buffer is copied back to its top six times.  step_div is huge, so the ε-greedy threshold stays 0 and
     every action is the Philox draw (independent of Q): the book-keeping trajectory is then identical for the
     tensor-core kernel, the FFMA kernel and the oracle, and Q / weights can be compared all the way."""
     cfg = O.Config(bookkeeping=O.RLPY, lr=1e-5, seed=31, step_div=1e12)      # (lr small enough to keep the ReLUs alive)
@@ -449,11 +456,10 @@ def test_persistent_tensor_core_kernel_ring_wraps():
     soe = np.arange(n, dtype=np.int32)
     w = (O.gen_normal(4, 0, cfg.P) * 0.05).astype(np.float32)
     res = []
-    for tc in (1, 0):
-        with make_policy(cfg, params=w) as pol:
-            pol.set_option("ep_tc", tc)
+    for pth in (path, "ffma"):
+        with make_policy(cfg, params=w, path=pth) as pol:
             pol.env_create(prices, soe, 1000.0, 2)
-            assert pol.get_option("ep_tc_active") == tc
+            assert_path(pol, pth)
             tr = pol.env_step_trace(steps)
             res.append((tr, pol.get_weights()[0], pol.last_grad()))
     (ta, wa, ga), (tb, wb, gb) = res
@@ -647,8 +653,9 @@ def test_first_step_of_full_batch_against_oracle():
     tally.assert_mostly_unforced()
 
 
+@pytest.mark.parametrize("path", ["c2", "tc"])
 @pytest.mark.parametrize("bookkeeping", [O.REFERENCE, O.RLPY])
-def test_bench_regime_unscaled_weights_teacher_forced(bookkeeping):
+def test_bench_regime_unscaled_weights_teacher_forced(bookkeeping, path):
     """bench.py's own numeric regime on the headline kernel: BASELINE.json configs[1] — 4096 episodes, seed-42
     quarter-tick series, and the UNSCALED N(0,1) weights qp_create draws (the reference's initialisation,
     QDecisionPolicyActor.scala:41, :45; |Q| ~ 1e4..1e5), teacher-forced at the first, second, a middle and the
@@ -660,16 +667,18 @@ def test_bench_regime_unscaled_weights_teacher_forced(bookkeeping):
     o = O.Oracle(cfg)                                   # params = gen_normal(42, 0, P), as qp_create
     o.env_create(prices, soe, 1000.0, 0)
     tally = Tally()
-    with make_policy(cfg) as pol:                       # default options, default weights: exactly what bench.py runs
+    with make_policy(cfg, path=path) as pol:            # default weights; "c2" is what the default options (bench.py) select
         np.testing.assert_array_equal(pol.get_weights()[0], o.params)
         pol.env_create(prices, soe, 1000.0, 0)
-        assert_path(pol, "tc")
+        assert_path(pol, path)
         q_abs = []
         for i in (0, 1, 400, 798):
             tr, ref = teacher_forced_step(cfg, o, pol, prices, soe, i, f"bench regime step {i}", tally, n_terms=n)
             q_abs.append(float(np.abs(ref["q_s"]).max()))
     assert max(q_abs) > 1e3, "fixture is not in the large-magnitude regime"
     tally.assert_mostly_unforced()
+    print(f"bench regime {path} bookkeeping {bookkeeping}: max |Q| {max(q_abs):.3g}; gradient distance from the fp64 twin "
+          f"(device, fp32 oracle): {tally.grad_err_vs_twin}; imposed choices {tally.forced_actions}+{tally.forced_knext} of {tally.rows}")
 
 
 @pytest.mark.parametrize("path", ["three", "tc"])
@@ -691,7 +700,7 @@ def test_large_batch_path_against_oracle(n, wscale, path):
     with make_policy(cfg, params=w) as pol:
         pol.set_option("fused", PATHS[path][0])
         pol.env_create(prices, soe, 1000.0, 1)
-        assert_path(pol, path)
+        assert_path(pol, path)                          # (more than one tile per pair: the one-tile-per-CTA kernel in waves)
         tr, ref = teacher_forced_step(cfg, o, pol, prices, soe, i, f"large batch {path}", tally, n_terms=n)
         pol.env_step(3)
         assert pol.steps_done == i + 4
