@@ -31,3 +31,6 @@ print("  A tile kk built (bw 0):", [round(rel(32 + k)) for k in range(7)])
 print("  MMA: A tile kk ready  :", [round(rel(16 + k)) for k in range(7)])
 print("  MMA: W tile kk ready  :", [round(rel(8 + k)) for k in range(7)])
 print("  last commit issued    :", round(rel(40)), "  forward complete seen by thread 0:", round(rel(41)))
+
+d = lambda a, b: round((c[:, b] - c[:, a]).mean())
+print("  S6 (thread 0): combine", d(52, 53), " boxes", d(53, 54), " next price", d(54, 55), " barrier", d(55, 58), "; warp 11 boxes", d(56, 57))

@@ -701,15 +701,16 @@ int ep_c2_prepare(qp_handle* h) {
     // the window buffer holds kC2Slide rows of slack behind window element wn + 1; the copy-back moves (wn + 1) * 16
     // float4 with 12 per thread; the epilogue stages 8 KB per warp over regA + regW; Nh <= 128 TMEM columns per accumulator
     if (hp.wn + 2 + kC2Slide > kC2Rows || (hp.wn + 1) * 16 > 12 * kC2Threads || Nh > 128 || 2 * Hh > kC2Threads ||
-        sm.regA_bytes + sm.regW_bytes < (size_t)kC2Warps * 8192 || sm.total + 1024 > (size_t)h->max_smem || grid < 8)
+        sm.total + 1024 > (size_t)h->max_smem || grid < 8)
         return QP_OK;
     {   // phase B's bulk-copy branch must apply (the kernel has no other)
         const int n_w1 = std::max(1, grid - 2);
         const int chunk = (int)(((h->P1 + n_w1 - 1) / n_w1 + 3) & ~(int64_t)3);
         const int chunk2 = ((3 * hp.H + 1) / 2 + 3) & ~3;
         const int pitch = std::max(chunk, chunk2);
-        const int rows_cap = std::min(128, (int)((sm.regA_bytes + sm.regW_bytes) / ((size_t)pitch * 4)) & ~3);
-        if (pitch > kC2Threads || rows_cap < 4) return QP_OK;
+        // the sum: (sub, float4 group) threads, at most 16 partials per thread; the sub sums meet in [8][pitch] floats
+        const int ng4 = pitch / 4, nsub = std::min(8, kC2Threads / std::max(1, ng4));
+        if (pitch > kC2Threads || nsub < 1 || (grid / 2 + nsub - 1) / nsub > 16 || (size_t)8 * pitch * 4 > sm.op_bytes) return QP_OK;
     }
     QP_CUDA(cudaFuncSetAttribute(episode_c2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sm.total + 1024)));
     {   // all pairs must be co-resident (cooperative launch of clusters of two)
@@ -845,11 +846,17 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
         x.ea = ea;
         x.w1T_hi = h->et_w_hi.p; x.w1T_lo = h->et_w_lo.p;
         x.Kp = h->et_Kp; x.nkb = h->et_nkb; x.Hh = h->c2_Hh; x.Nh = h->c2_Nh; x.dbg_mode = h->c2_dbg;
-        QP_TRY(h->et_published.ensure(1));
+        QP_TRY(h->et_published.ensure(2));
         x.published = h->et_published.p;
         x.p_pad = (int64_t)p2p_pad(h);
         for (int r = 0; r < ea.world && ea.world > 1; ++r)
             x.pdata[r] = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(h->p2p_peer_block[r]) + p2p_tc_offset(h));
+        if (h->want_cta_ns) {        // [n_steps][grid][8]
+            QP_TRY(h->dbg.ensure((size_t)n_steps * h->c2_grid * 8));
+            QP_CUDA(cudaMemsetAsync(h->dbg.p, 0, (size_t)n_steps * h->c2_grid * 8 * sizeof(long long), h->stream));
+            x.ea.dbg = nullptr;
+            x.cta_ns = h->dbg.p;
+        }
         if (h->want_fine) {          // fine stamps share the dbg buffer: [n_steps][64]
             QP_TRY(h->dbg.ensure((size_t)n_steps * 64));
             QP_CUDA(cudaMemsetAsync(h->dbg.p, 0, (size_t)n_steps * 64 * sizeof(long long), h->stream));
@@ -881,7 +888,7 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
             x.ea.dbg = nullptr;
             x.cta_ns = h->dbg.p;
         }
-        QP_TRY(h->et_published.ensure(1));
+        QP_TRY(h->et_published.ensure(2));
         x.published = h->et_published.p;
         x.p_pad = (int64_t)p2p_pad(h);
         for (int r = 0; r < ea.world && ea.world > 1; ++r) {

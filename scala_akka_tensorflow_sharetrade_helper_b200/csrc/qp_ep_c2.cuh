@@ -34,6 +34,7 @@ constexpr int kC2Envs = 64;             // episodes per CTA pair
 constexpr int kC2Rows = 256;            // rows of the window buffer
 constexpr int kC2Slide = 48;            // env-steps between copy-backs (a multiple of 8: the swizzle phase of a row is kept)
 constexpr int kC2AStages = 3;           // forward A operand ring: [128 rows x 32 k] tiles of 16 KB
+constexpr int kC2WStages = 3;           // W1^T ring: (hi, lo) tile pairs of 2 * Nh * 128 bytes
 constexpr int kC2Builders = 8;          // warps 2..9 transpose the A tiles
 constexpr int kC2Sub = kC2Warps / 2;    // warps per 32-episode lane group in the element-wise phases
 constexpr int kC2EStride = 65;          // padded row stride of the [column][episode] tiles
@@ -48,25 +49,32 @@ struct EpC2Args {
     unsigned long long* pdata[8];    // several GPUs: every rank's exchange block (see EpTcArgs)
     int64_t p_pad;
     int dbg_mode;                    // timing experiments (option "c2_dbg"); 0 in every real run
+    long long* cta_ns;               // tuning aid ("phase_clocks" = 2): [n_steps][gridDim][8] globaltimer stamps of every CTA
     long long* fine;                 // tuning aid ("phase_clocks" = 3): [n_steps][64] clock64 stamps inside the forward of CTA 0
 };
 
 // Shared-memory map (bytes from the 1024-aligned base); the host computes the same numbers.
+//   xt   : the window buffer, two 32-episode blocks of 256 rows x 128 bytes
+//   op   : the operand region.  Forward: A ring (kC2AStages x 16 KB) then W1^T ring (kC2WStages x 2 TBh).  Afterwards:
+//          z / h tiles at op, the twelve partial sums per warp (qpart) and then dZ1 hi / lo at op + bwd; then the
+//          epilogue's staging boxes; then phase B's stage.
 struct C2Smem {
-    size_t xt, regA, regW, tabs, w2s, wb, ws, xe, dz2s, kns, qpart, qsum, part5, bars, total;
-    size_t regA_bytes, regW_bytes, TBh;
+    size_t xt, op, op_bytes, wring, bwd, w2s, wb, ws, xe, dz2s, kns, qsum, part5, bars, total, TBh;
 };
 __host__ __device__ inline C2Smem c2_smem(int Hh, int Nh) {
     C2Smem m{};
     m.TBh = (size_t)Nh * 128;
     m.xt = 0;
-    m.regA = (size_t)2 * kC2Rows * 128;
-    size_t a = (size_t)kC2AStages * 16384, hz = (size_t)2 * Hh * kC2EStride * 4;
-    m.regA_bytes = ((a > hz ? a : hz) + 1023) & ~(size_t)1023;
-    m.regW = m.regA + m.regA_bytes;
-    m.regW_bytes = ((4 * m.TBh) + 1023) & ~(size_t)1023;
-    m.tabs = m.regW + m.regW_bytes;
-    size_t o = m.tabs;
+    m.op = (size_t)2 * kC2Rows * 128;
+    m.wring = m.op + (size_t)kC2AStages * 16384;
+    const size_t hz = (((size_t)2 * Hh * kC2EStride * 4) + 1023) & ~(size_t)1023;
+    m.bwd = m.op + hz;                                          // dZ1 hi / lo (4 TBh), qpart before them
+    size_t need = hz + 4 * m.TBh;
+    const size_t fwd = (size_t)kC2AStages * 16384 + (size_t)kC2WStages * 2 * m.TBh;
+    if (fwd > need) need = fwd;
+    if ((size_t)kC2Warps * 8192 > need) need = (size_t)kC2Warps * 8192;
+    m.op_bytes = (need + 1023) & ~(size_t)1023;
+    size_t o = m.op + m.op_bytes;
     m.w2s = o; o += (size_t)Hh * 16;
     m.wb = o; o += (size_t)Hh * 4;
     m.ws = o; o += (size_t)Hh * 4;
@@ -74,7 +82,6 @@ __host__ __device__ inline C2Smem c2_smem(int Hh, int Nh) {
     m.dz2s = o; o += kC2Envs * 4;
     m.kns = o; o += kC2Envs * 4;
     o = (o + 15) & ~(size_t)15;
-    m.qpart = o; o += (size_t)kC2Sub * 12 * kC2Envs * 4;
     m.qsum = o; o += (size_t)2 * 12 * kC2Envs * 4;
     m.part5 = o; o += (size_t)2 * 5 * Hh * 4;
     o = (o + 7) & ~(size_t)7;

@@ -25,30 +25,29 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     uint8_t* base = c2_smem_raw;
     if (tid == 0 && ((uint32_t)__cvta_generic_to_shared(base) & 1023u) != 0u) __trap();
     uint8_t* XT = base + sm.xt;                                 // [2 blocks][256 rows][32 episodes], SWIZZLE_128B by address
-    uint8_t* regA = base + sm.regA;                             // forward A ring -> z tiles -> epilogue boxes -> phase-B stage
-    uint8_t* regW = base + sm.regW;                             // W1^T ring -> dZ1 hi / lo -> epilogue boxes -> phase-B stage
+    uint8_t* regA = base + sm.op;                               // the operand region: forward A ring ...
+    uint8_t* regW = base + sm.wring;                            // ... and W1^T ring; then (see c2_smem):
     float* HS = reinterpret_cast<float*>(regA);                 // [Hh][65]: window part of z1(s), then h(s)
     float* ZN = HS + (size_t)Hh * kC2EStride;                   // [Hh][65]: window part of z1(s')
-    uint8_t* Bbwd_hi = regW;                                    // [2 episode blocks][Nh x 32]
-    uint8_t* Bbwd_lo = regW + 2 * (size_t)TBh;
+    uint8_t* Bbwd_hi = base + sm.bwd;                           // [2 episode blocks][Nh x 32]
+    uint8_t* Bbwd_lo = Bbwd_hi + 2 * (size_t)TBh;
     float* W2s = reinterpret_cast<float*>(base + sm.w2s);       // [Hh] float4
     float* Wb = reinterpret_cast<float*>(base + sm.wb);
     float* Ws = reinterpret_cast<float*>(base + sm.ws);
     float* XE = reinterpret_cast<float*>(base + sm.xe);         // [2][64]
     float* dz2s = reinterpret_cast<float*>(base + sm.dz2s);
     int* kns = reinterpret_cast<int*>(base + sm.kns);
-    float* qpart = reinterpret_cast<float*>(base + sm.qpart);   // [6 warps of a lane group][12][64]
+    float* qpart = reinterpret_cast<float*>(base + sm.bwd);     // [6 warps of a lane group][12][64] (consumed before dZ1 is written)
     float* qsum = reinterpret_cast<float*>(base + sm.qsum);     // [2 CTAs of the pair][12][64]
     float* part5 = reinterpret_cast<float*>(base + sm.part5);   // [2 lane groups][5][Hh]
     uint64_t* bars = reinterpret_cast<uint64_t*>(base + sm.bars);
-    uint64_t* w_full = bars;            // [2]
-    uint64_t* w_empty = bars + 2;       // [2]
-    uint64_t* a_full = bars + 4;        // [3]
-    uint64_t* a_empty = bars + 7;       // [3]
-    uint64_t* tf_fwd = bars + 10;
-    uint64_t* tf_bwd = bars + 11;
-    uint64_t* pb_bar = bars + 12;       // [4]
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 16);
+    uint64_t* w_full = bars;            // [kC2WStages <= 4]
+    uint64_t* w_empty = bars + 4;       // [kC2WStages]
+    uint64_t* a_full = bars + 8;        // [kC2AStages <= 4]
+    uint64_t* a_empty = bars + 12;      // [kC2AStages]
+    uint64_t* tf_fwd = bars + 16;
+    uint64_t* tf_bwd = bars + 17;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 22);
 
     const uint32_t crank = c2_cluster_rank();                   // which half of the hidden columns
     const int c0 = (int)crank * Hh;                             // first hidden column of this CTA
@@ -67,10 +66,9 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     const int q4 = warp & 3, part = warp >> 2;                  // TMEM lane quarter / column part of this warp
 
     if (tid == 0) {
-        mbar_init(w_full, 1); mbar_init(w_full + 1, 1); mbar_init(w_empty, 1); mbar_init(w_empty + 1, 1);
+        for (int s = 0; s < kC2WStages; ++s) { mbar_init(w_full + s, 1); mbar_init(w_empty + s, 1); }
         for (int s = 0; s < kC2AStages; ++s) { mbar_init(a_full + s, kC2Builders); mbar_init(a_empty + s, 1); }
         mbar_init(tf_fwd, 1); mbar_init(tf_bwd, 1);
-        for (int i = 0; i < 4; ++i) mbar_init(pb_bar + i, 1);
         mbar_fence_init();
     }
     if (warp == 2) {
@@ -78,7 +76,7 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
                          (uint32_t)__cvta_generic_to_shared(tmem_slot)), "r"(512u) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
     }
-    for (size_t i = tid; i < sm.tabs / 16; i += nthreads) reinterpret_cast<float4*>(base)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (size_t i = tid; i < (sm.op + sm.op_bytes) / 16; i += nthreads) reinterpret_cast<float4*>(base)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     double budget = a.budget[ec], share_value = a.share_value[ec];
     int32_t shares = a.shares[ec];
     const float* my_row = a.prices + (int64_t)a.series_of_env[ec] * a.T;
@@ -120,15 +118,23 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     const int chunk = (int)(((P1 + n_w1_ctas - 1) / n_w1_ctas + 3) & ~(int64_t)3);
     const int chunk2 = ((3 * H + 1) / 2 + 3) & ~3;
     const int pitch = max(chunk, chunk2);
-    const int rows_cap = min(128, (int)((sm.regA_bytes + sm.regW_bytes) / ((size_t)pitch * 4)) & ~3);
-    if (!(gridDim.x >= 8 && pitch <= nthreads && rows_cap >= 4 && x.published != nullptr)) __trap();
+    if (!(gridDim.x >= 8 && pitch <= nthreads && x.published != nullptr)) __trap();        // (the host has checked)
     const int n_publishers = (int)((P1 + chunk - 1) / chunk) + 2;
-    if (blockIdx.x == 0 && tid == 0) *x.published = 0ull;
+    // this CTA's share of the parameters and this thread's parameter (phase B)
+    const bool w2_cta = (int)blockIdx.x >= (int)gridDim.x - 2;
+    const float* pb_src = w2_cta ? a.dw2_part : ea.part1;
+    const int64_t pb_stride = w2_cta ? 3 * (int64_t)H : P1;
+    const int64_t pb_off = w2_cta ? (int64_t)((int)blockIdx.x - ((int)gridDim.x - 2)) * chunk2 : (int64_t)blockIdx.x * chunk;
+    const int64_t pb_p0 = w2_cta ? P1 + pb_off : pb_off;
+    const int pb_len = (int)max((int64_t)0, min((int64_t)(w2_cta ? chunk2 : chunk), pb_stride - pb_off));
+    float pb_w = 0.0f, pb_a = 0.0f, pb_g = 0.0f;
+    if (tid < pb_len) { pb_a = ea.acc[pb_p0 + tid]; pb_w = ea.params_rw[pb_p0 + tid]; }
+    if (blockIdx.x == 0 && tid == 0) { x.published[0] = 0ull; x.published[1] = 0ull; }
     __threadfence();
     grid.sync();
 
     const uint32_t idesc = tc_instr_desc(128, Nh);
-    uint32_t ring_it = 0, a_it = 0, pb_phase = 0, mma_it = 0;
+    uint32_t ring_it = 0, a_it = 0, mma_it = 0;
     const int kb_first = (int)(blockIdx.x % (unsigned)nkb);
     float* out = ea.part1 + (size_t)pair * ((size_t)D * H);
     float* out2 = a.dw2_part + (size_t)pair * (3 * H);
@@ -137,6 +143,14 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         const int32_t istep = ea.step0 + sidx;
         const int roff = sidx % kC2Slide;                       // row of window element 0
         auto stamp = [&](int i) { if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + i] = clock64(); };
+        auto cta_stamp = [&](int i) {
+            if (x.cta_ns && tid == 0) {
+                unsigned long long t;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                x.cta_ns[((size_t)sidx * gridDim.x + blockIdx.x) * 8 + i] = (long long)t;
+            }
+        };
+        cta_stamp(0);
         stamp(0);
         if (has_tile) {
 #include "qp_ep_c2_phaseA.inl"
@@ -145,13 +159,28 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         if (!ea.apply_in_kernel) { et_bulk_wait_all(); break; }
         et_bulk_wait_all();                                     // the partial is in global memory
         stamp(8);
+        cta_stamp(4);
+        // ---- grid barrier: every partial is complete.  One release-add per CTA on a counter that only grows, one
+        // acquiring poller per CTA (cooperative_groups' grid.sync took 1.8 us from the last arrival; this takes about 1).
         __threadfence();
-        grid.sync();
+        __syncthreads();
+        if (tid == 0) {
+            asm volatile("red.release.gpu.global.add.u64 [%0], %1;" ::"l"(x.published + 1), "l"(1ull) : "memory");
+            et_wait_count(x.published + 1, (unsigned long long)(sidx + 1) * (unsigned long long)gridDim.x);
+        }
+        __syncthreads();
         stamp(9);
+        cta_stamp(5);
 #include "qp_ep_c2_phaseB.inl"
         stamp(10);
+        cta_stamp(7);
     }
 
+    if (ea.apply_in_kernel && tid < pb_len) {                   // weights, accumulators and the last gradient sum go home
+        ea.params_rw[pb_p0 + tid] = pb_w;
+        ea.acc[pb_p0 + tid] = pb_a;
+        ea.grad[pb_p0 + tid] = pb_g;
+    }
     if (has_tile && crank == 0 && wsub == 0 && valid) {
         a.budget[e] = budget;
         a.shares[e] = shares;

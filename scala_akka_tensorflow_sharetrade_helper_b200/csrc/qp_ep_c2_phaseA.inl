@@ -34,15 +34,13 @@
     uint32_t rnd[4] = {0u, 0u, 0u, 0u};
 
     // ---- S0 / S1: forward contraction Z[128, Nh] = X[128, Kp] · W1[Kp, this CTA's columns] on the tensor core.
-    // Roles: warp 0 feeds the W1^T ring (and loads the small tables), warp 1 issues the MMAs, warps 2..9 transpose the
-    // A tiles out of the window buffer; the A tiles do not depend on the weights, so the builders run ahead of the
-    // split barrier.
+    // Roles: warp 0 feeds the W1^T ring by TMA, warp 1 issues the MMAs, warps 2..9 transpose the A tiles out of the
+    // window buffer (they do not depend on the weights and run ahead of the split barrier), warp 10 loads the small tables.
     auto fine = [&](int i) { if (x.fine && blockIdx.x == 0) x.fine[(size_t)sidx * 64 + i] = clock64(); };   // tuning aid
-    const int dbgm = x.dbg_mode;      // timing experiments only (results are wrong when non-zero): 1 no W stream, 2 no A build, 4 no MMA
+    if (tid == 0) fine(48);
     auto push_w_tiles = [&](int kk) {
-        if (dbgm & 1) return;
         const int kb = (kk + kb_first) % nkb;
-        const uint32_t it = ring_it + (uint32_t)kk, s = it & 1u, ph = (it >> 1) & 1u;
+        const uint32_t it = ring_it + (uint32_t)kk, s = it % kC2WStages, ph = (it / kC2WStages) & 1u;
         tc_wait(w_empty + s, ph ^ 1u);
         fine(kk);
         uint8_t* st = regW + (size_t)s * 2 * TBh;
@@ -55,9 +53,10 @@
             // the new weights are complete once every publisher of the previous step is through
             if (sidx > 0) et_wait_count(x.published, (unsigned long long)sidx * (unsigned long long)n_publishers);
             fence_proxy_async();                                // phase-B writes of W1^T -> TMA reads
-            for (int kk = 0; kk < min(2, nkb); ++kk) push_w_tiles(kk);
+            for (int kk = 0; kk < min(kC2WStages, nkb); ++kk) push_w_tiles(kk);
             stamp(1);                                           // (the wait for the other CTAs' phase B ends here)
-            for (int kk = 2; kk < nkb; ++kk) push_w_tiles(kk);
+            cta_stamp(1);
+            for (int kk = kC2WStages; kk < nkb; ++kk) push_w_tiles(kk);
         }
         __syncwarp();
     } else if (warp == 1) {
@@ -65,11 +64,10 @@
             bool first = true;
             for (int kk = 0; kk < nkb; ++kk) {
                 const int kb = (kk + kb_first) % nkb;
-                const uint32_t it = ring_it + (uint32_t)kk, s = it & 1u, ph = (it >> 1) & 1u;
+                const uint32_t it = ring_it + (uint32_t)kk, s = it % kC2WStages, ph = (it / kC2WStages) & 1u;
                 const uint32_t ait = a_it + (uint32_t)kk, sa = ait % kC2AStages, pha = (ait / kC2AStages) & 1u;
-                if (!(dbgm & 2)) tc_wait(a_full + sa, pha);
-                fine(16 + kk);
-                if (!(dbgm & 1)) tc_wait(w_full + s, ph);
+                tc_wait(a_full + sa, pha);
+                tc_wait(w_full + s, ph);
                 fine(8 + kk);
                 tc_fence_after();
                 uint8_t* st = regW + (size_t)s * 2 * TBh;
@@ -77,48 +75,58 @@
                 const uint64_t db_hi = tc_smem_desc(st), db_lo = tc_smem_desc(st + TBh);
 #pragma unroll
                 for (int k4 = 0; k4 < 4; ++k4) {
-                    if (kb * 32 + k4 * 8 < wn && !(dbgm & 4)) {    // (the columns past the window are zero on both sides)
+                    if (kb * 32 + k4 * 8 < wn) {                // (the columns past the window are zero on both sides)
                         tc_mma_tf32(tmem_base, da + 2 * k4, db_hi + 2 * k4, idesc, first ? 0u : 1u);
                         tc_mma_tf32(tmem_base, da + 2 * k4, db_lo + 2 * k4, idesc, 1u);
                         first = false;
                     }
                 }
-                if (!(dbgm & 1)) tc_commit(w_empty + s);
-                if (!(dbgm & 2)) tc_commit(a_empty + sa);
+                tc_commit(w_empty + s);
+                tc_commit(a_empty + sa);
             }
             tc_commit(tf_fwd);
             fine(40);
         }
         __syncwarp();                                           // (the other lanes park here instead of polling beside the issuer)
     } else if (warp < 2 + kC2Builders) {
+        // Each builder warp owns four (s or s', lane group, 16-byte chunk) items of every k-block.  Row r of a block sits
+        // at r * 128 with its 16-byte chunks XOR-ed by (r & 7); rows roff + k + half for consecutive k: the byte offset
+        // of the first k-block's element is precomputed per item and element, a k-block further is 32 rows = 4096 bytes.
         const int bw = warp - 2;
-        for (int kk = 0; kk < ((dbgm & 2) ? 0 : nkb); ++kk) {
+        uint32_t src[4][4], dsto[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int item = bw + kC2Builders * i;
+            const int half = item & 1, eg = (item >> 1) & 1, ch = item >> 2;
+#pragma unroll
+            for (int j = 0; j < 4; ++j)
+                src[i][j] = (uint32_t)__cvta_generic_to_shared(XT + (size_t)eg * 32768) + et_swz(roff + ch * 4 + j + half, lane);
+            const int row = half * 64 + eg * 32 + lane;
+            dsto[i] = (uint32_t)row * 128u + (uint32_t)((ch ^ (row & 7)) << 4);
+        }
+        for (int kk = 0; kk < nkb; ++kk) {
             const int kb = (kk + kb_first) % nkb;
             const uint32_t ait = a_it + (uint32_t)kk, sa = ait % kC2AStages, pha = (ait / kC2AStages) & 1u;
             if (lane == 0) tc_wait(a_empty + sa, pha ^ 1u);
             __syncwarp();
-            if (bw == 0 && lane == 0) fine(24 + kk);
-            uint8_t* At = regA + (size_t)sa * 16384;
+            const uint32_t At = (uint32_t)__cvta_generic_to_shared(regA + (size_t)sa * 16384);
+            // rows past the window hold old prices (finite) and meet zero columns of W1^T: no masking; the last rows
+            // read stay inside the block (roff + 223 + 1 < 256 + ... see kC2Slide)
 #pragma unroll
-            for (int i = 0; i < 32 / kC2Builders; ++i) {        // (s or s', lane group, 16-byte chunk of the k-block)
-                const int item = bw + kC2Builders * i;
-                const int half = item & 1, eg = (item >> 1) & 1, ch = item >> 2;
-                const int kbase = kb * 32 + ch * 4;
-                const uint8_t* blk = XT + (size_t)eg * 32768;
-                float vv[4];
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    vv[j] = kbase + j < wn ? *reinterpret_cast<const float*>(blk + et_swz(roff + kbase + j + half, lane)) : 0.0f;
-                const int row = half * 64 + eg * 32 + lane;
-                *reinterpret_cast<float4*>(At + (size_t)row * 128 + ((ch ^ (row & 7)) << 4)) = make_float4(vv[0], vv[1], vv[2], vv[3]);
+            for (int i = 0; i < 4; ++i) {
+                uint32_t v0, v1, v2, v3;
+                const uint32_t o = (uint32_t)kb * 4096u;
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v0) : "r"(src[i][0] + o));
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v1) : "r"(src[i][1] + o));
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v2) : "r"(src[i][2] + o));
+                asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v3) : "r"(src[i][3] + o));
+                asm volatile("st.shared.v4.u32 [%0], {%1, %2, %3, %4};" ::"r"(At + dsto[i]), "r"(v0), "r"(v1), "r"(v2), "r"(v3) : "memory");
             }
             et_fence_async_smem();
             __syncwarp();
             if (lane == 0) c2_mbar_arrive(a_full + sa);
-            if (bw == 0 && lane == 0) fine(32 + kk);
         }
-    }
-    else if (warp == 2 + kC2Builders) {
+    } else if (warp == 2 + kC2Builders) {
         // the small tables of this CTA's columns (W2, the budget / shares rows of W1): they need the new weights too, so
         // this warp watches the counter itself; every load is issued before the first store
         if (lane == 0 && sidx > 0) et_wait_count(x.published, (unsigned long long)sidx * (unsigned long long)n_publishers);
@@ -152,9 +160,12 @@
         cur = __dadd_rn(budget, __dmul_rn((double)shares, share_value));
         if (wsub == 0 && (int64_t)istep + wn + 1 < a.T) p_next = __ldg(my_row + istep + wn + 1);
     }
-    tc_wait(tf_fwd, par);
+    if (lane == 0) tc_wait(tf_fwd, par);                      // (one poller per warp)
+    __syncwarp();
     tc_fence_after();
     stamp(2);
+    cta_stamp(2);
+    if (tid == 0) fine(41);
     if (tid == 0) fine(41);
 
     // ---- S2: raw z out of TMEM into the [column][episode] tiles.  TMEM lane quarter q holds rows 32q..32q+31 of
@@ -297,5 +308,6 @@
     et_fence_async_smem();
     __syncthreads();
     stamp(5);
+    cta_stamp(3);
 #include "qp_ep_c2_backward.inl"
 }
