@@ -33,4 +33,6 @@ print("  MMA: W tile kk ready  :", [round(rel(8 + k)) for k in range(7)])
 print("  last commit issued    :", round(rel(40)), "  forward complete seen by thread 0:", round(rel(41)))
 
 d = lambda a, b: round((c[:, b] - c[:, a]).mean())
+print("  element-wise (thread 0): S2", d(41, 39), " S3 loop", d(39, 42), " barrier", d(42, 43), " reduce + peer store", d(43, 44),
+      " cluster barrier", d(44, 45), " select + dZ1 loop", d(45, 46), " rest of S4", d(46, 47), " barrier", d(47, 51))
 print("  S6 (thread 0): combine", d(52, 53), " boxes", d(53, 54), " next price", d(54, 55), " barrier", d(55, 58), "; warp 11 boxes", d(56, 57))

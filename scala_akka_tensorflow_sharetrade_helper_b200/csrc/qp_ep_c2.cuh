@@ -59,7 +59,7 @@ struct EpC2Args {
 //          z / h tiles at op, the twelve partial sums per warp (qpart) and then dZ1 hi / lo at op + bwd; then the
 //          epilogue's staging boxes; then phase B's stage.
 struct C2Smem {
-    size_t xt, op, op_bytes, wring, bwd, w2s, wb, ws, xe, dz2s, kns, qsum, part5, bars, total, TBh;
+    size_t xt, op, op_bytes, wring, bwd, stg_a, stg_b, w2s, wb, ws, xe, dz2s, kns, qsum, part5, bars, total, TBh;
 };
 __host__ __device__ inline C2Smem c2_smem(int Hh, int Nh) {
     C2Smem m{};
@@ -69,10 +69,13 @@ __host__ __device__ inline C2Smem c2_smem(int Hh, int Nh) {
     m.wring = m.op + (size_t)kC2AStages * 16384;
     const size_t hz = (((size_t)2 * Hh * kC2EStride * 4) + 1023) & ~(size_t)1023;
     m.bwd = m.op + hz;                                          // dZ1 hi / lo (4 TBh), qpart before them
-    size_t need = hz + 4 * m.TBh;
+    // the epilogue's staging boxes (4 KB per warp, 1024-byte aligned): six where z1(s') was, six behind dZ1
+    m.stg_a = (((size_t)Hh * kC2EStride * 4) + 1023) & ~(size_t)1023;
+    m.stg_b = hz + 4 * m.TBh;
+    size_t need = m.stg_b + (size_t)(kC2Warps - 6) * 4096;
+    if (m.stg_a + 6 * 4096 > hz) need = (size_t)1 << 30;      // (shape outside the kernel: the host refuses it)
     const size_t fwd = (size_t)kC2AStages * 16384 + (size_t)kC2WStages * 2 * m.TBh;
     if (fwd > need) need = fwd;
-    if ((size_t)kC2Warps * 8192 > need) need = (size_t)kC2Warps * 8192;
     m.op_bytes = (need + 1023) & ~(size_t)1023;
     size_t o = m.op + m.op_bytes;
     m.w2s = o; o += (size_t)Hh * 16;

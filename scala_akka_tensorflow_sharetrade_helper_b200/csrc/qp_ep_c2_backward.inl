@@ -2,7 +2,8 @@
 // dW1 partial out of TMEM into global memory, the next price into the window buffer.
 {
     // ---- S5: dW1[256, Nh] = X^T[256, 64] · dZ1[64, Nh] on the tensor core: the window buffer IS the K-major A operand
-    // (rows = time, starting at the row of window element 0), contraction over the 64 episodes in two 32-wide blocks
+    // (rows = time, starting at the row of window element 0), contraction over the 64 episodes in two 32-wide blocks.
+    // The two 128-row halves complete separately, so that the first leaves TMEM while the second is still computed.
     if (warp == 1 && lane == 0) {
         tc_fence_after();
         for (int hf = 0; hf < halves; ++hf) {
@@ -17,9 +18,11 @@
                     first = false;
                 }
             }
+            tc_commit(tf_bwd + hf);
         }
-        tc_commit(tf_bwd);
+        if (halves == 1) tc_commit(tf_bwd + 1);                 // (both barriers complete once per step)
     }
+    __syncwarp();
     // meanwhile: dW2[c][t] = sum_e [kn_e == t] h_e[c] dz2_e and the budget / shares rows of dW1, two threads per hidden
     // column (one per lane group), episodes summed sequentially out of shared memory (fixed order)
     if (tid < 2 * Hh) {
@@ -42,75 +45,43 @@
         float* p5 = part5 + (size_t)gg * 5 * Hh + c;
         p5[0] = s0; p5[Hh] = s1; p5[2 * Hh] = s2; p5[3 * Hh] = x0; p5[4 * Hh] = x1;
     }
-    if (lane == 0) tc_wait(tf_bwd, par);
-    __syncwarp();
-    tc_fence_after();
-    ++mma_it;
-    __syncthreads();
-    stamp(6);
-    if (tid == 0) fine(52);
-    if (tid < Hh) {
-        const float* pa = part5 + tid;
-        const float* pb = part5 + (size_t)5 * Hh + tid;
-        const int c = c0 + tid;
-        out2[c * 3 + 0] = pa[0] + pb[0]; out2[c * 3 + 1] = pa[Hh] + pb[Hh]; out2[c * 3 + 2] = pa[2 * Hh] + pb[2 * Hh];
-        out[(size_t)wn * H + c] = pa[3 * Hh] + pb[3 * Hh];
-        out[(size_t)(wn + 1) * H + c] = pa[4 * Hh] + pb[4 * Hh];
-    }
-    if (tid == 0) fine(53);
-    if (tid == 352) fine(56);
     // ---- S6: dW1 partial out of TMEM.  Row m of the accumulator is window element m (the A operand started at the
-    // window's first row).  A TMEM load hands every lane one ROW of the tile; stored straight to global memory that is
-    // 32 different lines per instruction.  Each warp therefore turns its [32 rows x 32 columns] boxes round in shared
-    // memory (128-byte swizzle, conflict-free both ways) and writes them out as whole 128-byte row segments, four rows
-    // per 16-byte-per-lane store.  (TMA tensor stores did this before: the engine moved the 80 KB at 18 B/clk.)
+    // window's first row).  A TMEM load hands every lane one ROW of the tile; each warp stages its [32 rows x 32 columns]
+    // boxes in shared memory (128-byte swizzle, conflict-free) and lane 0 hands them to the TMA engine, which writes
+    // whole row segments; the tensor map ([pair][row][half][column]) ends at row wn.  The staging buffers lie where
+    // z1(s') was and behind dZ1: neither h(s) (still read above) nor the operands of the running MMAs are touched.
+    // Warp (q4, part) takes column box `part` of its 32-row block in both halves; the columns past the last full box
+    // go out of the registers directly (part 2: first half, part 1: second half).
     {
         const int nfull = Hh >> 5, tail = Hh - (nfull << 5);
-        uint8_t* stg = regA + (size_t)warp * 8192;
-        const int rsub = lane >> 3, chunk = lane & 7;
-        int n_box = 0;
-        for (int i = part; i < halves * nfull; i += 3) {
-            const int hf = i / nfull, cb = i - hf * nfull;
+        uint8_t* buf = warp < 6 ? regA + sm.stg_a + (size_t)warp * 4096 : regA + sm.stg_b + (size_t)(warp - 6) * 4096;
+        bool pending = false;
+        for (int hf = 0; hf < halves; ++hf) {
             const int k0 = hf * 128 + q4 * 32;
+            if (lane == 0) tc_wait(tf_bwd + hf, par);
+            __syncwarp();
+            tc_fence_after();
             if (k0 >= wn) continue;
-            uint32_t r[32];
-            if (!(x.dbg_mode & 512)) et_tmem_ld32_nowait(tmem_base + ((uint32_t)(q4 * 32) << 16) + 128u + (uint32_t)(hf * 128 + cb * 32), r);
-            else { for (int j = 0; j < 32; ++j) r[j] = 0u; }
-            uint8_t* buf = stg + (size_t)(n_box & 1) * 4096;
-            et_tmem_wait_ld();
+            for (int cb = part; cb < nfull; cb += 3) {
+                uint32_t r[32];
+                et_tmem_ld32_nowait(tmem_base + ((uint32_t)(q4 * 32) << 16) + 128u + (uint32_t)(hf * 128 + cb * 32), r);
+                if (pending) {                                  // the buffer's previous box has left it
+                    if (lane == 0) et_bulk_wait_read0();
+                    __syncwarp();
+                }
+                et_tmem_wait_ld();
 #pragma unroll
-            for (int j = 0; j < 8; ++j)
-                *reinterpret_cast<uint4*>(buf + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
-            if (x.dbg_mode & 256) { ++n_box; continue; }        // (timing experiment: no stores)
-            if ((n_box & 1) == 0) {
-                // even boxes leave through the TMA engine (asynchronous), odd ones through the load/store unit: the
-                // two paths move about 20 and 30 B/clk per SM and do not share a queue
+                for (int j = 0; j < 8; ++j)
+                    *reinterpret_cast<uint4*>(buf + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
                 et_fence_async_smem();
                 __syncwarp();
                 if (lane == 0) {
                     c2_tma_store_4d(&tP, buf, cb * 32, (int)crank, k0, (int)pair);
                     et_bulk_commit();
                 }
-            } else {
-                __syncwarp();
-                float* dst = out + (size_t)k0 * H + c0 + cb * 32 + chunk * 4;
-#pragma unroll
-                for (int m = 0; m < 8; ++m) {
-                    const int row = m * 4 + rsub;
-                    const uint4 v = *reinterpret_cast<const uint4*>(buf + row * 128 + ((chunk ^ (row & 7)) << 4));
-                    if (k0 + row < wn) *reinterpret_cast<uint4*>(dst + (size_t)row * H) = v;
-                }
+                pending = true;
             }
-            ++n_box;
-            if (n_box >= 2) {                                   // the buffer about to be reused: its box has left it
-                if (lane == 0) et_bulk_wait_read0();
-                __syncwarp();
-            }
-        }
-        if (tail > 0 && !(x.dbg_mode & 1024)) {
-            for (int hf = part; hf < halves; hf += 3) {
-                const int k0 = hf * 128 + q4 * 32;
-                if (k0 >= wn) continue;
+            if (tail > 0 && part == 2 - hf) {
                 for (int t0 = 0; t0 < tail; t0 += 16) {
                     float v[16];
                     et_tmem_ld16(tmem_base + ((uint32_t)(q4 * 32) << 16) + 128u + (uint32_t)(hf * 128 + nfull * 32 + t0), v);
@@ -125,13 +96,20 @@
                 }
             }
         }
+        ++mma_it;
     }
-    if (tid == 0) fine(54);
-    if (tid == 352) fine(57);
     // ---- S7: slide the window: the next price of every episode into the row after the window's last
     if (wsub == 0) *reinterpret_cast<float*>(XT + (size_t)g * 32768 + et_swz(roff + wn + 1, lane)) = p_next;
-    if (tid == 0) fine(55);
     tc_fence_before();
     __syncthreads();
-    if (tid == 0) fine(58);
+    stamp(6);
+    if (tid >= nthreads - 128 && tid - (nthreads - 128) < Hh) {                 // the two lane groups' sums, in group order
+        const int cl = tid - (nthreads - 128);
+        const float* pa = part5 + cl;
+        const float* pb = part5 + (size_t)5 * Hh + cl;
+        const int c = c0 + cl;
+        out2[c * 3 + 0] = pa[0] + pb[0]; out2[c * 3 + 1] = pa[Hh] + pb[Hh]; out2[c * 3 + 2] = pa[2 * Hh] + pb[2 * Hh];
+        out[(size_t)wn * H + c] = pa[3 * Hh] + pb[3 * Hh];
+        out[(size_t)(wn + 1) * H + c] = pa[4 * Hh] + pb[4 * Hh];
+    }
 }

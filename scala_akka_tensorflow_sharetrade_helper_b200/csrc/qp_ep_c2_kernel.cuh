@@ -46,8 +46,9 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     uint64_t* a_full = bars + 8;        // [kC2AStages <= 4]
     uint64_t* a_empty = bars + 12;      // [kC2AStages]
     uint64_t* tf_fwd = bars + 16;
-    uint64_t* tf_bwd = bars + 17;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 22);
+    uint64_t* tf_bwd = bars + 17;       // [2]: one per 128-row half of the backward accumulator
+    uint64_t* qx_bar = bars + 19;       // the pair's exchange of the Q partial sums: one arrival per CTA and step
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 23);
 
     const uint32_t crank = c2_cluster_rank();                   // which half of the hidden columns
     const int c0 = (int)crank * Hh;                             // first hidden column of this CTA
@@ -68,7 +69,8 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     if (tid == 0) {
         for (int s = 0; s < kC2WStages; ++s) { mbar_init(w_full + s, 1); mbar_init(w_empty + s, 1); }
         for (int s = 0; s < kC2AStages; ++s) { mbar_init(a_full + s, kC2Builders); mbar_init(a_empty + s, 1); }
-        mbar_init(tf_fwd, 1); mbar_init(tf_bwd, 1);
+        mbar_init(tf_fwd, 1); mbar_init(tf_bwd, 1); mbar_init(tf_bwd + 1, 1);
+        mbar_init(qx_bar, 2);
         mbar_fence_init();
     }
     if (warp == 2) {

@@ -187,6 +187,7 @@
     tc_fence_before();
     __syncthreads();
     stamp(3);
+    if (tid == 0) fine(39);
 
     // the three states s' the decision can lead to (index = effective action; TrainerChildActor.scala:118-123)
     const double base_b = hp.bookkeeping == 0 ? a.B0 : budget;
@@ -220,8 +221,12 @@
 #pragma unroll
             for (int t = 0; t < 3; ++t) qpart[((wsub * 4 + j) * 3 + t) * kC2Envs + el] = pq[j][t];
     }
+    if (tid == 0) fine(42);
     __syncthreads();
-    // this CTA's half of the twelve sums per episode, fixed order, to both CTAs of the pair
+    if (tid == 0) fine(43);
+    // this CTA's half of the twelve sums per episode, fixed order, to both CTAs of the pair.  Every thread then
+    // One thread per CTA then arrives (release, cluster scope) on the exchange barrier of BOTH CTAs: a CTA's barrier
+    // completes when both halves of its copy are written — no cluster barrier (which cost 1.1 K cycles here).
     {
         const uint32_t peer = c2_map_peer(qsum, crank ^ 1u);
         for (int idx = tid; idx < 12 * kC2Envs; idx += nthreads) {
@@ -234,8 +239,25 @@
             qsum[crank * 12 * kC2Envs + idx] = s;
             c2_st_cluster(peer + (uint32_t)((crank * 12 * kC2Envs + idx) * 4), s);
         }
+        const uint32_t mine = (uint32_t)__cvta_generic_to_shared(qx_bar), theirs = c2_map_peer(qx_bar, crank ^ 1u);
+        __syncthreads();                                        // (orders every thread's stores before thread 0's release)
+        if (tid == 0) {
+            asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(mine) : "memory");
+            asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];\n" ::"r"(theirs) : "memory");
+            fine(44);
+        }
+        if (lane == 0) {
+            for (uint32_t spins = 0;; ++spins) {
+                uint32_t done;
+                asm volatile("{\n .reg .pred p;\n mbarrier.try_wait.parity.acquire.cluster.shared::cta.b64 p, [%1], %2;\n selp.u32 %0, 1, 0, p;\n}\n"
+                             : "=r"(done) : "r"(mine), "r"(par) : "memory");
+                if (done) break;
+                if (spins > (1u << 26)) __trap();
+            }
+        }
+        __syncwarp();
     }
-    c2_cluster_sync();
+    if (tid == 0) fine(45);
     {
         // SelectionAction (QDecisionPolicyActor.scala:56-62), decision, reward: every warp of the lane group keeps its copy
 #pragma unroll
@@ -278,6 +300,7 @@
             *reinterpret_cast<float*>(bh + off) = hi;
             *reinterpret_cast<float*>(bl + off) = d1 - hi;
         }
+        if (tid == 0) fine(46);
         for (int c = Hh + wsub; c < Nh; c += kC2Sub) {          // padding rows of the MMA's N
             const uint32_t off = et_swz(c, lane);
             *reinterpret_cast<float*>(bh + off) = 0.0f;
@@ -305,9 +328,11 @@
         }
         budget = nb; shares = ns; share_value = p_new;          // carry (TrainerChildActor.scala:99-102)
     }
+    if (tid == 0) fine(47);
     et_fence_async_smem();
     __syncthreads();
     stamp(5);
+    if (tid == 0) fine(51);
     cta_stamp(3);
 #include "qp_ep_c2_backward.inl"
 }
