@@ -342,6 +342,7 @@ def run_ours(args):
         problems = [x for pr in allp for x in pr]
     result_check = "ok" if not problems else "FAILED: " + "; ".join(sorted(set(problems)))
     data_plane = dict(fused_active=int(pol.get_option("fused_active")), ep_tc_active=int(pol.get_option("ep_tc_active")),
+                      ep_c2_active=int(pol.get_option("ep_c2_active")),
                       p2p_active=int(pol.get_option("p2p_active")), fused_step_active=int(pol.get_option("fused_step_active")),
                       tiles_per_sm=-(-((n_local + 31) // 32) // 148), params_digest=digest,
                       gradient_exchange=("none (one GPU)" if world == 1 else
@@ -437,9 +438,13 @@ def run_ours(args):
                                f"uniform-operand FFMA stream reaches {fp32_uniform_peak:.1f} TFLOP/s on the same GPU")
         if ep_tc:
             # contractions on tcgen05 kind::tf32; prices are tf32-exact, W1 / dZ1 are hi+lo pairs: two MMAs per product
+            ep_c2 = bool(pol.get_option("ep_c2_active"))
             tc_peak = peaks["bf16_tflops"] / 2.0 / 2.0
+            kname = ("episode_c2_kernel (persistent, all env-steps of a launch; CTA pairs split the hidden dimension, 64 episodes per pair; "
+                     "contractions on tcgen05, 2 x TF32 per product)" if ep_c2 else
+                     "episode_tc_kernel (persistent, all env-steps of a launch; contractions on tcgen05, 2 x TF32 per product)")
             roofline = dict(
-                bound="tensor", kernel="episode_tc_kernel (persistent, all env-steps of a launch; contractions on tcgen05, 2 x TF32 per product)",
+                bound="tensor", kernel=kname,
                 achieved=step_flops / dur / 1e12, peak=tc_peak, unit="TFLOP/s", frac=step_flops / dur / 1e12 / tc_peak,
                 traffic=None, peak_source=peaks["source"] + " bf16 burst / 2 (tf32) / 2 (hi and lo part of W1 / dZ1)",
                 avg_launch_us=ep_us * n_prof, us_per_env_step=ep_us,
@@ -449,14 +454,19 @@ def run_ours(args):
                 hbm=hbm, fp32_fma_equivalent=fma,
                 bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP,
                 three_kernel_path_us=dict(zip(names, split_us)))
-            # L2 traffic of one env-step by construction: every CTA streams W1^T hi+lo, writes its dW1/dW2
-            # partial, and the partials are read once by the gradient sum
-            n_tiles = (n_local + 31) // 32
-            kp, npad = -(-WINDOW // 32) * 32, -(-HIDDEN // 16) * 16
-            l2_bytes = n_tiles * (2.0 * kp * npad * 4 + 2.0 * 4 * P)
-            roofline["l2"] = dict(achieved=l2_bytes / dur / 1e9, unit="GB/s", bytes_per_step=l2_bytes,
-                                  note="by construction, not measured; the microarchitecture guide's L2 cap is ~6300 B/clk")
+            # DRAM and L2 traffic of one env-step: MEASURED, from this round's ncu --set full capture of a launch of the same
+            # kernel at this workload (profiles/r2_ncu_traffic.json: dram__bytes_read/write.sum, lts__t_bytes.sum, per env-step)
             single_wave = n_local <= 32 * 148
+            try:
+                tr = json.load(open(os.path.join(ROOT, "profiles", "r2_ncu_traffic.json")))
+                key = "episode_c2_kernel" if ep_c2 else "episode_tc_kernel"
+                if n_local == 4096 and HIDDEN == 200 and key in tr:
+                    roofline["traffic"] = tr[key]["dram_bytes_per_env_step"]
+                    roofline["l2"] = dict(bytes_per_step=tr[key]["l2_bytes_per_env_step"], achieved=tr[key]["l2_bytes_per_env_step"] / dur / 1e9,
+                                          unit="GB/s", note="lts__t_bytes.sum of the capture / env-steps of the captured launch")
+                    roofline["traffic_note"] = tr[key]["source"]
+            except Exception as exc:
+                roofline["traffic_note"] = f"no ncu traffic summary: {exc}"
             try:
                 if not single_wave:
                     raise RuntimeError("several tiles per CTA (waves): the per-phase stamps describe the last wave only; "
@@ -466,27 +476,36 @@ def run_ours(args):
                 pol.env_step(40)
                 c = pol.phase_clocks(40)[5:]
                 pol.set_option("phase_clocks", 0)
-                labels = ["S0 A-operand build + tables", "S1 W1^T stream + forward MMA", "S2 z out of TMEM", "S3 Q(s), select, book-keeping, Q(s')",
-                          "S4 TD target, dZ1 hi/lo", "S5 backward MMA, dW2, budget/shares rows", "S6 dW1 partial: TMEM -> TMA store, extra rows",
-                          "S7 window row + store completion", "grid barrier", "phase B: bulk-copy sum, AdaGrad, W1^T publish"]
-                d = np.diff(c[:, :11], axis=1).astype(np.float64).mean(axis=0)
+                if ep_c2:
+                    order = [0, 1, 2, 3, 4, 5, 6, 7, 8, 9, 15, 12, 10]
+                    labels = ["S0 wait for the last CTA's new weights (A tiles are built meanwhile)", "S1 W1^T stream + A-tile transpose + forward MMA",
+                              "S2 z out of TMEM", "S3 hidden layer, Q partial sums, pair exchange, select", "S4 TD target, dZ1 hi/lo",
+                              "S5 backward MMA (two halves), dW2 / budget / shares rows, first half of the partial out of TMEM",
+                              "S6 rest of the partial out, next price", "store completion", "grid barrier (fence + counter)",
+                              "phase B: partial segments summed (16-byte loads from L2)", "NVLink share exchange", "AdaGrad + W1^T publish"]
+                else:
+                    order = list(range(11))
+                    labels = ["S0 A-operand build + tables", "S1 W1^T stream + forward MMA", "S2 z out of TMEM", "S3 Q(s), select, book-keeping, Q(s')",
+                              "S4 TD target, dZ1 hi/lo", "S5 backward MMA, dW2, budget/shares rows", "S6 dW1 partial: TMEM -> TMA store, extra rows",
+                              "S7 window row + store completion", "grid barrier", "phase B: bulk-copy sum, AdaGrad, W1^T publish"]
+                d = np.array([(c[:, b_] - c[:, a_]).astype(np.float64).mean() for a_, b_ in zip(order[:-1], order[1:])])
                 tot = float((c[1:, 0] - c[:-1, 0]).mean())
                 roofline["phase_cycles"] = dict({k: float(v) for k, v in zip(labels, d)}, step_total=tot,
                                                 note="clock64 stamps of CTA 0, mean over 35 env-steps")
             except Exception as exc:  # stamps are a tuning aid, never fatal for the bench line
                 roofline["phase_cycles"] = dict(error=str(exc))
-            if n_local == 4096 and HIDDEN == 200:
-                # dram__bytes_read.sum + dram__bytes_write.sum of the committed ncu --set full capture of one 30-step
-                # launch of this kernel, per env-step; far below the algorithmic bytes because the windows stay in
-                # shared memory and weights / partials in L2
-                roofline["traffic"] = (4.754944e6 + 1.326592e6) / 30.0
-                roofline["traffic_note"] = "bytes per env-step of 4096 episodes, from profiles/r1_v6_ncu_episode_tc_kernel_summary.csv"
             if single_wave:
                 pol.set_option("ep_tc", 0)
                 pol.env_reset()
                 pol.env_step(20)
                 roofline["ffma_persistent_kernel_us_per_env_step"] = float(pol.env_step_timed(n_prof)[0]) / n_prof * 1e3
                 pol.set_option("ep_tc", 1)
+                if ep_c2:
+                    pol.set_option("ep_c2", 0)
+                    pol.env_reset()
+                    pol.env_step(20)
+                    roofline["one_tile_per_cta_kernel_us_per_env_step"] = float(pol.env_step_timed(n_prof)[0]) / n_prof * 1e3
+                    pol.set_option("ep_c2", 1)
             else:
                 roofline["kernel"] += f"; {-(-((n_local + 31) // 32) // 148)} waves per step"
         else:

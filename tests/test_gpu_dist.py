@@ -111,6 +111,9 @@ def test_n_gpus_match_one_gpu(tmp_path, world, p2p, ep_tc, n_local):
     _tol.assert_grad_close(parts[0]["grad_first"], g1_first, f"{world}-GPU vs 1-GPU gradient of the first step", n_terms=n)
     # ten updates later the two runs stand at slightly different weights (different summation orders, and the
     # tensor-core kernel on one side only): the last gradients agree to the drift of the weights, not to rounding
+    if np.linalg.norm(g1) == 0.0:       # (ten lr = 0.01 steps can leave every ReLU of a small batch dead: then both must be zero)
+        assert not parts[0]["grad"].any()
+        return
     d = np.linalg.norm(parts[0]["grad"] - g1) / np.linalg.norm(g1)
     assert d <= 2e-4, f"{world}-GPU vs 1-GPU gradient of the last step: relative Frobenius error {d:.3g}"
     assert np.abs(parts[0]["params"] - p1).max() <= (N_STEPS + 5) * _tol.W_ATOL
