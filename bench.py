@@ -342,12 +342,14 @@ def run_ours(args):
         problems = [x for pr in allp for x in pr]
     result_check = "ok" if not problems else "FAILED: " + "; ".join(sorted(set(problems)))
     data_plane = dict(fused_active=int(pol.get_option("fused_active")), ep_tc_active=int(pol.get_option("ep_tc_active")),
-                      ep_c2_active=int(pol.get_option("ep_c2_active")),
+                      ep_c2_active=int(pol.get_option("ep_c2_active")), nvls_active=int(pol.get_option("nvls_active")),
                       p2p_active=int(pol.get_option("p2p_active")), fused_step_active=int(pol.get_option("fused_step_active")),
                       tiles_per_sm=-(-((n_local + 31) // 32) // 148), params_digest=digest,
                       gradient_exchange=("none (one GPU)" if world == 1 else
-                                         ("in-kernel all-to-all over NVLink peer memory (tagged 64-bit stores), no NCCL call in the step"
-                                          if pol.get_option("p2p_active") else "ncclAllReduce between kernels")))
+                                         (("in-kernel exchange: one tagged 64-bit multicast store per share (multimem.st through the NVSwitch), "
+                                           "no NCCL call in the step") if pol.get_option("nvls_active") else
+                                          ("in-kernel all-to-all over NVLink peer memory (tagged 64-bit stores), no NCCL call in the step"
+                                           if pol.get_option("p2p_active") else "ncclAllReduce between kernels"))))
 
     # ---- roofline of the dominant kernel, measured live with CUDA events on the launching stream
     peaks = measured_peaks()

@@ -249,6 +249,14 @@ int qp_dist_nccl_version(int32_t* version);
 #define QP_DIST_IPC_BYTES 64
 int qp_dist_p2p_export(qp_handle* h, void* out, size_t out_bytes);
 int qp_dist_p2p_import(qp_handle* h, const void* handles, int32_t world);
+/* The same exchange over blocks the HOST runtime has set up (instead of export / import): block_ptrs[r] is rank r's block
+ * of qp_dist_p2p_bytes(h) bytes as mapped in THIS process (zero-filled, 256-byte aligned, the caller keeps them alive
+ * until qp_destroy), multicast_ptr the address of a multicast (NVLS) mapping of the same blocks, or 0.  With a
+ * multicast address the pair kernel sends each share as ONE store that the NVSwitch delivers to every rank, instead of
+ * world - 1 stores (option "nvls" = 0 keeps the unicast stores; "nvls_active" reads what the next step takes).  No
+ * counterpart in the reference. */
+int64_t qp_dist_p2p_bytes(const qp_handle* h);
+int qp_dist_p2p_attach(qp_handle* h, const uint64_t* block_ptrs, int32_t world, uint64_t multicast_ptr);
 
 /* ---- allocation-free variant.  No counterpart in the reference.
  *

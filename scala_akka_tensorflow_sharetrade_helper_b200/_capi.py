@@ -70,6 +70,8 @@ SIGNATURES = {
     "qp_iteration": (C.c_int64, [_H]),
     "qp_parse_prices": (C.c_int, [C.c_char_p, C.c_size_t, _P, C.c_int64, C.POINTER(C.c_int64)]),
     "qp_dist_unique_id": (C.c_int, [_P, C.c_size_t]),
+    "qp_dist_p2p_bytes": (C.c_int64, [_H]),
+    "qp_dist_p2p_attach": (C.c_int, [_H, _P, C.c_int32, C.c_uint64]),
     "qp_dist_init": (C.c_int, [_H, _P, C.c_int32, C.c_int32]),
     "qp_dist_p2p_export": (C.c_int, [_H, _P, C.c_size_t]),
     "qp_dist_p2p_import": (C.c_int, [_H, _P, C.c_int32]),

@@ -167,6 +167,8 @@ struct qp_handle {
     void* p2p_block = nullptr;
     void* p2p_peer_block[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     bool p2p_ready = false, allow_p2p = true;
+    bool p2p_external = false;          // the exchange blocks belong to the caller (qp_dist_p2p_attach): never freed / closed here
+    void* p2p_mc = nullptr;             // multicast address of the blocks (NVLS): one store reaches every rank's copy
     unsigned int p2p_flag_base = 0;
     // batching front-end (config 5): child actors enqueue rows, one flush = one GPU launch per kind
     // batching front-end: two generations of queued messages per kind, in pinned host memory.  Actors reserve a slot
@@ -223,6 +225,7 @@ struct qp_handle {
     int tc_S = 1;
     CUtensorMap tm_p_hi[4], tm_p_lo[4], tm_pT_hi, tm_pT_lo, tm_w_hi, tm_w_lo, tm_dz_hi, tm_dz_lo, tm_xe_hi, tm_xe_lo;
     bool allow_fused = true;            // qp_set_option("fused", 0) forces the three-kernel path
+    bool allow_nvls = true;             // qp_set_option("nvls", 0): unicast share exchange even where a multicast address exists
     DevBuf<long long> dbg;              // phase stamps of the persistent kernel (qp_debug_phase_clocks)
     bool want_dbg = false;
     bool want_fine = false;             // "phase_clocks" = 3: stamps inside the pair kernel's forward
@@ -851,6 +854,8 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
         x.p_pad = (int64_t)p2p_pad(h);
         for (int r = 0; r < ea.world && ea.world > 1; ++r)
             x.pdata[r] = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(h->p2p_peer_block[r]) + p2p_tc_offset(h));
+        x.mc_pdata = (ea.world > 1 && h->p2p_mc && h->allow_nvls)
+                         ? reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(h->p2p_mc) + p2p_tc_offset(h)) : nullptr;
         if (h->want_cta_ns) {        // [n_steps][grid][8]
             QP_TRY(h->dbg.ensure((size_t)n_steps * h->c2_grid * 8));
             QP_CUDA(cudaMemsetAsync(h->dbg.p, 0, (size_t)n_steps * h->c2_grid * 8 * sizeof(long long), h->stream));
@@ -1050,9 +1055,11 @@ int qp_destroy(qp_handle* h) {
     cudaSetDevice(h->device);
     if (h->stream) cudaStreamSynchronize(h->stream);
     if (h->comm && g_nccl.CommDestroy) g_nccl.CommDestroy(h->comm);
-    for (int r = 0; r < 8; ++r)
-        if (h->p2p_peer_block[r] && r != h->rank) cudaIpcCloseMemHandle(h->p2p_peer_block[r]);
-    if (h->p2p_block) cudaFree(h->p2p_block);
+    if (!h->p2p_external) {
+        for (int r = 0; r < 8; ++r)
+            if (h->p2p_peer_block[r] && r != h->rank) cudaIpcCloseMemHandle(h->p2p_peer_block[r]);
+        if (h->p2p_block) cudaFree(h->p2p_block);
+    }
     h->params.release(); h->acc.release(); h->grad.release();
     h->dz1.release(); h->xextra.release(); h->part1.release(); h->part2.release();
     h->m_states.release(); h->m_next.release(); h->m_rewards.release(); h->m_steps.release();
@@ -1862,6 +1869,7 @@ int qp_set_option(qp_handle* h, const char* key, int64_t value) {
     if (std::strcmp(key, "p2p") == 0) { h->allow_p2p = value != 0; return QP_OK; }
     if (std::strcmp(key, "ep_tc") == 0) { h->allow_ep_tc = value != 0; return QP_OK; }
     if (std::strcmp(key, "ep_c2") == 0) { h->allow_ep_c2 = value != 0; return QP_OK; }
+    if (std::strcmp(key, "nvls") == 0) { h->allow_nvls = value != 0; return QP_OK; }
     if (std::strcmp(key, "c2_dbg") == 0) { h->c2_dbg = (int)value; return QP_OK; }
     if (std::strcmp(key, "tc_passes") == 0) {
         if (value != 1 && value != 3) return fail(QP_EINVAL, "tc_passes must be 3 (3xTF32) or 1 (TF32)");
@@ -1887,6 +1895,10 @@ int qp_get_option(qp_handle* h, const char* key, int64_t* value) {
         return QP_OK;
     }
     if (std::strcmp(key, "ep_c2_active") == 0) { *value = (h->has_env && use_fused(h) && ep_c2_usable(h)) ? 1 : 0; return QP_OK; }
+    if (std::strcmp(key, "nvls_active") == 0) {
+        *value = (h->has_env && h->world > 1 && use_fused(h) && ep_c2_usable(h) && h->p2p_mc && h->allow_nvls) ? 1 : 0;
+        return QP_OK;
+    }
     if (std::strcmp(key, "p2p_active") == 0) { *value = (h->has_env && h->world > 1 && use_fused(h)) ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "tc_a_lo_zero") == 0) { *value = h->tc_a_lo_zero ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "tc_active") == 0) { *value = (h->wide && h->allow_tc && h->tc_ready) ? 1 : 0; return QP_OK; }
@@ -1948,6 +1960,26 @@ int qp_dist_p2p_import(qp_handle* h, const void* handles, int32_t world) {
         h->p2p_peer_block[r] = ptr;
     }
     h->p2p_ready = true;      // (p2p_flag_base keeps counting: the tags left in the blocks stay in the past)
+    return QP_OK;
+}
+
+int64_t qp_dist_p2p_bytes(const qp_handle* h) {
+    if (!h) return 0;
+    return (int64_t)(p2p_tc_offset(h) + (size_t)2 * 8 * p2p_pad(h) * sizeof(unsigned long long));
+}
+
+int qp_dist_p2p_attach(qp_handle* h, const uint64_t* block_ptrs, int32_t world, uint64_t multicast_ptr) {
+    if (!h || !block_ptrs) return fail(QP_EINVAL, "null argument");
+    if (world != h->world || world > 8 || world < 2) return fail(QP_EINVAL, "world must match qp_dist_init and be 2..8");
+    if (h->p2p_block) return fail(QP_ESTATE, "an exchange block exists already (qp_dist_p2p_export)");
+    for (int r = 0; r < world; ++r) {
+        if (!block_ptrs[r] || (block_ptrs[r] & 255u)) return fail(QP_EINVAL, "exchange blocks must be non-null and 256-byte aligned");
+        h->p2p_peer_block[r] = reinterpret_cast<void*>(block_ptrs[r]);
+    }
+    h->p2p_block = h->p2p_peer_block[h->rank];
+    h->p2p_external = true;
+    h->p2p_mc = reinterpret_cast<void*>(multicast_ptr);
+    h->p2p_ready = true;
     return QP_OK;
 }
 

@@ -47,6 +47,7 @@ struct EpC2Args {
     int Nh;                          // MMA N per CTA: Hh rounded up to 8
     unsigned long long* published;
     unsigned long long* pdata[8];    // several GPUs: every rank's exchange block (see EpTcArgs)
+    unsigned long long* mc_pdata;    // the same block through its multicast address (NVLS), or null: one store reaches every rank
     int64_t p_pad;
     int dbg_mode;                    // timing experiments (option "c2_dbg"); 0 in every real run
     long long* cta_ns;               // tuning aid ("phase_clocks" = 2): [n_steps][gridDim][8] globaltimer stamps of every CTA

@@ -46,11 +46,18 @@
             const unsigned int want = ea.flag_base + (unsigned int)sidx + 1u;
             const size_t slot = (size_t)(want & 1u) * (size_t)ea.world;
             const unsigned long long mine = ((unsigned long long)want << 32) | (unsigned long long)__float_as_uint(g);
+            if (x.mc_pdata) {
+                // NVLS: one store to the multicast address; the switch delivers it into the slot [parity][this rank][p] of
+                // EVERY rank's block (this rank's included): one NVLink crossing of 8 bytes instead of world - 1
+                asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" ::"l"(x.mc_pdata + (slot + (size_t)ea.rank) * (size_t)x.p_pad + p),
+                             "l"(mine) : "memory");
+            } else {
 #pragma unroll
-            for (int r = 0; r < 8; ++r)
-                if (r < ea.world && r != ea.rank)
-                    asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(x.pdata[r] + (slot + (size_t)ea.rank) * (size_t)x.p_pad + p),
-                                 "l"(mine) : "memory");
+                for (int r = 0; r < 8; ++r)
+                    if (r < ea.world && r != ea.rank)
+                        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(x.pdata[r] + (slot + (size_t)ea.rank) * (size_t)x.p_pad + p),
+                                     "l"(mine) : "memory");
+            }
             const unsigned long long* local = x.pdata[ea.rank] + slot * (size_t)x.p_pad + p;
             float pv[8];
 #pragma unroll

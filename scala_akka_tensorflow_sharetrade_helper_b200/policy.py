@@ -282,9 +282,13 @@ class QDecisionPolicy:
         self.n_envs = int(soe.size)
         return out
 
-    def dist_init(self, dist, rank: int, world: int, p2p: bool = True):
+    def dist_init(self, dist, rank: int, world: int, p2p: bool = True, nvls: bool = True):
         """Join the gradient all-reduce group.  `dist` is an initialised torch.distributed (any backend):
-        it only carries the 128-byte NCCL rendezvous id from rank 0 to the others."""
+        it only carries the 128-byte NCCL rendezvous id from rank 0 to the others, and the handles of the
+        exchange blocks.  p2p: the all-reduce runs inside the persistent kernel over NVLink peer memory.
+        nvls: the exchange blocks are torch symmetric memory with a multicast (NVLS) mapping where the
+        system offers one, so that a share is ONE store the NVSwitch delivers to every rank; otherwise
+        (or with nvls=False) plain cudaMalloc blocks shared by CUDA IPC and world - 1 stores per share."""
         import torch
         buf = (C.c_ubyte * 128)()
         if rank == 0:
@@ -294,23 +298,56 @@ class QDecisionPolicy:
             dist.broadcast_object_list(ids, src=0)
         uid = (C.c_ubyte * 128).from_buffer_copy(ids[0])
         check(self._lib.qp_dist_init(self._h, uid, int(rank), int(world)))
-        del torch
         self.p2p = False
+        self.nvls = False
+        self._symm = None
         if world > 1 and p2p:
-            # NVLink peer-memory all-reduce inside the persistent kernel: exchange CUDA IPC handles
-            hbuf = (C.c_ubyte * 64)()
-            ok = self._lib.qp_dist_p2p_export(self._h, hbuf, 64) == _capi.QP_OK
-            gathered = [None] * world
-            dist.all_gather_object(gathered, (ok, bytes(hbuf)))
-            if all(g[0] for g in gathered):
-                blob = b"".join(g[1] for g in gathered)
-                ok = self._lib.qp_dist_p2p_import(self._h, (C.c_ubyte * len(blob)).from_buffer_copy(blob), world) == _capi.QP_OK
-            else:
-                ok = False
-            flags = [None] * world
-            dist.all_gather_object(flags, bool(ok))
-            self.p2p = all(flags)
+            ok = False
+            if nvls:
+                ok = self._attach_symmetric_memory(torch, dist, world)
+                flags = [None] * world
+                dist.all_gather_object(flags, bool(ok))
+                ok = all(flags)
+                if not ok and self._symm is not None:
+                    raise QPolicyError("symmetric-memory exchange blocks attached on some ranks only")
+                self.nvls = ok and self._symm[2] != 0
+            if not ok:
+                # exchange CUDA IPC handles of cudaMalloc'd blocks
+                hbuf = (C.c_ubyte * 64)()
+                ok = self._lib.qp_dist_p2p_export(self._h, hbuf, 64) == _capi.QP_OK
+                gathered = [None] * world
+                dist.all_gather_object(gathered, (ok, bytes(hbuf)))
+                if all(g[0] for g in gathered):
+                    blob = b"".join(g[1] for g in gathered)
+                    ok = self._lib.qp_dist_p2p_import(self._h, (C.c_ubyte * len(blob)).from_buffer_copy(blob), world) == _capi.QP_OK
+                else:
+                    ok = False
+                flags = [None] * world
+                dist.all_gather_object(flags, bool(ok))
+                ok = all(flags)
+            self.p2p = ok
             self.set_option("p2p", 1 if self.p2p else 0)   # every rank must take the same path
+
+    def _attach_symmetric_memory(self, torch, dist, world) -> bool:
+        """Exchange blocks as torch symmetric memory (peer-mapped by the runtime, with a multicast address where
+        NVLS is available).  Collective; returns False (and leaves nothing attached) when this torch / system
+        cannot do it."""
+        try:
+            import torch.distributed._symmetric_memory as symm_mem
+            nbytes = int(self._lib.qp_dist_p2p_bytes(self._h))
+            dev = torch.device("cuda", self.config.device)
+            t = symm_mem.empty(nbytes, dtype=torch.uint8, device=dev)
+            t.zero_()
+            torch.cuda.synchronize(dev)
+            hdl = symm_mem.rendezvous(t, dist.group.WORLD)
+            ptrs = (C.c_uint64 * world)(*[int(p_) for p_ in hdl.buffer_ptrs])
+            mc = int(hdl.multicast_ptr) if getattr(hdl, "has_multicast_support", False) or hdl.multicast_ptr else 0
+            if self._lib.qp_dist_p2p_attach(self._h, ptrs, world, C.c_uint64(mc)) != _capi.QP_OK:
+                return False
+            self._symm = (t, hdl, mc)          # kept alive as long as the policy
+            return True
+        except Exception:
+            return False
 
     # ---- checkpoint (the reference's saveSnapshot stub, QDecisionPolicyActor.scala:74, :91-93) ------
     def save_checkpoint(self, path: str):

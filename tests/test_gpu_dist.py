@@ -23,7 +23,7 @@ def _n_gpus():
         return 0
 
 
-def _worker(rank, world, port, out_dir, p2p, ep_tc, n_local):
+def _worker(rank, world, port, out_dir, p2p, ep_tc, n_local, nvls=1):
     import torch
     import torch.distributed as dist
     import scala_akka_tensorflow_sharetrade_helper_b200 as q
@@ -37,10 +37,11 @@ def _worker(rank, world, port, out_dir, p2p, ep_tc, n_local):
     with q.QDecisionPolicy(q.PolicyConfig(bookkeeping=1, device=rank)) as pol:
         pol.set_weights(w)
         pol.set_option("ep_tc", ep_tc)
-        pol.dist_init(dist, rank, world, p2p=bool(p2p))
+        pol.dist_init(dist, rank, world, p2p=bool(p2p), nvls=bool(nvls))
         pol.env_create(prices, np.arange(count), 1000.0, 1, env_id_base=first)
         p2p_active = pol.get_option("p2p_active")
         ep_tc_active = pol.get_option("ep_tc_active")
+        nvls_active = pol.get_option("nvls_active")
         tr0 = pol.env_step_trace(1)
         g_first = pol.last_grad()                         # same weights on every configuration: strict check
         tr1 = pol.env_step_trace(N_STEPS - 1)
@@ -51,21 +52,25 @@ def _worker(rank, world, port, out_dir, p2p, ep_tc, n_local):
         g = pol.last_grad()
     np.savez(os.path.join(out_dir, f"rank{rank}.npz"), params=p, acc=a, grad=g, grad_first=g_first, shares=tr["shares"],
              budget=tr["budget"], action_sel=tr["action_sel"], q_s=tr["q_s"], shares2=tr2["shares"],
-             p2p_active=p2p_active, ep_tc_active=ep_tc_active)
+             p2p_active=p2p_active, ep_tc_active=ep_tc_active, nvls_active=nvls_active)
     dist.barrier()
     dist.destroy_process_group()
 
 
-CASES = [(2, 1, 1, N_LOCAL), (2, 1, 0, N_LOCAL), (2, 0, 0, N_LOCAL), (2, 1, 1, 5000),
-         (4, 1, 1, N_LOCAL), (4, 0, 0, N_LOCAL), (8, 1, 1, N_LOCAL), (8, 1, 0, N_LOCAL), (8, 1, 1, 5000)]
+# (world, p2p, ep_tc, episodes per rank, nvls)
+CASES = [(2, 1, 1, N_LOCAL, 1), (2, 1, 1, N_LOCAL, 0), (2, 1, 0, N_LOCAL, 1), (2, 0, 0, N_LOCAL, 1), (2, 1, 1, 5000, 1),
+         (4, 1, 1, N_LOCAL, 1), (4, 0, 0, N_LOCAL, 1), (8, 1, 1, N_LOCAL, 1), (8, 1, 1, N_LOCAL, 0), (8, 1, 0, N_LOCAL, 1),
+         (8, 1, 1, 5000, 1)]
 
 
-@pytest.mark.parametrize("world,p2p,ep_tc,n_local", CASES)
-def test_n_gpus_match_one_gpu(tmp_path, world, p2p, ep_tc, n_local):
+@pytest.mark.parametrize("world,p2p,ep_tc,n_local,nvls", CASES)
+def test_n_gpus_match_one_gpu(tmp_path, world, p2p, ep_tc, n_local, nvls):
     """world ranks, one per GPU (skipped on boxes with fewer), against one GPU holding every episode.
     p2p = 1: gradient all-reduce inside the persistent kernel over NVLink peer memory (ep_tc = 1: the
     tensor-core kernel, share-by-share exchange; ep_tc = 0: the FFMA kernel, whole-gradient exchange);
     p2p = 0: one fused step kernel per env-step + NCCL all-reduce between kernels.
+    nvls = 1: the exchange blocks are torch symmetric memory; where the system has NVLS the pair kernel sends each share as one
+    multicast store (the printed nvls_active says whether it did).
     n_local = 5000: more than one tile per SM, the tensor-core kernel runs in waves on both sides."""
     if _n_gpus() < world:
         pytest.skip(f"needs {world} GPUs")
@@ -75,7 +80,7 @@ def test_n_gpus_match_one_gpu(tmp_path, world, p2p, ep_tc, n_local):
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
     ctx = mp.get_context("spawn")
-    procs = [ctx.Process(target=_worker, args=(r, world, port, str(tmp_path), p2p, ep_tc, n_local)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, str(tmp_path), p2p, ep_tc, n_local, nvls)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:
@@ -84,6 +89,10 @@ def test_n_gpus_match_one_gpu(tmp_path, world, p2p, ep_tc, n_local):
     parts = [np.load(tmp_path / f"rank{r}.npz") for r in range(world)]
     assert all(int(p["p2p_active"]) == p2p for p in parts), "peer-memory path not taken as requested"
     assert all(int(p["ep_tc_active"]) == ep_tc for p in parts), "tensor-core kernel not (de)selected as requested"
+    assert len({int(p["nvls_active"]) for p in parts}) == 1, "ranks disagree on the multicast exchange"
+    if not nvls:
+        assert int(parts[0]["nvls_active"]) == 0
+    print(f"world {world} p2p {p2p} ep_tc {ep_tc} n_local {n_local}: nvls_active = {int(parts[0]['nvls_active'])}")
     # replicas bit-identical: same all-reduced sum, same AdaGrad arithmetic
     for r in range(1, world):
         np.testing.assert_array_equal(parts[0]["params"], parts[r]["params"], err_msg=f"rank {r} params")
@@ -113,7 +122,7 @@ def test_n_gpus_match_one_gpu(tmp_path, world, p2p, ep_tc, n_local):
     # tensor-core kernel on one side only): the last gradients agree to the drift of the weights, not to rounding
     if np.linalg.norm(g1) == 0.0:       # (ten lr = 0.01 steps can leave every ReLU of a small batch dead: then both must be zero)
         assert not parts[0]["grad"].any()
-        return
-    d = np.linalg.norm(parts[0]["grad"] - g1) / np.linalg.norm(g1)
-    assert d <= 2e-4, f"{world}-GPU vs 1-GPU gradient of the last step: relative Frobenius error {d:.3g}"
+    else:
+        d = np.linalg.norm(parts[0]["grad"] - g1) / np.linalg.norm(g1)
+        assert d <= 2e-4, f"{world}-GPU vs 1-GPU gradient of the last step: relative Frobenius error {d:.3g}"
     assert np.abs(parts[0]["params"] - p1).max() <= (N_STEPS + 5) * _tol.W_ATOL
