@@ -257,6 +257,7 @@ def run_ours(args):
 
     pol = q.QDecisionPolicy(q.PolicyConfig(window=WINDOW, hidden=HIDDEN, device=local, seed=SEED))
     if world > 1:
+        pol.set_option("rsag", args.rsag)
         pol.dist_init(dist, rank, world)
     stream = torch.cuda.ExternalStream(pol.stream, device=torch.device("cuda", local))
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=f"cuda:{local}")
@@ -345,6 +346,7 @@ def run_ours(args):
                       ep_c2_active=int(pol.get_option("ep_c2_active")), nvls_active=int(pol.get_option("nvls_active")),
                       p2p_active=int(pol.get_option("p2p_active")), fused_step_active=int(pol.get_option("fused_step_active")),
                       tiles_per_sm=-(-((n_local + 31) // 32) // 148), params_digest=digest,
+                      share_exchange=("none" if world == 1 else ("reduce-scatter + all-gather" if (args.rsag == 1 or (args.rsag < 0 and world >= 8)) else "all-to-all")),
                       gradient_exchange=("none (one GPU)" if world == 1 else
                                          (("in-kernel exchange: one tagged 64-bit multicast store per share (multimem.st through the NVSwitch), "
                                            "no NCCL call in the step") if pol.get_option("nvls_active") else
@@ -601,6 +603,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--workload", default="config2", choices=["config2", "wide"])
     ap.add_argument("--rollout-steps", type=int, default=0, help="env-steps per bench step (default: the whole episode)")
+    ap.add_argument("--rsag", type=int, default=-1, help="share exchange: 1 reduce-scatter + all-gather, 0 all-to-all, -1 by world size")
     args = ap.parse_args()
     set_workload(args.workload, args)
     if args.impl == "reference":

@@ -225,6 +225,7 @@ struct qp_handle {
     int tc_S = 1;
     CUtensorMap tm_p_hi[4], tm_p_lo[4], tm_pT_hi, tm_pT_lo, tm_w_hi, tm_w_lo, tm_dz_hi, tm_dz_lo, tm_xe_hi, tm_xe_lo;
     bool allow_fused = true;            // qp_set_option("fused", 0) forces the three-kernel path
+    int rsag_mode = -1;                 // qp_set_option("rsag", 0 | 1): share exchange as all-to-all / reduce-scatter + all-gather; -1: by world size
     bool allow_nvls = true;             // qp_set_option("nvls", 0): unicast share exchange even where a multicast address exists
     DevBuf<long long> dbg;              // phase stamps of the persistent kernel (qp_debug_phase_clocks)
     bool want_dbg = false;
@@ -715,12 +716,14 @@ int ep_c2_prepare(qp_handle* h) {
         const int ng4 = pitch / 4, nsub = std::min(8, kC2Threads / std::max(1, ng4));
         if (pitch > kC2Threads || nsub < 1 || (grid / 2 + nsub - 1) / nsub > 16 || (size_t)8 * pitch * 4 > sm.op_bytes) return QP_OK;
     }
-    QP_CUDA(cudaFuncSetAttribute(episode_c2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sm.total + 1024)));
+    QP_CUDA(cudaFuncSetAttribute(episode_c2_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sm.total + 1024)));
+    QP_CUDA(cudaFuncSetAttribute(episode_c2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sm.total + 1024)));
+    QP_CUDA(cudaFuncSetAttribute(episode_c2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sm.total + 1024)));
     {   // all pairs must be co-resident (cooperative launch of clusters of two)
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kC2Threads); cfg.dynamicSmemBytes = sm.total + 1024; cfg.stream = h->stream;
         int n_clusters = 0;
-        if (cudaOccupancyMaxActiveClusters(&n_clusters, episode_c2_kernel, &cfg) != cudaSuccess) { cudaGetLastError(); return QP_OK; }
+        if (cudaOccupancyMaxActiveClusters(&n_clusters, episode_c2_kernel<1>, &cfg) != cudaSuccess) { cudaGetLastError(); return QP_OK; }
         if (n_clusters * 2 < grid) return QP_OK;
     }
     QP_TRY(make_tmap(&h->tm_c2_hi, h->et_w_hi.p, h->et_Kp, hp.H, (uint64_t)h->et_Kp * sizeof(float), (uint32_t)Nh));
@@ -854,6 +857,7 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
         x.p_pad = (int64_t)p2p_pad(h);
         for (int r = 0; r < ea.world && ea.world > 1; ++r)
             x.pdata[r] = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(h->p2p_peer_block[r]) + p2p_tc_offset(h));
+        x.rsag = h->rsag_mode == 1 || (h->rsag_mode < 0 && ea.world >= 8) ? 1 : 0;
         x.mc_pdata = (ea.world > 1 && h->p2p_mc && h->allow_nvls)
                          ? reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(h->p2p_mc) + p2p_tc_offset(h)) : nullptr;
         if (h->want_cta_ns) {        // [n_steps][grid][8]
@@ -879,7 +883,9 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1;      // (the cluster shape is the kernel's own attribute)
         cfg.attrs = at; cfg.numAttrs = 1;
-        QP_CUDA(cudaLaunchKernelEx(&cfg, episode_c2_kernel, h->tm_c2_hi, h->tm_c2_lo, h->tm_c2_part, x));
+        if (ea.world > 1 && x.rsag) QP_CUDA(cudaLaunchKernelEx(&cfg, episode_c2_kernel<2>, h->tm_c2_hi, h->tm_c2_lo, h->tm_c2_part, x));
+        else if (ea.world > 1) QP_CUDA(cudaLaunchKernelEx(&cfg, episode_c2_kernel<1>, h->tm_c2_hi, h->tm_c2_lo, h->tm_c2_part, x));
+        else QP_CUDA(cudaLaunchKernelEx(&cfg, episode_c2_kernel<0>, h->tm_c2_hi, h->tm_c2_lo, h->tm_c2_part, x));
         h->launches++;
         return QP_OK;
     }
@@ -1870,6 +1876,7 @@ int qp_set_option(qp_handle* h, const char* key, int64_t value) {
     if (std::strcmp(key, "ep_tc") == 0) { h->allow_ep_tc = value != 0; return QP_OK; }
     if (std::strcmp(key, "ep_c2") == 0) { h->allow_ep_c2 = value != 0; return QP_OK; }
     if (std::strcmp(key, "nvls") == 0) { h->allow_nvls = value != 0; return QP_OK; }
+    if (std::strcmp(key, "rsag") == 0) { h->rsag_mode = (int)value; return QP_OK; }
     if (std::strcmp(key, "c2_dbg") == 0) { h->c2_dbg = (int)value; return QP_OK; }
     if (std::strcmp(key, "tc_passes") == 0) {
         if (value != 1 && value != 3) return fail(QP_EINVAL, "tc_passes must be 3 (3xTF32) or 1 (TF32)");

@@ -47,6 +47,7 @@ struct EpC2Args {
     int Nh;                          // MMA N per CTA: Hh rounded up to 8
     unsigned long long* published;
     unsigned long long* pdata[8];    // several GPUs: every rank's exchange block (see EpTcArgs)
+    int rsag;                        // 1: reduce-scatter + all-gather (two NVLink crossings, 1/4 of the bytes at eight ranks), 0: all-to-all
     unsigned long long* mc_pdata;    // the same block through its multicast address (NVLS), or null: one store reaches every rank
     int64_t p_pad;
     int dbg_mode;                    // timing experiments (option "c2_dbg"); 0 in every real run
@@ -121,6 +122,132 @@ __device__ __forceinline__ void c2_tma_store_4d(const CUtensorMap* tmap, const v
     asm volatile("cp.async.bulk.tensor.4d.global.shared::cta.bulk_group [%0, {%2, %3, %4, %5}], [%1];\n" ::"l"(tmap),
                  "r"((uint32_t)__cvta_generic_to_shared(smem_src)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
                  : "memory");
+}
+
+// The share exchange of phase B between the GPUs of a node (world > 1): takes this rank's sum of parameter p, returns the
+// sum over all ranks (the same bits everywhere).  kRsag picks the scheme at compile time: the kernel sits at its register
+// limit, and carrying both schemes (or a call) costs spills that slow every phase.
+template <bool kRsag>
+__device__ __forceinline__ float c2_share_exchange(const EpC2Args& x, float g, int64_t p, int32_t sidx, int cta) {
+    const EpisodeArgs& ea = x.ea;
+    if constexpr (kRsag) {
+            // ---- gradient all-reduce as reduce-scatter + all-gather over NVLink peer memory (eight ranks: the all-to-all
+            // below makes every GPU take in world - 1 copies of the whole gradient per step, 2.3 MB, which is what
+            // bounds it).  The chunk of CTA c belongs to rank c mod world.  Every other rank sends its local sum there,
+            // {value, step tag} in one 64-bit store; the owner adds the world values in rank order and sends the result
+            // back to everybody (one multicast store where there is NVLS), tagged the same way.  No fence, no flag; two
+            // NVLink crossings, 0.6 MB taken in per GPU and step.
+            const int owner = cta % ea.world;
+            const unsigned int want = ea.flag_base + (unsigned int)sidx + 1u;
+            const size_t slot = (size_t)(want & 1u) * (size_t)ea.world;
+            const unsigned long long* local = x.pdata[ea.rank] + slot * (size_t)x.p_pad + p;
+            unsigned long long t0 = 0;
+            auto overdue = [&](unsigned int spins) {
+                if ((spins & 4095u) == 4095u) {
+                    unsigned long long t;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                    if (t0 == 0) t0 = t;
+                    else if (t - t0 > 20000000000ull) __trap();   // a rank never arrived: fail instead of hanging
+                }
+            };
+            if (ea.rank != owner) {
+                const unsigned long long mine = ((unsigned long long)want << 32) | (unsigned long long)__float_as_uint(g);
+                asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(x.pdata[owner] + (slot + (size_t)ea.rank) * (size_t)x.p_pad + p),
+                             "l"(mine) : "memory");
+                for (unsigned int spins = 0;; ++spins) {        // the owner's sum arrives in the plane of the owner's rank
+                    unsigned long long v;
+                    asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(local + (size_t)owner * (size_t)x.p_pad) : "memory");
+                    if ((unsigned int)(v >> 32) == want) { g = __uint_as_float((unsigned int)v); break; }
+                    overdue(spins);
+                }
+            } else {
+                float pv[8];
+#pragma unroll
+                for (int r = 0; r < 8; ++r) pv[r] = 0.0f;
+                pv[ea.rank & 7] = g;
+                unsigned int pending = ((1u << ea.world) - 1u) & ~(1u << ea.rank);
+                for (unsigned int spins = 0; pending != 0u; ++spins) {
+                    unsigned long long vv[8];
+#pragma unroll
+                    for (int r = 0; r < 8; ++r)
+                        if ((pending >> r) & 1u)
+                            asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(vv[r]) : "l"(local + (size_t)r * (size_t)x.p_pad) : "memory");
+#pragma unroll
+                    for (int r = 0; r < 8; ++r)
+                        if (((pending >> r) & 1u) && (unsigned int)(vv[r] >> 32) == want) {
+                            pv[r] = __uint_as_float((unsigned int)vv[r]);
+                            pending &= ~(1u << r);
+                        }
+                    overdue(spins);
+                }
+                g = 0.0f;
+#pragma unroll
+                for (int r = 0; r < 8; ++r) g += pv[r];
+                const unsigned long long res = ((unsigned long long)want << 32) | (unsigned long long)__float_as_uint(g);
+                if (x.mc_pdata) {
+                    asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" ::"l"(x.mc_pdata + (slot + (size_t)owner) * (size_t)x.p_pad + p),
+                                 "l"(res) : "memory");
+                } else {
+#pragma unroll
+                    for (int r = 0; r < 8; ++r)
+                        if (r < ea.world && r != ea.rank)
+                            asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(x.pdata[r] + (slot + (size_t)owner) * (size_t)x.p_pad + p),
+                                         "l"(res) : "memory");
+                }
+            }
+    } else {
+
+            // ---- gradient all-reduce over NVLink peer memory, share by share and without a fence: every value travels
+            // as one 8-byte store {value, step tag} into the slot this rank owns in every peer's exchange block (posted
+            // writes, one NVLink crossing); the receiver spins on its LOCAL slots until the tag is this step's, then adds
+            // the values in rank order — the same bits on every rank.  Two buffers by (global) step parity.
+            const unsigned int want = ea.flag_base + (unsigned int)sidx + 1u;
+            const size_t slot = (size_t)(want & 1u) * (size_t)ea.world;
+            const unsigned long long mine = ((unsigned long long)want << 32) | (unsigned long long)__float_as_uint(g);
+            if (x.mc_pdata) {
+                // NVLS: one store to the multicast address; the switch delivers it into the slot [parity][this rank][p] of
+                // EVERY rank's block (this rank's included): one NVLink crossing of 8 bytes instead of world - 1
+                asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" ::"l"(x.mc_pdata + (slot + (size_t)ea.rank) * (size_t)x.p_pad + p),
+                             "l"(mine) : "memory");
+            } else {
+#pragma unroll
+                for (int r = 0; r < 8; ++r)
+                    if (r < ea.world && r != ea.rank)
+                        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(x.pdata[r] + (slot + (size_t)ea.rank) * (size_t)x.p_pad + p),
+                                     "l"(mine) : "memory");
+            }
+            const unsigned long long* local = x.pdata[ea.rank] + slot * (size_t)x.p_pad + p;
+            float pv[8];
+#pragma unroll
+            for (int r = 0; r < 8; ++r) pv[r] = 0.0f;
+            pv[ea.rank & 7] = g;
+            unsigned int pending = ((1u << ea.world) - 1u) & ~(1u << ea.rank);
+            unsigned long long t0 = 0;
+            for (unsigned int spins = 0; pending != 0u; ++spins) {
+                unsigned long long vv[8];
+#pragma unroll
+                for (int r = 0; r < 8; ++r)
+                    if ((pending >> r) & 1u)
+                        asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(vv[r])
+                                     : "l"(local + (size_t)r * (size_t)x.p_pad) : "memory");
+#pragma unroll
+                for (int r = 0; r < 8; ++r)
+                    if (((pending >> r) & 1u) && (unsigned int)(vv[r] >> 32) == want) {
+                        pv[r] = __uint_as_float((unsigned int)vv[r]);
+                        pending &= ~(1u << r);
+                    }
+                if ((spins & 4095u) == 4095u) {
+                    unsigned long long t;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                    if (t0 == 0) t0 = t;
+                    else if (t - t0 > 20000000000ull) __trap();   // a rank never arrived: fail instead of hanging
+                }
+            }
+            g = 0.0f;
+#pragma unroll
+            for (int r = 0; r < 8; ++r) g += pv[r];
+            }
+    return g;
 }
 
 #endif  // __CUDACC__

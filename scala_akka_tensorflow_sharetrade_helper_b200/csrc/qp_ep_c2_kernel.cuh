@@ -4,6 +4,10 @@
 namespace qp {
 #ifdef __CUDACC__
 
+// kXchg: 0 one GPU, 1 several GPUs with the all-to-all share exchange in phase B, 2 with reduce-scatter + all-gather.  A
+// template parameter because the kernel sits at the register limit of 384 threads per SM (168): each instantiation
+// carries only the scheme it runs, and every extra live value costs spills.
+template <int kXchg>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kC2Threads, 1)
 episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_constant__ CUtensorMap tW_lo,
                   const __grid_constant__ CUtensorMap tP, const EpC2Args x) {

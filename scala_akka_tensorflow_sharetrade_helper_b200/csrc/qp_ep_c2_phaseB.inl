@@ -16,17 +16,20 @@
         const int nsub = min(8, nthreads / ng4);
         const int gi = tid % ng4, sub = tid / ng4;
         if (sub < nsub) {
-            constexpr int kMaxRows = 16;                        // partials per thread: n1 <= 128, nsub >= ... see the host check
+            constexpr int kBatch = 8;                           // loads in flight per thread; at most 16 partials per thread (host check)
             const float* srcp = pb_src + pb_off + (size_t)gi * 4;
-            float4 v[kMaxRows];
+            float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+            for (int u0 = 0; u0 * nsub + sub < n1; u0 += kBatch) {
+                float4 v[kBatch];
 #pragma unroll
-            for (int u = 0; u < kMaxRows; ++u) {
-                const int j = sub + u * nsub;
-                v[u] = j < n1 ? __ldcg(reinterpret_cast<const float4*>(srcp + (size_t)j * pb_stride)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                for (int u = 0; u < kBatch; ++u) {
+                    const int j = sub + (u0 + u) * nsub;
+                    v[u] = j < n1 ? __ldcg(reinterpret_cast<const float4*>(srcp + (size_t)j * pb_stride)) : make_float4(0.f, 0.f, 0.f, 0.f);
+                }
+#pragma unroll
+                for (int u = 0; u < kBatch; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
             }
-            float4 s = v[0];
-#pragma unroll
-            for (int u = 1; u < kMaxRows; ++u) { s.x += v[u].x; s.y += v[u].y; s.z += v[u].z; s.w += v[u].w; }
             *reinterpret_cast<float4*>(red + (size_t)sub * pitch + gi * 4) = s;
         }
         __syncthreads();
@@ -37,57 +40,8 @@
             g = red[tid];
             for (int u = 1; u < nsub; ++u) g += red[(size_t)u * pitch + tid];
         }
-        if (ea.world > 1 && tid < pb_len) {
-            // ---- gradient all-reduce over NVLink peer memory, share by share and without a fence: every value travels
-            // as one 8-byte store {value, step tag} into the slot this rank owns in every peer's exchange block (posted
-            // writes, one NVLink crossing); the receiver spins on its LOCAL slots until the tag is this step's, then adds
-            // the values in rank order — the same bits on every rank.  Two buffers by (global) step parity.
-            const int64_t p = pb_p0 + tid;
-            const unsigned int want = ea.flag_base + (unsigned int)sidx + 1u;
-            const size_t slot = (size_t)(want & 1u) * (size_t)ea.world;
-            const unsigned long long mine = ((unsigned long long)want << 32) | (unsigned long long)__float_as_uint(g);
-            if (x.mc_pdata) {
-                // NVLS: one store to the multicast address; the switch delivers it into the slot [parity][this rank][p] of
-                // EVERY rank's block (this rank's included): one NVLink crossing of 8 bytes instead of world - 1
-                asm volatile("multimem.st.relaxed.sys.global.b64 [%0], %1;" ::"l"(x.mc_pdata + (slot + (size_t)ea.rank) * (size_t)x.p_pad + p),
-                             "l"(mine) : "memory");
-            } else {
-#pragma unroll
-                for (int r = 0; r < 8; ++r)
-                    if (r < ea.world && r != ea.rank)
-                        asm volatile("st.relaxed.sys.global.u64 [%0], %1;" ::"l"(x.pdata[r] + (slot + (size_t)ea.rank) * (size_t)x.p_pad + p),
-                                     "l"(mine) : "memory");
-            }
-            const unsigned long long* local = x.pdata[ea.rank] + slot * (size_t)x.p_pad + p;
-            float pv[8];
-#pragma unroll
-            for (int r = 0; r < 8; ++r) pv[r] = 0.0f;
-            pv[ea.rank & 7] = g;
-            unsigned int pending = ((1u << ea.world) - 1u) & ~(1u << ea.rank);
-            unsigned long long t0 = 0;
-            for (unsigned int spins = 0; pending != 0u; ++spins) {
-                unsigned long long vv[8];
-#pragma unroll
-                for (int r = 0; r < 8; ++r)
-                    if ((pending >> r) & 1u)
-                        asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(vv[r])
-                                     : "l"(local + (size_t)r * (size_t)x.p_pad) : "memory");
-#pragma unroll
-                for (int r = 0; r < 8; ++r)
-                    if (((pending >> r) & 1u) && (unsigned int)(vv[r] >> 32) == want) {
-                        pv[r] = __uint_as_float((unsigned int)vv[r]);
-                        pending &= ~(1u << r);
-                    }
-                if ((spins & 4095u) == 4095u) {
-                    unsigned long long t;
-                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-                    if (t0 == 0) t0 = t;
-                    else if (t - t0 > 20000000000ull) __trap();   // a rank never arrived: fail instead of hanging
-                }
-            }
-            g = 0.0f;
-#pragma unroll
-            for (int r = 0; r < 8; ++r) g += pv[r];
+        if constexpr (kXchg != 0) {
+            if (tid < pb_len) g = c2_share_exchange<kXchg == 2>(x, g, pb_p0 + tid, sidx, (int)blockIdx.x);
         }
         stamp(12);
         if (tid < pb_len) {

@@ -23,7 +23,7 @@ def _n_gpus():
         return 0
 
 
-def _worker(rank, world, port, out_dir, p2p, ep_tc, n_local, nvls=1):
+def _worker(rank, world, port, out_dir, p2p, ep_tc, n_local, nvls=1, rsag=-1):
     import torch
     import torch.distributed as dist
     import scala_akka_tensorflow_sharetrade_helper_b200 as q
@@ -37,6 +37,7 @@ def _worker(rank, world, port, out_dir, p2p, ep_tc, n_local, nvls=1):
     with q.QDecisionPolicy(q.PolicyConfig(bookkeeping=1, device=rank)) as pol:
         pol.set_weights(w)
         pol.set_option("ep_tc", ep_tc)
+        pol.set_option("rsag", rsag)
         pol.dist_init(dist, rank, world, p2p=bool(p2p), nvls=bool(nvls))
         pol.env_create(prices, np.arange(count), 1000.0, 1, env_id_base=first)
         p2p_active = pol.get_option("p2p_active")
@@ -57,14 +58,16 @@ def _worker(rank, world, port, out_dir, p2p, ep_tc, n_local, nvls=1):
     dist.destroy_process_group()
 
 
-# (world, p2p, ep_tc, episodes per rank, nvls)
-CASES = [(2, 1, 1, N_LOCAL, 1), (2, 1, 1, N_LOCAL, 0), (2, 1, 0, N_LOCAL, 1), (2, 0, 0, N_LOCAL, 1), (2, 1, 1, 5000, 1),
-         (4, 1, 1, N_LOCAL, 1), (4, 0, 0, N_LOCAL, 1), (8, 1, 1, N_LOCAL, 1), (8, 1, 1, N_LOCAL, 0), (8, 1, 0, N_LOCAL, 1),
-         (8, 1, 1, 5000, 1)]
+# (world, p2p, ep_tc, episodes per rank, nvls, rsag): rsag = 1 / 0 forces the share exchange to reduce-scatter + all-gather /
+# all-to-all, -1 leaves the choice to the library (reduce-scatter + all-gather from eight ranks on)
+CASES = [(2, 1, 1, N_LOCAL, 1, -1), (2, 1, 1, N_LOCAL, 0, -1), (2, 1, 1, N_LOCAL, 1, 1), (2, 1, 1, N_LOCAL, 0, 1), (2, 1, 0, N_LOCAL, 1, -1),
+         (2, 0, 0, N_LOCAL, 1, -1), (2, 1, 1, 5000, 1, -1),
+         (4, 1, 1, N_LOCAL, 1, -1), (4, 1, 1, N_LOCAL, 1, 1), (4, 0, 0, N_LOCAL, 1, -1),
+         (8, 1, 1, N_LOCAL, 1, -1), (8, 1, 1, N_LOCAL, 0, -1), (8, 1, 1, N_LOCAL, 1, 0), (8, 1, 0, N_LOCAL, 1, -1), (8, 1, 1, 5000, 1, -1)]
 
 
-@pytest.mark.parametrize("world,p2p,ep_tc,n_local,nvls", CASES)
-def test_n_gpus_match_one_gpu(tmp_path, world, p2p, ep_tc, n_local, nvls):
+@pytest.mark.parametrize("world,p2p,ep_tc,n_local,nvls,rsag", CASES)
+def test_n_gpus_match_one_gpu(tmp_path, world, p2p, ep_tc, n_local, nvls, rsag):
     """world ranks, one per GPU (skipped on boxes with fewer), against one GPU holding every episode.
     p2p = 1: gradient all-reduce inside the persistent kernel over NVLink peer memory (ep_tc = 1: the
     tensor-core kernel, share-by-share exchange; ep_tc = 0: the FFMA kernel, whole-gradient exchange);
@@ -80,7 +83,7 @@ def test_n_gpus_match_one_gpu(tmp_path, world, p2p, ep_tc, n_local, nvls):
         s.bind(("127.0.0.1", 0))
         port = s.getsockname()[1]
     ctx = mp.get_context("spawn")
-    procs = [ctx.Process(target=_worker, args=(r, world, port, str(tmp_path), p2p, ep_tc, n_local, nvls)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, str(tmp_path), p2p, ep_tc, n_local, nvls, rsag)) for r in range(world)]
     for p in procs:
         p.start()
     for p in procs:
