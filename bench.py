@@ -346,7 +346,7 @@ def run_ours(args):
                       ep_c2_active=int(pol.get_option("ep_c2_active")), nvls_active=int(pol.get_option("nvls_active")),
                       p2p_active=int(pol.get_option("p2p_active")), fused_step_active=int(pol.get_option("fused_step_active")),
                       tiles_per_sm=-(-((n_local + 31) // 32) // 148), params_digest=digest,
-                      share_exchange=("none" if world == 1 else ("reduce-scatter + all-gather" if (args.rsag == 1 or (args.rsag < 0 and world >= 8)) else "all-to-all")),
+                      share_exchange=("none" if world == 1 else ("reduce-scatter + all-gather" if pol.get_option("rsag_active") else "all-to-all")),
                       gradient_exchange=("none (one GPU)" if world == 1 else
                                          (("in-kernel exchange: one tagged 64-bit multicast store per share (multimem.st through the NVSwitch), "
                                            "no NCCL call in the step") if pol.get_option("nvls_active") else

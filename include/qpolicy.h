@@ -127,12 +127,26 @@ int qp_sync(qp_handle* h);
  *             fp32-grade).  Taken when the prices are tf32-exact (checked at qp_env_create) and the shape fits
  *             (window 193..203 at hidden 200); any number of episodes (waves).  Otherwise, and
  *             with 0, the FFMA form of the kernel runs, which needs the episodes to fit one 32-episode tile per SM.
+ *   "ep_c2"   the tensor-core kernel as CTA PAIRS (clusters of two) that split the hidden dimension: one 64-episode
+ *             tile per pair, each CTA holds half of W1^T's columns, Q-value halves meet over distributed shared
+ *             memory.  Taken when "ep_tc" is and the episodes fit one tile per pair (64 x SMs/2; 4736 on a B200) and
+ *             the shape fits (hidden a multiple of 8, <= 256; window + 50 <= 256 rows); otherwise, and with 0, the
+ *             one-CTA-per-tile tensor-core kernel runs (any number of episodes, in waves).
  *   "p2p"     several GPUs: gradient exchange inside the persistent kernel over NVLink peer memory
- *             (qp_dist_p2p_export / qp_dist_p2p_import); 0: one fused step kernel per env-step + NCCL all-reduce.
+ *             (qp_dist_p2p_export / qp_dist_p2p_import, or qp_dist_p2p_attach); 0: one fused step kernel per
+ *             env-step + NCCL all-reduce.
+ *   "nvls"    several GPUs, pair kernel, blocks attached with a multicast address: each share leaves as ONE
+ *             multimem store that the NVSwitch delivers to every rank; 0: world - 1 unicast stores.
+ *   "rsag"    several GPUs, pair kernel: 1 = the share exchange as reduce-scatter + all-gather (each share goes to ONE
+ *             owner rank, which adds the ranks' values in rank order and sends the sum to all), 0 = all-to-all (each
+ *             share to every rank, every rank adds), -1 (default) = reduce-scatter + all-gather from 8 ranks on.
+ *             Same sums bit for bit either way.
  *   "wide", "tc", "tc_passes"   the GEMM-organised path for policies whose W1 does not fit in shared memory.
- *   "phase_clocks"  tuning aid, see qp_debug_phase_clocks.
- * Read-only: "fused_active", "ep_tc_active", "p2p_active", "fused_step_active", "tc_active", "tc_a_lo_zero":
- * what the next qp_env_step would take. */
+ *   "phase_clocks"  tuning aid, see qp_debug_phase_clocks (1: CTA 0's phase stamps; 2: per-CTA wall-clock stamps;
+ *             3: fine stamps of the pair kernel).  "c2_dbg": reserved for timing experiments (no effect in this build).
+ * Read-only: "fused_active", "ep_tc_active", "ep_c2_active", "p2p_active", "nvls_active", "rsag_active",
+ * "fused_step_active", "tc_active", "tc_a_lo_zero": what the next qp_env_step would take.  With several GPUs all of
+ * them are facts the ranks have AGREED on at qp_env_create (the step protocols do not interoperate). */
 int qp_set_option(qp_handle* h, const char* key, int64_t value);
 int qp_get_option(qp_handle* h, const char* key, int64_t* value);
 /* Test hook for the tcgen05 tensor-core GEMM of the GEMM-organised path, on its own:
@@ -244,8 +258,8 @@ int qp_dist_nccl_version(int32_t* version);
  * in lock-step with the same n_steps.  If either call fails (no peer access) the NCCL path stays in use.
  * Call order with several GPUs: qp_dist_init, the p2p calls and every qp_set_option BEFORE qp_env_create —
  * qp_env_create is collective (one small NCCL MIN all-reduce) and fixes the execution path from what ALL
- * ranks can do (tf32-exact prices, tiles per SM, peer access), because the three multi-GPU step
- * protocols do not interoperate. */
+ * ranks can do (tf32-exact prices, tiles per SM or per CTA pair, peer access, multicast mapping, exchange
+ * scheme), because the multi-GPU step protocols do not interoperate. */
 #define QP_DIST_IPC_BYTES 64
 int qp_dist_p2p_export(qp_handle* h, void* out, size_t out_bytes);
 int qp_dist_p2p_import(qp_handle* h, const void* handles, int32_t world);

@@ -201,6 +201,7 @@ struct qp_handle {
     size_t c2_smem_bytes = 0;
     // several GPUs: what ALL ranks can do (MIN over the ranks at qp_env_create); a rank never picks a path alone
     bool agree_valid = false, agree_ep_tc = false, agree_fits = false, agree_fused = false, agree_p2p = false;
+    bool agree_c2 = false, agree_rsag = false, agree_nvls = false;   // pair kernel, its exchange scheme, multicast stores
     DevBuf<int32_t> flags4;             // small device scratch (tf32-exactness flag, rank agreement)
     int32_t* host_flag = nullptr;       // pinned: the flag's copy back rides on a synchronisation that happens anyway
     DevBuf<float> et_w_hi, et_w_lo;
@@ -678,9 +679,15 @@ bool ep_tc_usable(const qp_handle* h) {
 }
 
 // the pair kernel: one 64-episode tile per CTA pair (no waves), everything episode_tc_kernel needs plus its own shape limits
+bool ep_c2_local(const qp_handle* h) { return h->allow_ep_c2 && h->ep_c2_ready && h->n_envs <= (int64_t)kC2Envs * (h->c2_grid / 2); }
 bool ep_c2_usable(const qp_handle* h) {
-    return ep_tc_usable(h) && h->allow_ep_c2 && h->ep_c2_ready && h->n_envs <= (int64_t)kC2Envs * (h->c2_grid / 2);
+    return ep_tc_usable(h) && ep_c2_local(h) && (h->world == 1 || (h->agree_valid && h->agree_c2));
 }
+// several GPUs: the share-exchange scheme and the multicast stores, as ALL ranks have them (agreed at qp_env_create)
+bool c2_rsag_local(const qp_handle* h) { return h->rsag_mode == 1 || (h->rsag_mode < 0 && h->world >= 8); }
+bool c2_nvls_local(const qp_handle* h) { return h->p2p_mc != nullptr && h->allow_nvls; }
+bool c2_rsag(const qp_handle* h) { return h->world > 1 && c2_rsag_local(h) && h->agree_valid && h->agree_rsag; }
+bool c2_nvls(const qp_handle* h) { return h->world > 1 && c2_nvls_local(h) && h->agree_valid && h->agree_nvls; }
 
 // Which kernels serve qp_env_step.  With several GPUs every input of the decision is a fact ALL ranks share
 // (agreed at qp_env_create): the three multi-GPU step protocols do not interoperate.
@@ -792,17 +799,19 @@ int ep_tc_finish(qp_handle* h, bool flag_pending) {
     if (flag_pending && *h->host_flag != 0) h->ep_tc_ready = false;
     h->agree_valid = false;
     if (h->world > 1 && h->comm) {
-        const int32_t mine[4] = {
+        const int32_t mine[8] = {
             (h->allow_ep_tc && h->ep_tc_ready && h->et_flow_ok) ? 1 : 0,
             (h->n_envs <= (int64_t)kTileEnvs * h->num_sms) ? 1 : 0,
             (!h->wide && h->allow_fused && h->coop_launch && h->geo.ep_ok) ? 1 : 0,
-            (h->p2p_ready && h->allow_p2p) ? 1 : 0};
-        int32_t all[4] = {0, 0, 0, 0};
+            (h->p2p_ready && h->allow_p2p) ? 1 : 0,
+            ep_c2_local(h) ? 1 : 0, c2_rsag_local(h) ? 1 : 0, c2_nvls_local(h) ? 1 : 0, 0};
+        int32_t all[8] = {0, 0, 0, 0, 0, 0, 0, 0};
         QP_CUDA(cudaMemcpyAsync(h->flags4.p, mine, sizeof mine, cudaMemcpyHostToDevice, h->stream));
-        QP_NCCL(g_nccl.AllReduce(h->flags4.p, h->flags4.p, 4, kNcclInt32, kNcclMin, h->comm, h->stream));
+        QP_NCCL(g_nccl.AllReduce(h->flags4.p, h->flags4.p, 8, kNcclInt32, kNcclMin, h->comm, h->stream));
         QP_CUDA(cudaMemcpyAsync(all, h->flags4.p, sizeof all, cudaMemcpyDeviceToHost, h->stream));
         QP_CUDA(cudaStreamSynchronize(h->stream));
         h->agree_ep_tc = all[0] != 0; h->agree_fits = all[1] != 0; h->agree_fused = all[2] != 0; h->agree_p2p = all[3] != 0;
+        h->agree_c2 = all[4] != 0; h->agree_rsag = all[5] != 0; h->agree_nvls = all[6] != 0;
         h->agree_valid = true;
     }
     return QP_OK;
@@ -857,8 +866,8 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
         x.p_pad = (int64_t)p2p_pad(h);
         for (int r = 0; r < ea.world && ea.world > 1; ++r)
             x.pdata[r] = reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(h->p2p_peer_block[r]) + p2p_tc_offset(h));
-        x.rsag = h->rsag_mode == 1 || (h->rsag_mode < 0 && ea.world >= 8) ? 1 : 0;
-        x.mc_pdata = (ea.world > 1 && h->p2p_mc && h->allow_nvls)
+        x.rsag = (ea.world > 1 && c2_rsag(h)) ? 1 : 0;
+        x.mc_pdata = (ea.world > 1 && c2_nvls(h))
                          ? reinterpret_cast<unsigned long long*>(reinterpret_cast<char*>(h->p2p_mc) + p2p_tc_offset(h)) : nullptr;
         if (h->want_cta_ns) {        // [n_steps][grid][8]
             QP_TRY(h->dbg.ensure((size_t)n_steps * h->c2_grid * 8));
@@ -1036,7 +1045,7 @@ int qp_create(const qp_config* cfg, qp_handle** out) {
     QP_BAIL_CUDA(cudaStreamCreateWithFlags(&h->stream, cudaStreamNonBlocking));
     for (auto& e : h->ev) QP_BAIL_CUDA(cudaEventCreate(&e));
 #undef QP_BAIL_CUDA
-    if (h->params.ensure(h->P) || h->acc.ensure(h->P) || h->grad.ensure(h->P) || h->d_step.ensure(1) || h->flags4.ensure(4))
+    if (h->params.ensure(h->P) || h->acc.ensure(h->P) || h->grad.ensure(h->P) || h->d_step.ensure(1) || h->flags4.ensure(8))
         return bail(QP_ECUDA);
     if (cudaHostAlloc(reinterpret_cast<void**>(&h->host_flag), sizeof(int32_t), cudaHostAllocDefault) != cudaSuccess)
         return bail(fail(QP_ECUDA, "cudaHostAlloc failed"));
@@ -1903,9 +1912,10 @@ int qp_get_option(qp_handle* h, const char* key, int64_t* value) {
     }
     if (std::strcmp(key, "ep_c2_active") == 0) { *value = (h->has_env && use_fused(h) && ep_c2_usable(h)) ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "nvls_active") == 0) {
-        *value = (h->has_env && h->world > 1 && use_fused(h) && ep_c2_usable(h) && h->p2p_mc && h->allow_nvls) ? 1 : 0;
+        *value = (h->has_env && use_fused(h) && ep_c2_usable(h) && c2_nvls(h)) ? 1 : 0;
         return QP_OK;
     }
+    if (std::strcmp(key, "rsag_active") == 0) { *value = (h->has_env && use_fused(h) && ep_c2_usable(h) && c2_rsag(h)) ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "p2p_active") == 0) { *value = (h->has_env && h->world > 1 && use_fused(h)) ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "tc_a_lo_zero") == 0) { *value = h->tc_a_lo_zero ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "tc_active") == 0) { *value = (h->wide && h->allow_tc && h->tc_ready) ? 1 : 0; return QP_OK; }

@@ -1,10 +1,11 @@
 // qp_probe.cuh — a one-CTA test bench for single tcgen05.mma instructions (kind::tf32).
 //
-// The persistent kernels rest on operand layouts that no library builds for them (a price-window ring that is the
-// MN-major A operand of the forward contraction and, unchanged, the K-major A operand of the backward one).  This
-// kernel lets a test state such a layout as a plain byte image of shared memory plus the two 64-bit matrix
-// descriptors, issues the MMAs, and hands back all 128 lanes of the accumulator, so that every layout fact a kernel
-// relies on is pinned by a test against a numpy product (tests/test_gpu_umma_layouts.py).
+// The persistent kernels rest on operand layouts that no library builds for them (a price-window buffer whose rows,
+// from the row of window element 0 on, are the K-major A operand of the backward contraction; N = 104 per CTA; an
+// M = 64 accumulator read back lane by lane).  This kernel lets a test state such a layout as a plain byte image of
+// shared memory plus the two 64-bit matrix descriptors (or A as a block of tensor-memory columns), issues the MMAs,
+// and hands back all 128 lanes of the accumulator, so that every layout fact a kernel relies on is pinned by a test
+// against a numpy product (tests/test_gpu_umma_layouts.py; the explorations that led there: profiles/umma_*.py).
 #pragma once
 #include "qp_tc.cuh"
 
