@@ -192,6 +192,7 @@ struct qp_handle {
     int64_t snapshot_every = 500;
     // persistent kernel with tensor-core contractions (qp_ep_tc.cuh)
     bool allow_ep_tc = true, ep_tc_ready = false;   // qp_set_option("ep_tc", 0) keeps the FFMA persistent kernel
+    bool prices_exact = true;           // every price is a tf32 value (checked at qp_env_create)
     bool et_flow_ok = false;            // the shape takes phase B's bulk-copy branch (the only one with the NVLink exchange)
     // the same kernel on CTA pairs that split the hidden dimension (qp_ep_c2.cuh): the default where it applies
     bool allow_ep_c2 = true, ep_c2_ready = false;   // qp_set_option("ep_c2", 0) keeps episode_tc_kernel
@@ -673,16 +674,21 @@ int wide_prepare_tc(qp_handle* h) {
 size_t p2p_tc_offset(const qp_handle* h) { return (size_t)round_up(256 + (int64_t)2 * h->P * (int64_t)sizeof(float), 256); }
 size_t p2p_pad(const qp_handle* h) { return (size_t)round_up(h->P, 64); }
 
+// what both tensor-core persistent kernels need: the shape, the buffers, and (several GPUs) the flow form of phase B
+bool ep_tc_base(const qp_handle* h) { return h->allow_ep_tc && h->ep_tc_ready && (h->world == 1 || h->et_flow_ok); }
+// the one-tile-per-CTA kernel feeds the state matrix to the tensor core as it is: tf32-exact prices only
 bool ep_tc_usable(const qp_handle* h) {
-    const bool local = h->allow_ep_tc && h->ep_tc_ready && (h->world == 1 || h->et_flow_ok);
+    const bool local = ep_tc_base(h) && h->prices_exact;
     return h->world == 1 ? local : (local && h->agree_valid && h->agree_ep_tc);
 }
 
 // the pair kernel: one 64-episode tile per CTA pair (no waves), everything episode_tc_kernel needs plus its own shape limits
-bool ep_c2_local(const qp_handle* h) { return h->allow_ep_c2 && h->ep_c2_ready && h->n_envs <= (int64_t)kC2Envs * (h->c2_grid / 2); }
-bool ep_c2_usable(const qp_handle* h) {
-    return ep_tc_usable(h) && ep_c2_local(h) && (h->world == 1 || (h->agree_valid && h->agree_c2));
+// (prices that are not tf32-exact: 32 real + 32 virtual episodes per pair, see episode_c2_kernel's kSplit)
+int64_t c2_envs_per_pair(const qp_handle* h) { return h->prices_exact ? kC2Envs : kC2Envs / 2; }
+bool ep_c2_local(const qp_handle* h) {
+    return ep_tc_base(h) && h->allow_ep_c2 && h->ep_c2_ready && h->n_envs <= c2_envs_per_pair(h) * (h->c2_grid / 2);
 }
+bool ep_c2_usable(const qp_handle* h) { return ep_c2_local(h) && (h->world == 1 || (h->agree_valid && h->agree_c2)); }
 // several GPUs: the share-exchange scheme and the multicast stores, as ALL ranks have them (agreed at qp_env_create)
 bool c2_rsag_local(const qp_handle* h) { return h->rsag_mode == 1 || (h->rsag_mode < 0 && h->world >= 8); }
 bool c2_nvls_local(const qp_handle* h) { return h->p2p_mc != nullptr && h->allow_nvls; }
@@ -698,7 +704,7 @@ bool use_fused(const qp_handle* h) {
     const bool fits_local = h->n_envs <= (int64_t)kTileEnvs * h->num_sms;
     const bool fits = single ? fits_local : (fits_local && h->agree_fits);
     const bool fused_ok = !h->wide && h->allow_fused && h->coop_launch && h->geo.ep_ok && (single || h->agree_fused);
-    return fused_ok && (single || peers) && (fits || ep_tc_usable(h));
+    return fused_ok && (single || peers) && (fits || ep_tc_usable(h) || ep_c2_usable(h));
 }
 
 // The pair kernel (qp_ep_c2.cuh) on top of what ep_tc_prepare has set up; leaves ep_c2_ready false when the shape or
@@ -723,14 +729,14 @@ int ep_c2_prepare(qp_handle* h) {
         const int ng4 = pitch / 4, nsub = std::min(8, kC2Threads / std::max(1, ng4));
         if (pitch > kC2Threads || nsub < 1 || (grid / 2 + nsub - 1) / nsub > 16 || (size_t)8 * pitch * 4 > sm.op_bytes) return QP_OK;
     }
-    QP_CUDA(cudaFuncSetAttribute(episode_c2_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sm.total + 1024)));
-    QP_CUDA(cudaFuncSetAttribute(episode_c2_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sm.total + 1024)));
-    QP_CUDA(cudaFuncSetAttribute(episode_c2_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sm.total + 1024)));
+    for (auto* k : {episode_c2_kernel<0, false>, episode_c2_kernel<1, false>, episode_c2_kernel<2, false>,
+                    episode_c2_kernel<0, true>, episode_c2_kernel<1, true>, episode_c2_kernel<2, true>})
+        QP_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sm.total + 1024)));
     {   // all pairs must be co-resident (cooperative launch of clusters of two)
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kC2Threads); cfg.dynamicSmemBytes = sm.total + 1024; cfg.stream = h->stream;
         int n_clusters = 0;
-        if (cudaOccupancyMaxActiveClusters(&n_clusters, episode_c2_kernel<1>, &cfg) != cudaSuccess) { cudaGetLastError(); return QP_OK; }
+        if (cudaOccupancyMaxActiveClusters(&n_clusters, episode_c2_kernel<1, true>, &cfg) != cudaSuccess) { cudaGetLastError(); return QP_OK; }
         if (n_clusters * 2 < grid) return QP_OK;
     }
     QP_TRY(make_tmap(&h->tm_c2_hi, h->et_w_hi.p, h->et_Kp, hp.H, (uint64_t)h->et_Kp * sizeof(float), (uint32_t)Nh));
@@ -796,11 +802,11 @@ int ep_tc_prepare(qp_handle* h, bool* flag_pending) {
 // everything qp_env_create enqueued): read the exactness flag, and (several GPUs) agree on the execution path
 // with the other ranks.
 int ep_tc_finish(qp_handle* h, bool flag_pending) {
-    if (flag_pending && *h->host_flag != 0) h->ep_tc_ready = false;
+    h->prices_exact = !(flag_pending && *h->host_flag != 0);
     h->agree_valid = false;
     if (h->world > 1 && h->comm) {
         const int32_t mine[8] = {
-            (h->allow_ep_tc && h->ep_tc_ready && h->et_flow_ok) ? 1 : 0,
+            (h->allow_ep_tc && h->ep_tc_ready && h->et_flow_ok && h->prices_exact) ? 1 : 0,
             (h->n_envs <= (int64_t)kTileEnvs * h->num_sms) ? 1 : 0,
             (!h->wide && h->allow_fused && h->coop_launch && h->geo.ep_ok) ? 1 : 0,
             (h->p2p_ready && h->allow_p2p) ? 1 : 0,
@@ -856,8 +862,9 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
     }
     if (ep_c2_usable(h) && apply_in_kernel) {
         // CTA pairs that split the hidden dimension: one 64-episode tile per pair
-        const int64_t n_pairs = (h->n_envs + kC2Envs - 1) / kC2Envs;
+        const int64_t n_pairs = (h->n_envs + c2_envs_per_pair(h) - 1) / c2_envs_per_pair(h);
         EpC2Args x{};
+        x.split = h->prices_exact ? 0 : 1;
         x.ea = ea;
         x.w1T_hi = h->et_w_hi.p; x.w1T_lo = h->et_w_lo.p;
         x.Kp = h->et_Kp; x.nkb = h->et_nkb; x.Hh = h->c2_Hh; x.Nh = h->c2_Nh; x.dbg_mode = h->c2_dbg;
@@ -892,9 +899,10 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
         cudaLaunchAttribute at[1];
         at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1;      // (the cluster shape is the kernel's own attribute)
         cfg.attrs = at; cfg.numAttrs = 1;
-        if (ea.world > 1 && x.rsag) QP_CUDA(cudaLaunchKernelEx(&cfg, episode_c2_kernel<2>, h->tm_c2_hi, h->tm_c2_lo, h->tm_c2_part, x));
-        else if (ea.world > 1) QP_CUDA(cudaLaunchKernelEx(&cfg, episode_c2_kernel<1>, h->tm_c2_hi, h->tm_c2_lo, h->tm_c2_part, x));
-        else QP_CUDA(cudaLaunchKernelEx(&cfg, episode_c2_kernel<0>, h->tm_c2_hi, h->tm_c2_lo, h->tm_c2_part, x));
+        const int scheme = ea.world > 1 ? (x.rsag ? 2 : 1) : 0;
+        auto* kern = x.split ? (scheme == 2 ? episode_c2_kernel<2, true> : scheme == 1 ? episode_c2_kernel<1, true> : episode_c2_kernel<0, true>)
+                             : (scheme == 2 ? episode_c2_kernel<2, false> : scheme == 1 ? episode_c2_kernel<1, false> : episode_c2_kernel<0, false>);
+        QP_CUDA(cudaLaunchKernelEx(&cfg, kern, h->tm_c2_hi, h->tm_c2_lo, h->tm_c2_part, x));
         h->launches++;
         return QP_OK;
     }
@@ -1907,7 +1915,11 @@ int qp_get_option(qp_handle* h, const char* key, int64_t* value) {
     if (std::strcmp(key, "fused") == 0) { *value = h->allow_fused ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "wide") == 0) { *value = h->wide ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "ep_tc_active") == 0) {
-        *value = (h->has_env && use_fused(h) && ep_tc_usable(h)) ? 1 : 0;
+        *value = (h->has_env && use_fused(h) && (ep_tc_usable(h) || ep_c2_usable(h))) ? 1 : 0;
+        return QP_OK;
+    }
+    if (std::strcmp(key, "ep_c2_split_active") == 0) {
+        *value = (h->has_env && use_fused(h) && ep_c2_usable(h) && !h->prices_exact) ? 1 : 0;
         return QP_OK;
     }
     if (std::strcmp(key, "ep_c2_active") == 0) { *value = (h->has_env && use_fused(h) && ep_c2_usable(h)) ? 1 : 0; return QP_OK; }

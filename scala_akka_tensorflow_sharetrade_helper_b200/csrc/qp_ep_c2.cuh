@@ -51,6 +51,7 @@ struct EpC2Args {
     unsigned long long* mc_pdata;    // the same block through its multicast address (NVLS), or null: one store reaches every rank
     int64_t p_pad;
     int dbg_mode;                    // timing experiments (option "c2_dbg"); 0 in every real run
+    int split;                       // 1: prices not tf32-exact, 32 real + 32 virtual episodes per pair (host picks the instantiation)
     long long* cta_ns;               // tuning aid ("phase_clocks" = 2): [n_steps][gridDim][8] globaltimer stamps of every CTA
     long long* fine;                 // tuning aid ("phase_clocks" = 3): [n_steps][64] clock64 stamps inside the forward of CTA 0
 };
@@ -108,6 +109,15 @@ __device__ __forceinline__ uint32_t c2_cluster_rank() {
 __device__ __forceinline__ void c2_cluster_sync() {
     asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
     asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+// One of the twelve output-layer sums of an episode: this CTA's half plus the partner's, in an order both CTAs share
+// (kSplit: the two column subsets of the real episode's lane groups first).
+template <bool kSplit>
+__device__ __forceinline__ float c2_qsum(const float* qsum, int j, int el, int lane) {
+    if constexpr (kSplit)
+        return (qsum[j * kC2Envs + lane] + qsum[j * kC2Envs + 32 + lane]) + (qsum[(12 + j) * kC2Envs + lane] + qsum[(12 + j) * kC2Envs + 32 + lane]);
+    else
+        return qsum[j * kC2Envs + el] + qsum[(12 + j) * kC2Envs + el];
 }
 // address of the same shared-memory variable in the CTA with the given rank of this cluster
 __device__ __forceinline__ uint32_t c2_map_peer(const void* p, uint32_t rank) {

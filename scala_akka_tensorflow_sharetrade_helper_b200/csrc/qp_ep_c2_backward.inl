@@ -99,7 +99,10 @@
         ++mma_it;
     }
     // ---- S7: slide the window: the next price of every episode into the row after the window's last
-    if (wsub == 0) *reinterpret_cast<float*>(XT + (size_t)g * 32768 + et_swz(roff + wn + 1, lane)) = p_next;
+    if (wsub == 0) {
+        const float p_hi = kSplit ? et_tf32(p_next) : p_next;
+        *reinterpret_cast<float*>(XT + (size_t)g * 32768 + et_swz(roff + wn + 1, lane)) = (kSplit && g == 1) ? p_next - p_hi : p_hi;
+    }
     tc_fence_before();
     __syncthreads();
     stamp(6);

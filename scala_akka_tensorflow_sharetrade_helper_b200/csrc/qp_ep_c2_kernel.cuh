@@ -7,7 +7,7 @@ namespace qp {
 // kXchg: 0 one GPU, 1 several GPUs with the all-to-all share exchange in phase B, 2 with reduce-scatter + all-gather.  A
 // template parameter because the kernel sits at the register limit of 384 threads per SM (168): each instantiation
 // carries only the scheme it runs, and every extra live value costs spills.
-template <int kXchg>
+template <int kXchg, bool kSplit>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kC2Threads, 1)
 episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_constant__ CUtensorMap tW_lo,
                   const __grid_constant__ CUtensorMap tP, const EpC2Args x) {
@@ -58,11 +58,16 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     const int c0 = (int)crank * Hh;                             // first hidden column of this CTA
     const int64_t pair = (int64_t)(blockIdx.x >> 1);
     const int64_t B = a.B;
-    const int64_t n_pairs = (B + kC2Envs - 1) / kC2Envs;
+    // kSplit: prices that are not tf32-exact.  A pair then owns 32 episodes, whose windows lie in the buffer twice: block 0
+    // holds tf32(x), block 1 the remainder x - tf32(x) as the windows of 32 VIRTUAL episodes.  The window part of layer 1
+    // is linear in x, so the same MMAs give z(x_hi) and z(x_lo) in separate rows (added after the TMEM load), and the
+    // backward contraction over [32 real | 32 virtual] rows with dZ1 written to both blocks is X_hi^T dZ1 + X_lo^T dZ1.
+    constexpr int kEpp = kSplit ? 32 : kC2Envs;                 // real episodes per pair
+    const int64_t n_pairs = (B + kEpp - 1) / kEpp;
     const bool has_tile = pair < n_pairs;
     const int g = warp & 1, wsub = warp >> 1;                   // element-wise phases: lane group / column subset
     const int el = g * 32 + lane;                               // episode of this thread within the pair's 64
-    const int64_t e = pair * kC2Envs + el;
+    const int64_t e = pair * kEpp + (kSplit ? lane : el);
     const bool valid = has_tile && e < B;
     const int64_t ec = has_tile ? (valid ? e : B - 1) : 0;
     const float bias = hp.bias;
@@ -97,10 +102,18 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
             const int l = it & 31, k = ((it >> 5) << 5) + lane;
             const float* src = reinterpret_cast<const float*>(
                 __shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(my_row), l)) + ea.step0;
-            if (k <= wn) cp_async4(XT + (size_t)g * 32768 + et_swz(k, l), src + k);
+            if constexpr (kSplit) {
+                if (k <= wn) {
+                    const float v = __ldg(src + k), hi = et_tf32(v);
+                    *reinterpret_cast<float*>(XT + (size_t)g * 32768 + et_swz(k, l)) = g == 0 ? hi : v - hi;
+                }
+            } else {
+                if (k <= wn) cp_async4(XT + (size_t)g * 32768 + et_swz(k, l), src + k);
+            }
         }
         cp_async_commit();
         cp_async_wait_pending(0);
+        et_fence_async_smem();                                  // (the backward MMA reads the buffer through the async proxy)
     }
     const int64_t P1 = (int64_t)D * H, P = P1 + 3 * (int64_t)H;
     {   // K-major tf32 hi/lo copies of the current W1 (phase B keeps them current afterwards)
@@ -187,7 +200,7 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         ea.acc[pb_p0 + tid] = pb_a;
         ea.grad[pb_p0 + tid] = pb_g;
     }
-    if (has_tile && crank == 0 && wsub == 0 && valid) {
+    if (has_tile && crank == 0 && wsub == 0 && valid && (!kSplit || g == 0)) {
         a.budget[e] = budget;
         a.shares[e] = shares;
         a.share_value[e] = share_value;

@@ -156,7 +156,11 @@
     {
         const uint64_t env_id = (uint64_t)(a.env_id_base + e);
         philox4x32_10((uint32_t)env_id, (uint32_t)(env_id >> 32), (uint32_t)istep, 1u, (uint32_t)hp.seed, (uint32_t)(hp.seed >> 32), rnd);
-        p_new = (double)*reinterpret_cast<const float*>(XT + (size_t)g * 32768 + et_swz(roff + wn, lane));
+        if constexpr (kSplit)      // tf32(x) + (x - tf32(x)) = x, exactly
+            p_new = (double)__fadd_rn(*reinterpret_cast<const float*>(XT + et_swz(roff + wn, lane)),
+                                      *reinterpret_cast<const float*>(XT + 32768 + et_swz(roff + wn, lane)));
+        else
+            p_new = (double)*reinterpret_cast<const float*>(XT + (size_t)g * 32768 + et_swz(roff + wn, lane));
         cur = __dadd_rn(budget, __dmul_rn((double)shares, share_value));
         if (wsub == 0 && (int64_t)istep + wn + 1 < a.T) p_next = __ldg(my_row + istep + wn + 1);
     }
@@ -202,12 +206,16 @@
         const float xb = __double2float_rn(budget), xs = (float)shares;
         const float xnb[3] = {__double2float_rn(nbc[0]), __double2float_rn(nbc[1]), __double2float_rn(nbc[2])};
         const float xns[3] = {(float)nsc[0], (float)nsc[1], (float)nsc[2]};
+        // (kSplit: the twelve warps share the columns of the 32 real episodes; z = z(x_hi) + z(x_lo); h goes to both blocks)
 #pragma unroll 2
-        for (int c = wsub; c < Hh; c += kC2Sub) {
-            const float wb = Wb[c], ws = Ws[c], zn = ZN[c * kC2EStride + el];
+        for (int c = kSplit ? 2 * wsub + g : wsub; c < Hh; c += kSplit ? 2 * kC2Sub : kC2Sub) {
+            const float wb = Wb[c], ws = Ws[c];
+            const float zn = kSplit ? ZN[c * kC2EStride + lane] + ZN[c * kC2EStride + 32 + lane] : ZN[c * kC2EStride + el];
+            const float zs = kSplit ? HS[c * kC2EStride + lane] + HS[c * kC2EStride + 32 + lane] : HS[c * kC2EStride + el];
             const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
-            const float h = et_hidden(HS[c * kC2EStride + el], xb, xs, wb, ws, bias);
-            HS[c * kC2EStride + el] = h;                        // from here on the tile holds h(s)
+            const float h = et_hidden(zs, xb, xs, wb, ws, bias);
+            if constexpr (kSplit) { HS[c * kC2EStride + lane] = h; HS[c * kC2EStride + 32 + lane] = h; }
+            else HS[c * kC2EStride + el] = h;                   // from here on the tile holds h(s)
             pq[0][0] = fmaf(h, w2.x, pq[0][0]); pq[0][1] = fmaf(h, w2.y, pq[0][1]); pq[0][2] = fmaf(h, w2.z, pq[0][2]);
 #pragma unroll
             for (int j = 0; j < 3; ++j) {
@@ -262,7 +270,7 @@
         // SelectionAction (QDecisionPolicyActor.scala:56-62), decision, reward: every warp of the lane group keeps its copy
 #pragma unroll
         for (int t = 0; t < 3; ++t) {
-            const float s = (qsum[t * kC2Envs + el] + qsum[(12 + t) * kC2Envs + el]) + bias;
+            const float s = c2_qsum<kSplit>(qsum, t, el, lane) + bias;
             q_s[t] = s > 0.0f ? s : 0.0f;
         }
         const float u = (float)(rnd[0] >> 8) * (1.0f / 16777216.0f);
@@ -281,7 +289,7 @@
 #pragma unroll
         for (int t = 0; t < 3; ++t) {
             const int jt = (1 + a_eff) * 3 + t;
-            const float s = (qsum[jt * kC2Envs + el] + qsum[(12 + jt) * kC2Envs + el]) + bias;
+            const float s = c2_qsum<kSplit>(qsum, jt, el, lane) + bias;
             q_n[t] = s > 0.0f ? s : 0.0f;
         }
         kn = argmax3(q_n);
@@ -310,8 +318,8 @@
             XE[el] = __double2float_rn(budget);
             XE[kC2Envs + el] = (float)shares;
             kns[el] = kn;
-            dz2s[el] = dz2;
-            if (valid && crank == 0) {
+            dz2s[el] = (kSplit && g == 1) ? 0.0f : dz2;         // (virtual episodes add nothing to dW2 and the budget / shares rows)
+            if (valid && crank == 0 && (!kSplit || g == 0)) {
                 const TraceDev& t = a.trace;
                 const int64_t ti = (int64_t)(istep - a.trace_step0) * B + e;
                 if (t.action_sel) t.action_sel[ti] = action;

@@ -32,7 +32,9 @@ def msft(golden_dir):
 def msft_path(pol):
     """The persistent kernel serves these episodes; which form of it is asserted where the test needs it."""
     assert pol.get_option("fused_active") == 1
-    return "c2" if pol.get_option("ep_c2_active") == 1 else ("tc" if pol.get_option("ep_tc_active") == 1 else "ffma")
+    if pol.get_option("ep_c2_active") == 1:
+        return "c2s" if pol.get_option("ep_c2_split_active") == 1 else "c2"
+    return "tc" if pol.get_option("ep_tc_active") == 1 else "ffma"
 
 
 def test_share_trade_helper_run_reference_bookkeeping(msft):
@@ -47,6 +49,8 @@ def test_share_trade_helper_run_reference_bookkeeping(msft):
         ports = pol.train(msft[None, :], soe, 2400.0, 0)
         assert pol.steps_total == 5846 and pol.steps_done == 5846
         path = msft_path(pol)
+        # cent quotes are not tf32 values: the tensor-core pair kernel takes them as tf32(x) + remainder
+        assert path == "c2s" and pol.get_option("ep_tc_active") == 1
         assert (ports == 2400.0).all()
         assert pol.portfolio_stats() == (2400.0, 0.0)
         b, s, v = pol.env_state()
@@ -85,7 +89,7 @@ def test_msft_rlpy_teacher_forced(msft, path, wscale):
     with make_policy(cfg, path=None if path == "default" else path) as pol:
         pol.env_create(prices, soe, 2400.0, 2)
         if path == "default":
-            msft_path(pol)
+            assert msft_path(pol) == "c2s"
         else:
             assert_path(pol, path)
         for i in (0, 1, 2900, 5845):
@@ -110,7 +114,7 @@ def test_msft_rlpy_free_running(msft):
         ref.append(o.env_step(1, trace=True)[0])
     with make_policy(cfg, params=w) as pol:
         pol.env_create(prices, soe, 2400.0, 0)
-        msft_path(pol)
+        assert msft_path(pol) == "c2s"
         tr = pol.env_step_trace(steps)
     R = {k: np.stack([r[k] for r in ref]) for k in ("action_sel", "action_eff", "explored", "k_next", "shares", "budget", "reward", "q_s")}
     diverged = (tr["action_sel"] != R["action_sel"]) | (tr["k_next"] != R["k_next"])

@@ -22,7 +22,14 @@ def q_mod():
     return q
 
 
-PATHS = {"c2": (1, 1, 1), "tc": (1, 1, 0), "ffma": (1, 0, 0), "three": (0, 0, 0)}    # name -> (fused, ep_tc, ep_c2)
+# name -> (fused, ep_tc, ep_c2).  "c2s" is the pair kernel on prices that are NOT tf32-exact (32 real + 32 virtual episodes
+# per pair: x = tf32(x) + remainder, both through the same MMAs); the test multiplies its prices by INEXACT for it.
+PATHS = {"c2": (1, 1, 1), "c2s": (1, 1, 1), "tc": (1, 1, 0), "ffma": (1, 0, 0), "three": (0, 0, 0)}
+INEXACT = np.float32(1.0371)
+
+
+def prices_for(path, prices):
+    return prices * INEXACT if path == "c2s" else prices
 
 
 def make_policy(cfg: O.Config, params=None, acc=None, fused=None, ep_tc=None, path=None):
@@ -55,6 +62,7 @@ def assert_path(pol, path):
     fused, ep_tc, ep_c2 = PATHS[path]
     got = (pol.get_option("fused_active"), pol.get_option("ep_tc_active"), pol.get_option("ep_c2_active"))
     assert got == (fused, ep_tc, ep_c2), f"path {path} not taken: (fused, ep_tc, ep_c2) active = {got}"
+    assert pol.get_option("ep_c2_split_active") == (1 if path == "c2s" else 0), f"path {path}: wrong form of the pair kernel"
 
 
 # ------------------------------------------------------------------------------------------------
@@ -188,7 +196,7 @@ def test_update_q_batches(B, shape):
 # ------------------------------------------------------------------------------------------------
 # episode level
 # ------------------------------------------------------------------------------------------------
-@pytest.mark.parametrize("path", ["c2", "tc", "ffma", "three"])
+@pytest.mark.parametrize("path", ["c2", "c2s", "tc", "ffma", "three"])
 @pytest.mark.parametrize("bookkeeping", [O.REFERENCE, O.RLPY])
 @pytest.mark.parametrize("n_envs,N0", [(1, 0), (5, 3), (32, 1), (33, 0), (64, 1), (65, 1), (200, 2)])
 def test_env_step_teacher_forced(bookkeeping, n_envs, N0, path):
@@ -196,7 +204,7 @@ def test_env_step_teacher_forced(bookkeeping, n_envs, N0, path):
     everything the step produces is compared (tests/_teacher.py), on each of the three execution paths."""
     cfg = O.Config(bookkeeping=bookkeeping, seed=77)
     n_series = max(1, n_envs // 2)
-    prices = O.gen_prices(cfg.seed, 0, n_series, 400)        # quarter ticks: tf32-exact, as the tensor-core kernel requires
+    prices = prices_for(path, O.gen_prices(cfg.seed, 0, n_series, 400))    # quarter ticks: tf32-exact (c2s: times 1.0371, not exact)
     soe = (np.arange(n_envs) % n_series).astype(np.int32)
     w0 = (O.gen_normal(21, 0, cfg.P) * 0.05).astype(np.float32)
     o = O.Oracle(cfg, params=w0)
@@ -208,9 +216,9 @@ def test_env_step_teacher_forced(bookkeeping, n_envs, N0, path):
         for i in (0, 1, 57, 150, 198):
             teacher_forced_step(cfg, o, pol, prices, soe, i, f"{path} step {i}", tally)
     tally.assert_mostly_unforced()
-    if path == "c2":     # prices that are not tf32-exact keep the FFMA persistent kernel
-        with make_policy(cfg) as pol:
-            pol.env_create(prices * np.float32(1.0371), soe, 1000.0, N0)
+    if path == "tc":     # the one-tile-per-CTA kernel needs tf32-exact prices: without the pair kernel the FFMA form serves them
+        with make_policy(cfg, path="tc") as pol:
+            pol.env_create(prices * INEXACT, soe, 1000.0, N0)
             assert pol.get_option("ep_tc_active") == 0 and pol.get_option("fused_active") == 1
 
 
@@ -248,7 +256,7 @@ def test_golden_episodes_free_running(golden_dir, name, path):
         np.testing.assert_array_equal(ports, g["portfolios"])
 
 
-@pytest.mark.parametrize("path", ["c2", "tc"])
+@pytest.mark.parametrize("path", ["c2", "c2s", "tc"])
 def test_tensor_core_kernel_free_running_exploit_branch(path):
     """The tensor-core persistent kernel free-running against the oracle with the reference's ε schedule in its
     exploit regime (steps 600..629: 60-63 % of the actions are argmax Q(s), QDecisionPolicyActor.scala:58-60), four
@@ -256,7 +264,7 @@ def test_tensor_core_kernel_free_running_exploit_branch(path):
     be a tolerated one (oracle's top-two gap inside the Q tolerance at the weights of that step)."""
     cfg = O.Config(bookkeeping=O.RLPY, lr=1e-4, seed=17)
     n, T, i0, steps = 128, 900, 600, 30
-    prices = O.gen_prices(cfg.seed, 0, n, T)
+    prices = prices_for(path, O.gen_prices(cfg.seed, 0, n, T))
     soe = np.arange(n, dtype=np.int32)
     w = (O.gen_normal(6, 0, cfg.P) * 0.05).astype(np.float32)
     o = O.Oracle(cfg, params=w)
@@ -444,7 +452,7 @@ def test_persistent_tensor_core_kernel_other_shapes(shape):
     tally.assert_mostly_unforced()
 
 
-@pytest.mark.parametrize("path", ["c2", "tc"])
+@pytest.mark.parametrize("path", ["c2", "c2s", "tc"])
 def test_persistent_tensor_core_kernel_ring_wraps(path):
     """330 env-steps in ONE launch.  tc: the window ring (256 rows) wraps more than once, every row block of the
     dW1 partial takes the wrapped-store path in turn; c2: the window buffer is copied back to its top six times.  step_div is huge, so the ε-greedy threshold stays 0 and
@@ -452,7 +460,7 @@ def test_persistent_tensor_core_kernel_ring_wraps(path):
     tensor-core kernel, the FFMA kernel and the oracle, and Q / weights can be compared all the way."""
     cfg = O.Config(bookkeeping=O.RLPY, lr=1e-5, seed=31, step_div=1e12)      # (lr small enough to keep the ReLUs alive)
     n, T, steps = 96, 201 + 340, 330
-    prices = O.gen_prices(cfg.seed, 0, n, T)
+    prices = prices_for(path, O.gen_prices(cfg.seed, 0, n, T))
     soe = np.arange(n, dtype=np.int32)
     w = (O.gen_normal(4, 0, cfg.P) * 0.05).astype(np.float32)
     res = []
@@ -653,7 +661,7 @@ def test_first_step_of_full_batch_against_oracle():
     tally.assert_mostly_unforced()
 
 
-@pytest.mark.parametrize("path", ["c2", "tc"])
+@pytest.mark.parametrize("path", ["c2", "c2s", "tc"])
 @pytest.mark.parametrize("bookkeeping", [O.REFERENCE, O.RLPY])
 def test_bench_regime_unscaled_weights_teacher_forced(bookkeeping, path):
     """bench.py's own numeric regime on the headline kernel: BASELINE.json configs[1] — 4096 episodes, seed-42
@@ -661,8 +669,8 @@ def test_bench_regime_unscaled_weights_teacher_forced(bookkeeping, path):
     QDecisionPolicyActor.scala:41, :45; |Q| ~ 1e4..1e5), teacher-forced at the first, second, a middle and the
     last env-step of the episode.  The 2xTF32 split (22-bit products) is held to the same tolerance here."""
     cfg = O.Config(bookkeeping=bookkeeping, seed=42)
-    n = 4096
-    prices = O.gen_prices(42, 0, n, 1000)
+    n = 2368 if path == "c2s" else 4096                 # (c2s: as many episodes as the pair kernel takes at 32 per pair)
+    prices = prices_for(path, O.gen_prices(42, 0, n, 1000))
     soe = np.arange(n, dtype=np.int32)
     o = O.Oracle(cfg)                                   # params = gen_normal(42, 0, P), as qp_create
     o.env_create(prices, soe, 1000.0, 0)
