@@ -557,7 +557,7 @@ int enqueue_env_step_wide(qp_handle* h, const TraceDev* trace, int32_t trace_ste
         h->launches += 1;
     }
     const int row_blocks = (int)std::min<int64_t>((B + 7) / 8, (int64_t)h->num_sms * 4);
-    wide_row_kernel<<<row_blocks, 256, (size_t)hp.H * 6 * sizeof(float), h->stream>>>(a);
+    wide_row_kernel<0><<<row_blocks, 256, (size_t)hp.H * 6 * sizeof(float), h->stream>>>(a);
     QP_CUDA(cudaGetLastError());
     wide_dw2_kernel<<<dim3(colblocks, S2), 256, 0, h->stream>>>(a);
     QP_CUDA(cudaGetLastError());
@@ -1048,7 +1048,9 @@ int qp_create(const qp_config* cfg, qp_handle** out) {
     QP_BAIL_CUDA(cudaFuncSetAttribute(dw1_big_kernel<kMsgUpdate>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     QP_BAIL_CUDA(cudaFuncSetAttribute(episode_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     QP_BAIL_CUDA(cudaFuncSetAttribute(episode_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
-    QP_BAIL_CUDA(cudaFuncSetAttribute(wide_row_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(wide_row_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(wide_row_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
+    QP_BAIL_CUDA(cudaFuncSetAttribute(wide_row_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, h->max_smem));
     {
         int coop = 0;
         QP_BAIL_CUDA(cudaDeviceGetAttribute(&coop, cudaDevAttrCooperativeLaunch, h->device));
@@ -1144,6 +1146,55 @@ int qp_get_last_grad(qp_handle* h, float* grad) {
     return QP_OK;
 }
 
+// SelectionAction / UpdateQ on the GEMM-organised path (policies whose W1 does not fit in shared memory): the rows the
+// caller hands over take the place of the price windows.  G1 (fp32 FFMA GEMM over the window part of the rows), the row
+// kernel in its message form, and for UpdateQ E2, G2 over all D inputs and the AdaGrad step.  msg = 1 select, 2 update.
+int wide_message(qp_handle* h, int msg, int64_t B, bool have_ids) {
+    const Hyper& hp = h->hp;
+    const int64_t Bpad = round_up(B, kTileEnvs);
+    const int tiles_m = (hp.D + kWgBM - 1) / kWgBM, tiles_n = (hp.H + kWgBN - 1) / kWgBN;
+    const int S = (int)std::max<int64_t>(1, std::min<int64_t>({(int64_t)32, B / 256 > 0 ? B / 256 : 1,
+                                                               (h->num_sms * 6 + tiles_m * tiles_n - 1) / (tiles_m * tiles_n)}));
+    const int colblocks = (hp.H + 255) / 256;
+    const int S2 = (int)std::max<int64_t>(1, std::min<int64_t>(B / 64 > 0 ? B / 64 : 1, (h->num_sms * 2) / colblocks));
+    const int64_t rows = msg == 1 ? B : 2 * B;
+    QP_TRY(h->wZ1.ensure((size_t)rows * hp.H));
+    WideArgs a{};
+    a.hp = hp; a.params = h->params.p; a.d_step = h->d_step.p;
+    a.B = B; a.Bpad = Bpad; a.Z1 = h->wZ1.p; a.msg = msg;
+    a.m_states = h->m_states.p; a.m_steps = h->m_steps.p; a.m_ids = have_ids ? h->m_ids.p : nullptr;
+    a.m_actions = h->m_actions.p; a.m_q = msg == 1 ? h->m_q.p : nullptr;
+    if (msg == 2) {
+        QP_TRY(h->wdZ1.ensure((size_t)B * hp.H));
+        QP_TRY(h->wdz2.ensure(B));
+        QP_TRY(h->wkn.ensure(B));
+        QP_TRY(h->xextra.ensure((size_t)Bpad * 2));
+        QP_TRY(h->part1.ensure((size_t)S * h->P1));
+        QP_TRY(h->part2.ensure((size_t)S2 * 3 * hp.H));
+        a.m_next = h->m_next.p; a.m_rewards = h->m_rewards.p;
+        a.dZ1 = h->wdZ1.p; a.xextra = h->xextra.p; a.kn = h->wkn.p; a.dz2 = h->wdz2.p;
+        a.part1 = h->part1.p; a.part2 = h->part2.p; a.n_split = S; a.n_split2 = S2;
+    }
+    wide_gemm_kernel<0><<<dim3((unsigned)((rows + kWgBM - 1) / kWgBM), tiles_n), kWgThreads, 0, h->stream>>>(a);
+    QP_CUDA(cudaGetLastError());
+    const int row_blocks = (int)std::min<int64_t>((B + 7) / 8, (int64_t)h->num_sms * 4);
+    if (msg == 1) {
+        wide_row_kernel<1><<<row_blocks, 256, (size_t)hp.H * 6 * sizeof(float), h->stream>>>(a);
+        QP_CUDA(cudaGetLastError());
+        h->launches += 2;
+        return QP_OK;
+    }
+    wide_row_kernel<2><<<row_blocks, 256, (size_t)hp.H * 6 * sizeof(float), h->stream>>>(a);
+    QP_CUDA(cudaGetLastError());
+    wide_dw2_kernel<<<dim3(colblocks, S2), 256, 0, h->stream>>>(a);
+    QP_CUDA(cudaGetLastError());
+    wide_gemm_kernel<1><<<dim3(tiles_m, tiles_n, S), kWgThreads, 0, h->stream>>>(a);
+    QP_CUDA(cudaGetLastError());
+    h->launches += 4;
+    QP_TRY(launch_apply(h, S, S2, 1, 1, 0));
+    return QP_OK;
+}
+
 int qp_select_action(qp_handle* h, const float* states, int64_t state_len, const float* steps,
                      const int64_t* env_ids, int32_t* actions, float* q_out, int64_t B) {
     if (!h || !states || !steps || !actions) return fail(QP_EINVAL, "null argument");
@@ -1152,7 +1203,6 @@ int qp_select_action(qp_handle* h, const float* states, int64_t state_len, const
                                    ") and state(" + std::to_string(state_len) + ") size do not match");
     if (B < 0) return fail(QP_EINVAL, "B < 0");
     if (B == 0) return QP_OK;
-    if (h->wide) return fail(QP_EUNSUPPORTED, "message-level SelectionAction is not available on the GEMM path yet; use qp_env_*");
     QP_TRY(use_device(h));
     const int D = h->hp.D;
     QP_TRY(h->m_states.ensure((size_t)B * D));
@@ -1163,12 +1213,16 @@ int qp_select_action(qp_handle* h, const float* states, int64_t state_len, const
     QP_CUDA(cudaMemcpyAsync(h->m_states.p, states, (size_t)B * D * sizeof(float), cudaMemcpyHostToDevice, h->stream));
     QP_CUDA(cudaMemcpyAsync(h->m_steps.p, steps, B * sizeof(float), cudaMemcpyHostToDevice, h->stream));
     if (env_ids) QP_CUDA(cudaMemcpyAsync(h->m_ids.p, env_ids, B * sizeof(int64_t), cudaMemcpyHostToDevice, h->stream));
-    StepArgs s{};
-    s.hp = h->hp; s.params = h->params.p;
-    s.states = h->m_states.p; s.steps = h->m_steps.p; s.env_ids = env_ids ? h->m_ids.p : nullptr;
-    s.actions_out = h->m_actions.p; s.q_out = h->m_q.p; s.B = B; s.Bpad = round_up(B, kTileEnvs);
-    const int grid = (int)std::min<int64_t>(s.Bpad / kTileEnvs, h->num_sms);
-    QP_TRY(launch_step<kMsgSelect>(h, s, grid));
+    if (h->wide) {
+        QP_TRY(wide_message(h, 1, B, env_ids != nullptr));
+    } else {
+        StepArgs s{};
+        s.hp = h->hp; s.params = h->params.p;
+        s.states = h->m_states.p; s.steps = h->m_steps.p; s.env_ids = env_ids ? h->m_ids.p : nullptr;
+        s.actions_out = h->m_actions.p; s.q_out = h->m_q.p; s.B = B; s.Bpad = round_up(B, kTileEnvs);
+        const int grid = (int)std::min<int64_t>(s.Bpad / kTileEnvs, h->num_sms);
+        QP_TRY(launch_step<kMsgSelect>(h, s, grid));
+    }
     QP_CUDA(cudaMemcpyAsync(actions, h->m_actions.p, B * sizeof(int32_t), cudaMemcpyDeviceToHost, h->stream));
     if (q_out) QP_CUDA(cudaMemcpyAsync(q_out, h->m_q.p, (size_t)B * 3 * sizeof(float), cudaMemcpyDeviceToHost, h->stream));
     QP_CUDA(cudaStreamSynchronize(h->stream));
@@ -1184,27 +1238,30 @@ int qp_update_q(qp_handle* h, const float* states, int64_t state_len, const floa
                                    std::to_string(next_state_len) + ") do not match");
     if (B < 0) return fail(QP_EINVAL, "B < 0");
     if (B == 0) return QP_OK;
-    if (h->wide) return fail(QP_EUNSUPPORTED, "message-level UpdateQ is not available on the GEMM path yet; use qp_env_*");
     QP_TRY(use_device(h));
     const int D = h->hp.D;
     int g1 = 0, g2 = 0;
-    QP_TRY(ensure_scratch(h, B, &g1, &g2));
+    if (!h->wide) QP_TRY(ensure_scratch(h, B, &g1, &g2));
     QP_TRY(h->m_states.ensure((size_t)B * D));
     QP_TRY(h->m_next.ensure((size_t)B * D));
     QP_TRY(h->m_rewards.ensure(B));
     QP_CUDA(cudaMemcpyAsync(h->m_states.p, states, (size_t)B * D * sizeof(float), cudaMemcpyHostToDevice, h->stream));
     QP_CUDA(cudaMemcpyAsync(h->m_next.p, next_states, (size_t)B * D * sizeof(float), cudaMemcpyHostToDevice, h->stream));
     QP_CUDA(cudaMemcpyAsync(h->m_rewards.p, rewards, B * sizeof(float), cudaMemcpyHostToDevice, h->stream));
-    StepArgs s{};
-    s.hp = h->hp; s.params = h->params.p;
-    s.states = h->m_states.p; s.next_states = h->m_next.p; s.rewards = h->m_rewards.p;
-    s.B = B; s.Bpad = h->Bpad; s.dz1 = h->dz1.p; s.xextra = h->xextra.p; s.dw2_part = h->part2.p;
-    QP_TRY(launch_step<kMsgUpdate>(h, s, g1));
-    Dw1Args d{};
-    d.hp = h->hp; d.states = h->m_states.p; d.Bpad = h->Bpad; d.dz1 = h->dz1.p; d.B = B; d.part = h->part1.p;
-    d.n_rt = h->geo.n_rt; d.cg_max = h->geo.cg_max;
-    QP_TRY(launch_dw1<kMsgUpdate>(h, d, g2));
-    QP_TRY(launch_apply(h, g2, g1, 1, 1, 0));
+    if (h->wide) {
+        QP_TRY(wide_message(h, 2, B, false));
+    } else {
+        StepArgs s{};
+        s.hp = h->hp; s.params = h->params.p;
+        s.states = h->m_states.p; s.next_states = h->m_next.p; s.rewards = h->m_rewards.p;
+        s.B = B; s.Bpad = h->Bpad; s.dz1 = h->dz1.p; s.xextra = h->xextra.p; s.dw2_part = h->part2.p;
+        QP_TRY(launch_step<kMsgUpdate>(h, s, g1));
+        Dw1Args d{};
+        d.hp = h->hp; d.states = h->m_states.p; d.Bpad = h->Bpad; d.dz1 = h->dz1.p; d.B = B; d.part = h->part1.p;
+        d.n_rt = h->geo.n_rt; d.cg_max = h->geo.cg_max;
+        QP_TRY(launch_dw1<kMsgUpdate>(h, d, g2));
+        QP_TRY(launch_apply(h, g2, g1, 1, 1, 0));
+    }
     QP_CUDA(cudaStreamSynchronize(h->stream));
     // if (iteration % 500 == 0 && iteration != 0) saveSnapshot(...)  — QDecisionPolicyActor.scala:74;
     // the reference's saveSnapshot is an empty stub (:91-93), here it writes a checkpoint if a path is set

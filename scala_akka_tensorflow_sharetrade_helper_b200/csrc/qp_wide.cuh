@@ -38,6 +38,11 @@ struct WideArgs {
     // xe_row0 on, then budget, shares), as a K-major tf32 hi/lo matrix [kWideMaxExtraRows, xe_ld]
     float* xe_hi; float* xe_lo; int64_t xe_ld; int xe_row0;
     TraceDev trace; int32_t trace_step0;
+    // message-level calls on explicit rows (SelectionAction / UpdateQ, QDecisionPolicyActor.scala:56-76): msg = 1 / 2.
+    // The state rows [B, D] replace the price windows and the episode record; Z1 holds B (select) or 2B (update) rows.
+    int msg;
+    const float* m_states; const float* m_next; const float* m_rewards; const float* m_steps; const int64_t* m_ids;
+    int32_t* m_actions; float* m_q;
 };
 
 #ifdef __CUDACC__
@@ -55,9 +60,9 @@ __global__ void __launch_bounds__(kWgThreads, 2) wide_gemm_kernel(const WideArgs
     const Hyper& hp = a.hp;
     const int tid = threadIdx.x;
     const int H = hp.H, wn = hp.wn, D = hp.D;
-    const int32_t istep = *a.d_step;
+    const int32_t istep = a.msg ? 0 : *a.d_step;
     const int64_t B = a.B;
-    const int64_t M = (MODE == 0) ? 2 * B : (int64_t)D;
+    const int64_t M = (MODE == 0) ? (a.msg == 1 ? B : 2 * B) : (int64_t)D;
     const int64_t m0 = (int64_t)blockIdx.x * kWgBM;
     const int n0 = blockIdx.y * kWgBN;
     int64_t k_begin = 0, k_end = wn;
@@ -84,7 +89,8 @@ __global__ void __launch_bounds__(kWgThreads, 2) wide_gemm_kernel(const WideArgs
                 float v = 0.0f;
                 if (m < M && k < k_end) {
                     const int64_t e = m < B ? m : m - B;
-                    v = __ldg(a.prices + (int64_t)a.series_of_env[e] * a.T + istep + (m < B ? 0 : 1) + k);
+                    if (a.msg) v = __ldg((m < B ? a.m_states : a.m_next) + e * D + k);
+                    else v = __ldg(a.prices + (int64_t)a.series_of_env[e] * a.T + istep + (m < B ? 0 : 1) + k);
                 }
                 ra[j] = v;
             }
@@ -95,7 +101,9 @@ __global__ void __launch_bounds__(kWgThreads, 2) wide_gemm_kernel(const WideArgs
             for (int j = 0; j < 8; ++j) {
                 const int64_t e = kt + (tid >> 7) + 2 * j;
                 float v = 0.0f;
-                if (e < k_end) {
+                if (e < k_end && a.msg) {
+                    if (m < D) v = __ldg(a.m_states + e * D + m);
+                } else if (e < k_end) {
                     if (m < wn) v = __ldg(a.prices + (int64_t)a.series_of_env[e] * a.T + istep + m);
                     else if (m == wn) v = a.xextra[e];
                     else if (m == wn + 1) v = a.xextra[a.Bpad + e];
@@ -187,6 +195,7 @@ __device__ __forceinline__ float wide_hidden(float zwin, float xb, float xs, flo
 // ---------------------------------------------------------------------------------------------
 constexpr int kWideMaxColsPerLane = 64;   // hidden <= 2048 on this path
 
+template <int MSG>      // 0: env-step; 1: SelectionAction rows; 2: UpdateQ rows
 __global__ void __launch_bounds__(256) wide_row_kernel(const WideArgs a) {
     extern __shared__ __align__(16) float smem[];
     const Hyper& hp = a.hp;
@@ -207,15 +216,17 @@ __global__ void __launch_bounds__(256) wide_row_kernel(const WideArgs a) {
         Ws[p] = W1g[(size_t)(wn + 1) * H + c];
     }
     __syncthreads();
-    const int32_t istep = *a.d_step;
+    const int32_t istep = MSG ? 0 : *a.d_step;
     const float bias = hp.bias;
     const int nchunk = H >> 7;               // float4 chunks of 128 columns per warp pass
 
     for (int64_t e = (int64_t)blockIdx.x * nwarps + warp; e < a.B; e += (int64_t)gridDim.x * nwarps) {
-        const double budget = a.budget[e], share_value = a.share_value[e];
-        const int32_t shares = a.shares[e];
-        const float* prow = a.prices + (int64_t)a.series_of_env[e] * a.T + istep;
-        const float xb = __double2float_rn(budget), xs = (float)shares;
+        const double budget = MSG ? 0.0 : a.budget[e], share_value = MSG ? 0.0 : a.share_value[e];
+        const int32_t shares = MSG ? 0 : a.shares[e];
+        const float* prow = MSG ? nullptr : a.prices + (int64_t)a.series_of_env[e] * a.T + istep;
+        // (message rows carry their own budget / shares entries: the last two elements of the state)
+        const float xb = MSG ? __ldg(a.m_states + e * D + wn) : __double2float_rn(budget);
+        const float xs = MSG ? __ldg(a.m_states + e * D + wn + 1) : (float)shares;
         const float4* zs4 = reinterpret_cast<const float4*>(a.Z1 + e * H);
         const float4* zn4 = reinterpret_cast<const float4*>(a.Z1 + (a.B + e) * H);
 
@@ -224,7 +235,7 @@ __global__ void __launch_bounds__(256) wide_row_kernel(const WideArgs a) {
         float4 zsv[kWideMaxColsPerLane / 4], znv[kWideMaxColsPerLane / 4];
 #pragma unroll
         for (int j = 0; j < kWideMaxColsPerLane / 4; ++j)
-            if (j < nchunk) { zsv[j] = __ldcs(zs4 + j * 32 + lane); znv[j] = __ldcs(zn4 + j * 32 + lane); }
+            if (j < nchunk) { zsv[j] = __ldcs(zs4 + j * 32 + lane); if (MSG != 1) znv[j] = __ldcs(zn4 + j * 32 + lane); }
 
         // hidden layer of s and its Q-values (QDecisionPolicyActor.scala:43, :47)
         float hs[kWideMaxColsPerLane];
@@ -249,20 +260,28 @@ __global__ void __launch_bounds__(256) wide_row_kernel(const WideArgs a) {
         for (int x = 0; x < 3; ++x) { const float s = warp_sum(pq[x]) + bias; q_s[x] = s > 0.0f ? s : 0.0f; }
 
         // SelectionAction (:56-62)
-        int action, explored = 0;
-        {
-            const uint64_t env_id = (uint64_t)(a.env_id_base + e);
+        int action = 0, explored = 0;
+        if (MSG != 2) {
+            const float step_f = MSG ? a.m_steps[e] : (float)istep;
+            const uint64_t env_id = MSG ? (uint64_t)(a.m_ids ? a.m_ids[e] : e) : (uint64_t)(a.env_id_base + e);
             uint32_t r[4];
-            philox4x32_10((uint32_t)env_id, (uint32_t)(env_id >> 32), (uint32_t)istep, 1u,
+            philox4x32_10((uint32_t)env_id, (uint32_t)(env_id >> 32), MSG ? (uint32_t)step_f : (uint32_t)istep, 1u,
                           (uint32_t)hp.seed, (uint32_t)(hp.seed >> 32), r);
             const float u = (float)(r[0] >> 8) * (1.0f / 16777216.0f);
-            float thr = __fdiv_rn((float)istep, hp.step_div);
+            float thr = __fdiv_rn(step_f, hp.step_div);
             if (hp.epsilon < thr) thr = hp.epsilon;
             if (u < thr) action = argmax3(q_s);
             else { explored = 1; action = (int)(((uint64_t)r[1] * 3u) >> 32); }
         }
+        if (MSG == 1) {
+            if (lane == 0) {
+                a.m_actions[e] = action;
+                if (a.m_q) { a.m_q[e * 3] = q_s[0]; a.m_q[e * 3 + 1] = q_s[1]; a.m_q[e * 3 + 2] = q_s[2]; }
+            }
+            continue;
+        }
         // decision, reward, next state (TrainerChildActor.scala:92-96, :118-123, :136-146)
-        const double p_new = (double)__ldg(prow + wn);
+        const double p_new = MSG ? 0.0 : (double)__ldg(prow + wn);
         const double cur = __dadd_rn(budget, __dmul_rn((double)shares, share_value));
         const double base_b = hp.bookkeeping == 0 ? a.B0 : budget;
         const int32_t base_n = hp.bookkeeping == 0 ? a.N0 : shares;
@@ -270,8 +289,9 @@ __global__ void __launch_bounds__(256) wide_row_kernel(const WideArgs a) {
         if (action == 0 && base_b >= p_new) { nb = __dsub_rn(base_b, p_new); ns = base_n + 1; a_eff = 0; }
         else if (action == 1 && base_n > 0) { nb = __dadd_rn(base_b, p_new); ns = base_n - 1; a_eff = 1; }
         const double newp = __dadd_rn(nb, __dmul_rn((double)ns, p_new));
-        const float r32 = __double2float_rn(__dsub_rn(newp, cur));
-        const float xnb = __double2float_rn(nb), xns = (float)ns;
+        const float r32 = MSG ? a.m_rewards[e] : __double2float_rn(__dsub_rn(newp, cur));
+        const float xnb = MSG ? __ldg(a.m_next + e * D + wn) : __double2float_rn(nb);
+        const float xns = MSG ? __ldg(a.m_next + e * D + wn + 1) : (float)ns;
 
         // Q-values of s'
         pq[0] = pq[1] = pq[2] = 0.0f;
@@ -315,7 +335,7 @@ __global__ void __launch_bounds__(256) wide_row_kernel(const WideArgs a) {
                 dz4[c >> 2] = make_float4(v[0], v[1], v[2], v[3]);
             }
         }
-        if (a.xe_hi && lane < D - a.xe_row0) {
+        if (MSG == 0 && a.xe_hi && lane < D - a.xe_row0) {
             const int m = a.xe_row0 + lane;
             const float x = m < wn ? __ldg(prow + m) : (m == wn ? xb : xs);
             uint32_t t;
@@ -327,6 +347,9 @@ __global__ void __launch_bounds__(256) wide_row_kernel(const WideArgs a) {
         if (lane == 0) {
             a.xextra[e] = xb; a.xextra[a.Bpad + e] = xs;
             a.kn[e] = kn; a.dz2[e] = dz2;
+            if (MSG) {
+                if (a.m_q) { a.m_q[e * 3] = q_s[0]; a.m_q[e * 3 + 1] = q_s[1]; a.m_q[e * 3 + 2] = q_s[2]; }
+            } else {
             a.budget[e] = nb; a.shares[e] = ns; a.share_value[e] = p_new;
             const TraceDev& t = a.trace;
             const int64_t ti = (int64_t)(istep - a.trace_step0) * a.B + e;
@@ -340,6 +363,7 @@ __global__ void __launch_bounds__(256) wide_row_kernel(const WideArgs a) {
             if (t.shares) t.shares[ti] = ns;
             if (t.q_s) { t.q_s[ti * 3] = q_s[0]; t.q_s[ti * 3 + 1] = q_s[1]; t.q_s[ti * 3 + 2] = q_s[2]; }
             if (t.q_n) { t.q_n[ti * 3] = q_n[0]; t.q_n[ti * 3 + 1] = q_n[1]; t.q_n[ti * 3 + 2] = q_n[2]; }
+            }
         }
     }
 }

@@ -12,10 +12,13 @@ from tests.test_gpu_parity import make_policy, q_mod, states_of
 pytestmark = pytest.mark.gpu
 
 
-def test_enqueue_flush_equals_direct_batch():
-    """Eight 'child actors' on eight threads enqueue their messages; one flush answers them all."""
+@pytest.mark.parametrize("shape", [(201, 200), (62, 256)])
+def test_enqueue_flush_equals_direct_batch(shape):
+    """Eight 'child actors' on eight threads enqueue their messages; one flush answers them all.  (62, 256): a policy on
+    the GEMM-organised path (W1 outside the per-tile kernels' shared memory), where the message-level calls run G1 / row
+    kernel / G2."""
     q = q_mod()
-    cfg = O.Config(seed=3)
+    cfg = O.Config(wn=shape[0], hidden=shape[1], seed=3)
     n_threads, per = 8, 40
     n = n_threads * per
     rng = np.random.default_rng(0)
@@ -25,6 +28,7 @@ def test_enqueue_flush_equals_direct_batch():
     r = rng.uniform(-5, 5, n).astype(np.float32)
     steps = rng.integers(0, 1200, n).astype(np.float32)
     with make_policy(cfg, params=w) as direct, make_policy(cfg, params=w) as batched:
+        assert direct.get_option("wide") == (1 if shape[1] > 240 else 0)
         a_ref = direct.select_action(s, steps, np.arange(n))
         direct.update_q(s, r, s2)
         front = q.BatchingPolicy(batched)

@@ -585,11 +585,46 @@ def test_wide_path_matches_tile_path():
         np.testing.assert_array_equal(ta[k], tb[k], err_msg=k)
     np.testing.assert_allclose(ta["q_s"], tb["q_s"], rtol=1e-4, atol=1e-3)
     assert np.abs(wa - wb).max() <= 20 * _tol.W_ATOL
-    q = q_mod()
-    with make_policy(cfg, params=w) as pol:
-        pol.set_option("wide", 1)
-        with pytest.raises(q.QPolicyError, match="GEMM path"):
-            pol.select_action(np.zeros((1, cfg.D), np.float32), 0.0)
+
+
+@pytest.mark.parametrize("B", [1, 70, 300])
+@pytest.mark.parametrize("shape,wscale", [((513, 2048), 0.02), ((30, 128), 0.1)])
+def test_wide_policy_message_level_calls(shape, wscale, B):
+    """SelectionAction / UpdateQ (QDecisionPolicyActor.scala:56-76) on the GEMM-organised path — BASELINE.json
+    configs[3]'s 515 -> 2048 policy, whose W1 does not fit in shared memory — against the oracle, as
+    test_select_action_batches / test_update_q_batches do for the reference shape; and through the batching front-end."""
+    cfg = O.Config(wn=shape[0], hidden=shape[1], seed=13)
+    rng = np.random.default_rng(B + shape[1] + 1000)
+    w = (O.gen_normal(5, 0, cfg.P) * np.float32(wscale)).astype(np.float32)
+    acc = rng.uniform(0.5, 2.0, cfg.P).astype(np.float32)
+    x = rng.uniform(50, 150, (B, cfg.D)).astype(np.float32)
+    x2 = x + rng.uniform(-1, 1, (B, cfg.D)).astype(np.float32)
+    r = rng.uniform(-5, 5, B).astype(np.float32)
+    steps = rng.integers(0, 1200, B).astype(np.float32)
+    ids = rng.integers(0, 2 ** 40, B).astype(np.int64)
+    o = O.Oracle(cfg, params=w, acc=acc)
+    a_ref, q_ref, e_ref = o.select_action(x, steps, ids)
+    g_ref, info = o.td_grad(x, r, x2)
+    assert np.abs(g_ref).max() > 0, "fixture must produce a live gradient"
+    o.update_q(x, r, x2)
+    with make_policy(cfg, params=w, acc=acc) as pol:
+        if shape[1] <= 240:
+            pol.set_option("wide", 1)
+        assert pol.get_option("wide") == 1
+        a, qv = pol.select_action(x, steps, ids, return_q=True)
+        _tol.assert_q_close(cfg, w, x, qv, q_ref)
+        _tol.assert_actions_match(cfg, w, x, a, a_ref, q_ref)
+        np.testing.assert_array_equal(a[e_ref == 1], a_ref[e_ref == 1])      # explored rows depend on Philox alone
+        with pytest.raises(q_mod().IllegalArgumentException):                # the size guard (:56-57) holds here too
+            pol.select_action(x[:, :-1], steps)
+        pol.update_q(x, r, x2)
+        g = pol.last_grad()
+        p, a1 = pol.get_weights()
+    _tol.assert_grad_close(g, g_ref)
+    # acc = acc0 + g^2 with |dg| <= GRAD_RTOL * max|g| per element (a million parameters: some have a small g next to the largest)
+    dg = _tol.GRAD_RTOL * np.abs(g_ref).max()
+    assert (np.abs(a1.astype(np.float64) - o.acc) <= 1e-3 * o.acc + 2 * np.abs(g_ref) * dg + dg * dg).all()
+    assert np.abs(p - o.params).max() <= _tol.W_ATOL
 
 
 # ------------------------------------------------------------------------------------------------
