@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(_HERE, "libqpolicy.so")
 SOURCES = [os.path.join(_HERE, "csrc", "qp_api.cu")]
 HEADERS = [os.path.join(_HERE, "csrc", "qp_kernels.cuh"), os.path.join(_HERE, "csrc", "qp_wide.cuh"),
            os.path.join(_HERE, "csrc", "qp_tc.cuh"), os.path.join(_HERE, "csrc", "qp_ep_tc.cuh"),
-           os.path.join(_HERE, "csrc", "qp_probe.cuh"), os.path.join(_HERE, "csrc", "qp_ep_c2.cuh"),
+           os.path.join(_HERE, "csrc", "qp_probe.cuh"), os.path.join(_HERE, "csrc", "qp_fanout.cuh"), os.path.join(_HERE, "csrc", "qp_ep_c2.cuh"),
            os.path.join(_HERE, "csrc", "qp_ep_c2_kernel.cuh"), os.path.join(_HERE, "csrc", "qp_ep_c2_phaseA.inl"),
            os.path.join(_HERE, "csrc", "qp_ep_c2_backward.inl"), os.path.join(_HERE, "csrc", "qp_ep_c2_phaseB.inl"),
            os.path.join(os.path.dirname(_HERE), "include", "qpolicy.h")]

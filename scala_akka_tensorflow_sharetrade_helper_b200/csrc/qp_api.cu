@@ -8,6 +8,7 @@
 #include "qp_ep_tc.cuh"
 #include "qp_ep_c2.cuh"
 #include "qp_probe.cuh"
+#include "qp_fanout.cuh"
 #include "../../include/qpolicy.h"
 
 #include <dlfcn.h>
@@ -193,6 +194,13 @@ struct qp_handle {
     // persistent kernel with tensor-core contractions (qp_ep_tc.cuh)
     bool allow_ep_tc = true, ep_tc_ready = false;   // qp_set_option("ep_tc", 0) keeps the FFMA persistent kernel
     bool prices_exact = true;           // every price is a tf32 value (checked at qp_env_create)
+    // router fan-out path (qp_fanout.cuh): episodes grouped by series, chunks of <= kFanChunk episodes of one series
+    int allow_fanout = 1;               // qp_set_option("fanout", 0 | 1 | 2): never / where it pays / wherever it applies
+    bool fan_ok = false;
+    int fan_n_chunks = 0;
+    std::vector<int32_t> fan_chunks_host;
+    DevBuf<int32_t> fan_chunks;
+    DevBuf<float> fan_zw, fan_part;
     bool et_flow_ok = false;            // the shape takes phase B's bulk-copy branch (the only one with the NVLink exchange)
     // the same kernel on CTA pairs that split the hidden dimension (qp_ep_c2.cuh): the default where it applies
     bool allow_ep_c2 = true, ep_c2_ready = false;   // qp_set_option("ep_c2", 0) keeps episode_tc_kernel
@@ -406,6 +414,34 @@ int enqueue_env_step(qp_handle* h, const TraceDev* trace, int32_t trace_step0, b
         QP_TRY(launch_apply(h, g2, g1, 1, 1, 1));
     }
     if (timed) QP_CUDA(cudaEventRecord(h->ev[3], h->stream));
+    return QP_OK;
+}
+
+// One env-step on the fan-out path: F1, F2, F3, AdaGrad (see qp_fanout.cuh).
+int enqueue_env_step_fanout(qp_handle* h, const TraceDev* trace, int32_t trace_step0) {
+    const Hyper& hp = h->hp;
+    QP_TRY(h->fan_zw.ensure((size_t)h->n_series * 2 * hp.H));
+    QP_TRY(h->fan_part.ensure((size_t)h->fan_n_chunks * 6 * hp.H));
+    FanArgs a{};
+    a.hp = hp; a.params = h->params.p;
+    a.prices = h->prices.p; a.T = h->series_len; a.n_series = h->n_series; a.d_step = h->d_step.p;
+    a.budget = h->budget.p; a.shares = h->shares.p; a.share_value = h->share_value.p;
+    a.B0 = h->B0; a.N0 = h->N0; a.env_id_base = h->env_id_base; a.B = h->n_envs;
+    a.chunks = reinterpret_cast<const int4*>(h->fan_chunks.p); a.n_chunks = h->fan_n_chunks;
+    a.zw = h->fan_zw.p; a.part = h->fan_part.p; a.grad = h->grad.p;
+    if (trace) a.trace = *trace;
+    a.trace_step0 = trace_step0;
+    const int threads1 = (int)round_up(hp.H, 32);
+    fan_zwin_kernel<<<(unsigned)((h->n_series + kFanSeriesPerCta - 1) / kFanSeriesPerCta), threads1,
+                      (size_t)kFanSeriesPerCta * (hp.wn + 1) * sizeof(float), h->stream>>>(a);
+    QP_CUDA(cudaGetLastError());
+    fan_row_kernel<<<h->fan_n_chunks, kFanChunk, ((size_t)2 * hp.H + kFanChunk) * sizeof(float4), h->stream>>>(a);
+    QP_CUDA(cudaGetLastError());
+    fan_grad_kernel<<<(unsigned)((h->P + 255) / 256), 256, 0, h->stream>>>(a);
+    QP_CUDA(cudaGetLastError());
+    h->launches += 3;
+    if (h->world > 1) QP_NCCL(g_nccl.AllReduce(h->grad.p, h->grad.p, (size_t)h->P, kNcclFloat32, kNcclSum, h->comm, h->stream));
+    QP_TRY(launch_apply(h, 0, 0, 0, 1, 1));
     return QP_OK;
 }
 
@@ -709,6 +745,16 @@ bool use_fused(const qp_handle* h) {
     // several GPUs, where it carries the in-kernel exchange.
     const bool ffma_form = fits && (!single || !h->allow_ep_tc);
     return fused_ok && (single || peers) && (ffma_form || ep_tc_usable(h) || ep_c2_usable(h));
+}
+
+// The fan-out path (qp_fanout.cuh): episodes grouped by series.  Taken on its own where it pays: at least eight episodes
+// per series on average and no pair kernel for the batch (the one-tile-per-CTA kernel in waves and the three-kernel path
+// both redo the window contraction per episode).  Several GPUs: only when asked for ("fanout" = 2 on every rank), with
+// the NCCL all-reduce between the gradient sum and AdaGrad.
+bool use_fanout(const qp_handle* h) {
+    if (h->wide || !h->has_env || !h->fan_ok || h->allow_fanout == 0 || h->hp.H > kFanChunk) return false;
+    if (h->allow_fanout >= 2) return true;
+    return h->world == 1 && h->n_envs >= 8 * h->n_series && !(use_fused(h) && ep_c2_usable(h));
 }
 
 // The pair kernel (qp_ep_c2.cuh) on top of what ep_tc_prepare has set up; leaves ep_c2_ready false when the shape or
@@ -1108,6 +1154,7 @@ int qp_destroy(qp_handle* h) {
     h->prices.release(); h->series_of_env.release(); h->shares.release();
     h->budget.release(); h->share_value.release(); h->portfolio.release(); h->blocksum.release();
     h->d_step.release(); h->dbg.release(); h->flags4.release();
+    h->fan_chunks.release(); h->fan_zw.release(); h->fan_part.release();
     if (h->host_flag) cudaFreeHost(h->host_flag);
     for (auto& e : h->ev) if (e) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -1301,6 +1348,25 @@ int qp_env_create(qp_handle* h, const float* prices, int64_t series_len, int64_t
     h->B0 = budget0; h->N0 = shares0;
     h->has_env = true;
     h->tc_ready = false;
+    {   // fan-out path: are the episodes grouped by series (series_of_env non-decreasing)?  Then cut every series'
+        // run of episodes into chunks of at most kFanChunk.
+        h->fan_ok = n_envs < ((int64_t)1 << 31);
+        for (int64_t e = 1; h->fan_ok && e < n_envs; ++e) h->fan_ok = series_of_env[e] >= series_of_env[e - 1];
+        h->fan_chunks_host.clear();
+        h->fan_n_chunks = 0;
+        if (h->fan_ok) {
+            for (int64_t e = 0; e < n_envs;) {
+                int64_t end = e + 1;
+                while (end < n_envs && end - e < kFanChunk && series_of_env[end] == series_of_env[e]) ++end;
+                h->fan_chunks_host.insert(h->fan_chunks_host.end(), {series_of_env[e], (int32_t)e, (int32_t)(end - e), 0});
+                e = end;
+            }
+            h->fan_n_chunks = (int)(h->fan_chunks_host.size() / 4);
+            QP_TRY(h->fan_chunks.ensure(h->fan_chunks_host.size()));
+            QP_CUDA(cudaMemcpyAsync(h->fan_chunks.p, h->fan_chunks_host.data(), h->fan_chunks_host.size() * sizeof(int32_t),
+                                    cudaMemcpyHostToDevice, h->stream));      // (qp_env_reset below synchronises)
+        }
+    }
     bool flag_pending = false;
     QP_TRY(ep_tc_prepare(h, &flag_pending));
     if (h->wide || (h->hp.H % 128 == 0 && h->hp.H / 32 <= kWideMaxColsPerLane)) {
@@ -1336,6 +1402,8 @@ int qp_env_step_async(qp_handle* h, int32_t n_steps) {
     QP_TRY(use_device(h));
     if (h->wide) {
         for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_wide(h, nullptr, 0, h->steps_done + i));
+    } else if (use_fanout(h)) {
+        for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_fanout(h, nullptr, 0));
     } else if (use_fused(h)) {
         QP_TRY(enqueue_env_steps_fused(h, n_steps, nullptr, 0));
     } else if (use_fused_step(h)) {
@@ -1367,6 +1435,15 @@ int qp_env_step_timed(qp_handle* h, int32_t n_steps, float* ms_sum) {
     if (h->wide) {        // five kernels per step; the whole batch of steps is timed into slot QP_KERNEL_STEP
         QP_CUDA(cudaEventRecord(h->ev[0], h->stream));
         for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_wide(h, nullptr, 0, h->steps_done + i));
+        QP_CUDA(cudaEventRecord(h->ev[1], h->stream));
+        QP_CUDA(cudaEventSynchronize(h->ev[1]));
+        QP_CUDA(cudaEventElapsedTime(&ms_sum[0], h->ev[0], h->ev[1]));
+        h->steps_done += n_steps;
+        return QP_OK;
+    }
+    if (use_fanout(h)) {       // four kernels per step, timed as a whole
+        QP_CUDA(cudaEventRecord(h->ev[0], h->stream));
+        for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_fanout(h, nullptr, 0));
         QP_CUDA(cudaEventRecord(h->ev[1], h->stream));
         QP_CUDA(cudaEventSynchronize(h->ev[1]));
         QP_CUDA(cudaEventElapsedTime(&ms_sum[0], h->ev[0], h->ev[1]));
@@ -1443,6 +1520,8 @@ int qp_env_step_trace(qp_handle* h, int32_t n_steps, const qp_trace* out) {
     const int32_t step0 = (int32_t)h->steps_done;
     if (h->wide) {
         for (int32_t i = 0; i < n_steps && st == QP_OK; ++i) st = enqueue_env_step_wide(h, &t, step0, h->steps_done + i);
+    } else if (use_fanout(h)) {
+        for (int32_t i = 0; i < n_steps && st == QP_OK; ++i) st = enqueue_env_step_fanout(h, &t, step0);
     } else if (use_fused(h)) {
         st = enqueue_env_steps_fused(h, n_steps, &t, step0);
     } else if (use_fused_step(h)) {
@@ -1953,6 +2032,7 @@ int qp_set_option(qp_handle* h, const char* key, int64_t value) {
     if (std::strcmp(key, "p2p") == 0) { h->allow_p2p = value != 0; return QP_OK; }
     if (std::strcmp(key, "ep_tc") == 0) { h->allow_ep_tc = value != 0; return QP_OK; }
     if (std::strcmp(key, "ep_c2") == 0) { h->allow_ep_c2 = value != 0; return QP_OK; }
+    if (std::strcmp(key, "fanout") == 0) { h->allow_fanout = (int)value; return QP_OK; }
     if (std::strcmp(key, "nvls") == 0) { h->allow_nvls = value != 0; return QP_OK; }
     if (std::strcmp(key, "rsag") == 0) { h->rsag_mode = (int)value; return QP_OK; }
     if (std::strcmp(key, "c2_dbg") == 0) { h->c2_dbg = (int)value; return QP_OK; }
@@ -1976,24 +2056,25 @@ int qp_get_option(qp_handle* h, const char* key, int64_t* value) {
     if (std::strcmp(key, "fused") == 0) { *value = h->allow_fused ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "wide") == 0) { *value = h->wide ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "ep_tc_active") == 0) {
-        *value = (h->has_env && use_fused(h) && (ep_tc_usable(h) || ep_c2_usable(h))) ? 1 : 0;
+        *value = (h->has_env && !use_fanout(h) && use_fused(h) && (ep_tc_usable(h) || ep_c2_usable(h))) ? 1 : 0;
         return QP_OK;
     }
     if (std::strcmp(key, "ep_c2_split_active") == 0) {
-        *value = (h->has_env && use_fused(h) && ep_c2_usable(h) && !h->prices_exact) ? 1 : 0;
+        *value = (h->has_env && !use_fanout(h) && use_fused(h) && ep_c2_usable(h) && !h->prices_exact) ? 1 : 0;
         return QP_OK;
     }
-    if (std::strcmp(key, "ep_c2_active") == 0) { *value = (h->has_env && use_fused(h) && ep_c2_usable(h)) ? 1 : 0; return QP_OK; }
+    if (std::strcmp(key, "fanout_active") == 0) { *value = use_fanout(h) ? 1 : 0; return QP_OK; }
+    if (std::strcmp(key, "ep_c2_active") == 0) { *value = (h->has_env && !use_fanout(h) && use_fused(h) && ep_c2_usable(h)) ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "nvls_active") == 0) {
-        *value = (h->has_env && use_fused(h) && ep_c2_usable(h) && c2_nvls(h)) ? 1 : 0;
+        *value = (h->has_env && !use_fanout(h) && use_fused(h) && ep_c2_usable(h) && c2_nvls(h)) ? 1 : 0;
         return QP_OK;
     }
-    if (std::strcmp(key, "rsag_active") == 0) { *value = (h->has_env && use_fused(h) && ep_c2_usable(h) && c2_rsag(h)) ? 1 : 0; return QP_OK; }
-    if (std::strcmp(key, "p2p_active") == 0) { *value = (h->has_env && h->world > 1 && use_fused(h)) ? 1 : 0; return QP_OK; }
+    if (std::strcmp(key, "rsag_active") == 0) { *value = (h->has_env && !use_fanout(h) && use_fused(h) && ep_c2_usable(h) && c2_rsag(h)) ? 1 : 0; return QP_OK; }
+    if (std::strcmp(key, "p2p_active") == 0) { *value = (h->has_env && !use_fanout(h) && h->world > 1 && use_fused(h)) ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "tc_a_lo_zero") == 0) { *value = h->tc_a_lo_zero ? 1 : 0; return QP_OK; }
     if (std::strcmp(key, "tc_active") == 0) { *value = (h->wide && h->allow_tc && h->tc_ready) ? 1 : 0; return QP_OK; }
-    if (std::strcmp(key, "fused_active") == 0) { *value = (h->has_env && use_fused(h)) ? 1 : 0; return QP_OK; }
-    if (std::strcmp(key, "fused_step_active") == 0) { *value = (h->has_env && use_fused_step(h)) ? 1 : 0; return QP_OK; }
+    if (std::strcmp(key, "fused_active") == 0) { *value = (h->has_env && !use_fanout(h) && use_fused(h)) ? 1 : 0; return QP_OK; }
+    if (std::strcmp(key, "fused_step_active") == 0) { *value = (h->has_env && !use_fanout(h) && use_fused_step(h)) ? 1 : 0; return QP_OK; }
     return fail(QP_EINVAL, std::string("unknown option: ") + key);
 }
 
