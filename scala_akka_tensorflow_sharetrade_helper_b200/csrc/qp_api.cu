@@ -418,30 +418,40 @@ int enqueue_env_step(qp_handle* h, const TraceDev* trace, int32_t trace_step0, b
 }
 
 // One env-step on the fan-out path: F1, F2, F3, AdaGrad (see qp_fanout.cuh).
-int enqueue_env_step_fanout(qp_handle* h, const TraceDev* trace, int32_t trace_step0) {
+int enqueue_env_step_fanout(qp_handle* h, const TraceDev* trace, int32_t trace_step0, bool timed = false) {
     const Hyper& hp = h->hp;
     QP_TRY(h->fan_zw.ensure((size_t)h->n_series * 2 * hp.H));
     QP_TRY(h->fan_part.ensure((size_t)h->fan_n_chunks * 6 * hp.H));
+    QP_TRY(h->part1.ensure((size_t)kFanKSplit * h->P1));
+    QP_TRY(h->part2.ensure((size_t)kFanKSplit * 3 * hp.H));
     FanArgs a{};
     a.hp = hp; a.params = h->params.p;
     a.prices = h->prices.p; a.T = h->series_len; a.n_series = h->n_series; a.d_step = h->d_step.p;
     a.budget = h->budget.p; a.shares = h->shares.p; a.share_value = h->share_value.p;
     a.B0 = h->B0; a.N0 = h->N0; a.env_id_base = h->env_id_base; a.B = h->n_envs;
     a.chunks = reinterpret_cast<const int4*>(h->fan_chunks.p); a.n_chunks = h->fan_n_chunks;
-    a.zw = h->fan_zw.p; a.part = h->fan_part.p; a.grad = h->grad.p;
+    a.zw = h->fan_zw.p; a.part = h->fan_part.p; a.part1 = h->part1.p; a.part2 = h->part2.p;
     if (trace) a.trace = *trace;
     a.trace_step0 = trace_step0;
-    const int threads1 = (int)round_up(hp.H, 32);
-    fan_zwin_kernel<<<(unsigned)((h->n_series + kFanSeriesPerCta - 1) / kFanSeriesPerCta), threads1,
-                      (size_t)kFanSeriesPerCta * (hp.wn + 1) * sizeof(float), h->stream>>>(a);
+    if (timed) QP_CUDA(cudaEventRecord(h->ev[0], h->stream));
+    fan_zwin_kernel<<<dim3((unsigned)((h->n_series + kFanSeriesPerCta - 1) / kFanSeriesPerCta), (unsigned)((hp.H + 31) / 32)), 32 * kFanKSplit,
+                      ((size_t)kFanSeriesPerCta * (hp.wn + 1) + (size_t)kFanKSplit * 2 * kFanSeriesPerCta * 32) * sizeof(float), h->stream>>>(a);
     QP_CUDA(cudaGetLastError());
+    if (timed) QP_CUDA(cudaEventRecord(h->ev[1], h->stream));
     fan_row_kernel<<<h->fan_n_chunks, kFanChunk, ((size_t)2 * hp.H + kFanChunk) * sizeof(float4), h->stream>>>(a);
     QP_CUDA(cudaGetLastError());
-    fan_grad_kernel<<<(unsigned)((h->P + 255) / 256), 256, 0, h->stream>>>(a);
+    if (timed) QP_CUDA(cudaEventRecord(h->ev[2], h->stream));
+    fan_grad_kernel<<<dim3((unsigned)((hp.H + kFanTile - 1) / kFanTile), (unsigned)((hp.wn + kFanTile - 1) / kFanTile + 1), kFanKSplit), 256, 0, h->stream>>>(a);
     QP_CUDA(cudaGetLastError());
     h->launches += 3;
-    if (h->world > 1) QP_NCCL(g_nccl.AllReduce(h->grad.p, h->grad.p, (size_t)h->P, kNcclFloat32, kNcclSum, h->comm, h->stream));
-    QP_TRY(launch_apply(h, 0, 0, 0, 1, 1));
+    if (h->world > 1) {
+        QP_TRY(launch_apply(h, kFanKSplit, kFanKSplit, 1, 0, 0));
+        QP_NCCL(g_nccl.AllReduce(h->grad.p, h->grad.p, (size_t)h->P, kNcclFloat32, kNcclSum, h->comm, h->stream));
+        QP_TRY(launch_apply(h, 0, 0, 0, 1, 1));
+    } else {
+        QP_TRY(launch_apply(h, kFanKSplit, kFanKSplit, 1, 1, 1));
+    }
+    if (timed) QP_CUDA(cudaEventRecord(h->ev[3], h->stream));
     return QP_OK;
 }
 
@@ -1441,16 +1451,8 @@ int qp_env_step_timed(qp_handle* h, int32_t n_steps, float* ms_sum) {
         h->steps_done += n_steps;
         return QP_OK;
     }
-    if (use_fanout(h)) {       // four kernels per step, timed as a whole
-        QP_CUDA(cudaEventRecord(h->ev[0], h->stream));
-        for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_fanout(h, nullptr, 0));
-        QP_CUDA(cudaEventRecord(h->ev[1], h->stream));
-        QP_CUDA(cudaEventSynchronize(h->ev[1]));
-        QP_CUDA(cudaEventElapsedTime(&ms_sum[0], h->ev[0], h->ev[1]));
-        h->steps_done += n_steps;
-        return QP_OK;
-    }
-    if (use_fused_step(h)) {   // fused step kernel + sum + all-reduce + AdaGrad per step, timed as a whole
+    const bool fan = use_fanout(h);
+    if (!fan && use_fused_step(h)) {   // fused step kernel + sum + all-reduce + AdaGrad per step, timed as a whole
         QP_CUDA(cudaEventRecord(h->ev[0], h->stream));
         for (int32_t i = 0; i < n_steps; ++i) QP_TRY(enqueue_env_step_fused_dist(h, nullptr, 0, i));
         QP_CUDA(cudaEventRecord(h->ev[1], h->stream));
@@ -1459,7 +1461,7 @@ int qp_env_step_timed(qp_handle* h, int32_t n_steps, float* ms_sum) {
         h->steps_done += n_steps;
         return QP_OK;
     }
-    if (use_fused(h)) {   // one persistent kernel: its whole duration goes to slot QP_KERNEL_STEP
+    if (!fan && use_fused(h)) {   // one persistent kernel: its whole duration goes to slot QP_KERNEL_STEP
         QP_CUDA(cudaEventRecord(h->ev[0], h->stream));
         QP_TRY(enqueue_env_steps_fused(h, n_steps, nullptr, 0));
         QP_CUDA(cudaEventRecord(h->ev[1], h->stream));
@@ -1479,7 +1481,8 @@ int qp_env_step_timed(qp_handle* h, int32_t n_steps, float* ms_sum) {
         const int nb = std::min<int32_t>(kBatch, n_steps - done);
         for (int i = 0; i < nb && st == QP_OK; ++i) {
             for (int k = 0; k < 4; ++k) h->ev[k] = evs[(size_t)i * 4 + k];
-            st = enqueue_env_step(h, nullptr, 0, true);
+            // (fan-out path: slots = F1 | F2 | F3 + AdaGrad)
+            st = use_fanout(h) ? enqueue_env_step_fanout(h, nullptr, 0, true) : enqueue_env_step(h, nullptr, 0, true);
         }
         if (st == QP_OK && cudaStreamSynchronize(h->stream) != cudaSuccess) st = fail(QP_ECUDA, "sync failed");
         for (int i = 0; i < nb && st == QP_OK; ++i)
