@@ -41,12 +41,22 @@ SCALING = "weak"                                          # per-GPU episodes fix
 METRIC = "env-steps/sec (act+TD update)"
 UNIT = "env-steps/s"
 WORKLOAD_NAME = "configs[1]"
+EPISODES_PER_SERIES = 1                                    # configs[4] (router fan-out): 256 episodes share a series
 
 
 def set_workload(name: str, args):
     """configs[1] (default): 4096 episodes, window 201, hidden 200.  'wide' = configs[3]: hist 512
     (window 513), hidden 2048, batch 65 536 on one GPU; a bench step is then a 16-env-step slice."""
-    global WINDOW, HIDDEN, D, P, FLOP_PER_ENV_STEP, ROLLOUT, WORKLOAD_NAME, SCALING
+    global WINDOW, HIDDEN, D, P, FLOP_PER_ENV_STEP, ROLLOUT, WORKLOAD_NAME, SCALING, EPISODES_PER_SERIES
+    if name == "fanout":
+        # configs[4]: the router's fan-out (TrainerRouterActor.scala:60-66): 512 tickers x 256 episodes per GPU, the episodes
+        # of a ticker on ONE series (series_of_env = repeat(tickers, 256))
+        WORKLOAD_NAME, EPISODES_PER_SERIES = "configs[4] (router fan-out, 256 episodes per ticker)", 256
+        if args.envs_per_gpu == 4096:
+            args.envs_per_gpu = 131072
+        if args.rollout_steps:
+            ROLLOUT = args.rollout_steps
+        return
     if name == "wide":
         WINDOW, HIDDEN, WORKLOAD_NAME = 513, 2048, "configs[3] (wide policy)"
         D = WINDOW + 2
@@ -58,6 +68,16 @@ def set_workload(name: str, args):
             SCALING = "strong"
     elif args.rollout_steps:
         ROLLOUT = args.rollout_steps
+
+
+def workload_inputs(O, first_env: int, n_envs: int):
+    """Prices and episode -> series map of n_envs episodes starting at global episode first_env."""
+    if EPISODES_PER_SERIES == 1:
+        return O.gen_prices(SEED, first_env, n_envs, SERIES_LEN), np.arange(n_envs, dtype=np.int32)
+    first_series = first_env // EPISODES_PER_SERIES
+    n_series = -(-(first_env + n_envs) // EPISODES_PER_SERIES) - first_series
+    soe = ((first_env + np.arange(n_envs)) // EPISODES_PER_SERIES - first_series).astype(np.int32)
+    return O.gen_prices(SEED, first_series, n_series, SERIES_LEN), soe
 
 
 def bytes_per_env_step(envs_per_gpu: int) -> float:
@@ -180,9 +200,9 @@ def run_reference(args):
     n_envs = args.envs_per_gpu * max(1, args.gpus)
     threads = O.max_threads()
     cfg = O.Config(wn=WINDOW, hidden=HIDDEN)
-    prices = O.gen_prices(SEED, 0, n_envs, SERIES_LEN)
+    prices, soe = workload_inputs(O, 0, n_envs)
     o = O.Oracle(cfg)
-    o.env_create(prices, np.arange(n_envs, dtype=np.int32), BUDGET0, SHARES0)
+    o.env_create(prices, soe, BUDGET0, SHARES0)
     # size one step as a bounded sample: the first S env-steps of the workload's episodes
     t0 = time.perf_counter()
     o.env_step(1, threads=threads)
@@ -220,9 +240,11 @@ def workload_config(args, n_envs):
                          f"hidden {HIDDEN}, fp32, {SERIES_LEN}-step random-walk series per episode, budget 1000",
                 episodes=n_envs, env_steps_per_bench_step=ROLLOUT, series_len=SERIES_LEN,
                 bookkeeping="REFERENCE", l2="flushed between bench steps (256 MiB write inside the timed region)",
+                episodes_per_series=EPISODES_PER_SERIES,
                 parallelism=f"dp{max(1, args.gpus)} (episodes sharded, gradient all-reduce per env-step)" if args.gpus > 1
                 else ("single GPU, GEMM-organised step (tcgen05 3xTF32 GEMMs)" if HIDDEN > 256
-                      else "single GPU, persistent cooperative kernel"))
+                      else ("single GPU, fan-out path (window part of layer 1 once per series; three kernels + AdaGrad per env-step)"
+                            if EPISODES_PER_SERIES > 1 else "single GPU, persistent cooperative kernel")))
 
 
 # =================================================================================================
@@ -249,8 +271,7 @@ def run_ours(args):
     n_total = n_local * world
     n_env_steps = ROLLOUT
     # synthetic inputs: this rank's shard of the global series / episodes
-    prices_np = O.gen_prices(SEED, rank * n_local, n_local, SERIES_LEN)
-    soe_np = np.arange(n_local, dtype=np.int32)
+    prices_np, soe_np = workload_inputs(O, rank * n_local, n_local)
     prices_pin = torch.from_numpy(prices_np).pin_memory()
     soe_pin = torch.from_numpy(soe_np).pin_memory()
     ports_pin = torch.empty(n_local, dtype=torch.float64).pin_memory()
@@ -342,7 +363,8 @@ def run_ours(args):
         dist.all_gather_object(allp, problems)
         problems = [x for pr in allp for x in pr]
     result_check = "ok" if not problems else "FAILED: " + "; ".join(sorted(set(problems)))
-    data_plane = dict(fused_active=int(pol.get_option("fused_active")), ep_tc_active=int(pol.get_option("ep_tc_active")),
+    data_plane = dict(fanout_active=int(pol.get_option("fanout_active")),
+                      fused_active=int(pol.get_option("fused_active")), ep_tc_active=int(pol.get_option("ep_tc_active")),
                       ep_c2_active=int(pol.get_option("ep_c2_active")), nvls_active=int(pol.get_option("nvls_active")),
                       p2p_active=int(pol.get_option("p2p_active")), fused_step_active=int(pol.get_option("fused_step_active")),
                       tiles_per_sm=-(-((n_local + 31) // 32) // 148), params_digest=digest,
@@ -368,7 +390,27 @@ def run_ours(args):
         return (kms / n_prof * 1e3).tolist()
 
     fused_step = bool(pol.get_option("fused_step_active"))
-    if fused_step:
+    if pol.get_option("fanout_active"):
+        # three kernels + AdaGrad per env-step; the row kernel dominates and is bound by fp32 instruction issue
+        per_kernel_us = split_path_us()
+        names = ["fan_zwin_kernel", "fan_row_kernel", "fan_grad_kernel + apply_kernel"]
+        dur = per_kernel_us[1] * 1e-6
+        step_us = sum(per_kernel_us)
+        # what fan_row_kernel does per (episode, hidden column): four hidden evaluations (2 FMA + max) with their three Q
+        # FMAs each (40 flop), and the backward sums (hidden again, h*dz2, three masked sums: 11 flop)
+        row_flops = float(n_local) * HIDDEN * 51.0
+        row_bytes = float(n_local) * 40.0 + (len(np.unique(soe_np)) * 2.0 + 6.0 * -(-n_local // 256)) * HIDDEN * 4.0
+        roofline = dict(
+            bound="hbm", kernel="fan_row_kernel (fan-out path: per-episode part of the step; the window part of layer 1 is computed once per series)",
+            achieved=row_bytes / dur / 1e9, peak=peaks["hbm_gbs"], unit="GB/s", frac=row_bytes / dur / 1e9 / peaks["hbm_gbs"], traffic=None,
+            peak_source=peaks["source"] + " (burst copy)", avg_launch_us=per_kernel_us[1], kernel_us=dict(zip(names, per_kernel_us)),
+            binding=dict(bound="fp32-fma", achieved=row_flops / dur / 1e12, peak=fp32_peak, unit="TFLOP/s",
+                         frac=row_flops / dur / 1e12 / fp32_peak if fp32_peak else None,
+                         note="flops the kernel executes (51 per episode and hidden column), not the 246 800 per env-step of the unfactorised step",
+                         peak_source="measured live: qp_measure_fp32_outer_peak (8x8 outer-product FFMA, three register sources)"),
+            step=dict(us=step_us, unfactorised_flop_per_env_step=FLOP_PER_ENV_STEP,
+                      unfactorised_equivalent_tflops=FLOP_PER_ENV_STEP * n_local / (step_us * 1e-6) / 1e12))
+    elif fused_step:
         pol.env_reset()
         pol.env_step(20)
         ep_us = float(pol.env_step_timed(n_prof)[0]) / n_prof * 1e3
@@ -550,7 +592,9 @@ def run_ours(args):
                       bytes_per_env_step=bytes_per_env_step(n_local), flop_per_env_step=FLOP_PER_ENV_STEP),
         )
 
-    if data_plane["ep_tc_active"]:
+    if data_plane["fanout_active"]:
+        dtype = "fp32 (FFMA; window part of layer 1 once per series; book-keeping fp64)"
+    elif data_plane["ep_tc_active"]:
         dtype = "fp32 (contractions on tcgen05 as 2xTF32: tf32-exact prices x tf32 hi/lo weight pairs, fp32 accumulate in TMEM; element-wise fp32, book-keeping fp64)"
     elif wide and pol.get_option("tc_active"):
         dtype = "fp32 (GEMMs on tcgen05 as 3xTF32 hi/lo splits, fp32 accumulate in TMEM; element-wise fp32, book-keeping fp64)"
@@ -601,7 +645,7 @@ def main():
     ap.add_argument("--envs-per-gpu", type=int, default=4096)
     ap.add_argument("--cpu-sample-steps", type=int, default=30)
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--workload", default="config2", choices=["config2", "wide"])
+    ap.add_argument("--workload", default="config2", choices=["config2", "wide", "fanout"])
     ap.add_argument("--rollout-steps", type=int, default=0, help="env-steps per bench step (default: the whole episode)")
     ap.add_argument("--rsag", type=int, default=-1, help="share exchange: 1 reduce-scatter + all-gather, 0 all-to-all, -1 by world size")
     args = ap.parse_args()
