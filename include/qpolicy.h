@@ -141,10 +141,15 @@ int qp_sync(qp_handle* h);
  *             owner rank, which adds the ranks' values in rank order and sends the sum to all), 0 = all-to-all (each
  *             share to every rank, every rank adds), -1 (default) = reduce-scatter + all-gather from 8 ranks on.
  *             Same sums bit for bit either way.
+ *   "fanout"  the router fan-out path for episodes grouped by series (series_of_env non-decreasing): the window part of
+ *             the hidden layer once per (series, env-step), the backward of the window rows as an outer product per
+ *             series.  1 (default): taken where it pays (one GPU, at least 8 episodes per series on average, more
+ *             episodes than the pair kernel takes); 2: wherever the grouping allows (several GPUs: set it on every rank;
+ *             NCCL all-reduce of the gradient per step); 0: never.  Sums over episodes are re-associated: same tolerance.
  *   "wide", "tc", "tc_passes"   the GEMM-organised path for policies whose W1 does not fit in shared memory.
  *   "phase_clocks"  tuning aid, see qp_debug_phase_clocks (1: CTA 0's phase stamps; 2: per-CTA wall-clock stamps;
  *             3: fine stamps of the pair kernel).  "c2_dbg": reserved for timing experiments (no effect in this build).
- * Read-only: "fused_active", "ep_tc_active", "ep_c2_active", "p2p_active", "nvls_active", "rsag_active",
+ * Read-only: "fanout_active", "fused_active", "ep_tc_active", "ep_c2_active", "p2p_active", "nvls_active", "rsag_active",
  * "fused_step_active", "tc_active", "tc_a_lo_zero": what the next qp_env_step would take.  With several GPUs all of
  * them are facts the ranks have AGREED on at qp_env_create (the step protocols do not interoperate). */
 int qp_set_option(qp_handle* h, const char* key, int64_t value);
