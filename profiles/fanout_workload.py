@@ -16,13 +16,14 @@ steps = int(sys.argv[2]) if len(sys.argv) > 2 else 40
 n = 131072
 prices = O.gen_prices(42, 0, tickers, 1000)
 soe = (np.arange(n) // (n // tickers)).astype(np.int32)
-for name, opts in (("fan-out path (window part once per series)", {}), ("tensor-core kernel in waves", {"fanout": 0}),
+for name, opts in (("default", {}), ("pair kernel in waves", {"fanout": 0}),
+                   ("one-tile-per-CTA tensor-core kernel in waves", {"fanout": 0, "ep_c2": 0}),
                    ("three kernels per step", {"fanout": 0, "fused": 0})):
     with q.QDecisionPolicy(q.PolicyConfig()) as pol:
         for k, v in opts.items():
             pol.set_option(k, v)
         pol.env_create(prices, soe, 1000.0, 0)
-        act = {k: int(pol.get_option(k)) for k in ("fanout_active", "fused_active", "ep_tc_active")}
+        act = {k: int(pol.get_option(k)) for k in ("fanout_active", "fused_active", "ep_tc_active", "ep_c2_active")}
         pol.env_step(10)
         t0 = time.perf_counter()
         pol.env_step(steps)

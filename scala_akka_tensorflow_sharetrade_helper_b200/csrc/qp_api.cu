@@ -195,6 +195,11 @@ struct qp_handle {
     bool allow_ep_tc = true, ep_tc_ready = false;   // qp_set_option("ep_tc", 0) keeps the FFMA persistent kernel
     bool prices_exact = true;           // every price is a tf32 value (checked at qp_env_create)
     // router fan-out path (qp_fanout.cuh): episodes grouped by series, chunks of <= kFanChunk episodes of one series
+    bool env_identity = false;          // episode e runs on series e
+    DevBuf<float> c2_pT;                // pair kernel in waves: transposed price matrix [T][series padded to 64]
+    CUtensorMap tm_c2_win{};
+    bool c2_win_ready = false;
+    bool allow_c2_waves = true;         // qp_set_option("ep_c2_waves"): the pair kernel also where a pair has several tiles
     int allow_fanout = 1;               // qp_set_option("fanout", 0 | 1 | 2): never / where it pays / wherever it applies
     bool fan_ok = false;
     int fan_n_chunks = 0;
@@ -731,8 +736,10 @@ bool ep_tc_usable(const qp_handle* h) {
 // the pair kernel: one 64-episode tile per CTA pair (no waves), everything episode_tc_kernel needs plus its own shape limits
 // (prices that are not tf32-exact: 32 real + 32 virtual episodes per pair, see episode_c2_kernel's kSplit)
 int64_t c2_envs_per_pair(const qp_handle* h) { return h->prices_exact ? kC2Envs : kC2Envs / 2; }
+bool c2_one_tile(const qp_handle* h) { return h->n_envs <= c2_envs_per_pair(h) * (h->c2_grid / 2); }
+// more tiles than pairs: the pair kernel in waves (tf32-exact prices only; option "ep_c2_waves")
 bool ep_c2_local(const qp_handle* h) {
-    return ep_tc_base(h) && h->allow_ep_c2 && h->ep_c2_ready && h->n_envs <= c2_envs_per_pair(h) * (h->c2_grid / 2);
+    return ep_tc_base(h) && h->allow_ep_c2 && h->ep_c2_ready && (c2_one_tile(h) || (h->prices_exact && h->allow_c2_waves));
 }
 bool ep_c2_usable(const qp_handle* h) { return ep_c2_local(h) && (h->world == 1 || (h->agree_valid && h->agree_c2)); }
 // several GPUs: the share-exchange scheme and the multicast stores, as ALL ranks have them (agreed at qp_env_create)
@@ -764,7 +771,36 @@ bool use_fused(const qp_handle* h) {
 bool use_fanout(const qp_handle* h) {
     if (h->wide || !h->has_env || !h->fan_ok || h->allow_fanout == 0 || h->hp.H > kFanChunk) return false;
     if (h->allow_fanout >= 2) return true;
-    return h->world == 1 && h->n_envs >= 8 * h->n_series && !(use_fused(h) && ep_c2_usable(h));
+    return h->world == 1 && h->n_envs >= 8 * h->n_series && !(use_fused(h) && ep_c2_usable(h) && c2_one_tile(h));
+}
+
+// dst[c][r] = src[r][c] (dst rows of ld_dst floats, the columns r >= R left as they are: zero-filled by the caller)
+__global__ void transpose_kernel(const float* __restrict__ src, int64_t R, int64_t C, float* __restrict__ dst, int64_t ld_dst) {
+    __shared__ float tile[32][33];
+    const int64_t r0 = (int64_t)blockIdx.y * 32, c0 = (int64_t)blockIdx.x * 32;
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int64_t r = r0 + i, c = c0 + threadIdx.x;
+        tile[i][threadIdx.x] = (r < R && c < C) ? src[r * C + c] : 0.0f;
+    }
+    __syncthreads();
+    for (int i = threadIdx.y; i < 32; i += blockDim.y) {
+        const int64_t c = c0 + i, r = r0 + threadIdx.x;
+        if (c < C && r < R) dst[c * ld_dst + r] = tile[threadIdx.x][i];
+    }
+}
+
+// The pair kernel in waves fetches a tile's window with TMA where episode e is series e: needs the transposed price matrix.
+int c2_window_prepare(qp_handle* h) {
+    if (h->c2_win_ready) return QP_OK;
+    const int64_t T = h->series_len, Ns = h->n_series, ld = round_up(Ns, 64);
+    QP_TRY(h->c2_pT.ensure((size_t)T * ld));
+    QP_CUDA(cudaMemsetAsync(h->c2_pT.p, 0, (size_t)T * ld * sizeof(float), h->stream));
+    transpose_kernel<<<dim3((unsigned)((T + 31) / 32), (unsigned)((Ns + 31) / 32)), dim3(32, 8), 0, h->stream>>>(h->prices.p, Ns, T, h->c2_pT.p, ld);
+    QP_CUDA(cudaGetLastError());
+    h->launches += 1;
+    QP_TRY(make_tmap(&h->tm_c2_win, h->c2_pT.p, (uint64_t)ld, (uint64_t)T, (uint64_t)ld * sizeof(float), (uint32_t)(h->hp.wn + 1)));
+    h->c2_win_ready = true;
+    return QP_OK;
 }
 
 // The pair kernel (qp_ep_c2.cuh) on top of what ep_tc_prepare has set up; leaves ep_c2_ready false when the shape or
@@ -789,14 +825,15 @@ int ep_c2_prepare(qp_handle* h) {
         const int ng4 = pitch / 4, nsub = std::min(8, kC2Threads / std::max(1, ng4));
         if (pitch > kC2Threads || nsub < 1 || (grid / 2 + nsub - 1) / nsub > 16 || (size_t)8 * pitch * 4 > sm.op_bytes) return QP_OK;
     }
-    for (auto* k : {episode_c2_kernel<0, false>, episode_c2_kernel<1, false>, episode_c2_kernel<2, false>,
-                    episode_c2_kernel<0, true>, episode_c2_kernel<1, true>, episode_c2_kernel<2, true>})
+    for (auto* k : {episode_c2_kernel<0, false, false>, episode_c2_kernel<1, false, false>, episode_c2_kernel<2, false, false>,
+                    episode_c2_kernel<0, true, false>, episode_c2_kernel<1, true, false>, episode_c2_kernel<2, true, false>,
+                    episode_c2_kernel<0, false, true>, episode_c2_kernel<1, false, true>, episode_c2_kernel<2, false, true>})
         QP_CUDA(cudaFuncSetAttribute(k, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sm.total + 1024)));
     {   // all pairs must be co-resident (cooperative launch of clusters of two)
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3(grid); cfg.blockDim = dim3(kC2Threads); cfg.dynamicSmemBytes = sm.total + 1024; cfg.stream = h->stream;
         int n_clusters = 0;
-        if (cudaOccupancyMaxActiveClusters(&n_clusters, episode_c2_kernel<1, true>, &cfg) != cudaSuccess) { cudaGetLastError(); return QP_OK; }
+        if (cudaOccupancyMaxActiveClusters(&n_clusters, episode_c2_kernel<1, false, true>, &cfg) != cudaSuccess) { cudaGetLastError(); return QP_OK; }
         if (n_clusters * 2 < grid) return QP_OK;
     }
     QP_TRY(make_tmap(&h->tm_c2_hi, h->et_w_hi.p, h->et_Kp, hp.H, (uint64_t)h->et_Kp * sizeof(float), (uint32_t)Nh));
@@ -948,11 +985,12 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
             x.ea.dbg = nullptr;
             x.fine = h->dbg.p;
         }
-        if (h->tm_c2_part_ptr != h->part1.p || h->tm_c2_part_pairs != n_pairs) {
-            const uint64_t dims[4] = {(uint64_t)h->c2_Hh, 2, (uint64_t)h->hp.wn, (uint64_t)n_pairs};
+        const int64_t n_parts = std::min<int64_t>(n_pairs, h->c2_grid / 2);          // one partial per pair
+        if (h->tm_c2_part_ptr != h->part1.p || h->tm_c2_part_pairs != n_parts) {
+            const uint64_t dims[4] = {(uint64_t)h->c2_Hh, 2, (uint64_t)h->hp.wn, (uint64_t)n_parts};
             const uint64_t pitch[3] = {(uint64_t)h->c2_Hh * sizeof(float), (uint64_t)h->hp.H * sizeof(float), (uint64_t)h->P1 * sizeof(float)};
             QP_TRY(make_tmap4_store(&h->tm_c2_part, h->part1.p, dims, pitch));
-            h->tm_c2_part_ptr = h->part1.p; h->tm_c2_part_pairs = n_pairs;
+            h->tm_c2_part_ptr = h->part1.p; h->tm_c2_part_pairs = n_parts;
         }
         cudaLaunchConfig_t cfg{};
         cfg.gridDim = dim3(h->c2_grid); cfg.blockDim = dim3(kC2Threads); cfg.dynamicSmemBytes = h->c2_smem_bytes; cfg.stream = h->stream;
@@ -960,9 +998,15 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
         at[0].id = cudaLaunchAttributeCooperative; at[0].val.cooperative = 1;      // (the cluster shape is the kernel's own attribute)
         cfg.attrs = at; cfg.numAttrs = 1;
         const int scheme = ea.world > 1 ? (x.rsag ? 2 : 1) : 0;
-        auto* kern = x.split ? (scheme == 2 ? episode_c2_kernel<2, true> : scheme == 1 ? episode_c2_kernel<1, true> : episode_c2_kernel<0, true>)
-                             : (scheme == 2 ? episode_c2_kernel<2, false> : scheme == 1 ? episode_c2_kernel<1, false> : episode_c2_kernel<0, false>);
-        QP_CUDA(cudaLaunchKernelEx(&cfg, kern, h->tm_c2_hi, h->tm_c2_lo, h->tm_c2_part, x));
+        const bool waves = n_pairs > h->c2_grid / 2;
+        if (waves && h->env_identity && h->series_len * (int64_t)sizeof(float) > 0) {
+            QP_TRY(c2_window_prepare(h));
+            x.win_tma = 1;
+        }
+        auto* kern = x.split ? (scheme == 2 ? episode_c2_kernel<2, true, false> : scheme == 1 ? episode_c2_kernel<1, true, false> : episode_c2_kernel<0, true, false>)
+                     : waves ? (scheme == 2 ? episode_c2_kernel<2, false, true> : scheme == 1 ? episode_c2_kernel<1, false, true> : episode_c2_kernel<0, false, true>)
+                             : (scheme == 2 ? episode_c2_kernel<2, false, false> : scheme == 1 ? episode_c2_kernel<1, false, false> : episode_c2_kernel<0, false, false>);
+        QP_CUDA(cudaLaunchKernelEx(&cfg, kern, h->tm_c2_hi, h->tm_c2_lo, h->tm_c2_part, x.win_tma ? h->tm_c2_win : h->tm_c2_part, x));
         h->launches++;
         return QP_OK;
     }
@@ -1164,7 +1208,7 @@ int qp_destroy(qp_handle* h) {
     h->prices.release(); h->series_of_env.release(); h->shares.release();
     h->budget.release(); h->share_value.release(); h->portfolio.release(); h->blocksum.release();
     h->d_step.release(); h->dbg.release(); h->flags4.release();
-    h->fan_chunks.release(); h->fan_zw.release(); h->fan_part.release();
+    h->fan_chunks.release(); h->fan_zw.release(); h->fan_part.release(); h->c2_pT.release();
     if (h->host_flag) cudaFreeHost(h->host_flag);
     for (auto& e : h->ev) if (e) cudaEventDestroy(e);
     if (h->stream) cudaStreamDestroy(h->stream);
@@ -1358,6 +1402,9 @@ int qp_env_create(qp_handle* h, const float* prices, int64_t series_len, int64_t
     h->B0 = budget0; h->N0 = shares0;
     h->has_env = true;
     h->tc_ready = false;
+    h->c2_win_ready = false;
+    h->env_identity = n_series == n_envs;
+    for (int64_t e = 0; h->env_identity && e < n_envs; ++e) h->env_identity = series_of_env[e] == e;
     {   // fan-out path: are the episodes grouped by series (series_of_env non-decreasing)?  Then cut every series'
         // run of episodes into chunks of at most kFanChunk.
         h->fan_ok = n_envs < ((int64_t)1 << 31);
@@ -2035,6 +2082,7 @@ int qp_set_option(qp_handle* h, const char* key, int64_t value) {
     if (std::strcmp(key, "p2p") == 0) { h->allow_p2p = value != 0; return QP_OK; }
     if (std::strcmp(key, "ep_tc") == 0) { h->allow_ep_tc = value != 0; return QP_OK; }
     if (std::strcmp(key, "ep_c2") == 0) { h->allow_ep_c2 = value != 0; return QP_OK; }
+    if (std::strcmp(key, "ep_c2_waves") == 0) { h->allow_c2_waves = value != 0; return QP_OK; }
     if (std::strcmp(key, "fanout") == 0) { h->allow_fanout = (int)value; return QP_OK; }
     if (std::strcmp(key, "nvls") == 0) { h->allow_nvls = value != 0; return QP_OK; }
     if (std::strcmp(key, "rsag") == 0) { h->rsag_mode = (int)value; return QP_OK; }

@@ -51,6 +51,7 @@ struct EpC2Args {
     unsigned long long* mc_pdata;    // the same block through its multicast address (NVLS), or null: one store reaches every rank
     int64_t p_pad;
     int dbg_mode;                    // timing experiments (option "c2_dbg"); 0 in every real run
+    int win_tma;                     // waves: 1 = episode e is series e and tX maps the transposed price matrix [T][series]
     int split;                       // 1: prices not tf32-exact, 32 real + 32 virtual episodes per pair (host picks the instantiation)
     long long* cta_ns;               // tuning aid ("phase_clocks" = 2): [n_steps][gridDim][8] globaltimer stamps of every CTA
     long long* fine;                 // tuning aid ("phase_clocks" = 3): [n_steps][64] clock64 stamps inside the forward of CTA 0

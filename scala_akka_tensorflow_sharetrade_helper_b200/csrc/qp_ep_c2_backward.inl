@@ -7,7 +7,7 @@
     if (warp == 1 && lane == 0) {
         tc_fence_after();
         for (int hf = 0; hf < halves; ++hf) {
-            bool first = true;
+            bool first = first_tile;                            // (kWaves: the later tiles of a step add to the first one's sum)
             for (int kb = 0; kb < 2; ++kb) {
                 const uint64_t da = tc_smem_desc(XT + (size_t)kb * 32768 + (size_t)(roff + hf * 128) * 128);
                 const uint64_t db_hi = tc_smem_desc(Bbwd_hi + (size_t)kb * TBh), db_lo = tc_smem_desc(Bbwd_lo + (size_t)kb * TBh);
@@ -43,7 +43,8 @@
             x1 = fmaf(XE[kC2Envs + ee], d1, x1);
         }
         float* p5 = part5 + (size_t)gg * 5 * Hh + c;
-        p5[0] = s0; p5[Hh] = s1; p5[2 * Hh] = s2; p5[3 * Hh] = x0; p5[4 * Hh] = x1;
+        if (first_tile) { p5[0] = s0; p5[Hh] = s1; p5[2 * Hh] = s2; p5[3 * Hh] = x0; p5[4 * Hh] = x1; }
+        else { p5[0] += s0; p5[Hh] += s1; p5[2 * Hh] += s2; p5[3 * Hh] += x0; p5[4 * Hh] += x1; }
     }
     // ---- S6: dW1 partial out of TMEM.  Row m of the accumulator is window element m (the A operand started at the
     // window's first row).  A TMEM load hands every lane one ROW of the tile; each warp stages its [32 rows x 32 columns]
@@ -61,7 +62,7 @@
             if (lane == 0) tc_wait(tf_bwd + hf, par);
             __syncwarp();
             tc_fence_after();
-            if (k0 >= wn) continue;
+            if (k0 >= wn || !last_tile) continue;                 // (kWaves: the sum leaves TMEM after the step's last tile)
             for (int cb = part; cb < nfull; cb += 3) {
                 uint32_t r[32];
                 et_tmem_ld32_nowait(tmem_base + ((uint32_t)(q4 * 32) << 16) + 128u + (uint32_t)(hf * 128 + cb * 32), r);
@@ -76,7 +77,7 @@
                 et_fence_async_smem();
                 __syncwarp();
                 if (lane == 0) {
-                    c2_tma_store_4d(&tP, buf, cb * 32, (int)crank, k0, (int)pair);
+                    c2_tma_store_4d(&tP, buf, cb * 32, (int)crank, k0, (int)cidx);
                     et_bulk_commit();
                 }
                 pending = true;
@@ -99,14 +100,14 @@
         ++mma_it;
     }
     // ---- S7: slide the window: the next price of every episode into the row after the window's last
-    if (wsub == 0) {
+    if (!kWaves && wsub == 0) {
         const float p_hi = kSplit ? et_tf32(p_next) : p_next;
         *reinterpret_cast<float*>(XT + (size_t)g * 32768 + et_swz(roff + wn + 1, lane)) = (kSplit && g == 1) ? p_next - p_hi : p_hi;
     }
     tc_fence_before();
     __syncthreads();
     stamp(6);
-    if (tid >= nthreads - 128 && tid - (nthreads - 128) < Hh) {                 // the two lane groups' sums, in group order
+    if (last_tile && tid >= nthreads - 128 && tid - (nthreads - 128) < Hh) {    // the two lane groups' sums, in group order
         const int cl = tid - (nthreads - 128);
         const float* pa = part5 + cl;
         const float* pb = part5 + (size_t)5 * Hh + cl;

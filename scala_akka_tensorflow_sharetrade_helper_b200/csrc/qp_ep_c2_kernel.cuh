@@ -7,10 +7,15 @@ namespace qp {
 // kXchg: 0 one GPU, 1 several GPUs with the all-to-all share exchange in phase B, 2 with reduce-scatter + all-gather.  A
 // template parameter because the kernel sits at the register limit of 384 threads per SM (168): each instantiation
 // carries only the scheme it runs, and every extra live value costs spills.
-template <int kXchg, bool kSplit>
+// kWaves: more tiles than pairs.  Pair i then takes the tiles i, i + pairs, ... one after the other in every env-step: the
+// window of a tile is gathered from the price matrix per (tile, step) and its episode record lives in global memory between
+// steps; the small tables and the wait for the new weights happen once per step; the backward MMAs of all tiles of a step
+// accumulate into the SAME TMEM accumulator (and dW2 / the budget and shares rows into the same shared-memory sums), so the
+// pair still stores ONE partial per step, after its last tile.
+template <int kXchg, bool kSplit, bool kWaves>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kC2Threads, 1)
 episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_constant__ CUtensorMap tW_lo,
-                  const __grid_constant__ CUtensorMap tP, const EpC2Args x) {
+                  const __grid_constant__ CUtensorMap tP, const __grid_constant__ CUtensorMap tX, const EpC2Args x) {
     namespace cg = cooperative_groups;
     cg::grid_group grid = cg::this_grid();
     extern __shared__ __align__(1024) uint8_t c2_smem_raw[];
@@ -52,11 +57,13 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     uint64_t* tf_fwd = bars + 16;
     uint64_t* tf_bwd = bars + 17;       // [2]: one per 128-row half of the backward accumulator
     uint64_t* qx_bar = bars + 19;       // the pair's exchange of the Q partial sums: one arrival per CTA and step
+    uint64_t* xw_full = bars + 20;      // kWaves: the tile's window has arrived (TMA from the transposed price matrix)
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 23);
 
     const uint32_t crank = c2_cluster_rank();                   // which half of the hidden columns
     const int c0 = (int)crank * Hh;                             // first hidden column of this CTA
-    const int64_t pair = (int64_t)(blockIdx.x >> 1);
+    const int64_t cidx = (int64_t)(blockIdx.x >> 1), n_clusters = (int64_t)(gridDim.x >> 1);
+    int64_t pair = cidx;                                        // (kWaves: the tile in hand)
     const int64_t B = a.B;
     // kSplit: prices that are not tf32-exact.  A pair then owns 32 episodes, whose windows lie in the buffer twice: block 0
     // holds tf32(x), block 1 the remainder x - tf32(x) as the windows of 32 VIRTUAL episodes.  The window part of layer 1
@@ -64,12 +71,12 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     // backward contraction over [32 real | 32 virtual] rows with dZ1 written to both blocks is X_hi^T dZ1 + X_lo^T dZ1.
     constexpr int kEpp = kSplit ? 32 : kC2Envs;                 // real episodes per pair
     const int64_t n_pairs = (B + kEpp - 1) / kEpp;
-    const bool has_tile = pair < n_pairs;
+    const bool has_tile = pair < n_pairs;                       // (kWaves: whether this pair has any tile)
     const int g = warp & 1, wsub = warp >> 1;                   // element-wise phases: lane group / column subset
     const int el = g * 32 + lane;                               // episode of this thread within the pair's 64
-    const int64_t e = pair * kEpp + (kSplit ? lane : el);
-    const bool valid = has_tile && e < B;
-    const int64_t ec = has_tile ? (valid ? e : B - 1) : 0;
+    int64_t e = pair * kEpp + (kSplit ? lane : el);
+    bool valid = has_tile && e < B;
+    int64_t ec = has_tile ? (valid ? e : B - 1) : 0;
     const float bias = hp.bias;
     const float* W1g = a.params;
     const float* W2g = a.params + (size_t)D * H;
@@ -80,6 +87,7 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         for (int s = 0; s < kC2AStages; ++s) { mbar_init(a_full + s, kC2Builders); mbar_init(a_empty + s, 1); }
         mbar_init(tf_fwd, 1); mbar_init(tf_bwd, 1); mbar_init(tf_bwd + 1, 1);
         mbar_init(qx_bar, 2);
+        mbar_init(xw_full, 1);
         mbar_fence_init();
     }
     if (warp == 2) {
@@ -90,18 +98,18 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     for (size_t i = tid; i < (sm.op + sm.op_bytes) / 16; i += nthreads) reinterpret_cast<float4*>(base)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     double budget = a.budget[ec], share_value = a.share_value[ec];
     int32_t shares = a.shares[ec];
-    const float* my_row = a.prices + (int64_t)a.series_of_env[ec] * a.T;
+    const float* my_row = a.prices + (int64_t)a.series_of_env[ec] * a.T;      // (kWaves: set again per tile)
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
-    if (has_tile) {
-        // the window of every episode of the pair: element k of episode (g, l) at row k of block g
+    // the window of every episode of the tile: element k of episode (g, l) at row k of block g
+    auto load_window = [&](int32_t first_step) {
         const int segs = (wn + 1 + 31) >> 5, items = 32 * segs;
         for (int it = wsub; it < items; it += kC2Sub) {
             const int l = it & 31, k = ((it >> 5) << 5) + lane;
             const float* src = reinterpret_cast<const float*>(
-                __shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(my_row), l)) + ea.step0;
+                __shfl_sync(0xffffffffu, reinterpret_cast<unsigned long long>(my_row), l)) + first_step;
             if constexpr (kSplit) {
                 if (k <= wn) {
                     const float v = __ldg(src + k), hi = et_tf32(v);
@@ -114,7 +122,8 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         cp_async_commit();
         cp_async_wait_pending(0);
         et_fence_async_smem();                                  // (the backward MMA reads the buffer through the async proxy)
-    }
+    };
+    if (has_tile && !kWaves) load_window(ea.step0);
     const int64_t P1 = (int64_t)D * H, P = P1 + 3 * (int64_t)H;
     {   // K-major tf32 hi/lo copies of the current W1 (phase B keeps them current afterwards)
         for (int64_t p = ((int64_t)blockIdx.x * nthreads + tid) * 4; p < P1; p += (int64_t)gridDim.x * nthreads * 4) {
@@ -132,7 +141,7 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         }
     }
     // phase B's division of the parameters over the CTAs (as episode_tc_kernel; the host has checked `flow`)
-    const int n1 = (int)n_pairs;                                // one partial per pair
+    const int n1 = (int)min(n_pairs, n_clusters);               // one partial per pair
     const int n_w1_ctas = max(1, (int)gridDim.x - 2);
     const int chunk = (int)(((P1 + n_w1_ctas - 1) / n_w1_ctas + 3) & ~(int64_t)3);
     const int chunk2 = ((3 * H + 1) / 2 + 3) & ~3;
@@ -153,14 +162,14 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     grid.sync();
 
     const uint32_t idesc = tc_instr_desc(128, Nh);
-    uint32_t ring_it = 0, a_it = 0, mma_it = 0;
+    uint32_t ring_it = 0, a_it = 0, mma_it = 0, xw_it = 0;
     const int kb_first = (int)(blockIdx.x % (unsigned)nkb);
-    float* out = ea.part1 + (size_t)pair * ((size_t)D * H);
-    float* out2 = a.dw2_part + (size_t)pair * (3 * H);
+    float* out = ea.part1 + (size_t)cidx * ((size_t)D * H);
+    float* out2 = a.dw2_part + (size_t)cidx * (3 * H);
 
     for (int32_t sidx = 0; sidx < ea.n_steps; ++sidx) {
         const int32_t istep = ea.step0 + sidx;
-        const int roff = sidx % kC2Slide;                       // row of window element 0
+        const int roff = kWaves ? 0 : sidx % kC2Slide;          // row of window element 0
         auto stamp = [&](int i) { if (ea.dbg && blockIdx.x == 0 && tid == 0) ea.dbg[(size_t)sidx * kDbgSlots + i] = clock64(); };
         auto cta_stamp = [&](int i) {
             if (x.cta_ns && tid == 0) {
@@ -171,8 +180,72 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         };
         cta_stamp(0);
         stamp(0);
-        if (has_tile) {
+        auto fine = [&](int i) { if (x.fine && blockIdx.x == 0) x.fine[(size_t)sidx * 64 + i] = clock64(); };   // tuning aid
+        // the W1^T ring: (hi, lo) tiles of this CTA's rows for k-block kk of the tile in hand
+        auto push_w_tiles = [&](int kk) {
+            const int kb = (kk + kb_first) % nkb;
+            const uint32_t it = ring_it + (uint32_t)kk, s = it % kC2WStages, ph = (it / kC2WStages) & 1u;
+            tc_wait(w_empty + s, ph ^ 1u);
+            fine(kk);
+            uint8_t* st = regW + (size_t)s * 2 * TBh;
+            mbar_arrive_expect_tx(w_full + s, 2 * TBh);
+            tma_load_2d(st, &tW_hi, kb * 32, c0, w_full + s);
+            tma_load_2d(st + TBh, &tW_lo, kb * 32, c0, w_full + s);
+        };
+        if constexpr (!kWaves) {
+            constexpr bool first_tile = true, last_tile = true;
+            if (has_tile) {
 #include "qp_ep_c2_phaseA.inl"
+            }
+        } else {
+            for (int64_t tile = cidx; tile < n_pairs; tile += n_clusters) {
+                const bool first_tile = tile == cidx, last_tile = tile + n_clusters >= n_pairs;
+                pair = tile;
+                e = pair * kEpp + el;
+                valid = e < B;
+                ec = valid ? e : B - 1;
+                if (last_tile) stamp(11);
+                budget = a.budget[ec]; share_value = a.share_value[ec]; shares = a.shares[ec];
+                my_row = a.prices + (int64_t)a.series_of_env[ec] * a.T;
+                // (the previous tile's backward MMAs have completed: its S6 waits for them)
+                if (x.win_tma) {
+                    // episode e is series e: the window of the tile is two boxes [wn + 1 rows x 32 episodes] of the transposed
+                    // price matrix, fetched by the TMA engine straight into the buffer's swizzled layout; the first W1^T tiles
+                    // of the tile are queued behind them
+                    if (warp == 0 && lane == 0) {
+                        mbar_arrive_expect_tx(xw_full, 2u * (uint32_t)(wn + 1) * 128u);
+                        tma_load_2d(XT, &tX, (int)(pair * kC2Envs), istep, xw_full);
+                        tma_load_2d(XT + 32768, &tX, (int)(pair * kC2Envs) + 32, istep, xw_full);
+                        if (first_tile) {
+                            if (sidx > 0) et_wait_count(x.published, (unsigned long long)sidx * (unsigned long long)n_publishers);
+                            fence_proxy_async();                // phase-B writes of W1^T -> TMA reads (once per step)
+                        }
+                        for (int kk = 0; kk < min(kC2WStages, nkb); ++kk) push_w_tiles(kk);
+                    }
+                    if (lane == 0) tc_wait(xw_full, xw_it & 1u);
+                    __syncwarp();
+                    ++xw_it;
+                } else {
+                    // any episode -> series map: gathered with 4-byte copies (the W1^T stream starts afterwards: started
+                    // before, it slowed the gather down four-fold)
+                    load_window(istep);
+                    __syncthreads();
+                    if (warp == 0 && lane == 0) {
+                        if (first_tile) {
+                            if (sidx > 0) et_wait_count(x.published, (unsigned long long)sidx * (unsigned long long)n_publishers);
+                            fence_proxy_async();
+                        }
+                        for (int kk = 0; kk < min(kC2WStages, nkb); ++kk) push_w_tiles(kk);
+                    }
+                }
+                if (last_tile) stamp(13);
+#include "qp_ep_c2_phaseA.inl"
+                if (crank == 0 && wsub == 0 && valid) {         // the episode record goes home between steps
+                    a.budget[e] = budget;
+                    a.shares[e] = shares;
+                    a.share_value[e] = share_value;
+                }
+            }
         }
         stamp(7);
         if (!ea.apply_in_kernel) { et_bulk_wait_all(); break; }
@@ -200,7 +273,7 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         ea.acc[pb_p0 + tid] = pb_a;
         ea.grad[pb_p0 + tid] = pb_g;
     }
-    if (has_tile && crank == 0 && wsub == 0 && valid && (!kSplit || g == 0)) {
+    if (!kWaves && has_tile && crank == 0 && wsub == 0 && valid && (!kSplit || g == 0)) {
         a.budget[e] = budget;
         a.shares[e] = shares;
         a.share_value[e] = share_value;

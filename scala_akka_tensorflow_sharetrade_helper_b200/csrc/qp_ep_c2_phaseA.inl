@@ -4,7 +4,7 @@
     const uint32_t par = mma_it & 1u;
     // ---- slide: every kC2Slide steps the live rows go back to the top of the buffer.  Source and destination overlap:
     // everything is read into registers first.  (kC2Slide is a multiple of 8, so a row keeps its swizzle phase.)
-    if (sidx > 0 && roff == 0) {
+    if (!kWaves && sidx > 0 && roff == 0) {
         constexpr int kMaxCopy = 12;
         const int n_items = (wn + 1) * 16;                      // (block, row, 16-byte chunk)
         float4 v[kMaxCopy];
@@ -36,24 +36,15 @@
     // ---- S0 / S1: forward contraction Z[128, Nh] = X[128, Kp] · W1[Kp, this CTA's columns] on the tensor core.
     // Roles: warp 0 feeds the W1^T ring by TMA, warp 1 issues the MMAs, warps 2..9 transpose the A tiles out of the
     // window buffer (they do not depend on the weights and run ahead of the split barrier), warp 10 loads the small tables.
-    auto fine = [&](int i) { if (x.fine && blockIdx.x == 0) x.fine[(size_t)sidx * 64 + i] = clock64(); };   // tuning aid
     if (tid == 0) fine(48);
-    auto push_w_tiles = [&](int kk) {
-        const int kb = (kk + kb_first) % nkb;
-        const uint32_t it = ring_it + (uint32_t)kk, s = it % kC2WStages, ph = (it / kC2WStages) & 1u;
-        tc_wait(w_empty + s, ph ^ 1u);
-        fine(kk);
-        uint8_t* st = regW + (size_t)s * 2 * TBh;
-        mbar_arrive_expect_tx(w_full + s, 2 * TBh);
-        tma_load_2d(st, &tW_hi, kb * 32, c0, w_full + s);
-        tma_load_2d(st + TBh, &tW_lo, kb * 32, c0, w_full + s);
-    };
     if (warp == 0) {
         if (lane == 0) {
-            // the new weights are complete once every publisher of the previous step is through
-            if (sidx > 0) et_wait_count(x.published, (unsigned long long)sidx * (unsigned long long)n_publishers);
-            fence_proxy_async();                                // phase-B writes of W1^T -> TMA reads
-            for (int kk = 0; kk < min(kC2WStages, nkb); ++kk) push_w_tiles(kk);
+            if constexpr (!kWaves) {                            // (kWaves: done before the tile's window is gathered)
+                // the new weights are complete once every publisher of the previous step is through
+                if (sidx > 0) et_wait_count(x.published, (unsigned long long)sidx * (unsigned long long)n_publishers);
+                fence_proxy_async();                            // phase-B writes of W1^T -> TMA reads
+                for (int kk = 0; kk < min(kC2WStages, nkb); ++kk) push_w_tiles(kk);
+            }
             stamp(1);                                           // (the wait for the other CTAs' phase B ends here)
             cta_stamp(1);
             for (int kk = kC2WStages; kk < nkb; ++kk) push_w_tiles(kk);
@@ -126,7 +117,7 @@
             __syncwarp();
             if (lane == 0) c2_mbar_arrive(a_full + sa);
         }
-    } else if (warp == 2 + kC2Builders) {
+    } else if (warp == 2 + kC2Builders && first_tile) {
         // the small tables of this CTA's columns (W2, the budget / shares rows of W1): they need the new weights too, so
         // this warp watches the counter itself; every load is issued before the first store
         if (lane == 0 && sidx > 0) et_wait_count(x.published, (unsigned long long)sidx * (unsigned long long)n_publishers);
@@ -162,7 +153,7 @@
         else
             p_new = (double)*reinterpret_cast<const float*>(XT + (size_t)g * 32768 + et_swz(roff + wn, lane));
         cur = __dadd_rn(budget, __dmul_rn((double)shares, share_value));
-        if (wsub == 0 && (int64_t)istep + wn + 1 < a.T) p_next = __ldg(my_row + istep + wn + 1);
+        if (!kWaves && wsub == 0 && (int64_t)istep + wn + 1 < a.T) p_next = __ldg(my_row + istep + wn + 1);
     }
     if (lane == 0) tc_wait(tf_fwd, par);                      // (one poller per warp)
     __syncwarp();

@@ -105,7 +105,8 @@ def teacher_forced_step(cfg, o, pol, prices, soe, i, what, tally=None, n_terms=1
     kink = (np.abs(z) <= 1e-6 * zc).any(axis=0)
     keep = np.ones(cfg.P, bool)
     keep[:D * H] = np.tile(~kink, D)
-    assert kink.sum() <= max(2, H // 50), f"{what}: {kink.sum()} hidden units on their ReLU kink"
+    # (the chance that SOME episode puts a unit within 1e-6 of its kink grows with the number of rows)
+    assert kink.sum() <= max(2, H // 50, x.shape[0] // 1500), f"{what}: {kink.sum()} hidden units on their ReLU kink"
     g_cmp, ref_cmp = np.where(keep, g, 0.0), np.where(keep, ref["grad"], 0.0)
     if n_terms >= 2048:
         # Thousands of episodes: the oracle adds the episodes' gradients one after the other in fp32 (the device adds

@@ -55,6 +55,8 @@ def make_policy(cfg: O.Config, params=None, acc=None, fused=None, ep_tc=None, pa
         pol.set_option("ep_tc", int(ep_tc))
     if ep_c2 is not None:
         pol.set_option("ep_c2", int(ep_c2))
+    if path is not None or fused is not None:
+        pol.set_option("fanout", 0)          # (a test that names its path means that kernel, not the fan-out path)
     return pol
 
 
@@ -724,12 +726,46 @@ def test_bench_regime_unscaled_weights_teacher_forced(bookkeeping, path):
           f"(device, fp32 oracle): {tally.grad_err_vs_twin}; imposed choices {tally.forced_actions}+{tally.forced_knext} of {tally.rows}")
 
 
-@pytest.mark.parametrize("path", ["three", "tc"])
+@pytest.mark.parametrize("bookkeeping", [O.REFERENCE, O.RLPY])
+def test_pair_kernel_in_waves_one_series_per_episode(bookkeeping):
+    """BASELINE.json configs[2]'s per-GPU shape in small: every episode on its own series (episode e = series e), more
+    tiles than CTA pairs (9 500 episodes = 149 tiles over 74 pairs: 2-3 per pair, the last one ragged).  The pair kernel
+    then fetches a tile's window with TMA from the transposed price matrix.  Teacher-forced at two steps, then free-running
+    against the one-tile-per-CTA kernel."""
+    cfg = O.Config(bookkeeping=bookkeeping, seed=40)
+    n = 9500
+    prices = O.gen_prices(cfg.seed, 0, n, 280)
+    soe = np.arange(n, dtype=np.int32)
+    w = (O.gen_normal(15, 0, cfg.P) * 0.05).astype(np.float32)
+    o = O.Oracle(cfg, params=w)
+    o.env_create(prices, soe, 1000.0, 1)
+    tally = Tally()
+    with make_policy(cfg, params=w, path="c2") as pol:
+        pol.env_create(prices, soe, 1000.0, 1)
+        assert_path(pol, "c2")
+        for i in (0, 41):
+            teacher_forced_step(cfg, o, pol, prices, soe, i, f"pair kernel in waves, step {i}", tally, n_terms=n)
+    tally.assert_mostly_unforced()
+    res = []
+    for path in ("c2", "tc"):
+        with make_policy(cfg, params=w * np.float32(0.2), path=path) as pol:      # (small weights, lr as is: ReLUs stay alive)
+            pol.env_create(prices, soe, 1000.0, 1)
+            tr = pol.env_step_trace(6)
+            res.append((tr, pol.get_weights()[0], pol.env_state()))
+    (ta, wa, sa), (tb, wb, sb) = res
+    for k in ("explored", "reward"):
+        np.testing.assert_array_equal(ta[k][0], tb[k][0], err_msg=k)
+    same = (ta["action_sel"] == tb["action_sel"]).mean()
+    assert same > 0.999, f"the two tensor-core kernels agree on {same:.4f} of the actions only"
+
+
+@pytest.mark.parametrize("path", ["three", "tc", "c2"])
 @pytest.mark.parametrize("n,wscale", [(19000, 0.05), (40007, 0.05), (19000, 1.0)])
 def test_large_batch_path_against_oracle(n, wscale, path):
     """More than 128 episodes per SM.  three: the three-kernel path with the large-batch dW1 kernel (one split per
     SM, 16 x 8 register tiles); tc: the tensor-core persistent kernel in waves (5 / 9 tiles per CTA, the last wave
-    ragged, the last tile partly filled), whose later waves add their dW1 partial to the first wave's.  One
+    ragged, the last tile partly filled), whose later waves add their dW1 partial to the first wave's; c2: the pair
+    kernel in waves (297 / 626 tiles of 64 episodes over 74 pairs: 4-5 / 8-9 tiles per pair and step, accumulated in TMEM).  One
     teacher-forced step against the oracle (wscale = 1.0: the unscaled N(0,1) weights of the bench), then three more
     free-running steps."""
     cfg = O.Config(bookkeeping=O.RLPY, seed=31)
@@ -740,10 +776,9 @@ def test_large_batch_path_against_oracle(n, wscale, path):
     o = O.Oracle(cfg, params=w)
     o.env_create(prices, soe, 1000.0, 1)
     tally = Tally()
-    with make_policy(cfg, params=w) as pol:
-        pol.set_option("fused", PATHS[path][0])
+    with make_policy(cfg, params=w, path=path) as pol:
         pol.env_create(prices, soe, 1000.0, 1)
-        assert_path(pol, path)                          # (more than one tile per pair: the one-tile-per-CTA kernel in waves)
+        assert_path(pol, path)
         tr, ref = teacher_forced_step(cfg, o, pol, prices, soe, i, f"large batch {path}", tally, n_terms=n)
         pol.env_step(3)
         assert pol.steps_done == i + 4
