@@ -129,9 +129,12 @@ int qp_sync(qp_handle* h);
  *             with 0, the FFMA form of the kernel runs, which needs the episodes to fit one 32-episode tile per SM.
  *   "ep_c2"   the tensor-core kernel as CTA PAIRS (clusters of two) that split the hidden dimension: one 64-episode
  *             tile per pair, each CTA holds half of W1^T's columns, Q-value halves meet over distributed shared
- *             memory.  Taken when "ep_tc" is and the episodes fit one tile per pair (64 x SMs/2; 4736 on a B200) and
- *             the shape fits (hidden a multiple of 8, <= 256; window + 50 <= 256 rows); otherwise, and with 0, the
- *             one-CTA-per-tile tensor-core kernel runs (any number of episodes, in waves).
+ *             memory.  Taken when "ep_tc" is and the shape fits (hidden a multiple of 8, <= 256; window + 50 <= 256
+ *             rows); more episodes than one tile per pair (64 x SMs/2; 4736 on a B200) run in waves.  Prices that are
+ *             not tf32-exact: 32 episodes per pair, one tile per pair only.  Otherwise, and with 0, the
+ *             one-CTA-per-tile tensor-core kernel runs (tf32-exact prices, any number of episodes, in waves).
+ *   "ep_c2_waves"  the pair kernel also where a pair has several tiles per env-step (tf32-exact prices); 0: the
+ *             one-tile-per-CTA kernel takes those batches.
  *   "p2p"     several GPUs: gradient exchange inside the persistent kernel over NVLink peer memory
  *             (qp_dist_p2p_export / qp_dist_p2p_import, or qp_dist_p2p_attach); 0: one fused step kernel per
  *             env-step + NCCL all-reduce.
