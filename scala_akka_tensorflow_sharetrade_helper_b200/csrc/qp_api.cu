@@ -513,15 +513,16 @@ int make_tmap3_store(CUtensorMap* m, const float* base, uint64_t d0, uint64_t d1
 }
 
 // 4-D fp32 tensor [d3][d2][d1][d0] for TMA stores of [32 (d2) x 32 (d0)] boxes (128-byte rows, 128-byte swizzle)
-int make_tmap4_store(CUtensorMap* m, const float* base, const uint64_t dims_in[4], const uint64_t pitch_bytes[3]) {
+int make_tmap4_store(CUtensorMap* m, const float* base, const uint64_t dims_in[4], const uint64_t pitch_bytes[3], bool row_boxes = false) {
     EncodeTiledFn enc = nullptr;
     QP_TRY(get_encode_tiled(&enc));
     const cuuint64_t dims[4] = {dims_in[0], dims_in[1], dims_in[2], dims_in[3]};
     const cuuint64_t strides[3] = {pitch_bytes[0], pitch_bytes[1], pitch_bytes[2]};
-    const cuuint32_t box[4] = {32, 1, 32, 1};
+    // row_boxes: [32 (d1) x 32 (d0)] boxes, rows of 128 bytes laid out linearly in shared memory (no swizzle)
+    const cuuint32_t box[4] = {32, row_boxes ? 32u : 1u, row_boxes ? 1u : 32u, 1};
     const cuuint32_t estr[4] = {1, 1, 1, 1};
     const CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, (void*)base, dims, strides, box, estr,
-                           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
+                           CU_TENSOR_MAP_INTERLEAVE_NONE, row_boxes ? CU_TENSOR_MAP_SWIZZLE_NONE : CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE,
                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(QP_ECUDA, "cuTensorMapEncodeTiled (4-D) failed with code " + std::to_string((int)r));
     return QP_OK;
@@ -723,7 +724,8 @@ int wide_prepare_tc(qp_handle* h) {
 }
 
 size_t p2p_tc_offset(const qp_handle* h) { return (size_t)round_up(256 + (int64_t)2 * h->P * (int64_t)sizeof(float), 256); }
-size_t p2p_pad(const qp_handle* h) { return (size_t)round_up(h->P, 64); }
+// (the pair kernel indexes its shares in the transposed space [column][row padded to 4] + W2)
+size_t p2p_pad(const qp_handle* h) { return (size_t)round_up(std::max<int64_t>(h->P, (int64_t)h->hp.H * c2_kk(h->hp.D) + 3 * h->hp.H), 64); }
 
 // what both tensor-core persistent kernels need: the shape, the buffers, and (several GPUs) the flow form of phase B
 bool ep_tc_base(const qp_handle* h) { return h->allow_ep_tc && h->ep_tc_ready && (h->world == 1 || h->et_flow_ok); }
@@ -818,7 +820,8 @@ int ep_c2_prepare(qp_handle* h) {
         return QP_OK;
     {   // phase B's bulk-copy branch must apply (the kernel has no other)
         const int n_w1 = std::max(1, grid - 2);
-        const int chunk = (int)(((h->P1 + n_w1 - 1) / n_w1 + 3) & ~(int64_t)3);
+        const int64_t P1T = (int64_t)hp.H * c2_kk(hp.D);       // the pair kernel's partial is [column][row padded to 4]
+        const int chunk = (int)(((P1T + n_w1 - 1) / n_w1 + 3) & ~(int64_t)3);
         const int chunk2 = ((3 * hp.H + 1) / 2 + 3) & ~3;
         const int pitch = std::max(chunk, chunk2);
         // the sum: (sub, float4 group) threads, at most 16 partials per thread; the sub sums meet in [8][pitch] floats
@@ -926,7 +929,7 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
     if (n_steps <= 0) return QP_OK;
     const int64_t Bpad = round_up(h->n_envs, kTileEnvs);
     const int64_t n_tiles = Bpad / kTileEnvs;
-    QP_TRY(h->part1.ensure((size_t)n_tiles * h->P1));
+    QP_TRY(h->part1.ensure((size_t)n_tiles * (size_t)((int64_t)h->hp.H * c2_kk(h->hp.D))));      // (the pair kernel's partials: [column][row padded to 4])
     QP_TRY(h->part2.ensure((size_t)n_tiles * 3 * h->hp.H));
     EpisodeArgs ea{};
     StepArgs& s = ea.s;
@@ -987,9 +990,11 @@ int enqueue_env_steps_fused(qp_handle* h, int32_t n_steps, const TraceDev* trace
         }
         const int64_t n_parts = std::min<int64_t>(n_pairs, h->c2_grid / 2);          // one partial per pair
         if (h->tm_c2_part_ptr != h->part1.p || h->tm_c2_part_pairs != n_parts) {
-            const uint64_t dims[4] = {(uint64_t)h->c2_Hh, 2, (uint64_t)h->hp.wn, (uint64_t)n_parts};
-            const uint64_t pitch[3] = {(uint64_t)h->c2_Hh * sizeof(float), (uint64_t)h->hp.H * sizeof(float), (uint64_t)h->P1 * sizeof(float)};
-            QP_TRY(make_tmap4_store(&h->tm_c2_part, h->part1.p, dims, pitch));
+            // [pair][half][column][row]: rows end at wn, columns at Hh (the boxes are clipped there)
+            const uint64_t Kk = (uint64_t)c2_kk(h->hp.D);
+            const uint64_t dims[4] = {(uint64_t)h->hp.wn, (uint64_t)h->c2_Hh, 2, (uint64_t)n_parts};
+            const uint64_t pitch[3] = {Kk * sizeof(float), (uint64_t)h->c2_Hh * Kk * sizeof(float), (uint64_t)h->hp.H * Kk * sizeof(float)};
+            QP_TRY(make_tmap4_store(&h->tm_c2_part, h->part1.p, dims, pitch, /*row_boxes=*/true));
             h->tm_c2_part_ptr = h->part1.p; h->tm_c2_part_pairs = n_parts;
         }
         cudaLaunchConfig_t cfg{};

@@ -39,6 +39,12 @@ constexpr int kC2Builders = 8;          // warps 2..9 transpose the A tiles
 constexpr int kC2Sub = kC2Warps / 2;    // warps per 32-episode lane group in the element-wise phases
 constexpr int kC2EStride = 65;          // padded row stride of the [column][episode] tiles
 
+// The dW1 partial of a pair is stored TRANSPOSED, [hidden column][input row] with rows of c2_kk(D) floats (D rounded up to
+// 4): phase B owns contiguous ranges of it, so consecutive threads own consecutive window rows k of one column n — which
+// is the order W1^T is laid out in: the tf32 hi / lo of the new weights go out as coalesced 128-byte stores (with the
+// partial in W1's own [row][column] order they were 4-byte stores 896 bytes apart: 2.6 MB of sector writes per step).
+__host__ __device__ inline int c2_kk(int D) { return (D + 3) & ~3; }
+
 struct EpC2Args {
     EpisodeArgs ea;
     float* w1T_hi; float* w1T_lo;   // [H, Kp] K-major tf32 hi/lo copies of W1[0:wn, :] (as episode_tc_kernel)

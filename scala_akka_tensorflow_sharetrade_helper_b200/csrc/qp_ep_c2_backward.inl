@@ -46,15 +46,15 @@
         if (first_tile) { p5[0] = s0; p5[Hh] = s1; p5[2 * Hh] = s2; p5[3 * Hh] = x0; p5[4 * Hh] = x1; }
         else { p5[0] += s0; p5[Hh] += s1; p5[2 * Hh] += s2; p5[3 * Hh] += x0; p5[4 * Hh] += x1; }
     }
-    // ---- S6: dW1 partial out of TMEM.  Row m of the accumulator is window element m (the A operand started at the
-    // window's first row).  A TMEM load hands every lane one ROW of the tile; each warp stages its [32 rows x 32 columns]
-    // boxes in shared memory (128-byte swizzle, conflict-free) and lane 0 hands them to the TMA engine, which writes
-    // whole row segments; the tensor map ([pair][row][half][column]) ends at row wn.  The staging buffers lie where
-    // z1(s') was and behind dZ1: neither h(s) (still read above) nor the operands of the running MMAs are touched.
-    // Warp (q4, part) takes column box `part` of its 32-row block in both halves; the columns past the last full box
-    // go out of the registers directly (part 2: first half, part 1: second half).
+    // ---- S6: dW1 partial out of TMEM, stored TRANSPOSED ([column][row], see c2_kk).  Row m of the accumulator is window
+    // element m (the A operand started at the window's first row).  A TMEM load hands every lane one ROW of the tile; each
+    // warp stages a [32 columns x 32 rows] box in shared memory — lane = row writes word (column, lane): 32 consecutive
+    // words per store instruction, conflict-free — and lane 0 hands it to the TMA engine, which writes 128-byte row
+    // segments; the tensor map ([pair][half][column][row]) ends at row wn and at column Hh, which clips the boxes.  The
+    // staging buffers lie where z1(s') was and behind dZ1: neither h(s) (still read above) nor the operands of the
+    // running MMAs are touched.  Warp (q4, part) takes the column boxes part, part + 3 of its 32-row block in both halves.
     {
-        const int nfull = Hh >> 5, tail = Hh - (nfull << 5);
+        const int nbox = (Hh + 31) >> 5;
         uint8_t* buf = warp < 6 ? regA + sm.stg_a + (size_t)warp * 4096 : regA + sm.stg_b + (size_t)(warp - 6) * 4096;
         bool pending = false;
         for (int hf = 0; hf < halves; ++hf) {
@@ -63,7 +63,14 @@
             __syncwarp();
             tc_fence_after();
             if (k0 >= wn || !last_tile) continue;                 // (kWaves: the sum leaves TMEM after the step's last tile)
-            for (int cb = part; cb < nfull; cb += 3) {
+            // full boxes part, part + 3, ...; the box of the last few columns (clipped) goes to a different part in each half
+            const int nfull = Hh >> 5;
+            for (int cbi = part; cbi < nfull + 3; cbi += 3) {
+                int cb = cbi;
+                if (cbi >= nfull) {
+                    if (nbox == nfull || part != 2 - hf) break;
+                    cb = nfull;
+                }
                 uint32_t r[32];
                 et_tmem_ld32_nowait(tmem_base + ((uint32_t)(q4 * 32) << 16) + 128u + (uint32_t)(hf * 128 + cb * 32), r);
                 if (pending) {                                  // the buffer's previous box has left it
@@ -71,30 +78,17 @@
                     __syncwarp();
                 }
                 et_tmem_wait_ld();
+                const int nj = min(32, Hh - cb * 32);           // (rows past column Hh are clipped by the tensor map: not staged)
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
-                    *reinterpret_cast<uint4*>(buf + lane * 128 + ((j ^ (lane & 7)) << 4)) = make_uint4(r[4 * j], r[4 * j + 1], r[4 * j + 2], r[4 * j + 3]);
+                for (int j = 0; j < 32; ++j)
+                    if (j < nj) reinterpret_cast<uint32_t*>(buf)[j * 32 + lane] = r[j];
                 et_fence_async_smem();
                 __syncwarp();
                 if (lane == 0) {
-                    c2_tma_store_4d(&tP, buf, cb * 32, (int)crank, k0, (int)cidx);
+                    c2_tma_store_4d(&tP, buf, k0, cb * 32, (int)crank, (int)cidx);
                     et_bulk_commit();
                 }
                 pending = true;
-            }
-            if (tail > 0 && part == 2 - hf) {
-                for (int t0 = 0; t0 < tail; t0 += 16) {
-                    float v[16];
-                    et_tmem_ld16(tmem_base + ((uint32_t)(q4 * 32) << 16) + 128u + (uint32_t)(hf * 128 + nfull * 32 + t0), v);
-                    const int k = k0 + lane;
-                    if (k < wn) {
-#pragma unroll
-                        for (int j = 0; j < 4; ++j)
-                            if (t0 + 4 * j < tail)
-                                *reinterpret_cast<float4*>(out + (size_t)k * H + c0 + nfull * 32 + t0 + 4 * j) =
-                                    make_float4(v[4 * j], v[4 * j + 1], v[4 * j + 2], v[4 * j + 3]);
-                    }
-                }
             }
         }
         ++mma_it;
@@ -113,7 +107,7 @@
         const float* pb = part5 + (size_t)5 * Hh + cl;
         const int c = c0 + cl;
         out2[c * 3 + 0] = pa[0] + pb[0]; out2[c * 3 + 1] = pa[Hh] + pb[Hh]; out2[c * 3 + 2] = pa[2 * Hh] + pb[2 * Hh];
-        out[(size_t)wn * H + c] = pa[3 * Hh] + pb[3 * Hh];
-        out[(size_t)(wn + 1) * H + c] = pa[4 * Hh] + pb[4 * Hh];
+        out[(size_t)c * Kk + wn] = pa[3 * Hh] + pb[3 * Hh];     // (the partial is [column][row])
+        out[(size_t)c * Kk + wn + 1] = pa[4 * Hh] + pb[4 * Hh];
     }
 }

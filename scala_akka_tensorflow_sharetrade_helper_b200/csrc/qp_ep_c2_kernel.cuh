@@ -142,21 +142,36 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     }
     // phase B's division of the parameters over the CTAs (as episode_tc_kernel; the host has checked `flow`)
     const int n1 = (int)min(n_pairs, n_clusters);               // one partial per pair
+    const int Kk = c2_kk(D);
+    const int64_t P1T = (int64_t)H * Kk;                        // the transposed W1 index space (one pad element per column)
     const int n_w1_ctas = max(1, (int)gridDim.x - 2);
-    const int chunk = (int)(((P1 + n_w1_ctas - 1) / n_w1_ctas + 3) & ~(int64_t)3);
+    const int chunk = (int)(((P1T + n_w1_ctas - 1) / n_w1_ctas + 3) & ~(int64_t)3);
     const int chunk2 = ((3 * H + 1) / 2 + 3) & ~3;
     const int pitch = max(chunk, chunk2);
     if (!(gridDim.x >= 8 && pitch <= nthreads && x.published != nullptr)) __trap();        // (the host has checked)
-    const int n_publishers = (int)((P1 + chunk - 1) / chunk) + 2;
+    const int n_publishers = (int)((P1T + chunk - 1) / chunk) + 2;
     // this CTA's share of the parameters and this thread's parameter (phase B)
     const bool w2_cta = (int)blockIdx.x >= (int)gridDim.x - 2;
     const float* pb_src = w2_cta ? a.dw2_part : ea.part1;
-    const int64_t pb_stride = w2_cta ? 3 * (int64_t)H : P1;
+    const int64_t pb_stride = w2_cta ? 3 * (int64_t)H : P1T;
     const int64_t pb_off = w2_cta ? (int64_t)((int)blockIdx.x - ((int)gridDim.x - 2)) * chunk2 : (int64_t)blockIdx.x * chunk;
-    const int64_t pb_p0 = w2_cta ? P1 + pb_off : pb_off;
+    const int64_t pb_p0 = w2_cta ? P1T + pb_off : pb_off;       // (index in the exchange blocks: the same on every rank)
+    // the parameter thread t of this CTA owns, or -1 for a pad element: W1[k][n] for the transposed index n * Kk + k
+    auto pb_param = [&](int t) -> int64_t {
+        if (w2_cta) return P1 + pb_off + t;
+        const int64_t q = pb_off + t;
+        const int n = (int)(q / Kk), k = (int)(q - (int64_t)n * Kk);
+        return k < D ? (int64_t)k * H + n : (int64_t)-1;
+    };
     const int pb_len = (int)max((int64_t)0, min((int64_t)(w2_cta ? chunk2 : chunk), pb_stride - pb_off));
+    // (column, row) of this thread's element of the transposed index space, packed: computed once, used every step
+    unsigned int pb_nk = 0u;
+    if (!w2_cta) {
+        const unsigned int qq = (unsigned int)pb_off + (unsigned int)tid, nq0 = qq / (unsigned int)Kk;
+        pb_nk = (nq0 << 16) | (qq - nq0 * (unsigned int)Kk);
+    }
     float pb_w = 0.0f, pb_a = 0.0f, pb_g = 0.0f;
-    if (tid < pb_len) { pb_a = ea.acc[pb_p0 + tid]; pb_w = ea.params_rw[pb_p0 + tid]; }
+    if (tid < pb_len && pb_param(tid) >= 0) { pb_a = ea.acc[pb_param(tid)]; pb_w = ea.params_rw[pb_param(tid)]; }
     if (blockIdx.x == 0 && tid == 0) { x.published[0] = 0ull; x.published[1] = 0ull; }
     __threadfence();
     grid.sync();
@@ -164,7 +179,7 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
     const uint32_t idesc = tc_instr_desc(128, Nh);
     uint32_t ring_it = 0, a_it = 0, mma_it = 0, xw_it = 0;
     const int kb_first = (int)(blockIdx.x % (unsigned)nkb);
-    float* out = ea.part1 + (size_t)cidx * ((size_t)D * H);
+    float* out = ea.part1 + (size_t)cidx * (size_t)P1T;        // [H][Kk]
     float* out2 = a.dw2_part + (size_t)cidx * (3 * H);
 
     for (int32_t sidx = 0; sidx < ea.n_steps; ++sidx) {
@@ -268,10 +283,11 @@ episode_c2_kernel(const __grid_constant__ CUtensorMap tW_hi, const __grid_consta
         cta_stamp(7);
     }
 
-    if (ea.apply_in_kernel && tid < pb_len) {                   // weights, accumulators and the last gradient sum go home
-        ea.params_rw[pb_p0 + tid] = pb_w;
-        ea.acc[pb_p0 + tid] = pb_a;
-        ea.grad[pb_p0 + tid] = pb_g;
+    if (ea.apply_in_kernel && tid < pb_len && pb_param(tid) >= 0) {   // weights, accumulators and the last gradient sum go home
+        const int64_t p = pb_param(tid);
+        ea.params_rw[p] = pb_w;
+        ea.acc[p] = pb_a;
+        ea.grad[p] = pb_g;
     }
     if (!kWaves && has_tile && crank == 0 && wsub == 0 && valid && (!kSplit || g == 0)) {
         a.budget[e] = budget;

@@ -40,22 +40,23 @@
             g = red[tid];
             for (int u = 1; u < nsub; ++u) g += red[(size_t)u * pitch + tid];
         }
+        // this thread's element of the transposed index space: column nq, row kq (kq = D .. Kk - 1: padding, nobody's)
+        const int nq = (int)(pb_nk >> 16), kq = (int)(pb_nk & 0xffffu);
+        const bool real = w2_cta || kq < D;
         if constexpr (kXchg != 0) {
-            if (tid < pb_len) g = c2_share_exchange<kXchg == 2>(x, g, pb_p0 + tid, sidx, (int)blockIdx.x);
+            if (tid < pb_len && real) g = c2_share_exchange<kXchg == 2>(x, g, pb_p0 + tid, sidx, (int)blockIdx.x);
         }
         stamp(12);
-        if (tid < pb_len) {
-            const int64_t p = pb_p0 + tid;
+        if (tid < pb_len && real) {
             pb_g = g;
             pb_a = __fadd_rn(pb_a, __fmul_rn(g, g));
             pb_w = __fsub_rn(pb_w, __fmul_rn(__fmul_rn(g, hp.lr), __fdiv_rn(1.0f, __fsqrt_rn(pb_a))));
-            const int k = (int)(p / H), n = (int)(p - (int64_t)k * H);
-            if (k < wn) {                                       // a window row of W1: what the forward streams
-                const float hi = et_tf32(pb_w);
-                x.w1T_hi[(size_t)n * x.Kp + k] = hi;
-                x.w1T_lo[(size_t)n * x.Kp + k] = pb_w - hi;
+            if (!w2_cta && kq < wn) {                           // a window row of W1: what the forward streams (consecutive
+                const float hi = et_tf32(pb_w);                 // threads = consecutive k of one column: coalesced stores)
+                x.w1T_hi[(size_t)nq * x.Kp + kq] = hi;
+                x.w1T_lo[(size_t)nq * x.Kp + kq] = pb_w - hi;
             } else {                                            // budget / shares rows of W1, W2: read as they are
-                ea.params_rw[p] = pb_w;
+                ea.params_rw[w2_cta ? P1 + pb_off + tid : (int64_t)kq * H + nq] = pb_w;
             }
         }
         // tell the consumers
