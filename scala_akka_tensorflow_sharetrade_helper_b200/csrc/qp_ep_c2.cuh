@@ -25,6 +25,7 @@
 // exchange, the split grid barrier — is episode_tc_kernel's, on 64-episode tiles.
 #pragma once
 #include "qp_ep_tc.cuh"
+#include <type_traits>
 
 namespace qp {
 

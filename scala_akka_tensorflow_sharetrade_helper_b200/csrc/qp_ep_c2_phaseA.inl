@@ -198,23 +198,35 @@
         const float xnb[3] = {__double2float_rn(nbc[0]), __double2float_rn(nbc[1]), __double2float_rn(nbc[2])};
         const float xns[3] = {(float)nsc[0], (float)nsc[1], (float)nsc[2]};
         // (kSplit: the twelve warps share the columns of the 32 real episodes; z = z(x_hi) + z(x_lo); h goes to both blocks)
+        // An outcome that no episode of the warp can reach (nobody can afford the share / nobody holds one) is left out of
+        // the sweep: its sums stay zero and are never selected.  The six warps of a lane group and the partner CTA hold
+        // the same 32 episodes, so they all decide alike.  (The reference's stateless book-keeping from zero shares never sells.)
+        const bool any_buy = __any_sync(0xffffffffu, can_buy), any_sell = __any_sync(0xffffffffu, can_sell);
+        auto sweep = [&](auto buy_c, auto sell_c) {
+            constexpr bool kBuy = decltype(buy_c)::value, kSell = decltype(sell_c)::value;
 #pragma unroll 2
-        for (int c = kSplit ? 2 * wsub + g : wsub; c < Hh; c += kSplit ? 2 * kC2Sub : kC2Sub) {
-            const float wb = Wb[c], ws = Ws[c];
-            const float zn = kSplit ? ZN[c * kC2EStride + lane] + ZN[c * kC2EStride + 32 + lane] : ZN[c * kC2EStride + el];
-            const float zs = kSplit ? HS[c * kC2EStride + lane] + HS[c * kC2EStride + 32 + lane] : HS[c * kC2EStride + el];
-            const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
-            const float h = et_hidden(zs, xb, xs, wb, ws, bias);
-            if constexpr (kSplit) { HS[c * kC2EStride + lane] = h; HS[c * kC2EStride + 32 + lane] = h; }
-            else HS[c * kC2EStride + el] = h;                   // from here on the tile holds h(s)
-            pq[0][0] = fmaf(h, w2.x, pq[0][0]); pq[0][1] = fmaf(h, w2.y, pq[0][1]); pq[0][2] = fmaf(h, w2.z, pq[0][2]);
+            for (int c = kSplit ? 2 * wsub + g : wsub; c < Hh; c += kSplit ? 2 * kC2Sub : kC2Sub) {
+                const float wb = Wb[c], ws = Ws[c];
+                const float zn = kSplit ? ZN[c * kC2EStride + lane] + ZN[c * kC2EStride + 32 + lane] : ZN[c * kC2EStride + el];
+                const float zs = kSplit ? HS[c * kC2EStride + lane] + HS[c * kC2EStride + 32 + lane] : HS[c * kC2EStride + el];
+                const float4 w2 = reinterpret_cast<const float4*>(W2s)[c];
+                const float h = et_hidden(zs, xb, xs, wb, ws, bias);
+                if constexpr (kSplit) { HS[c * kC2EStride + lane] = h; HS[c * kC2EStride + 32 + lane] = h; }
+                else HS[c * kC2EStride + el] = h;               // from here on the tile holds h(s)
+                pq[0][0] = fmaf(h, w2.x, pq[0][0]); pq[0][1] = fmaf(h, w2.y, pq[0][1]); pq[0][2] = fmaf(h, w2.z, pq[0][2]);
 #pragma unroll
-            for (int j = 0; j < 3; ++j) {
-                const float hn = et_hidden(zn, xnb[j], xns[j], wb, ws, bias);
-                pq[1 + j][0] = fmaf(hn, w2.x, pq[1 + j][0]); pq[1 + j][1] = fmaf(hn, w2.y, pq[1 + j][1]);
-                pq[1 + j][2] = fmaf(hn, w2.z, pq[1 + j][2]);
+                for (int j = 0; j < 3; ++j) {
+                    if ((j == 0 && !kBuy) || (j == 1 && !kSell)) continue;
+                    const float hn = et_hidden(zn, xnb[j], xns[j], wb, ws, bias);
+                    pq[1 + j][0] = fmaf(hn, w2.x, pq[1 + j][0]); pq[1 + j][1] = fmaf(hn, w2.y, pq[1 + j][1]);
+                    pq[1 + j][2] = fmaf(hn, w2.z, pq[1 + j][2]);
+                }
             }
-        }
+        };
+        if (any_buy && any_sell) sweep(std::true_type{}, std::true_type{});
+        else if (any_buy) sweep(std::true_type{}, std::false_type{});
+        else if (any_sell) sweep(std::false_type{}, std::true_type{});
+        else sweep(std::false_type{}, std::false_type{});
 #pragma unroll
         for (int j = 0; j < 4; ++j)
 #pragma unroll
