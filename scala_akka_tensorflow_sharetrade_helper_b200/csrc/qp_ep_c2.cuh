@@ -22,7 +22,9 @@
 //   * B of the forward = this CTA's rows of W1^T (tf32 hi / lo), streamed by TMA as before; B of the backward =
 //     dZ1 (hi / lo), written by the element-wise phase.
 // Everything else — select / book-keeping / TD arithmetic, the gradient all-to-all (phase B), the NVLink share
-// exchange, the split grid barrier — is episode_tc_kernel's, on 64-episode tiles.
+// exchange, the split grid barrier — is episode_tc_kernel's, on 64-episode tiles, with three differences: the dW1 partial
+// is stored transposed (c2_kk below), prices that are not tf32-exact are taken as two episodes each (kSplit), and more
+// tiles than pairs run in waves whose backward sums stay in TMEM (kWaves); see qp_ep_c2_kernel.cuh.
 #pragma once
 #include "qp_ep_tc.cuh"
 #include <type_traits>

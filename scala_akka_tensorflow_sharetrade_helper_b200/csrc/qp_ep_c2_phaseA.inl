@@ -235,7 +235,7 @@
     if (tid == 0) fine(42);
     __syncthreads();
     if (tid == 0) fine(43);
-    // this CTA's half of the twelve sums per episode, fixed order, to both CTAs of the pair.  Every thread then
+    // this CTA's half of the twelve sums per episode, fixed order, to both CTAs of the pair.
     // One thread per CTA then arrives (release, cluster scope) on the exchange barrier of BOTH CTAs: a CTA's barrier
     // completes when both halves of its copy are written — no cluster barrier (which cost 1.1 K cycles here).
     {

@@ -1,7 +1,8 @@
 // qp_ep_c2_phaseB.inl — gradient sum over the pairs' partials + AdaGrad + tf32 hi/lo of the new W1.
-// CTA c owns `chunk` consecutive parameters (the last two CTAs: W2), thread t of it parameter p0 + t for the WHOLE
-// launch: its weight and AdaGrad accumulator stay in registers from the first step to the last (pb_w, pb_a) and go
-// back to global memory once, at the end; per step only what other CTAs read is written — the tf32 hi / lo copy of
+// CTA c owns `chunk` consecutive elements of W1 in the TRANSPOSED index space [column][row padded to 4] the pairs'
+// partials are stored in (c2_kk; the last two CTAs: W2), thread t of it element p0 + t for the WHOLE launch: its weight and
+// AdaGrad accumulator stay in registers from the first step to the last (pb_w, pb_a) and go back to global memory once,
+// at the end (one element per column is padding and owns nothing); per step only what other CTAs read is written — the tf32 hi / lo copy of
 // a window row of W1, or the parameter itself for the budget / shares rows of W1 and for W2 (the small tables).
 //   sum     : the chunk's segment of every partial is read straight from global memory (L2) with 16-byte loads, all
 //             of a thread's loads in flight at once: thread (sub, group) adds the partials sub, sub + nsub, ... of
