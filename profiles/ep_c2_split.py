@@ -22,7 +22,7 @@ for n in sizes:
             act = {k: int(pol.get_option(k)) for k in ("fused_active", "ep_tc_active", "ep_c2_active", "ep_c2_split_active")}
             pol.env_step(40)
             steps = 200 if act["fused_active"] else 50
-            us = pol.env_step_timed(steps)[0] / steps * 1e3
+            us = float(np.sum(pol.env_step_timed(steps))) / steps * 1e3      # (all kernels of a step: the three-kernel path fills three slots)
             row.append(f"{name}: {us:7.2f} us/step ({n / us * 1e6:.3g} env-steps/s) {act}")
     print(f"{n} episodes, inexact prices")
     for r in row:

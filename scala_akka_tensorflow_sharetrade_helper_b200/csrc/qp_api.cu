@@ -759,11 +759,9 @@ bool use_fused(const qp_handle* h) {
     const bool fits_local = h->n_envs <= (int64_t)kTileEnvs * h->num_sms;
     const bool fits = single ? fits_local : (fits_local && h->agree_fits);
     const bool fused_ok = !h->wide && h->allow_fused && h->coop_launch && h->geo.ep_ok && (single || h->agree_fused);
-    // The FFMA form of the persistent kernel (52 us per env-step at the reference shape) loses to the three-kernel path
-    // (34 us) on one GPU: it runs only where the tensor cores are switched off by option ("ep_tc" = 0), or between
-    // several GPUs, where it carries the in-kernel exchange.
-    const bool ffma_form = fits && (!single || !h->allow_ep_tc);
-    return fused_ok && (single || peers) && (ffma_form || ep_tc_usable(h) || ep_c2_usable(h));
+    // (the FFMA form of the persistent kernel, 52-54 us per env-step at the reference shape against 72 for the three-kernel
+    // path, serves what fits one tile per SM and no tensor-core kernel takes)
+    return fused_ok && (single || peers) && (fits || ep_tc_usable(h) || ep_c2_usable(h));
 }
 
 // The fan-out path (qp_fanout.cuh): episodes grouped by series.  Taken on its own where it pays: at least eight episodes

@@ -218,10 +218,10 @@ def test_env_step_teacher_forced(bookkeeping, n_envs, N0, path):
         for i in (0, 1, 57, 150, 198):
             teacher_forced_step(cfg, o, pol, prices, soe, i, f"{path} step {i}", tally)
     tally.assert_mostly_unforced()
-    if path == "tc":     # the one-tile-per-CTA kernel needs tf32-exact prices: without the pair kernel the three-kernel path serves them
+    if path == "tc":     # the one-tile-per-CTA kernel needs tf32-exact prices: without the pair kernel the FFMA form serves them
         with make_policy(cfg, path="tc") as pol:
             pol.env_create(prices * INEXACT, soe, 1000.0, N0)
-            assert pol.get_option("ep_tc_active") == 0 and pol.get_option("fused_active") == 0
+            assert pol.get_option("ep_tc_active") == 0 and pol.get_option("fused_active") == 1
 
 
 GOLDEN_CASES = [(n, p_) for n in ("episode_rlpy", "episode_reference", "episode_late") for p_ in ("c2", "tc", "ffma", "three")] + \
