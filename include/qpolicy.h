@@ -152,8 +152,9 @@ int qp_sync(qp_handle* h);
  *   "wide", "tc", "tc_passes"   the GEMM-organised path for policies whose W1 does not fit in shared memory.
  *   "phase_clocks"  tuning aid, see qp_debug_phase_clocks (1: CTA 0's phase stamps; 2: per-CTA wall-clock stamps;
  *             3: fine stamps of the pair kernel).  "c2_dbg": reserved for timing experiments (no effect in this build).
- * Read-only: "fanout_active", "fused_active", "ep_tc_active", "ep_c2_active", "p2p_active", "nvls_active", "rsag_active",
- * "fused_step_active", "tc_active", "tc_a_lo_zero": what the next qp_env_step would take.  With several GPUs all of
+ * Read-only: "fanout_active", "fused_active", "ep_tc_active" (a tensor-core persistent kernel: either form),
+ * "ep_c2_active", "ep_c2_split_active" (the pair kernel on prices that are not tf32-exact), "p2p_active", "nvls_active",
+ * "rsag_active", "fused_step_active", "tc_active", "tc_a_lo_zero": what the next qp_env_step would take.  With several GPUs all of
  * them are facts the ranks have AGREED on at qp_env_create (the step protocols do not interoperate). */
 int qp_set_option(qp_handle* h, const char* key, int64_t value);
 int qp_get_option(qp_handle* h, const char* key, int64_t* value);
