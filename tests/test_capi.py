@@ -78,3 +78,15 @@ def test_invalid_config_is_rejected_before_touching_the_device(built_lib):
     assert L.qp_create(C.byref(cfg), C.byref(h)) == _capi.QP_EINVAL
     assert b"multiple of 4" in L.qp_last_error()
     assert L.qp_create(None, C.byref(h)) == _capi.QP_EINVAL
+
+
+def test_every_option_key_is_documented_in_the_header():
+    """qp_set_option / qp_get_option keys (strcmp(key, "...") in qp_api.cu) against the option list of include/qpolicy.h."""
+    import re
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    src = open(os.path.join(root, "scala_akka_tensorflow_sharetrade_helper_b200", "csrc", "qp_api.cu")).read()
+    hdr = open(os.path.join(root, "include", "qpolicy.h")).read()
+    keys = set(re.findall(r'strcmp\(key, "([a-z0-9_]+)"\)', src))
+    assert len(keys) >= 20
+    missing = sorted(k for k in keys if f'"{k}"' not in hdr)
+    assert not missing, f"options not documented in include/qpolicy.h: {missing}"
